@@ -1,0 +1,221 @@
+/*
+ * lsv2.h -- C ABI of liblsv2.so: the B200 (sm_100a) implementation of the LangSplatV2
+ * rasterization hot path (preprocess -> binning -> blend with sparse-coefficient
+ * accumulation -> global codebook decode, and the coefficient/codebook backward).
+ *
+ * This is the drop-in boundary.  It replaces what the reference binds through
+ *   `from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer`
+ *   (/root/reference/gaussian_renderer/__init__.py:15, settings :37-52, call :108-119),
+ * i.e. the `_C.rasterize_gaussians` / `_C.rasterize_gaussians_backward` / `_C.mark_visible`
+ * pybind entry points of the (un-vendored) submodule
+ *   submodules/efficient-langsplat-rasterization @ 1305b7c23ff64092cd6c4b0e4996d6557e56c76a,
+ * plus the Python decode helpers that every caller runs right after the op
+ *   (eval_lerf.py:210-220, scene/gaussian_model.py:520-549, train.py:38-58).
+ *
+ * Conventions
+ *   - plain C, no torch / pybind types; every pointer is a DEVICE pointer unless the name
+ *     ends in `_host`; all tensors are dense, row-major, fp32 unless stated.
+ *   - every call is asynchronous on `stream` (pass torch.cuda.current_stream().cuda_stream),
+ *     allocates nothing and never synchronises; scratch comes from the caller.
+ *   - return value: 0 on success, otherwise an LSV2_E* code (lsv2_strerror()).
+ *   - instance buffers are capacity-bounded: `capacity` instances are addressable; the
+ *     true count is written to status[LSV2_STATUS_NUM_RENDERED] on the device and
+ *     status[LSV2_STATUS_OVERFLOW] is set when it exceeds `capacity` (the frame is then
+ *     rendered from the first `capacity` emitted instances and must be re-run).  The
+ *     reference instead copies the count to the host between two kernels (one blocking
+ *     sync per frame); lsv2_preprocess + a host read + lsv2_bin reproduces that.
+ */
+#ifndef LSV2_H
+#define LSV2_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LSV2_ABI_VERSION 1
+#define LSV2_TILE 16
+
+/* error codes */
+enum {
+    LSV2_OK = 0,
+    LSV2_EINVAL = 1,      /* bad argument combination (reference: Python Exception)          */
+    LSV2_ECUDA = 2,       /* a CUDA launch / API call failed (lsv2_last_cuda_error())         */
+    LSV2_ENOSPC = 3,      /* scratch too small                                                */
+    LSV2_EUNSUPPORTED = 4 /* shape outside what the kernels are built for                     */
+};
+
+/* feature modes (reference: settings.include_feature / settings.quick_render,
+ * gaussian_renderer/__init__.py:50-51,87-103) */
+enum {
+    LSV2_MODE_RGB = 0,     /* RGB only; weight map not produced                               */
+    LSV2_MODE_DENSE = 1,   /* include_feature: language_feature_precomp f32[P][L]             */
+    LSV2_MODE_QUICK = 2    /* quick_render: weights f32[P][K] + float-typed indices f32[P][K] */
+};
+
+/* status words (uint32 each) */
+enum {
+    LSV2_STATUS_NUM_RENDERED = 0,
+    LSV2_STATUS_OVERFLOW = 1,
+    LSV2_STATUS_BAD_INDEX = 2,   /* quick mode: an index outside [0,L) was seen and skipped */
+    LSV2_STATUS_WORDS = 8
+};
+
+/* Per-view settings == GaussianRasterizationSettings (gaussian_renderer/__init__.py:37-52).
+ * The four matrices/vectors stay on the device exactly as the reference passes them
+ * (transposed / row-vector 4x4s, scene/cameras.py:55-58). */
+typedef struct lsv2_view {
+    int32_t width, height;
+    float tanfovx, tanfovy;
+    float scale_modifier;
+    int32_t sh_degree;        /* active degree 0..3 */
+    const float* viewmatrix;  /* f32[16] world_view_transform                 */
+    const float* projmatrix;  /* f32[16] full_proj_transform                  */
+    const float* campos;      /* f32[3]  camera_center                        */
+    const float* bg;          /* f32[3]                                       */
+} lsv2_view;
+
+/* Borrowed Gaussian parameters == the tensor kwargs of GaussianRasterizer.forward
+ * (gaussian_renderer/__init__.py:108-119).  Exactly one of shs / colors_precomp and exactly
+ * one of (scales, rotations) / cov3d_precomp must be non-NULL. */
+typedef struct lsv2_scene {
+    int32_t P;
+    int32_t sh_coeffs;           /* M in shs f32[P][M][3]; 0 when colors_precomp is used */
+    const float* means3d;        /* f32[P][3] */
+    const float* opacities;      /* f32[P]    */
+    const float* scales;         /* f32[P][3] */
+    const float* rotations;      /* f32[P][4] (w,x,y,z), used as given */
+    const float* cov3d_precomp;  /* f32[P][6] */
+    const float* shs;            /* f32[P][M][3] */
+    const float* colors_precomp; /* f32[P][3] */
+} lsv2_scene;
+
+/* Per-Gaussian state written by lsv2_preprocess (the reference's opaque geomBuffer). */
+typedef struct lsv2_geom {
+    int32_t* radii;          /* i32[P]   (also the op's 3rd return value)         */
+    float* xy;               /* f32[P][2] pixel-space mean                         */
+    float* depth;            /* f32[P]                                             */
+    float* conic_opacity;    /* f32[P][4] (conic a,b,c, opacity)                   */
+    float* rgb;              /* f32[P][3]                                          */
+    uint8_t* clamped;        /* u8[P][3]  SH colour clamped at 0 (may be NULL)     */
+    uint32_t* tiles_touched; /* u32[P]                                             */
+    uint32_t* offsets;       /* u32[P]    inclusive scan of tiles_touched          */
+    float* cov3d;            /* f32[P][6] or NULL                                  */
+    int32_t* rect;           /* i32[P][4] (minx,miny,maxx,maxy) or NULL            */
+} lsv2_geom;
+
+/* Per-instance state (the reference's binningBuffer) + per-tile ranges. */
+typedef struct lsv2_binning {
+    uint64_t capacity;       /* instances addressable in each array below          */
+    uint64_t* keys;          /* u64[capacity]  sorted (tile<<32 | depth bits)      */
+    uint32_t* point_list;    /* u32[capacity]  sorted Gaussian ids                 */
+    uint64_t* keys_alt;      /* u64[capacity]  unsorted keys / ping-pong buffer    */
+    uint32_t* vals_alt;      /* u32[capacity]                                      */
+    uint32_t* ranges;        /* u32[tiles][2]  (start,end) per 16x16 tile          */
+    void* scratch;           /* lsv2_sort_scratch_bytes(capacity, P)               */
+    size_t scratch_bytes;
+    uint32_t* status;        /* u32[LSV2_STATUS_WORDS]                             */
+} lsv2_binning;
+
+/* Sparse-coefficient inputs of the blend. */
+typedef struct lsv2_features {
+    int32_t mode;                /* LSV2_MODE_*                                            */
+    int32_t L;                   /* weight-map channels (64 train, 192 quick)              */
+    int32_t K;                   /* quick: entries per Gaussian                            */
+    const float* coeff_dense;    /* DENSE: f32[P][L]                                       */
+    const float* weights_quick;  /* QUICK: f32[P][K]                                       */
+    const float* indices_quick;  /* QUICK: f32[P][K] float-typed integers in [0,L)         */
+    /* DENSE only: compacted rows written by lsv2_compact_coeff (scratch, may be NULL to
+     * let lsv2_render_forward read the dense rows directly) */
+    uint32_t* sparse_count;      /* u32[P]  non-zeros per row, 0xFFFFFFFF = row too dense  */
+    uint16_t* sparse_index;      /* u16[P][LSV2_SPARSE_CAP]                                */
+    float* sparse_weight;        /* f32[P][LSV2_SPARSE_CAP]                                */
+} lsv2_features;
+#define LSV2_SPARSE_CAP 16
+
+/* Per-pixel outputs (rendered image, weight map, and the reference's imgBuffer). */
+typedef struct lsv2_image {
+    float* color;         /* f32[3][H][W]  = sum c*alpha*T + T*bg               */
+    float* wmap;          /* f32[L][H][W]  no background term; NULL in RGB mode  */
+    float* final_T;       /* f32[H][W]                                           */
+    uint32_t* n_contrib;  /* u32[H][W]     index (1-based) of the last contributor in the tile list */
+} lsv2_image;
+
+/* ---- library ------------------------------------------------------------------- */
+int lsv2_abi_version(void);
+const char* lsv2_strerror(int code);
+const char* lsv2_last_cuda_error(void);   /* text of the last CUDA failure on this thread */
+
+/* ---- sizes --------------------------------------------------------------------- */
+size_t lsv2_sort_scratch_bytes(uint64_t capacity, int32_t P);
+
+/* ---- forward stages (each replaces a stage of _C.rasterize_gaussians) ------------ */
+
+/* preprocessCUDA + InclusiveSum: fills geom, status[NUM_RENDERED].  `scratch` is
+ * binning->scratch (only scratch/scratch_bytes/status of `binning` are used). */
+int lsv2_preprocess(const lsv2_view* view, const lsv2_scene* scene, const lsv2_geom* geom,
+                    const lsv2_binning* binning, void* stream);
+
+/* duplicateWithKeys + stable radix sort on the (tile|depth) key + identifyTileRanges. */
+int lsv2_bin(const lsv2_view* view, int32_t P, const lsv2_geom* geom,
+             const lsv2_binning* binning, void* stream);
+
+/* DENSE mode helper: compact rows of coeff_dense for Gaussians with radii > 0. */
+int lsv2_compact_coeff(int32_t P, const lsv2_geom* geom, const lsv2_features* feat, void* stream);
+
+/* renderCUDA forward. */
+int lsv2_render_forward(const lsv2_view* view, const lsv2_geom* geom, const lsv2_binning* binning,
+                        const lsv2_features* feat, const lsv2_image* image, void* stream);
+
+/* all of the above back to back, no host involvement (CUDA-graph capturable). */
+int lsv2_forward(const lsv2_view* view, const lsv2_scene* scene, const lsv2_geom* geom,
+                 const lsv2_binning* binning, const lsv2_features* feat, const lsv2_image* image,
+                 void* stream);
+
+/* _C.mark_visible: present[i] = (view-space z > 0.2). */
+int lsv2_mark_visible(int32_t P, const float* means3d, const float* viewmatrix, uint8_t* present,
+                      void* stream);
+
+/* ---- backward (replaces _C.rasterize_gaussians_backward for the frozen-geometry
+ *      feature stage: scene/gaussian_model.py:238-243, train.py:173) ------------------
+ * dL_dcoeff f32[P][L] must be zero-initialised by the caller; it receives
+ *   sum_pix alpha*T * dL_dwmap[c][pix]
+ * on every channel (dense_grad != 0) or only on each row's non-zero support (== what
+ * survives autograd through torch.where in utils/vq_utils.py:20).  dL_dcolors f32[P][3]
+ * (zero-initialised) receives the colour gradient when dL_dcolor is non-NULL. */
+int lsv2_render_backward(const lsv2_view* view, const lsv2_geom* geom, const lsv2_binning* binning,
+                         const lsv2_features* feat, const lsv2_image* image,
+                         const float* dL_dwmap, const float* dL_dcolor, int32_t dense_grad,
+                         float* dL_dcoeff, float* dL_dcolors, void* stream);
+
+/* ---- global codebook decode (eval_lerf.py:214-218; scene/gaussian_model.py:533-549) ---
+ * wmap f32[levels*Lc][HW], codebooks f32[levels][Lc][D] -> out [levels][D][HW]
+ * out = C_l^T W_l, optionally divided by (||.||_2 over D + 1e-10).
+ * precision: LSV2_DECODE_FP32 (CUDA cores, fp32 FMA) or LSV2_DECODE_BF16 (tcgen05 tensor
+ * cores, bf16 operands, fp32 accumulate in TMEM).  out_dtype: 0 = f32, 1 = bf16. */
+enum { LSV2_DECODE_FP32 = 0, LSV2_DECODE_BF16 = 1 };
+size_t lsv2_decode_scratch_bytes(int32_t levels, int32_t Lc, int32_t D);
+int lsv2_decode(int32_t levels, int32_t Lc, int32_t D, int64_t HW, const float* wmap,
+                const float* codebooks, int32_t normalize, int32_t precision, int32_t out_dtype,
+                void* out, void* scratch, size_t scratch_bytes, void* stream);
+
+/* autograd of the un-normalised decode (scene/gaussian_model.py:538):
+ *   dW[l*Lc+k][p] = sum_d C[l][k][d] dF[l][d][p]   (f32[levels*Lc][HW])
+ *   dC[l][k][d]  += sum_p W[l*Lc+k][p] dF[l][d][p] (f32[levels][Lc][D], zero-initialised) */
+int lsv2_decode_backward(int32_t levels, int32_t Lc, int32_t D, int64_t HW, const float* wmap,
+                         const float* codebooks, const float* dF, float* dW, float* dC,
+                         void* stream);
+
+/* ---- sparse-coefficient producer (utils/vq_utils.py:9-40) ---------------------------
+ * logits f32[N][C] -> softmax, keep top-k, renormalise by (sum + 1e-10).
+ * dense f32[N][C] (may be NULL); weights f32[N][k] / indices f32[N][k] in ascending channel
+ * order (may be NULL). */
+int lsv2_topk_soft_code(int64_t N, int32_t C, int32_t k, const float* logits, float* dense,
+                        float* weights, float* indices, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LSV2_H */

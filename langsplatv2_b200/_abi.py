@@ -1,0 +1,139 @@
+"""ctypes binding of liblsv2.so (C ABI in include/lsv2.h).
+
+The product path has no CPU fallback: if the shared library is missing or a call fails, this
+module raises.  Nothing here imports ``oracle``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "liblsv2.so")
+
+LSV2_ABI_VERSION = 1
+TILE = 16
+SPARSE_CAP = 16
+STATUS_WORDS = 8
+STATUS_NUM_RENDERED, STATUS_OVERFLOW, STATUS_BAD_INDEX = 0, 1, 2
+MODE_RGB, MODE_DENSE, MODE_QUICK = 0, 1, 2
+DECODE_FP32, DECODE_BF16 = 0, 1
+
+_vp = C.c_void_p
+
+
+class View(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("tanfovx", C.c_float), ("tanfovy", C.c_float),
+                ("scale_modifier", C.c_float), ("sh_degree", C.c_int32),
+                ("viewmatrix", _vp), ("projmatrix", _vp), ("campos", _vp), ("bg", _vp)]
+
+
+class Scene(C.Structure):
+    _fields_ = [("P", C.c_int32), ("sh_coeffs", C.c_int32), ("means3d", _vp), ("opacities", _vp),
+                ("scales", _vp), ("rotations", _vp), ("cov3d_precomp", _vp), ("shs", _vp),
+                ("colors_precomp", _vp)]
+
+
+class Geom(C.Structure):
+    _fields_ = [("radii", _vp), ("xy", _vp), ("depth", _vp), ("conic_opacity", _vp), ("rgb", _vp),
+                ("clamped", _vp), ("tiles_touched", _vp), ("offsets", _vp), ("cov3d", _vp), ("rect", _vp)]
+
+
+class Binning(C.Structure):
+    _fields_ = [("capacity", C.c_uint64), ("keys", _vp), ("point_list", _vp), ("keys_alt", _vp),
+                ("vals_alt", _vp), ("ranges", _vp), ("scratch", _vp), ("scratch_bytes", C.c_size_t),
+                ("status", _vp)]
+
+
+class Features(C.Structure):
+    _fields_ = [("mode", C.c_int32), ("L", C.c_int32), ("K", C.c_int32), ("coeff_dense", _vp),
+                ("weights_quick", _vp), ("indices_quick", _vp), ("sparse_count", _vp),
+                ("sparse_index", _vp), ("sparse_weight", _vp)]
+
+
+class Image(C.Structure):
+    _fields_ = [("color", _vp), ("wmap", _vp), ("final_T", _vp), ("n_contrib", _vp)]
+
+
+EXPORTS = [
+    "lsv2_abi_version", "lsv2_strerror", "lsv2_last_cuda_error", "lsv2_sort_scratch_bytes",
+    "lsv2_preprocess", "lsv2_bin", "lsv2_compact_coeff", "lsv2_render_forward", "lsv2_forward",
+    "lsv2_mark_visible", "lsv2_render_backward", "lsv2_decode_scratch_bytes", "lsv2_decode",
+    "lsv2_decode_backward", "lsv2_topk_soft_code",
+]
+
+_lib = None
+
+
+class Lsv2Error(RuntimeError):
+    pass
+
+
+def lib() -> C.CDLL:
+    """Load liblsv2.so; raises if it has not been built (``python -c 'import __graft_entry__ as g; g.build()'``)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise Lsv2Error(f"{LIB_PATH} is missing: the CUDA extension has not been built "
+                        "(run __graft_entry__.build()); there is no CPU fallback")
+    L = C.CDLL(LIB_PATH)
+    L.lsv2_abi_version.restype = C.c_int
+    if L.lsv2_abi_version() != LSV2_ABI_VERSION:
+        raise Lsv2Error("liblsv2.so ABI version mismatch; rebuild")
+    L.lsv2_strerror.restype = C.c_char_p
+    L.lsv2_strerror.argtypes = [C.c_int]
+    L.lsv2_last_cuda_error.restype = C.c_char_p
+    L.lsv2_sort_scratch_bytes.restype = C.c_size_t
+    L.lsv2_sort_scratch_bytes.argtypes = [C.c_uint64, C.c_int32]
+    P = C.POINTER
+    L.lsv2_preprocess.argtypes = [P(View), P(Scene), P(Geom), P(Binning), _vp]
+    L.lsv2_bin.argtypes = [P(View), C.c_int32, P(Geom), P(Binning), _vp]
+    L.lsv2_compact_coeff.argtypes = [C.c_int32, P(Geom), P(Features), _vp]
+    L.lsv2_render_forward.argtypes = [P(View), P(Geom), P(Binning), P(Features), P(Image), _vp]
+    L.lsv2_forward.argtypes = [P(View), P(Scene), P(Geom), P(Binning), P(Features), P(Image), _vp]
+    L.lsv2_mark_visible.argtypes = [C.c_int32, _vp, _vp, _vp, _vp]
+    L.lsv2_render_backward.argtypes = [P(View), P(Geom), P(Binning), P(Features), P(Image), _vp, _vp,
+                                       C.c_int32, _vp, _vp, _vp]
+    L.lsv2_decode_scratch_bytes.restype = C.c_size_t
+    L.lsv2_decode_scratch_bytes.argtypes = [C.c_int32, C.c_int32, C.c_int32]
+    L.lsv2_decode.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int64, _vp, _vp, C.c_int32, C.c_int32,
+                              C.c_int32, _vp, _vp, C.c_size_t, _vp]
+    L.lsv2_decode_backward.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int64, _vp, _vp, _vp, _vp, _vp, _vp]
+    L.lsv2_topk_soft_code.argtypes = [C.c_int64, C.c_int32, C.c_int32, _vp, _vp, _vp, _vp, _vp]
+    if hasattr(L, "lsv2_render_decode"):
+        L.lsv2_render_decode.argtypes = [P(View), P(Geom), P(Binning), P(Features), P(Image), _vp, C.c_int32,
+                                         C.c_int32, C.c_int32, C.c_int32, _vp, _vp, C.c_size_t, _vp]
+    for name in ("lsv2_preprocess", "lsv2_bin", "lsv2_compact_coeff", "lsv2_render_forward", "lsv2_forward",
+                 "lsv2_mark_visible", "lsv2_render_backward", "lsv2_decode", "lsv2_decode_backward",
+                 "lsv2_topk_soft_code"):
+        getattr(L, name).restype = C.c_int
+    _lib = L
+    return L
+
+
+def check(code: int, what: str) -> None:
+    if code != 0:
+        L = lib()
+        msg = L.lsv2_strerror(code).decode()
+        if code == 2:
+            msg += ": " + L.lsv2_last_cuda_error().decode()
+        raise Lsv2Error(f"{what} failed: {msg}")
+
+
+def ptr(t) -> int | None:
+    """Device pointer of a contiguous CUDA tensor (None passes NULL)."""
+    if t is None:
+        return None
+    return t.data_ptr()
+
+
+def stream_ptr(device=None) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def require_cuda(t: torch.Tensor, name: str) -> None:
+    if not t.is_cuda:
+        raise Lsv2Error(f"{name} must be a CUDA tensor: langsplatv2_b200 has no CPU path")

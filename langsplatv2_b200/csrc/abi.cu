@@ -1,0 +1,187 @@
+// abi.cu -- extern "C" entry points of liblsv2.so (see include/lsv2.h for the contract and
+// the reference interfaces each one replaces).
+#include <stdio.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace lsv2 {
+
+static thread_local char g_cuda_error[512] = "";
+
+void set_cuda_error(cudaError_t e, const char* what)
+{
+    snprintf(g_cuda_error, sizeof g_cuda_error, "%s: %s (%s)", what, cudaGetErrorString(e), cudaGetErrorName(e));
+}
+
+int sort_num_passes(int depth_bits, int tile_bits);
+int launch_decode_fp32(int levels, int Lc, int D, int64_t HW, const float* wmap, const float* codebooks,
+                       int normalize, float* out, cudaStream_t st);
+int launch_decode_tc(int levels, int Lc, int D, int64_t HW, const float* wmap, const float* codebooks,
+                     int normalize, int out_dtype, void* out, void* scratch, size_t scratch_bytes, cudaStream_t st);
+size_t decode_tc_scratch_bytes(int levels, int Lc, int D);
+int launch_decode_backward(int levels, int Lc, int D, int64_t HW, const float* wmap, const float* codebooks,
+                           const float* dF, float* dW, float* dC, cudaStream_t st);
+int launch_topk_soft_code(int64_t N, int C, int k, const float* logits, float* dense, float* weights,
+                          float* indices, cudaStream_t st);
+
+static int tile_bits_for(const lsv2_view& v)
+{
+    const int gx = (v.width + TILE - 1) / TILE, gy = (v.height + TILE - 1) / TILE;
+    const int64_t tiles = (int64_t)gx * gy;
+    int bits = 1;
+    while ((1ll << bits) < tiles) ++bits;
+    return bits;
+}
+
+// depth keys are positive floats (z > NEAR_Z), so bit 31 of the low word is always clear
+constexpr int DEPTH_KEY_BITS = 31;
+
+static bool view_ok(const lsv2_view* v)
+{
+    return v && v->width > 0 && v->height > 0 && v->viewmatrix && v->projmatrix && v->campos && v->bg &&
+           v->tanfovx > 0.f && v->tanfovy > 0.f;
+}
+
+}  // namespace lsv2
+
+using namespace lsv2;
+
+extern "C" {
+
+int lsv2_abi_version(void) { return LSV2_ABI_VERSION; }
+
+const char* lsv2_strerror(int code)
+{
+    switch (code) {
+        case LSV2_OK: return "ok";
+        case LSV2_EINVAL: return "invalid argument combination";
+        case LSV2_ECUDA: return "CUDA error";
+        case LSV2_ENOSPC: return "scratch buffer too small";
+        case LSV2_EUNSUPPORTED: return "shape not supported by the sm_100a kernels";
+        default: return "unknown error";
+    }
+}
+
+const char* lsv2_last_cuda_error(void) { return g_cuda_error; }
+
+size_t lsv2_sort_scratch_bytes(uint64_t capacity, int32_t P)
+{
+    const size_t a = sort_scratch_bytes(capacity);
+    const size_t b = scan_scratch_bytes(P);
+    return (a > b ? a : b) + 256;
+}
+
+int lsv2_preprocess(const lsv2_view* view, const lsv2_scene* scene, const lsv2_geom* geom,
+                    const lsv2_binning* binning, void* stream)
+{
+    if (!view_ok(view) || !scene || !geom || !binning || !binning->status || scene->P < 0) return LSV2_EINVAL;
+    if (scene->P > 0 && (!scene->means3d || !scene->opacities || !geom->radii || !geom->xy || !geom->depth ||
+                         !geom->conic_opacity || !geom->rgb || !geom->tiles_touched || !geom->offsets))
+        return LSV2_EINVAL;
+    cudaStream_t st = (cudaStream_t)stream;
+    LSV2_CUDA_TRY(cudaMemsetAsync(binning->status, 0, LSV2_STATUS_WORDS * sizeof(uint32_t), st));
+    int rc = launch_preprocess(*view, *scene, *geom, st);
+    if (rc) return rc;
+    return launch_scan(scene->P, geom->tiles_touched, geom->offsets, binning->status + LSV2_STATUS_NUM_RENDERED,
+                       binning->scratch, binning->scratch_bytes, st);
+}
+
+int lsv2_bin(const lsv2_view* view, int32_t P, const lsv2_geom* geom, const lsv2_binning* binning, void* stream)
+{
+    if (!view_ok(view) || !geom || !binning || !binning->status || !binning->ranges) return LSV2_EINVAL;
+    if (binning->capacity > 0 && (!binning->keys || !binning->point_list || !binning->keys_alt || !binning->vals_alt))
+        return LSV2_EINVAL;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int tb = tile_bits_for(*view);
+    const int npass = sort_num_passes(DEPTH_KEY_BITS, tb);
+    // emit the unsorted pairs into the buffer from which an npass ping-pong ends in (keys, point_list)
+    lsv2_binning emit = *binning;
+    if (!(npass & 1)) { emit.keys_alt = binning->keys; emit.vals_alt = binning->point_list; }
+    int rc = launch_duplicate(*view, P, *geom, emit, st);
+    if (rc) return rc;
+    rc = launch_sort(*binning, DEPTH_KEY_BITS, tb, binning->scratch, binning->scratch_bytes, st);
+    if (rc) return rc;
+    return launch_ranges(*view, *binning, st);
+}
+
+int lsv2_compact_coeff(int32_t P, const lsv2_geom* geom, const lsv2_features* feat, void* stream)
+{
+    if (!geom || !feat) return LSV2_EINVAL;
+    return launch_compact_coeff(P, *geom, *feat, (cudaStream_t)stream);
+}
+
+int lsv2_render_forward(const lsv2_view* view, const lsv2_geom* geom, const lsv2_binning* binning,
+                        const lsv2_features* feat, const lsv2_image* image, void* stream)
+{
+    if (!view_ok(view) || !geom || !binning || !feat || !image) return LSV2_EINVAL;
+    if (!image->color || !image->final_T || !image->n_contrib) return LSV2_EINVAL;
+    return launch_render_forward(*view, *geom, *binning, *feat, *image, (cudaStream_t)stream);
+}
+
+int lsv2_forward(const lsv2_view* view, const lsv2_scene* scene, const lsv2_geom* geom,
+                 const lsv2_binning* binning, const lsv2_features* feat, const lsv2_image* image, void* stream)
+{
+    int rc = lsv2_preprocess(view, scene, geom, binning, stream);
+    if (rc) return rc;
+    rc = lsv2_bin(view, scene->P, geom, binning, stream);
+    if (rc) return rc;
+    if (feat && feat->mode == LSV2_MODE_DENSE && feat->sparse_count) {
+        rc = lsv2_compact_coeff(scene->P, geom, feat, stream);
+        if (rc) return rc;
+    }
+    return lsv2_render_forward(view, geom, binning, feat, image, stream);
+}
+
+int lsv2_mark_visible(int32_t P, const float* means3d, const float* viewmatrix, uint8_t* present, void* stream)
+{
+    if (P < 0 || (P > 0 && (!means3d || !viewmatrix || !present))) return LSV2_EINVAL;
+    return launch_mark_visible(P, means3d, viewmatrix, present, (cudaStream_t)stream);
+}
+
+int lsv2_render_backward(const lsv2_view* view, const lsv2_geom* geom, const lsv2_binning* binning,
+                         const lsv2_features* feat, const lsv2_image* image, const float* dL_dwmap,
+                         const float* dL_dcolor, int32_t dense_grad, float* dL_dcoeff, float* dL_dcolors,
+                         void* stream)
+{
+    if (!view_ok(view) || !geom || !binning || !feat || !image) return LSV2_EINVAL;
+    return launch_render_backward(*view, *geom, *binning, *feat, *image, dL_dwmap, dL_dcolor, dense_grad,
+                                  dL_dcoeff, dL_dcolors, (cudaStream_t)stream);
+}
+
+size_t lsv2_decode_scratch_bytes(int32_t levels, int32_t Lc, int32_t D)
+{
+    return decode_tc_scratch_bytes(levels, Lc, D);
+}
+
+int lsv2_decode(int32_t levels, int32_t Lc, int32_t D, int64_t HW, const float* wmap, const float* codebooks,
+                int32_t normalize, int32_t precision, int32_t out_dtype, void* out, void* scratch,
+                size_t scratch_bytes, void* stream)
+{
+    if (levels < 0 || Lc <= 0 || D <= 0 || HW < 0 || !wmap || !codebooks || !out) return LSV2_EINVAL;
+    if (precision == LSV2_DECODE_FP32) {
+        if (out_dtype != 0) return LSV2_EUNSUPPORTED;
+        return launch_decode_fp32(levels, Lc, D, HW, wmap, codebooks, normalize, (float*)out, (cudaStream_t)stream);
+    }
+    if (precision == LSV2_DECODE_BF16)
+        return launch_decode_tc(levels, Lc, D, HW, wmap, codebooks, normalize, out_dtype, out, scratch,
+                                scratch_bytes, (cudaStream_t)stream);
+    return LSV2_EINVAL;
+}
+
+int lsv2_decode_backward(int32_t levels, int32_t Lc, int32_t D, int64_t HW, const float* wmap,
+                         const float* codebooks, const float* dF, float* dW, float* dC, void* stream)
+{
+    if (levels < 0 || Lc <= 0 || D <= 0 || HW < 0 || !dF) return LSV2_EINVAL;
+    if ((dW && !codebooks) || (dC && !wmap)) return LSV2_EINVAL;
+    return launch_decode_backward(levels, Lc, D, HW, wmap, codebooks, dF, dW, dC, (cudaStream_t)stream);
+}
+
+int lsv2_topk_soft_code(int64_t N, int32_t C, int32_t k, const float* logits, float* dense, float* weights,
+                        float* indices, void* stream)
+{
+    if (N < 0 || !logits) return LSV2_EINVAL;
+    return launch_topk_soft_code(N, C, k, logits, dense, weights, indices, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,127 @@
+// common.cuh -- shared constants and device helpers of liblsv2 (sm_100a only).
+//
+// NUMERIC POLICY: the library is compiled with --fmad=false; every fp32 multiply/add is
+// rounded separately unless fmaf()/__fmaf_rn() is written out.  This is the same policy as
+// the CPU checker (gcc -ffp-contract=off), which is what lets the integer outputs (radii,
+// tiles_touched, sort keys, ranges, n_contrib) be compared bit for bit.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/lsv2.h"
+
+#if !defined(__CUDA_ARCH__) || (__CUDA_ARCH__ >= 1000)
+#else
+#error "liblsv2 is written for sm_100a (B200) only"
+#endif
+
+namespace lsv2 {
+
+// Constants of the 3DGS tile rasterizer that the LangSplatV2 fork chain shares.  None of
+// them can be read from /root/reference (the submodule is absent), so they live in one place.
+constexpr int TILE = LSV2_TILE;
+constexpr int TILE_PIX = TILE * TILE;
+constexpr float NEAR_Z = 0.2f;
+constexpr float W_GUARD = 0.0000001f;
+constexpr float FRUSTUM_CLAMP = 1.3f;
+constexpr float LOWPASS = 0.3f;
+constexpr float EIG_FLOOR = 0.1f;
+constexpr float RADIUS_SIGMA = 3.0f;
+constexpr float ALPHA_MAX = 0.99f;
+constexpr float ALPHA_MIN = 1.0f / 255.0f;
+constexpr float T_MIN = 0.0001f;
+
+constexpr int NUM_SMS = 148;
+
+// Thread-local text of the last CUDA failure (host side).
+void set_cuda_error(cudaError_t e, const char* what);
+
+#define LSV2_CUDA_TRY(expr)                                   \
+    do {                                                      \
+        cudaError_t _e = (expr);                              \
+        if (_e != cudaSuccess) {                              \
+            ::lsv2::set_cuda_error(_e, #expr);                \
+            return LSV2_ECUDA;                                \
+        }                                                     \
+    } while (0)
+
+#define LSV2_LAUNCH_CHECK(name)                               \
+    do {                                                      \
+        cudaError_t _e = cudaGetLastError();                  \
+        if (_e != cudaSuccess) {                              \
+            ::lsv2::set_cuda_error(_e, name);                 \
+            return LSV2_ECUDA;                                \
+        }                                                     \
+    } while (0)
+
+static inline int ceil_div(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
+
+// exp(x) for x <= 0 as a fixed-order polynomial: the same sequence of binary32 operations on
+// every machine, so the alpha thresholds of the blend (and with them n_contrib) reproduce.
+// <= 2 ulp from the correctly rounded value on [-87, 0].
+__device__ __forceinline__ float repro_expf(float x)
+{
+    if (!(x >= -87.0f)) return 0.0f;
+    if (x > 0.0f) x = 0.0f;
+    const float t = __fmul_rn(x, 1.44269504088896341f);
+    const float n = __fsub_rn(__fadd_rn(t, 12582912.0f), 12582912.0f);
+    float r = __fmaf_rn(n, -0.693145751953125f, x);
+    r = __fmaf_rn(n, -1.42860682030941723212e-6f, r);
+    float p = 1.9875691500e-4f;
+    p = __fmaf_rn(p, r, 1.3981999507e-3f);
+    p = __fmaf_rn(p, r, 8.3334519073e-3f);
+    p = __fmaf_rn(p, r, 4.1665795894e-2f);
+    p = __fmaf_rn(p, r, 1.6666665459e-1f);
+    p = __fmaf_rn(p, r, 5.0000001201e-1f);
+    const float r2 = __fmul_rn(r, r);
+    float y = __fmaf_rn(p, r2, r);
+    y = __fadd_rn(y, 1.0f);
+    return __int_as_float(__float_as_int(y) + (((int)n) << 23));
+}
+
+// Tile rectangle covered by a splat of integer radius `rad` centred at (px, py).
+__device__ __forceinline__ void tile_rect(float px, float py, float rad, int gx, int gy,
+                                          int& minx, int& miny, int& maxx, int& maxy)
+{
+    minx = min(gx, max(0, (int)((px - rad) / (float)TILE)));
+    miny = min(gy, max(0, (int)((py - rad) / (float)TILE)));
+    maxx = min(gx, max(0, (int)((px + rad + (float)(TILE - 1)) / (float)TILE)));
+    maxy = min(gy, max(0, (int)((py + rad + (float)(TILE - 1)) / (float)TILE)));
+}
+
+// Streaming (evict-first, no L1 allocate) global stores for write-once outputs.
+__device__ __forceinline__ void st_stream_f32(float* p, float v)
+{
+    asm volatile("st.global.cs.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+__device__ __forceinline__ void st_stream_f32x4(float* p, float a, float b, float c, float d)
+{
+    asm volatile("st.global.cs.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d)
+                 : "memory");
+}
+
+}  // namespace lsv2
+
+// ---- internal launchers (one per .cu) --------------------------------------------------
+namespace lsv2 {
+int launch_preprocess(const lsv2_view& v, const lsv2_scene& s, const lsv2_geom& g, cudaStream_t st);
+int launch_scan(int P, const uint32_t* in, uint32_t* out_inclusive, uint32_t* total_out,
+                void* scratch, size_t scratch_bytes, cudaStream_t st);
+size_t scan_scratch_bytes(int P);
+int launch_duplicate(const lsv2_view& v, int P, const lsv2_geom& g, const lsv2_binning& b, cudaStream_t st);
+int launch_ranges(const lsv2_view& v, const lsv2_binning& b, cudaStream_t st);
+size_t sort_scratch_bytes(uint64_t capacity);
+// sorts (keys_alt, vals_alt)[0..*n) on key bits selected by (lo_bits of the low word, hi_bits of
+// the high word) into (keys, point_list); stable.
+int launch_sort(const lsv2_binning& b, int depth_bits, int tile_bits, void* scratch, size_t scratch_bytes,
+                cudaStream_t st);
+int launch_compact_coeff(int P, const lsv2_geom& g, const lsv2_features& f, cudaStream_t st);
+int launch_render_forward(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b,
+                          const lsv2_features& f, const lsv2_image& img, cudaStream_t st);
+int launch_render_backward(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b,
+                           const lsv2_features& f, const lsv2_image& img, const float* dL_dwmap,
+                           const float* dL_dcolor, int dense_grad, float* dL_dcoeff, float* dL_dcolors,
+                           cudaStream_t st);
+int launch_mark_visible(int P, const float* means3d, const float* viewmatrix, uint8_t* present, cudaStream_t st);
+}  // namespace lsv2

@@ -1,0 +1,325 @@
+// decode_fp32.cu -- K7 (exact variant): global codebook decode + L2 normalisation on CUDA cores
+// with fp32 FMA accumulation.  Replaces the Python helpers every caller of the reference runs
+// after the rasterizer (/root/reference/eval_lerf.py:214-218, scene/gaussian_model.py:533-549,
+// train.py:38-58):
+//     F_l[D, HW] = C_l^T[D x Lc] . W_l[Lc x HW];   F_l /= (||F_l||_2 over D + 1e-10)
+// The tensor-core variant lives in decode_tc.cu; this one is the fp32-exact option and the
+// backward GEMMs of the decode.
+#include "common.cuh"
+
+namespace lsv2 {
+
+constexpr int DF_THREADS = 256;
+constexpr int DF_PIX = 128;    // pixels per CTA
+constexpr int DF_FEAT = 128;   // features per chunk
+constexpr int DF_KMAX = 32;    // codebook entries staged per sweep
+
+// grid: (ceil(HW/128), levels).  Thread tile 8 px x 8 features.
+__global__ void __launch_bounds__(DF_THREADS)
+k_decode_fp32(int Lc, int D, int64_t HW, const float* __restrict__ wmap, const float* __restrict__ codebooks,
+              int normalize, float* __restrict__ out)
+{
+    __shared__ __align__(16) float s_w[DF_KMAX][DF_PIX];
+    __shared__ __align__(16) float s_c[DF_KMAX][DF_FEAT];
+    __shared__ float s_ss[DF_PIX];
+
+    const int tid = threadIdx.x;
+    const int level = blockIdx.y;
+    const int64_t p0 = (int64_t)blockIdx.x * DF_PIX;
+    const int fg = tid & 15, pg = tid >> 4;           // feature group / pixel group (8 each)
+    const float* W = wmap + (size_t)level * Lc * HW;
+    const float* C = codebooks + (size_t)level * Lc * D;
+    float* O = out + (size_t)level * D * HW;
+
+    if (tid < DF_PIX) s_ss[tid] = 0.0f;
+    const int passes = normalize ? 2 : 1;
+    float inv[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) inv[i] = 1.0f;
+
+    for (int pass = 0; pass < passes; ++pass) {
+        const bool write = (pass == passes - 1);
+        float ss[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) ss[i] = 0.0f;
+        for (int f0 = 0; f0 < D; f0 += DF_FEAT) {
+            float acc[8][8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[i][j] = 0.0f;
+            for (int k0 = 0; k0 < Lc; k0 += DF_KMAX) {
+                const int kn = min(DF_KMAX, Lc - k0);
+                __syncthreads();
+                for (int e = tid; e < kn * DF_PIX; e += DF_THREADS) {
+                    const int k = e / DF_PIX, p = e % DF_PIX;
+                    s_w[k][p] = (p0 + p < HW) ? W[(size_t)(k0 + k) * HW + p0 + p] : 0.0f;
+                }
+                for (int e = tid; e < kn * DF_FEAT; e += DF_THREADS) {
+                    const int k = e / DF_FEAT, f = e % DF_FEAT;
+                    s_c[k][f] = (f0 + f < D) ? C[(size_t)(k0 + k) * D + f0 + f] : 0.0f;
+                }
+                __syncthreads();
+                for (int k = 0; k < kn; ++k) {
+                    const float4 wa = *reinterpret_cast<const float4*>(&s_w[k][pg * 8]);
+                    const float4 wb = *reinterpret_cast<const float4*>(&s_w[k][pg * 8 + 4]);
+                    const float4 ca = *reinterpret_cast<const float4*>(&s_c[k][fg * 8]);
+                    const float4 cb = *reinterpret_cast<const float4*>(&s_c[k][fg * 8 + 4]);
+                    const float wv[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+                    const float cv[8] = {ca.x, ca.y, ca.z, ca.w, cb.x, cb.y, cb.z, cb.w};
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(wv[i], cv[j], acc[i][j]);
+                }
+            }
+            if (!write) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) ss[i] = fmaf(acc[i][j], acc[i][j], ss[i]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int f = f0 + fg * 8 + j;
+                    if (f >= D) continue;
+                    float* dst = O + (size_t)f * HW + p0 + pg * 8;
+                    if (p0 + pg * 8 + 8 <= HW && (HW & 3) == 0) {
+                        st_stream_f32x4(dst, acc[0][j] * inv[0], acc[1][j] * inv[1], acc[2][j] * inv[2], acc[3][j] * inv[3]);
+                        st_stream_f32x4(dst + 4, acc[4][j] * inv[4], acc[5][j] * inv[5], acc[6][j] * inv[6], acc[7][j] * inv[7]);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i)
+                            if (p0 + pg * 8 + i < HW) dst[i] = acc[i][j] * inv[i];
+                    }
+                }
+            }
+        }
+        if (!write) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) atomicAdd(&s_ss[pg * 8 + i], ss[i]);
+            __syncthreads();
+#pragma unroll
+            for (int i = 0; i < 8; ++i) inv[i] = 1.0f / (sqrtf(s_ss[pg * 8 + i]) + 1e-10f);
+        }
+    }
+}
+
+int launch_decode_fp32(int levels, int Lc, int D, int64_t HW, const float* wmap, const float* codebooks,
+                       int normalize, float* out, cudaStream_t st)
+{
+    if (levels <= 0 || HW <= 0) return LSV2_OK;
+    dim3 grid((unsigned)ceil_div(HW, DF_PIX), (unsigned)levels);
+    k_decode_fp32<<<grid, DF_THREADS, 0, st>>>(Lc, D, HW, wmap, codebooks, normalize, out);
+    LSV2_LAUNCH_CHECK("k_decode_fp32");
+    return LSV2_OK;
+}
+
+// ---- decode backward (fp32) -------------------------------------------------------------
+// dW[l*Lc+k][p] = sum_d C[l][k][d] dF[l][d][p]
+// grid: (ceil(HW/128), levels); thread = (pixel, 32-channel half); dF column chunk staged in smem.
+__global__ void __launch_bounds__(256)
+k_decode_bwd_dW(int Lc, int D, int64_t HW, const float* __restrict__ codebooks, const float* __restrict__ dF,
+                float* __restrict__ dW)
+{
+    __shared__ float s_c[32][65];                    // [d chunk][k] (k < 64 per sweep)
+    const int tid = threadIdx.x;
+    const int level = blockIdx.y;
+    const int p = tid & 127, kh = tid >> 7;          // pixel in block, which half of a 64-k sweep
+    const int64_t pix = (int64_t)blockIdx.x * 128 + p;
+    const float* C = codebooks + (size_t)level * Lc * D;
+    const float* F = dF + (size_t)level * D * HW;
+    for (int k0 = 0; k0 < Lc; k0 += 64) {
+        float acc[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) acc[i] = 0.0f;
+        for (int d0 = 0; d0 < D; d0 += 32) {
+            __syncthreads();
+            for (int e = tid; e < 64 * 32; e += 256) {
+                const int k = e >> 5, d = e & 31;
+                s_c[d][k] = (k0 + k < Lc && d0 + d < D) ? C[(size_t)(k0 + k) * D + d0 + d] : 0.0f;
+            }
+            __syncthreads();
+            for (int d = 0; d < 32 && d0 + d < D; ++d) {
+                const float f = pix < HW ? F[(size_t)(d0 + d) * HW + pix] : 0.0f;
+#pragma unroll
+                for (int i = 0; i < 32; ++i) acc[i] = fmaf(s_c[d][kh * 32 + i], f, acc[i]);
+            }
+        }
+        if (pix < HW) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                const int k = k0 + kh * 32 + i;
+                if (k < Lc) dW[((size_t)level * Lc + k) * HW + pix] = acc[i];
+            }
+        }
+    }
+}
+
+// dC[l][k][d] += sum_p W[l*Lc+k][p] dF[l][d][p]
+// grid: (pixel slabs, D/64, levels); CTA tile 64 k x 64 d, thread tile 4 x 4; one atomic per
+// output element per CTA.
+constexpr int DC_SLAB = 4096;
+__global__ void __launch_bounds__(256)
+k_decode_bwd_dC(int Lc, int D, int64_t HW, const float* __restrict__ wmap, const float* __restrict__ dF,
+                float* __restrict__ dC)
+{
+    __shared__ __align__(16) float s_w[64][33];
+    __shared__ __align__(16) float s_f[64][33];
+    const int tid = threadIdx.x;
+    const int level = blockIdx.z;
+    const int d0 = blockIdx.y * 64;
+    const int64_t pbeg = (int64_t)blockIdx.x * DC_SLAB;
+    const int64_t pend = min(HW, pbeg + DC_SLAB);
+    const int kt = tid >> 4, dt = tid & 15;          // 16 x 16 threads, 4 x 4 outputs each
+    for (int k0 = 0; k0 < Lc; k0 += 64) {
+        float acc[4][4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[i][j] = 0.0f;
+        for (int64_t pp = pbeg; pp < pend; pp += 32) {
+            __syncthreads();
+            for (int e = tid; e < 64 * 32; e += 256) {
+                const int r = e >> 5, q = e & 31;
+                const bool okp = pp + q < pend;
+                s_w[r][q] = (okp && k0 + r < Lc) ? wmap[((size_t)level * Lc + k0 + r) * HW + pp + q] : 0.0f;
+                s_f[r][q] = (okp && d0 + r < D) ? dF[((size_t)level * D + d0 + r) * HW + pp + q] : 0.0f;
+            }
+            __syncthreads();
+#pragma unroll 8
+            for (int q = 0; q < 32; ++q) {
+                float wv[4], fv[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) { wv[i] = s_w[kt * 4 + i][q]; fv[i] = s_f[dt * 4 + i][q]; }
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(wv[i], fv[j], acc[i][j]);
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int k = k0 + kt * 4 + i, d = d0 + dt * 4 + j;
+                if (k < Lc && d < D && acc[i][j] != 0.0f)
+                    atomicAdd(dC + ((size_t)level * Lc + k) * D + d, acc[i][j]);
+            }
+    }
+}
+
+int launch_decode_backward(int levels, int Lc, int D, int64_t HW, const float* wmap, const float* codebooks,
+                           const float* dF, float* dW, float* dC, cudaStream_t st)
+{
+    if (levels <= 0 || HW <= 0) return LSV2_OK;
+    if (dW) {
+        dim3 grid((unsigned)ceil_div(HW, 128), (unsigned)levels);
+        k_decode_bwd_dW<<<grid, 256, 0, st>>>(Lc, D, HW, codebooks, dF, dW);
+        LSV2_LAUNCH_CHECK("k_decode_bwd_dW");
+    }
+    if (dC) {
+        dim3 grid((unsigned)ceil_div(HW, DC_SLAB), (unsigned)ceil_div(D, 64), (unsigned)levels);
+        k_decode_bwd_dC<<<grid, 256, 0, st>>>(Lc, D, HW, wmap, dF, dC);
+        LSV2_LAUNCH_CHECK("k_decode_bwd_dC");
+    }
+    return LSV2_OK;
+}
+
+// ---- softmax -> top-k -> renormalise (utils/vq_utils.py:9-40) -----------------------------
+// One warp per row; C <= 256.  Ties: the lower channel wins (torch.topk on CPU and the
+// checker agree on that for distinct values; exact ties are measure-zero for real logits).
+__global__ void __launch_bounds__(256)
+k_topk_soft_code(int64_t N, int C, int k, const float* __restrict__ logits, float* __restrict__ dense,
+                 float* __restrict__ weights, float* __restrict__ indices)
+{
+    const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (row >= N) return;
+    const float* x = logits + (size_t)row * C;
+    float v[8];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int c = i * 32 + lane;
+        v[i] = c < C ? x[c] : -INFINITY;
+        mx = fmaxf(mx, v[i]);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    // softmax in channel order to follow the checker's summation order is not possible in
+    // parallel; the sum is taken as a tree (differs from a serial sum in the last ulps).
+    float s = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int c = i * 32 + lane;
+        v[i] = c < C ? expf(v[i] - mx) : 0.0f;
+        s += v[i];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] = v[i] / s;
+    uint32_t sel = 0;   // bit i: element i*32+lane selected
+    float ts = 0.0f;
+    for (int j = 0; j < k; ++j) {
+        float best = -1.0f;
+        int bc = 0x7fffffff;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int c = i * 32 + lane;
+            if (c < C && !((sel >> i) & 1u) && (v[i] > best)) { best = v[i]; bc = c; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+            const int oc = __shfl_xor_sync(0xffffffffu, bc, o);
+            if (ob > best || (ob == best && oc < bc)) { best = ob; bc = oc; }
+        }
+        if ((bc & 31) == lane && bc < C) sel |= 1u << (bc >> 5);
+        ts += best;     // same value on every lane
+    }
+    // the checker sums the selected probabilities in channel order
+    float tsum = 0.0f;
+    {
+        // serial over channels, but only k terms are non-zero: gather them in order
+        for (int i = 0; i < 8; ++i) {
+            for (int l = 0; l < 32; ++l) {
+                const uint32_t bit = __shfl_sync(0xffffffffu, (sel >> i) & 1u, l);
+                if (bit) tsum += __shfl_sync(0xffffffffu, v[i], l);
+            }
+            if ((i + 1) * 32 >= C) break;
+        }
+    }
+    (void)ts;
+    const float den = tsum + 1e-10f;
+    int before = 0;   // number of selected channels below this lane's element i
+    for (int i = 0; i < 8; ++i) {
+        const int c = i * 32 + lane;
+        const uint32_t bits = __ballot_sync(0xffffffffu, (sel >> i) & 1u);
+        const int o = before + __popc(bits & ((1u << lane) - 1u));
+        const bool on = (sel >> i) & 1u;
+        const float val = on ? v[i] / den : 0.0f;
+        if (c < C) {
+            if (dense) dense[(size_t)row * C + c] = val;
+            if (on && o < k) {
+                if (weights) weights[(size_t)row * k + o] = val;
+                if (indices) indices[(size_t)row * k + o] = (float)c;
+            }
+        }
+        before += __popc(bits);
+        if ((i + 1) * 32 >= C) break;
+    }
+}
+
+int launch_topk_soft_code(int64_t N, int C, int k, const float* logits, float* dense, float* weights,
+                          float* indices, cudaStream_t st)
+{
+    if (N <= 0) return LSV2_OK;
+    if (C <= 0 || C > 256 || k <= 0 || k > C) return LSV2_EUNSUPPORTED;
+    k_topk_soft_code<<<ceil_div(N * 32, 256), 256, 0, st>>>(N, C, k, logits, dense, weights, indices);
+    LSV2_LAUNCH_CHECK("k_topk_soft_code");
+    return LSV2_OK;
+}
+
+}  // namespace lsv2

@@ -1,0 +1,356 @@
+"""Host-side mirror of the reference's operator API for the rasterization hot path.
+
+``GaussianRasterizationSettings`` / ``GaussianRasterizer`` keep the names, argument meaning and
+error behaviour of the ``diff_gaussian_rasterization`` package that the reference imports at
+/root/reference/gaussian_renderer/__init__.py:15 and calls at :37-54,108-119, so ``render()``,
+``train.py`` and the ``eval_*.py`` scripts can use this module as a drop-in.  Everything below the
+Python signatures is new: PyTorch only owns device memory and streams, the work is done by the
+hand-written sm_100a kernels in liblsv2.so, reached through the C ABI (include/lsv2.h).
+
+There is no CPU path.  A missing extension or a non-CUDA tensor raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import NamedTuple, Optional
+
+import torch
+import torch.nn as nn
+
+from . import _abi
+from ._abi import (Binning, Features, Geom, Image, Scene, View, MODE_DENSE, MODE_QUICK, MODE_RGB,
+                   SPARSE_CAP, STATUS_BAD_INDEX, STATUS_NUM_RENDERED, STATUS_OVERFLOW, STATUS_WORDS, TILE)
+
+#: strict per-channel gradient for ``language_feature_precomp`` (every channel of every touched
+#: Gaussian) instead of the support-only gradient (channels whose coefficient is non-zero).
+#: The two agree end to end because the reference masks non-top-k channels with ``torch.where``
+#: (utils/vq_utils.py:20); strict mode exists for parity tests at the operator boundary.
+DENSE_COEFF_GRAD = False
+
+
+class GaussianRasterizationSettings(NamedTuple):
+    """Same fields, same order as the keyword construction at gaussian_renderer/__init__.py:37-52."""
+    image_height: int
+    image_width: int
+    tanfovx: float
+    tanfovy: float
+    bg: torch.Tensor
+    scale_modifier: float
+    viewmatrix: torch.Tensor
+    projmatrix: torch.Tensor
+    sh_degree: int
+    campos: torch.Tensor
+    prefiltered: bool
+    debug: bool
+    include_feature: bool = False
+    quick_render: bool = False
+
+
+@dataclass
+class FrameState:
+    """Everything one forward leaves on the device (the reference's geom/binning/img buffers,
+    as named tensors instead of opaque byte blobs)."""
+    P: int
+    H: int
+    W: int
+    mode: int
+    L: int
+    K: int
+    view: View = None
+    geom: dict = field(default_factory=dict)
+    binning: dict = field(default_factory=dict)
+    image: dict = field(default_factory=dict)
+    feat: dict = field(default_factory=dict)
+    status: torch.Tensor = None
+    capacity: int = 0
+    keep: list = field(default_factory=list)    # tensors the View struct points into
+
+    @property
+    def num_rendered(self) -> int:
+        return int(self.status[STATUS_NUM_RENDERED].item()) & 0xFFFFFFFF
+
+    @property
+    def overflowed(self) -> bool:
+        return bool(self.status[STATUS_OVERFLOW].item())
+
+    def c_geom(self) -> Geom:
+        g = self.geom
+        return Geom(*[_abi.ptr(g.get(k)) for k in ("radii", "xy", "depth", "conic_opacity", "rgb", "clamped",
+                                                   "tiles_touched", "offsets", "cov3d", "rect")])
+
+    def c_binning(self) -> Binning:
+        b = self.binning
+        sc = b.get("scratch")
+        return Binning(self.capacity, _abi.ptr(b.get("keys")), _abi.ptr(b.get("point_list")),
+                       _abi.ptr(b.get("keys_alt")), _abi.ptr(b.get("vals_alt")), _abi.ptr(b.get("ranges")),
+                       _abi.ptr(sc), 0 if sc is None else sc.numel(), _abi.ptr(self.status))
+
+    def c_features(self) -> Features:
+        f = self.feat
+        return Features(self.mode, self.L, self.K, _abi.ptr(f.get("coeff_dense")), _abi.ptr(f.get("weights_quick")),
+                        _abi.ptr(f.get("indices_quick")), _abi.ptr(f.get("sparse_count")),
+                        _abi.ptr(f.get("sparse_index")), _abi.ptr(f.get("sparse_weight")))
+
+    def c_image(self) -> Image:
+        i = self.image
+        return Image(_abi.ptr(i.get("color")), _abi.ptr(i.get("wmap")), _abi.ptr(i.get("final_T")),
+                     _abi.ptr(i.get("n_contrib")))
+
+
+def _f32c(t: torch.Tensor, name: str) -> torch.Tensor:
+    _abi.require_cuda(t, name)
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+def _make_view(rs: GaussianRasterizationSettings, dev, keep: list) -> View:
+    vm = _f32c(rs.viewmatrix.to(dev), "viewmatrix")
+    pm = _f32c(rs.projmatrix.to(dev), "projmatrix")
+    cp = _f32c(rs.campos.to(dev), "campos")
+    bg = _f32c(rs.bg.to(dev), "bg")
+    if vm.numel() != 16 or pm.numel() != 16 or cp.numel() != 3 or bg.numel() != 3:
+        raise ValueError("viewmatrix/projmatrix must be 4x4, campos/bg 3-vectors")
+    keep += [vm, pm, cp, bg]
+    return View(int(rs.image_width), int(rs.image_height), float(rs.tanfovx), float(rs.tanfovy),
+                float(rs.scale_modifier), int(rs.sh_degree), vm.data_ptr(), pm.data_ptr(), cp.data_ptr(),
+                bg.data_ptr())
+
+
+def feature_mode(rs: GaussianRasterizationSettings) -> int:
+    """Mode comes from the settings flags, never from tensor shapes: the reference passes 1-element
+    float placeholders for the inputs a mode does not use (gaussian_renderer/__init__.py:93-103)."""
+    if rs.quick_render:
+        return MODE_QUICK
+    if rs.include_feature:
+        return MODE_DENSE
+    return MODE_RGB
+
+
+def rasterize_forward(rs: GaussianRasterizationSettings, means3D, opacities, shs=None, colors_precomp=None,
+                      scales=None, rotations=None, cov3D_precomp=None, language_feature_precomp=None,
+                      language_feature_weights_quick=None, language_feature_indices=None,
+                      capacity: Optional[int] = None, debug_buffers: bool = False,
+                      render: bool = True) -> FrameState:
+    """Preprocess -> bin -> blend.  ``capacity=None`` reads the instance count back between the two
+    halves (one host sync, as the reference does); an integer capacity runs the whole frame with no
+    host involvement and flags overflow in ``state.status``."""
+    L_ = _abi.lib()
+    dev = means3D.device
+    _abi.require_cuda(means3D, "means3D")
+    P = int(means3D.shape[0])
+    H, W = int(rs.image_height), int(rs.image_width)
+    mode = feature_mode(rs)
+    means3D = _f32c(means3D, "means3D")
+    opacities = _f32c(opacities, "opacities").reshape(-1)
+    if opacities.numel() != P:
+        raise ValueError("opacities must have one entry per Gaussian")
+
+    sh_coeffs = 0
+    if shs is not None:
+        shs = _f32c(shs, "shs")
+        if shs.dim() != 3 or shs.shape[0] != P or shs.shape[2] != 3:
+            raise ValueError("shs must be [P, M, 3]")
+        sh_coeffs = int(shs.shape[1])
+    if colors_precomp is not None:
+        colors_precomp = _f32c(colors_precomp, "colors_precomp")
+    if scales is not None:
+        scales = _f32c(scales, "scales")
+    if rotations is not None:
+        rotations = _f32c(rotations, "rotations")
+    if cov3D_precomp is not None:
+        cov3D_precomp = _f32c(cov3D_precomp, "cov3D_precomp")
+
+    L = K = 0
+    feat = {}
+    if mode == MODE_DENSE:
+        if language_feature_precomp is None or language_feature_precomp.dim() != 2 or \
+                language_feature_precomp.shape[0] != P:
+            raise ValueError("include_feature needs language_feature_precomp of shape [P, L]")
+        cd = _f32c(language_feature_precomp, "language_feature_precomp")
+        L = int(cd.shape[1])
+        feat["coeff_dense"] = cd
+        feat["sparse_count"] = torch.empty(P, dtype=torch.int32, device=dev)
+        feat["sparse_index"] = torch.empty((P, SPARSE_CAP), dtype=torch.int16, device=dev)
+        feat["sparse_weight"] = torch.empty((P, SPARSE_CAP), dtype=torch.float32, device=dev)
+    elif mode == MODE_QUICK:
+        wq, iq = language_feature_weights_quick, language_feature_indices
+        if wq is None or iq is None or wq.dim() != 2 or wq.shape != iq.shape or wq.shape[0] != P:
+            raise ValueError("quick_render needs language_feature_weights_quick / language_feature_indices "
+                             "of shape [P, K]")
+        feat["weights_quick"] = _f32c(wq, "language_feature_weights_quick")
+        feat["indices_quick"] = _f32c(iq, "language_feature_indices")
+        K = int(wq.shape[1])
+        # callers hard-wire 3 levels x 64 codes (eval_lerf.py:215); tolerate other level counts
+        L = int(getattr(rs, "quick_channels", 0) or QUICK_CHANNELS)
+
+    st = FrameState(P=P, H=H, W=W, mode=mode, L=L, K=K)
+    st.feat = feat
+    st.view = _make_view(rs, dev, st.keep)
+    st.keep += [means3D, opacities, shs, colors_precomp, scales, rotations, cov3D_precomp]
+    gx, gy = (W + TILE - 1) // TILE, (H + TILE - 1) // TILE
+
+    i32 = dict(dtype=torch.int32, device=dev)
+    f32 = dict(dtype=torch.float32, device=dev)
+    g = st.geom
+    g["radii"] = torch.empty(P, **i32)
+    g["xy"] = torch.empty((P, 2), **f32)
+    g["depth"] = torch.empty(P, **f32)
+    g["conic_opacity"] = torch.empty((P, 4), **f32)
+    g["rgb"] = torch.empty((P, 3), **f32)
+    g["clamped"] = torch.empty((P, 3), dtype=torch.uint8, device=dev)
+    g["tiles_touched"] = torch.empty(P, **i32)
+    g["offsets"] = torch.empty(P, **i32)
+    if debug_buffers:
+        g["cov3d"] = torch.empty((P, 6), **f32)
+        g["rect"] = torch.empty((P, 4), **i32)
+    st.status = torch.zeros(STATUS_WORDS, **i32)
+
+    scene = Scene(P, sh_coeffs, _abi.ptr(means3D), _abi.ptr(opacities), _abi.ptr(scales), _abi.ptr(rotations),
+                  _abi.ptr(cov3D_precomp), _abi.ptr(shs), _abi.ptr(colors_precomp))
+    stream = _abi.stream_ptr(dev)
+
+    img = st.image
+    img["color"] = torch.empty((3, H, W), **f32)
+    img["final_T"] = torch.empty((H, W), **f32)
+    img["n_contrib"] = torch.empty((H, W), **i32)
+    if mode != MODE_RGB:
+        img["wmap"] = torch.empty((L, H, W), **f32)
+
+    def alloc_binning(cap: int):
+        b = st.binning
+        st.capacity = cap
+        n = max(cap, 1)
+        b["keys"] = torch.empty(n, dtype=torch.int64, device=dev)
+        b["point_list"] = torch.empty(n, **i32)
+        b["keys_alt"] = torch.empty(n, dtype=torch.int64, device=dev)
+        b["vals_alt"] = torch.empty(n, **i32)
+        b["ranges"] = torch.empty((gx * gy, 2), **i32)
+        b["scratch"] = torch.empty(L_.lsv2_sort_scratch_bytes(cap, P), dtype=torch.uint8, device=dev)
+
+    if capacity is None:
+        st.binning["scratch"] = torch.empty(L_.lsv2_sort_scratch_bytes(0, P), dtype=torch.uint8, device=dev)
+        geom_c, bin_c = st.c_geom(), st.c_binning()
+        _abi.check(L_.lsv2_preprocess(C.byref(st.view), C.byref(scene), C.byref(geom_c), C.byref(bin_c), stream),
+                   "lsv2_preprocess")
+        R = st.num_rendered                                   # the one host sync of the frame
+        alloc_binning(R)
+        bin_c = st.c_binning()
+        _abi.check(L_.lsv2_bin(C.byref(st.view), P, C.byref(geom_c), C.byref(bin_c), stream), "lsv2_bin")
+        if render:
+            feat_c, img_c = st.c_features(), st.c_image()
+            if mode == MODE_DENSE:
+                _abi.check(L_.lsv2_compact_coeff(P, C.byref(geom_c), C.byref(feat_c), stream), "lsv2_compact_coeff")
+            _abi.check(L_.lsv2_render_forward(C.byref(st.view), C.byref(geom_c), C.byref(bin_c), C.byref(feat_c),
+                                              C.byref(img_c), stream), "lsv2_render_forward")
+    else:
+        alloc_binning(int(capacity))
+        geom_c, bin_c, feat_c, img_c = st.c_geom(), st.c_binning(), st.c_features(), st.c_image()
+        if render:
+            _abi.check(L_.lsv2_forward(C.byref(st.view), C.byref(scene), C.byref(geom_c), C.byref(bin_c),
+                                       C.byref(feat_c), C.byref(img_c), stream), "lsv2_forward")
+        else:
+            _abi.check(L_.lsv2_preprocess(C.byref(st.view), C.byref(scene), C.byref(geom_c), C.byref(bin_c), stream),
+                       "lsv2_preprocess")
+            _abi.check(L_.lsv2_bin(C.byref(st.view), P, C.byref(geom_c), C.byref(bin_c), stream), "lsv2_bin")
+    if rs.debug:
+        torch.cuda.synchronize(dev)
+        if st.overflowed:
+            raise _abi.Lsv2Error(f"instance capacity {st.capacity} too small for {st.num_rendered} instances")
+        if mode == MODE_QUICK and int(st.status[STATUS_BAD_INDEX].item()):
+            raise _abi.Lsv2Error(f"language_feature_indices outside [0, {L})")
+    return st
+
+
+#: weight-map channels in quick mode: the callers view the result as (3, 64, H, W)
+#: (eval_lerf.py:215, eval_3d_ovs.py:281, eval_mip_nerf360.py:173).
+QUICK_CHANNELS = 192
+
+
+def rasterize_backward(st: FrameState, grad_wmap: Optional[torch.Tensor], grad_color: Optional[torch.Tensor] = None,
+                       dense_grad: Optional[bool] = None):
+    """dL/d language_feature_precomp [P, L] (and dL/d colours [P, 3] when grad_color is given)."""
+    L_ = _abi.lib()
+    if st.mode != MODE_DENSE:
+        raise _abi.Lsv2Error("backward is defined for include_feature (dense coefficient) mode only")
+    dev = st.status.device
+    dense = DENSE_COEFF_GRAD if dense_grad is None else dense_grad
+    gw = _f32c(grad_wmap, "grad_wmap")
+    gc = _f32c(grad_color, "grad_color") if grad_color is not None else None
+    d_coeff = torch.zeros((st.P, st.L), dtype=torch.float32, device=dev)
+    d_colors = torch.zeros((st.P, 3), dtype=torch.float32, device=dev) if gc is not None else None
+    geom_c, bin_c, feat_c, img_c = st.c_geom(), st.c_binning(), st.c_features(), st.c_image()
+    _abi.check(L_.lsv2_render_backward(C.byref(st.view), C.byref(geom_c), C.byref(bin_c), C.byref(feat_c),
+                                       C.byref(img_c), _abi.ptr(gw), _abi.ptr(gc), 1 if dense else 0,
+                                       _abi.ptr(d_coeff), _abi.ptr(d_colors), _abi.stream_ptr(dev)),
+               "lsv2_render_backward")
+    return d_coeff, d_colors
+
+
+class _RasterizeGaussians(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, colors_precomp, language_feature_precomp, weights_quick, indices_quick,
+                opacities, scales, rotations, cov3Ds_precomp, raster_settings):
+        st = rasterize_forward(raster_settings, means3D, opacities, shs=sh, colors_precomp=colors_precomp,
+                               scales=scales, rotations=rotations, cov3D_precomp=cov3Ds_precomp,
+                               language_feature_precomp=language_feature_precomp,
+                               language_feature_weights_quick=weights_quick, language_feature_indices=indices_quick)
+        ctx.state = st
+        ctx.color_is_precomp = colors_precomp is not None
+        H, W = st.H, st.W
+        wmap = st.image.get("wmap")
+        if wmap is None:
+            wmap = torch.zeros((0, H, W), dtype=torch.float32, device=means3D.device)
+        radii = st.geom["radii"]
+        ctx.mark_non_differentiable(radii)
+        return st.image["color"], wmap, radii
+
+    @staticmethod
+    def backward(ctx, grad_color, grad_wmap, _grad_radii):
+        st = ctx.state
+        need = ctx.needs_input_grad
+        # inputs: 0 means3D, 1 means2D, 2 sh, 3 colors_precomp, 4 language_feature_precomp, 5 weights_quick,
+        #         6 indices_quick, 7 opacities, 8 scales, 9 rotations, 10 cov3Ds_precomp, 11 settings
+        if need[0] or need[2] or need[7] or need[8] or need[9] or need[10]:
+            raise NotImplementedError(
+                "geometry / SH / opacity gradients (the RGB stage of train.py) are outside this build's hot path; "
+                "the feature stage freezes them (scene/gaussian_model.py:238-243)")
+        d_coeff = d_colors = None
+        if st.mode == MODE_DENSE and need[4]:
+            gc = grad_color if (need[3] and ctx.color_is_precomp) else None
+            d_coeff, d_colors = rasterize_backward(st, grad_wmap, gc)
+        elif need[3]:
+            raise NotImplementedError("colour gradients are produced together with the feature backward only")
+        return (None, None, None, d_colors, d_coeff, None, None, None, None, None, None, None)
+
+
+class GaussianRasterizer(nn.Module):
+    """Drop-in for ``diff_gaussian_rasterization.GaussianRasterizer``."""
+
+    def __init__(self, raster_settings: GaussianRasterizationSettings):
+        super().__init__()
+        self.raster_settings = raster_settings
+
+    def markVisible(self, positions: torch.Tensor) -> torch.Tensor:
+        L_ = _abi.lib()
+        with torch.no_grad():
+            pos = _f32c(positions, "positions")
+            vm = _f32c(self.raster_settings.viewmatrix.to(pos.device), "viewmatrix")
+            out = torch.empty(pos.shape[0], dtype=torch.uint8, device=pos.device)
+            _abi.check(L_.lsv2_mark_visible(pos.shape[0], pos.data_ptr(), vm.data_ptr(), out.data_ptr(),
+                                            _abi.stream_ptr(pos.device)), "lsv2_mark_visible")
+        return out.bool()
+
+    def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, language_feature_precomp=None,
+                language_feature_weights_quick=None, language_feature_indices=None, scales=None, rotations=None,
+                cov3D_precomp=None):
+        rs = self.raster_settings
+        if (shs is None and colors_precomp is None) or (shs is not None and colors_precomp is not None):
+            raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or \
+                ((scales is not None or rotations is not None) and cov3D_precomp is not None):
+            raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+        return _RasterizeGaussians.apply(means3D, means2D, shs, colors_precomp, language_feature_precomp,
+                                         language_feature_weights_quick, language_feature_indices, opacities,
+                                         scales, rotations, cov3D_precomp, rs)

@@ -1,0 +1,230 @@
+"""CUDA path vs the CPU checker on the same seeded inputs.
+
+Integer outputs (radii, tiles_touched, offsets, sort keys, sorted ids, tile ranges, n_contrib) are
+compared bit for bit.  The blend reproduces the checker's binary32 operation order, so colour,
+weight map and final_T are also expected bit-identical; the test states the tolerance it would
+accept (1e-4 of the per-pixel feature norm) and additionally reports exact equality.
+Gradients (fp32 atomics vs the checker's float64 sums): max-abs <= 1e-4 * max|ref| + 1e-6.
+"""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from tests import helpers as hp
+
+pytestmark = pytest.mark.gpu
+
+BG = (0.1, 0.2, 0.3)
+
+
+def _check_geom_bin(st, pre, binned):
+    g = st.geom
+    np.testing.assert_array_equal(g["radii"].cpu().numpy(), pre["radii"])
+    np.testing.assert_array_equal(hp.u32(g["tiles_touched"]), pre["tiles_touched"])
+    np.testing.assert_array_equal(g["rect"].cpu().numpy(), pre["rect"])
+    np.testing.assert_array_equal(hp.u32(g["offsets"]), binned["offsets"])
+    for k in ("xy", "depth", "conic_opacity", "rgb", "cov3d"):
+        np.testing.assert_array_equal(g[k].cpu().numpy().view(np.uint32), pre[k].view(np.uint32), err_msg=k)
+    np.testing.assert_array_equal(g["clamped"].cpu().numpy(), pre["clamped"])
+    R = binned["R"]
+    assert st.num_rendered == R and not st.overflowed
+    np.testing.assert_array_equal(hp.u64(st.binning["keys"])[:R], binned["keys"])
+    np.testing.assert_array_equal(hp.u32(st.binning["point_list"])[:R], binned["point_list"])
+    np.testing.assert_array_equal(hp.u32(st.binning["ranges"]), binned["ranges"])
+
+
+def _check_image(st, fwd, L):
+    img = st.image
+    np.testing.assert_array_equal(hp.u32(img["n_contrib"]), fwd["n_contrib"])
+    np.testing.assert_array_equal(img["final_T"].cpu().numpy().view(np.uint32), fwd["final_T"].view(np.uint32))
+    np.testing.assert_allclose(img["color"].cpu().numpy(), fwd["color"], rtol=0, atol=1e-5)
+    if L:
+        w = img["wmap"].cpu().numpy()
+        norm = np.sqrt((fwd["wmap"] ** 2).sum(0, keepdims=True)) + 1e-12
+        assert np.max(np.abs(w - fwd["wmap"]) / np.maximum(norm, 1e-3)) <= 1e-4
+        np.testing.assert_array_equal(w.view(np.uint32), fwd["wmap"].view(np.uint32))
+
+
+@pytest.mark.parametrize("N,W,H,view", [(3000, 160, 96, 0), (20000, 256, 256, 3), (5000, 250, 131, 5)])
+def test_rgb_mode(N, W, H, view):
+    scene, cam = hp.make_case(N, W, H, seed=N, scale_boost=3.0)
+    pre, binned, fwd = oracle.forward(hp.oracle_scene(scene), hp.oracle_view(cam), mode=0, bg=BG)
+    st = hp.run_cuda(scene, cam, BG, hp.MODE_RGB)
+    _check_geom_bin(st, pre, binned)
+    _check_image(st, fwd, 0)
+
+
+@pytest.mark.parametrize("N,W,H", [(4000, 128, 80), (50000, 256, 256)])
+def test_dense_mode(N, W, H):
+    scene, cam = hp.make_case(N, W, H, seed=7, levels=1, scale_boost=3.0 if N < 10000 else 1.5)
+    dense, _, _ = hp.coeffs(scene, k=4)
+    pre, binned, fwd = oracle.forward(hp.oracle_scene(scene), hp.oracle_view(cam), mode=1, L=64,
+                                      coeff_dense=dense, bg=BG)
+    st = hp.run_cuda(scene, cam, BG, hp.MODE_DENSE, dense=dense)
+    _check_geom_bin(st, pre, binned)
+    _check_image(st, fwd, 64)
+
+
+def test_dense_mode_rows_denser_than_cap():
+    """rows with more than 16 non-zeros take the dense-row path of the blend"""
+    scene, cam = hp.make_case(3000, 128, 96, seed=11, levels=1, scale_boost=3.0)
+    dense, _, _ = hp.coeffs(scene, k=4)
+    rng = np.random.default_rng(0)
+    dense[::3] = rng.random((dense[::3].shape[0], 64), dtype=np.float32)
+    pre, binned, fwd = oracle.forward(hp.oracle_scene(scene), hp.oracle_view(cam), mode=1, L=64,
+                                      coeff_dense=dense, bg=BG)
+    st = hp.run_cuda(scene, cam, BG, hp.MODE_DENSE, dense=dense)
+    _check_image(st, fwd, 64)
+
+
+@pytest.mark.parametrize("N,W,H", [(4000, 144, 100), (30000, 320, 240)])
+def test_quick_mode(N, W, H):
+    scene, cam = hp.make_case(N, W, H, seed=5, levels=3, scale_boost=2.0)
+    _, wq, iq = hp.coeffs(scene, k=4)
+    pre, binned, fwd = oracle.forward(hp.oracle_scene(scene), hp.oracle_view(cam), mode=2, L=192,
+                                      weights_quick=wq, indices_quick=iq, bg=BG)
+    st = hp.run_cuda(scene, cam, BG, hp.MODE_QUICK, wq=wq, iq=iq)
+    _check_geom_bin(st, pre, binned)
+    _check_image(st, fwd, 192)
+
+
+def test_bounded_capacity_matches_exact_and_flags_overflow():
+    scene, cam = hp.make_case(8000, 200, 120, seed=2, scale_boost=2.0)
+    _, wq, iq = hp.coeffs(scene, k=4)
+    exact = hp.run_cuda(scene, cam, BG, hp.MODE_QUICK, wq=wq, iq=iq)
+    R = exact.num_rendered
+    bounded = hp.run_cuda(scene, cam, BG, hp.MODE_QUICK, wq=wq, iq=iq, capacity=R + 1000)
+    assert bounded.num_rendered == R and not bounded.overflowed
+    assert torch.equal(bounded.image["wmap"], exact.image["wmap"])
+    assert torch.equal(bounded.binning["point_list"][:R], exact.binning["point_list"][:R])
+    small = hp.run_cuda(scene, cam, BG, hp.MODE_QUICK, wq=wq, iq=iq, capacity=R // 2)
+    assert small.overflowed and small.num_rendered == R
+
+
+def test_empty_and_degenerate_inputs():
+    scene, cam = hp.make_case(64, 48, 40, seed=1)
+    # everything behind the camera -> nothing rendered, image == background
+    scene["xyz"] = scene["xyz"] * 0 + torch.tensor([100.0, 0.0, 0.0])
+    cam2 = hp.synth.ring_camera(0, 8, 48, 40)
+    st = hp.run_cuda(scene, cam2, BG, hp.MODE_RGB)
+    assert st.num_rendered == 0
+    assert int((st.geom["radii"] != 0).sum()) == 0
+    col = st.image["color"].cpu()
+    for c in range(3):
+        assert torch.all(col[c] == BG[c])
+    assert int(st.image["n_contrib"].sum()) == 0
+
+
+def test_sort_large_random_keys_properties():
+    """Full-size property check (size-independent): sorted order, stability, permutation."""
+    scene, cam = hp.make_case(300000, 1008, 756, seed=3)
+    st = hp.run_cuda(scene, cam, BG, hp.MODE_RGB)
+    R = st.num_rendered
+    keys = hp.u64(st.binning["keys"])[:R]
+    ids = hp.u32(st.binning["point_list"])[:R]
+    assert np.all(keys[1:] >= keys[:-1])
+    same = keys[1:] == keys[:-1]
+    assert np.all(ids[1:][same] > ids[:-1][same])           # stable: emission order is id-ascending
+    depth = st.geom["depth"].cpu().numpy().view(np.uint32)
+    assert np.array_equal((keys & 0xFFFFFFFF).astype(np.uint32), depth[ids])
+    counts = np.bincount(ids, minlength=scene["xyz"].shape[0])
+    assert np.array_equal(counts.astype(np.uint32), hp.u32(st.geom["tiles_touched"]))
+    ranges = hp.u32(st.binning["ranges"])
+    tiles = (keys >> 32).astype(np.int64)
+    nz = ranges[:, 1] > ranges[:, 0]
+    assert (ranges[nz, 1] - ranges[nz, 0]).sum() == R
+    for t in np.nonzero(nz)[0][:: max(1, nz.sum() // 50)]:
+        assert np.all(tiles[ranges[t, 0]:ranges[t, 1]] == t)
+
+
+@pytest.mark.parametrize("dense_grad", [False, True])
+def test_backward_coeff_grad(dense_grad):
+    from langsplatv2_b200.rasterizer import rasterize_backward
+    N, W, H = 6000, 128, 96
+    scene, cam = hp.make_case(N, W, H, seed=9, levels=1, scale_boost=3.0)
+    dense, _, _ = hp.coeffs(scene, k=4)
+    pre, binned, fwd = oracle.forward(hp.oracle_scene(scene), hp.oracle_view(cam), mode=1, L=64,
+                                      coeff_dense=dense, bg=BG)
+    rng = np.random.default_rng(1)
+    dW = rng.standard_normal((64, H, W)).astype(np.float32)
+    dCol = rng.standard_normal((3, H, W)).astype(np.float32)
+    ref, ref_c = oracle.render_backward_coeff(pre, binned, fwd, W, H, 64, dW, dense=dense_grad,
+                                              coeff_dense=dense, dL_dcolor=dCol)
+    st = hp.run_cuda(scene, cam, BG, hp.MODE_DENSE, dense=dense)
+    g, gc = rasterize_backward(st, torch.tensor(dW).cuda(), torch.tensor(dCol).cuda(), dense_grad=dense_grad)
+    tol = 1e-4 * np.abs(ref).max() + 1e-6
+    assert np.max(np.abs(g.cpu().numpy() - ref)) <= tol
+    assert np.max(np.abs(gc.cpu().numpy() - ref_c)) <= 1e-4 * np.abs(ref_c).max() + 1e-6
+    if not dense_grad:
+        assert np.all(g.cpu().numpy()[dense == 0] == 0)
+
+
+def test_autograd_function_matches_backward_call():
+    from langsplatv2_b200 import GaussianRasterizer
+    N, W, H = 3000, 96, 64
+    scene, cam = hp.make_case(N, W, H, seed=4, levels=1, scale_boost=3.0)
+    dense, _, _ = hp.coeffs(scene, k=4)
+    rs = hp.settings(cam, scene, BG, include_feature=True)
+    coeff = torch.tensor(dense).cuda().requires_grad_(True)
+    rast = GaussianRasterizer(raster_settings=rs)
+    means2D = torch.zeros(N, 3, device="cuda", requires_grad=True)
+    ph = torch.zeros((1,), device="cuda")
+    color, wmap, radii = rast(means3D=scene["xyz"].cuda(), means2D=means2D, shs=scene["features"].cuda(),
+                              colors_precomp=None, language_feature_precomp=coeff,
+                              language_feature_weights_quick=ph, language_feature_indices=ph,
+                              opacities=scene["opacity"].cuda(), scales=scene["scaling"].cuda(),
+                              rotations=scene["rotation"].cuda(), cov3D_precomp=None)
+    assert color.shape == (3, H, W) and wmap.shape == (64, H, W) and radii.shape == (N,) and radii.dtype == torch.int32
+    target = torch.randn_like(wmap)
+    (wmap * target).sum().backward()
+    pre, binned, fwd = oracle.forward(hp.oracle_scene(scene), hp.oracle_view(cam), mode=1, L=64,
+                                      coeff_dense=dense, bg=BG)
+    ref = oracle.render_backward_coeff(pre, binned, fwd, W, H, 64, target.cpu().numpy(), dense=False,
+                                       coeff_dense=dense)
+    assert np.max(np.abs(coeff.grad.cpu().numpy() - ref)) <= 1e-4 * np.abs(ref).max() + 1e-6
+
+
+@pytest.mark.parametrize("levels,HW", [(1, 1000), (3, 16 * 333 + 5)])
+def test_decode_fp32(levels, HW):
+    from langsplatv2_b200 import decode_feature_map
+    rng = np.random.default_rng(levels)
+    w = rng.random((levels * 64, HW), dtype=np.float32)
+    w[rng.random(w.shape) < 0.6] = 0
+    cb = rng.standard_normal((levels, 64, 512)).astype(np.float32)
+    for normalize in (True, False):
+        ref = oracle.decode(w, cb, normalize=normalize)
+        out = decode_feature_map(torch.tensor(w).cuda(), torch.tensor(cb).cuda(), normalize=normalize,
+                                 precision="fp32").cpu().numpy()
+        scale = np.abs(ref).max()
+        assert np.max(np.abs(out - ref)) <= 2e-6 * max(scale, 1.0) * (1 if normalize else 64)
+
+
+def test_decode_backward_fp32():
+    from langsplatv2_b200 import decode_feature_map
+    rng = np.random.default_rng(3)
+    levels, HW = 2, 4500
+    w = rng.random((levels * 64, HW), dtype=np.float32)
+    cb = rng.standard_normal((levels, 64, 512)).astype(np.float32)
+    dF = rng.standard_normal((levels, 512, HW)).astype(np.float32)
+    dW_ref, dC_ref = oracle.decode_backward(w, cb, dF)
+    wt = torch.tensor(w).cuda().requires_grad_(True)
+    ct = torch.tensor(cb).cuda().requires_grad_(True)
+    F = decode_feature_map(wt, ct, normalize=False)
+    F.backward(torch.tensor(dF).cuda())
+    assert np.max(np.abs(wt.grad.cpu().numpy() - dW_ref)) <= 1e-4 * np.abs(dW_ref).max()
+    assert np.max(np.abs(ct.grad.cpu().numpy() - dC_ref)) <= 1e-4 * np.abs(dC_ref).max()
+
+
+def test_topk_soft_code():
+    from langsplatv2_b200 import softmax_to_topk_soft_code, get_weights_and_indices
+    rng = np.random.default_rng(0)
+    logits = rng.standard_normal((5000, 64)).astype(np.float32)
+    ref = oracle.topk_soft_code(logits, 4)
+    out = softmax_to_topk_soft_code(torch.tensor(logits).cuda(), 4).cpu().numpy()
+    assert np.array_equal(out != 0, ref != 0)
+    np.testing.assert_allclose(out, ref, rtol=2e-6, atol=1e-8)
+    w_ref, i_ref = oracle.weights_and_indices(logits, 4)
+    w, i = get_weights_and_indices(torch.tensor(logits).cuda(), 4)
+    assert np.array_equal(i.cpu().numpy(), i_ref)
+    np.testing.assert_allclose(w.cpu().numpy(), w_ref, rtol=2e-6, atol=1e-8)
