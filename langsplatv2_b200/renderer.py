@@ -1,0 +1,98 @@
+"""Resident-scene feature renderer: the serving-shaped wrapper around the op.
+
+Equivalent of ``render_language_feature_map_quick`` + the model hoisting it needs
+(/root/reference/eval_lerf.py:210-220 with the per-frame reload of :321-345 hoisted out of the image
+loop): the merged top-k weights/indices of all levels and the codebooks stay on the device, each call
+takes a camera and returns the L2-normalised ``[levels, 512, H, W]`` feature map.
+
+``bounded=True`` runs a frame with no host synchronisation at all (instance buffers are sized once from
+a measured high-water mark and overflow is flagged on the device); ``bounded=False`` reads the instance
+count back between preprocess and binning like the reference does.
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional
+
+import torch
+
+from . import _abi
+from .decode import decode_feature_map
+from .rasterizer import GaussianRasterizationSettings, FrameState, rasterize_forward
+from .sparse import get_weights_and_indices
+
+
+class FeatureRenderer:
+    def __init__(self, scene: Dict, topk: int = 4, device="cuda", precision: str = "bf16",
+                 out_dtype: torch.dtype = torch.float32, bounded: bool = True, headroom: float = 1.25):
+        dev = torch.device(device)
+        self.device = dev
+        self.levels = int(scene["levels"])
+        self.codebook_size = int(scene["codebook_size"])
+        self.sh_degree = int(scene["sh_degree"])
+        self.xyz = scene["xyz"].to(dev).contiguous()
+        self.opacity = scene["opacity"].to(dev).contiguous()
+        self.scaling = scene["scaling"].to(dev).contiguous()
+        self.rotation = scene["rotation"].to(dev).contiguous()
+        self.features = scene["features"].to(dev).contiguous()
+        self.codebooks = scene["codebooks"].to(dev).contiguous()
+        logits = scene["logits"].to(dev)
+        ws, idx = [], []
+        for l in range(self.levels):            # eval_lerf.py:333-345
+            w, i = get_weights_and_indices(logits[:, l * self.codebook_size:(l + 1) * self.codebook_size], topk)
+            ws.append(w)
+            idx.append(i + l * self.codebook_size)
+        self.weights = torch.cat(ws, dim=1).contiguous()
+        self.indices = torch.cat(idx, dim=1).contiguous()
+        self.precision = precision
+        self.out_dtype = out_dtype
+        self.bounded = bounded
+        self.headroom = headroom
+        self.capacity: Optional[int] = None
+        self.bg = torch.zeros(3, dtype=torch.float32, device=dev)
+        self.last_state: Optional[FrameState] = None
+        self.hook = None                        # optional callable(tag) for event timing in bench.py
+
+    def settings(self, cam: Dict) -> GaussianRasterizationSettings:
+        return GaussianRasterizationSettings(
+            image_height=int(cam["image_height"]), image_width=int(cam["image_width"]),
+            tanfovx=float(cam["tanfovx"]), tanfovy=float(cam["tanfovy"]), bg=self.bg, scale_modifier=1.0,
+            viewmatrix=cam["world_view_transform"], projmatrix=cam["full_proj_transform"],
+            sh_degree=self.sh_degree, campos=cam["camera_center"], prefiltered=False, debug=False,
+            include_feature=True, quick_render=True)
+
+    def calibrate(self, cams) -> int:
+        """Size the instance buffers from the largest view of ``cams`` (exact, synchronising frames)."""
+        peak = 0
+        for cam in cams:
+            st = self._raster(cam, capacity=None, render=False)
+            peak = max(peak, st.num_rendered)
+        self.capacity = int(peak * self.headroom) + 4096
+        return self.capacity
+
+    def _raster(self, cam, capacity, render=True) -> FrameState:
+        return rasterize_forward(self.settings(cam), self.xyz, self.opacity, shs=self.features,
+                                 scales=self.scaling, rotations=self.rotation,
+                                 language_feature_weights_quick=self.weights,
+                                 language_feature_indices=self.indices, capacity=capacity, render=render)
+
+    @torch.no_grad()
+    def render(self, cam: Dict) -> torch.Tensor:
+        """-> [levels, 512, H, W] normalised feature map (also keeps the RGB render in ``last_state``)."""
+        cap = self.capacity if self.bounded else None
+        if self.bounded and cap is None:
+            cap = self.calibrate([cam])
+        st = self._raster(cam, cap)
+        self.last_state = st
+        if self.hook:
+            self.hook("decode_begin")
+        out = decode_feature_map(st.image["wmap"], self.codebooks, normalize=True, precision=self.precision,
+                                 out_dtype=self.out_dtype)
+        if self.hook:
+            self.hook("decode_end")
+        return out
+
+    def check_overflow(self) -> None:
+        st = self.last_state
+        if st is not None and st.overflowed:
+            raise _abi.Lsv2Error(f"instance capacity {st.capacity} overflowed ({st.num_rendered} needed); "
+                                 "call calibrate() with representative views")

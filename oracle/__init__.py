@@ -117,19 +117,28 @@ def bin_instances(pre: dict, W: int, H: int):
 
 
 def render_forward(pre: dict, binned: dict, W: int, H: int, bg, mode: int = 0, L: int = 0,
-                   coeff_dense=None, weights_quick=None, indices_quick=None):
+                   coeff_dense=None, weights_quick=None, indices_quick=None, tile_stride: int = 1,
+                   tile_phase: int = 0):
     bg = _f32(bg).reshape(3)
     coeff_dense, wq, iq = _f32(coeff_dense), _f32(weights_quick), _f32(indices_quick)
     K = 0 if wq is None else wq.shape[1]
     out = dict(color=np.zeros((3, H, W), np.float32), wmap=np.zeros((max(L, 0), H, W), np.float32),
                final_T=np.zeros((H, W), np.float32), n_contrib=np.zeros((H, W), np.uint32))
     pl = np.ascontiguousarray(binned["point_list"]) if binned["R"] > 0 else np.zeros(1, np.uint32)
-    lib().lsv2o_render_forward(
+    lib().lsv2o_render_forward_tiles(
         C.c_int(W), C.c_int(H), _p(binned["ranges"]), _p(pl), _p(pre["xy"]),
         _p(pre["conic_opacity"]), _p(pre["rgb"]), C.c_int(mode), C.c_int(L), C.c_int(K),
         _p(coeff_dense), _p(wq), _p(iq), _p(bg),
-        _p(out["color"]), _p(out["wmap"]), _p(out["final_T"]), _p(out["n_contrib"]))
+        _p(out["color"]), _p(out["wmap"]), _p(out["final_T"]), _p(out["n_contrib"]),
+        C.c_int(tile_stride), C.c_int(tile_phase))
     return out
+
+
+def tile_pixel_mask(W: int, H: int, tile_stride: int, tile_phase: int = 0) -> np.ndarray:
+    """bool [H, W]: pixels of the tiles that render_forward(tile_stride, tile_phase) renders."""
+    gx, gy = grid(W, H)
+    ty, tx = np.meshgrid(np.arange(H) // TILE, np.arange(W) // TILE, indexing="ij")
+    return ((ty * gx + tx) % tile_stride) == tile_phase
 
 
 def render_backward_coeff(pre: dict, binned: dict, fwd: dict, W: int, H: int, L: int, dL_dwmap,

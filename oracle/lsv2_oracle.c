@@ -385,13 +385,14 @@ static inline float blend_power(const float* xy, const float* co, float px, floa
     return fmaf(ax * dx, dx, fmaf(az * dy, dy, (b * dx) * dy));
 }
 
-int lsv2o_render_forward(int W, int H, const uint32_t* ranges, const uint32_t* point_list,
+static int render_forward_impl(int W, int H, const uint32_t* ranges, const uint32_t* point_list,
                          const float* xy, const float* conic_opacity, const float* rgb,
                          int mode, int L, int K,
                          const float* coeff_dense, const float* wq, const float* iq,
                          const float* bg,
                          float* out_color /*[3][H][W]*/, float* out_wmap /*[L][H][W]*/,
-                         float* final_T /*[H][W]*/, uint32_t* n_contrib /*[H][W]*/)
+                         float* final_T /*[H][W]*/, uint32_t* n_contrib /*[H][W]*/,
+                         int tile_stride, int tile_phase)
 {
     const int gx = (W + LSV2O_TILE - 1) / LSV2O_TILE, gy = (H + LSV2O_TILE - 1) / LSV2O_TILE;
     const size_t HW = (size_t)H * W;
@@ -400,6 +401,7 @@ int lsv2o_render_forward(int W, int H, const uint32_t* ranges, const uint32_t* p
         float* acc = (float*)malloc(sizeof(float) * (size_t)(L > 0 ? L : 1));
 #pragma omp for schedule(dynamic, 1)
         for (int tile = 0; tile < gx * gy; ++tile) {
+            if (tile % tile_stride != tile_phase) continue;
             const int tx = tile % gx, ty = tile / gx;
             const uint32_t r0 = ranges[2 * tile], r1 = ranges[2 * tile + 1];
             for (int ly = 0; ly < LSV2O_TILE; ++ly)
@@ -445,6 +447,32 @@ int lsv2o_render_forward(int W, int H, const uint32_t* ranges, const uint32_t* p
         free(acc);
     }
     return 0;
+}
+
+int lsv2o_render_forward(int W, int H, const uint32_t* ranges, const uint32_t* point_list,
+                         const float* xy, const float* conic_opacity, const float* rgb,
+                         int mode, int L, int K,
+                         const float* coeff_dense, const float* wq, const float* iq,
+                         const float* bg, float* out_color, float* out_wmap, float* final_T,
+                         uint32_t* n_contrib)
+{
+    return render_forward_impl(W, H, ranges, point_list, xy, conic_opacity, rgb, mode, L, K, coeff_dense,
+                               wq, iq, bg, out_color, out_wmap, final_T, n_contrib, 1, 0);
+}
+
+/* Same blend, but only the tiles with tile % stride == phase are rendered (the other pixels of
+ * the outputs are left untouched).  Used by bench.py to time a bounded sample of a large frame. */
+int lsv2o_render_forward_tiles(int W, int H, const uint32_t* ranges, const uint32_t* point_list,
+                               const float* xy, const float* conic_opacity, const float* rgb,
+                               int mode, int L, int K,
+                               const float* coeff_dense, const float* wq, const float* iq,
+                               const float* bg, float* out_color, float* out_wmap, float* final_T,
+                               uint32_t* n_contrib, int tile_stride, int tile_phase)
+{
+    if (tile_stride < 1) tile_stride = 1;
+    return render_forward_impl(W, H, ranges, point_list, xy, conic_opacity, rgb, mode, L, K, coeff_dense,
+                               wq, iq, bg, out_color, out_wmap, final_T, n_contrib, tile_stride,
+                               tile_phase % tile_stride);
 }
 
 /* ------------------------------------------------------------------------- */

@@ -228,3 +228,40 @@ def test_topk_soft_code():
     w, i = get_weights_and_indices(torch.tensor(logits).cuda(), 4)
     assert np.array_equal(i.cpu().numpy(), i_ref)
     np.testing.assert_allclose(w.cpu().numpy(), w_ref, rtol=2e-6, atol=1e-8)
+
+
+@pytest.mark.parametrize("levels,HW,normalize", [(1, 128 * 5, True), (3, 16 * 333 + 5, True), (3, 40000, False),
+                                                 (2, 1008 * 756, True)])
+def test_decode_bf16_tensor_core(levels, HW, normalize):
+    """tcgen05 decode: bf16 operands, fp32 accumulate.  Tolerance (stated in SURVEY.md §8c): max-abs error
+    <= 4e-3 of the per-pixel feature norm, cosine >= 0.9999 against the checker's float64 result."""
+    from langsplatv2_b200 import decode_feature_map
+    rng = np.random.default_rng(levels + HW)
+    if HW > 100000:      # full C2 size: compare a strided subset of pixels against the checker
+        w = rng.random((levels * 64, HW), dtype=np.float32)
+        w[rng.random(w.shape) < 0.5] = 0
+        sel = np.arange(0, HW, 97)
+    else:
+        w = rng.random((levels * 64, HW), dtype=np.float32)
+        w[rng.random(w.shape) < 0.6] = 0
+        sel = np.arange(HW)
+    cb = rng.standard_normal((levels, 64, 512)).astype(np.float32)
+    ref = oracle.decode(np.ascontiguousarray(w[:, sel]), cb, normalize=normalize)
+    out = decode_feature_map(torch.tensor(w).cuda(), torch.tensor(cb).cuda(), normalize=normalize,
+                             precision="bf16").cpu().numpy()[:, :, sel]
+    norm = np.sqrt((ref.astype(np.float64) ** 2).sum(1, keepdims=True)) + 1e-12
+    assert np.max(np.abs(out - ref) / norm) <= 4e-3
+    cos = (out * ref).sum(1) / (np.sqrt((out.astype(np.float64) ** 2).sum(1)) * norm[:, 0] + 1e-12)
+    assert cos.min() >= 0.9999
+    if normalize:
+        np.testing.assert_allclose(np.sqrt((out.astype(np.float64) ** 2).sum(1)), 1.0, atol=1e-4)
+
+
+def test_decode_bf16_output_dtype():
+    from langsplatv2_b200 import decode_feature_map
+    rng = np.random.default_rng(0)
+    w = rng.random((192, 3000), dtype=np.float32)
+    cb = rng.standard_normal((3, 64, 512)).astype(np.float32)
+    a = decode_feature_map(torch.tensor(w).cuda(), torch.tensor(cb).cuda(), precision="bf16")
+    b = decode_feature_map(torch.tensor(w).cuda(), torch.tensor(cb).cuda(), precision="bf16", out_dtype=torch.bfloat16)
+    assert b.dtype == torch.bfloat16 and torch.allclose(a, b.float(), atol=4e-3 * float(a.abs().max()))
