@@ -104,6 +104,8 @@ typedef struct lsv2_geom {
     uint32_t* offsets;       /* u32[P]    inclusive scan of tiles_touched          */
     float* cov3d;            /* f32[P][6] or NULL                                  */
     int32_t* rect;           /* i32[P][4] (minx,miny,maxx,maxy) or NULL            */
+    float* blend_rec;        /* f32[P][12] packed per-Gaussian record the blend reads:
+                                (x, y, -a/2, -b), (-c/2, power cut-off, opacity, r), (g, b, 0, 0) */
 } lsv2_geom;
 
 /* Per-instance state (the reference's binningBuffer) + per-tile ranges. */

@@ -38,7 +38,7 @@ class Scene(C.Structure):
 
 class Geom(C.Structure):
     _fields_ = [("radii", _vp), ("xy", _vp), ("depth", _vp), ("conic_opacity", _vp), ("rgb", _vp),
-                ("clamped", _vp), ("tiles_touched", _vp), ("offsets", _vp), ("cov3d", _vp), ("rect", _vp)]
+                ("clamped", _vp), ("tiles_touched", _vp), ("offsets", _vp), ("cov3d", _vp), ("rect", _vp), ("blend_rec", _vp)]
 
 
 class Binning(C.Structure):

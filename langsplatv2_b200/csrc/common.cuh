@@ -80,6 +80,16 @@ __device__ __forceinline__ float repro_expf(float x)
     return __int_as_float(__float_as_int(y) + (((int)n) << 23));
 }
 
+// Power cut-off of a splat: alpha = op*exp(power) < 1/255 for every power below it.  The margin
+// (0.01 in the exponent, ~1 % in alpha) dwarfs the 2-ulp error of repro_expf, so skipping the
+// exponential (or a whole pixel strip) below the cut-off never changes a decision.  A cut-off
+// >= 0 means the splat can never contribute.
+__device__ __forceinline__ float power_cutoff(float op)
+{
+    if (!(op > 0.0f)) return 1.0f;
+    return -__logf(255.0f * op) - 0.01f;
+}
+
 // Tile rectangle covered by a splat of integer radius `rad` centred at (px, py).
 __device__ __forceinline__ void tile_rect(float px, float py, float rad, int gx, int gy,
                                           int& minx, int& miny, int& maxx, int& maxy)

@@ -33,6 +33,7 @@ struct PreArgs {
     uint32_t* tiles;
     float* cov3d;
     int32_t* rect;
+    float4* blend_rec;
 };
 
 __global__ void __launch_bounds__(PRE_THREADS) k_preprocess(PreArgs a)
@@ -232,6 +233,18 @@ __global__ void __launch_bounds__(PRE_THREADS) k_preprocess(PreArgs a)
 #pragma unroll
         for (int k = 0; k < 6; ++k) a.cov3d[6 * (size_t)i + k] = c6[k];
     }
+    if (a.blend_rec) {
+        float4* rec = a.blend_rec + 3 * (size_t)i;
+        if (vis) {
+            rec[0] = make_float4(px, py, -0.5f * con0, -con1);
+            rec[1] = make_float4(-0.5f * con2, power_cutoff(op), op, rgb[0]);
+            rec[2] = make_float4(rgb[1], rgb[2], 0.f, 0.f);
+        } else {
+            rec[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+            rec[1] = make_float4(0.f, 1.0f, 0.f, 0.f);
+            rec[2] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    }
     if (a.rect) {
         reinterpret_cast<int4*>(a.rect)[i] =
             vis ? make_int4(rminx, rminy, rmaxx, rmaxy) : make_int4(0, 0, 0, 0);
@@ -261,6 +274,7 @@ int launch_preprocess(const lsv2_view& v, const lsv2_scene& s, const lsv2_geom& 
     a.radii = g.radii; a.xy = reinterpret_cast<float2*>(g.xy); a.depth = g.depth;
     a.conic_opacity = reinterpret_cast<float4*>(g.conic_opacity); a.rgb = g.rgb;
     a.clamped = g.clamped; a.tiles = g.tiles_touched; a.cov3d = g.cov3d; a.rect = g.rect;
+    a.blend_rec = reinterpret_cast<float4*>(g.blend_rec);
     k_preprocess<<<ceil_div(s.P, PRE_THREADS), PRE_THREADS, 0, st>>>(a);
     LSV2_LAUNCH_CHECK("k_preprocess");
     return LSV2_OK;

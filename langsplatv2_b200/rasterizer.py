@@ -77,7 +77,7 @@ class FrameState:
     def c_geom(self) -> Geom:
         g = self.geom
         return Geom(*[_abi.ptr(g.get(k)) for k in ("radii", "xy", "depth", "conic_opacity", "rgb", "clamped",
-                                                   "tiles_touched", "offsets", "cov3d", "rect")])
+                                                   "tiles_touched", "offsets", "cov3d", "rect", "blend_rec")])
 
     def c_binning(self) -> Binning:
         b = self.binning
@@ -202,6 +202,7 @@ def rasterize_forward(rs: GaussianRasterizationSettings, means3D, opacities, shs
     g["clamped"] = torch.empty((P, 3), dtype=torch.uint8, device=dev)
     g["tiles_touched"] = torch.empty(P, **i32)
     g["offsets"] = torch.empty(P, **i32)
+    g["blend_rec"] = torch.empty((P, 12), **f32)
     if debug_buffers:
         g["cov3d"] = torch.empty((P, 6), **f32)
         g["rect"] = torch.empty((P, 4), **i32)
