@@ -1,0 +1,87 @@
+"""View-sharded data parallelism over one 8xB200 box.
+
+Rendering shards by camera view with no data-path collective: view ``v`` belongs to rank
+``v % world``.  Training (feature stage, geometry frozen: /root/reference/scene/gaussian_model.py:238-243)
+renders a different view on every rank and sums the gradients of the sparse-coefficient logits and the
+codebooks with ONE all-reduce over a flat fp32 bucket per step.  SUM (not mean) is the anchor: a world of B
+ranks is then the reference's single-GPU ``--accum_iter B`` (train.py:261-263,348 -- gradients accumulate,
+the loss is not rescaled).
+
+One process per GPU (torchrun); backend NCCL on the box, gloo in the CPU tests.
+"""
+from __future__ import annotations
+
+import os
+from typing import Iterable, List, Sequence
+
+import torch
+import torch.distributed as dist
+
+
+def world_info():
+    """(rank, world, local_rank) from the torchrun environment (1-process defaults)."""
+    return (int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")),
+            int(os.environ.get("LOCAL_RANK", "0")))
+
+
+def shard_views(num_views: int, rank: int, world: int) -> List[int]:
+    """Round-robin ownership of views; every view has exactly one owner."""
+    if world <= 0 or not (0 <= rank < world):
+        raise ValueError(f"bad rank/world {rank}/{world}")
+    return list(range(rank, num_views, world))
+
+
+def step_views(step: int, num_views: int, rank: int, world: int) -> int:
+    """View rendered by ``rank`` at training step ``step``: consecutive ranks take consecutive views, so a
+    world of B ranks covers the same views per step as ``--accum_iter B`` does in B iterations."""
+    return (step * world + rank) % num_views
+
+
+class GradBucket:
+    """Flat fp32 bucket over a fixed list of parameters: grads are packed, all-reduced once (SUM) and
+    unpacked in place.  The bucket is allocated once and reused every step."""
+
+    def __init__(self, params: Sequence[torch.Tensor]):
+        self.params = list(params)
+        if not self.params:
+            raise ValueError("GradBucket needs at least one parameter")
+        dev = self.params[0].device
+        self.sizes = [p.numel() for p in self.params]
+        self.flat = torch.zeros(sum(self.sizes), dtype=torch.float32, device=dev)
+        self.views = []
+        o = 0
+        for p, n in zip(self.params, self.sizes):
+            self.views.append(self.flat[o:o + n].view(p.shape))
+            o += n
+
+    @property
+    def nbytes(self) -> int:
+        return self.flat.numel() * 4
+
+    def pack(self) -> None:
+        for p, v in zip(self.params, self.views):
+            if p.grad is None:
+                v.zero_()
+            else:
+                v.copy_(p.grad)
+
+    def all_reduce(self) -> None:
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
+
+    def unpack(self) -> None:
+        for p, v in zip(self.params, self.views):
+            if p.grad is None:
+                p.grad = v.clone()
+            else:
+                p.grad.copy_(v)
+
+    def sync(self) -> None:
+        self.pack()
+        self.all_reduce()
+        self.unpack()
+
+
+def all_reduce_grads(params: Iterable[torch.Tensor]) -> None:
+    """One-shot helper (allocates a bucket); training loops should hold a GradBucket instead."""
+    GradBucket(list(params)).sync()
