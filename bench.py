@@ -182,11 +182,12 @@ def run_reference(args, wl):
 # GPU arm
 # ----------------------------------------------------------------------------------------------
 def kernels_per_frame(W, H, fused: bool) -> int:
+    """liblsv2 kernels launched per frame (torch's own fill kernels are not counted)."""
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
     tb = max(1, math.ceil(math.log2(tiles)))
-    sort_passes = 4 + (tb + 7) // 8
+    sort_passes = (31 + tb + 7) // 8
     n = 1 + 1 + 1 + 1 + sort_passes + 1     # preprocess, scan, duplicate, histogram, onesweep passes, ranges
-    n += 1 if fused else 2                  # blend(+decode)
+    n += 2 if fused else 3                  # codebook prep + fused blend/decode | blend + codebook prep + decode
     return n
 
 
@@ -208,7 +209,9 @@ def run_gpu(args, wl):
     scene, cams = make_inputs(wl)
     cams = [{k: (v.to(dev) if torch.is_tensor(v) else v) for k, v in c.items()} for c in cams]
     my_views = [v for v in range(VIEWS) if v % world == rank]
-    r = FeatureRenderer(scene, topk=TOPK, device=dev, precision=args.precision, bounded=True)
+    r = FeatureRenderer(scene, topk=TOPK, device=dev, precision=args.precision, bounded=True,
+                        fused=not args.unfused)
+    fused = r.fused
     r.calibrate([cams[v] for v in my_views[:: max(1, len(my_views) // 8)]])
 
     ev = {"b": [], "e": []}
@@ -243,6 +246,13 @@ def run_gpu(args, wl):
     clocks = sampler.stop()
     r.check_overflow()
     realised = r.last_state.num_rendered
+    # instances the blend had to read: per tile, the largest n_contrib of its pixels (early termination
+    # makes the rest of each depth-sorted list dead); computed after the timed region
+    st = r.last_state
+    gx_, gy_ = (wl["W"] + 15) // 16, (wl["H"] + 15) // 16
+    nc = st.image["n_contrib"].to(torch.int64)
+    nc = torch.nn.functional.pad(nc, (0, gx_ * 16 - wl["W"], 0, gy_ * 16 - wl["H"]))
+    consumed = int(nc.view(gy_, 16, gx_, 16).amax(dim=(1, 3)).sum().item())
     ms_total = t_b.elapsed_time(t_e)
     dom_ms = float(np.mean([b.elapsed_time(e) for b, e in zip(ev["b"], ev["e"])]))
     r.hook = None
@@ -293,16 +303,25 @@ def run_gpu(args, wl):
         HW = H * W
         L = LEVELS * CODES
         out_bytes = LEVELS * D * HW * (4 if r.out_dtype == torch.float32 else 2)
-        dom_bytes = L * HW * 4 + out_bytes + LEVELS * CODES * D * 4     # decode: read weight map + codebooks, write features
+        if fused:
+            # blend+decode: consumed instances x (id 4 + packed record 48 + top-k weights/indices 2*4*K) + rgb, final_T,
+            # n_contrib (20 B/px) + features out; the L-channel weight map is not traffic any more
+            dom_bytes = consumed * (4 + 48 + 8 * LEVELS * TOPK) + 20 * HW + out_bytes + LEVELS * CODES * D * 2
+            dom_name = "render_decode (blend + codebook decode + L2 normalise, fused)"
+        else:
+            dom_bytes = L * HW * 4 + out_bytes + LEVELS * CODES * D * 4     # decode: read weight map + codebooks, write features
+            dom_name = "decode (codebook GEMM + L2 normalise)"
         peak, peak_src = peaks()
         achieved = dom_bytes / (dom_ms * 1e-3) / 1e9
         line = {
             "metric": METRIC, "value": world * args.steps / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32 blend, bf16 x bf16 -> f32 decode" if args.precision == "bf16" else "f32",
+            "dtype": ("f32 alpha/T, f16 x f16 -> f32 tensor-core accumulate + decode" if fused else
+                      ("f32 blend, bf16 x bf16 -> f32 decode" if args.precision == "bf16" else "f32")),
             "data": "synthetic",
             "config": {"workload": wl["name"], "views": VIEWS, "instances_per_frame": realised,
+                       "instances_consumed_by_blend": consumed, "fused_blend_decode": fused,
                        "instance_capacity": r.capacity, "sharding": f"views round-robin over {world} rank(s)",
                        "l2": "each step writes >= %.1f GB, far beyond the 126 MB L2; no explicit flush" % (out_bytes / 1e9),
                        "decode_precision": args.precision},
@@ -310,8 +329,8 @@ def run_gpu(args, wl):
             "e2e": {"value": world * args.steps / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 35 * 4,
                     "d2h_bytes_per_step": 3 * HW * 4 + 32,
                     "note": "camera from pinned host memory; RGB render + status read back to the host; the 512-d map stays on the device as in the reference's API"},
-            "gpu_launches": kernels_per_frame(W, H, fused=False) * args.steps,
-            "roofline": {"kernel": "decode (codebook GEMM + L2 normalise)", "bound": "hbm", "achieved": achieved,
+            "gpu_launches": kernels_per_frame(W, H, fused) * args.steps,
+            "roofline": {"kernel": dom_name, "bound": "hbm", "achieved": achieved,
                          "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                          "peak_source": peak_src, "algorithmic_bytes_per_launch": dom_bytes,
                          "avg_launch_ms": dom_ms},
@@ -333,6 +352,7 @@ def main():
     ap.add_argument("--workload", default="1080p", choices=sorted(WORKLOADS))
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--unfused", action="store_true", help="two-call path: blend to an fp32 weight map, then decode")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     wl = WORKLOADS[args.workload]

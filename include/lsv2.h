@@ -203,6 +203,22 @@ int lsv2_decode(int32_t levels, int32_t Lc, int32_t D, int64_t HW, const float* 
                 const float* codebooks, int32_t normalize, int32_t precision, int32_t out_dtype,
                 void* out, void* scratch, size_t scratch_bytes, void* stream);
 
+/* ---- fused blend + decode (the serving path: eval_lerf.py:321-352 renders, then decodes) ----
+ * renderCUDA forward and the codebook decode in ONE kernel: the blend's sparse-coefficient
+ * accumulation runs on the tensor cores (fp16 alpha*T and coefficients, fp32 accumulate in
+ * TMEM) and the L-channel weight map goes straight from TMEM into the decode contraction, so
+ * it never exists in HBM.  Same inputs as lsv2_render_forward (QUICK, or DENSE with the
+ * compacted rows of lsv2_compact_coeff) + codebooks f32[levels][Lc][D]; feat->L must equal
+ * levels*Lc.  image->color / final_T / n_contrib are written as by lsv2_render_forward
+ * (bit-identical); image->wmap may be NULL (if not, it receives the TMEM weight map, fp32).
+ * out: [levels][D][H][W], out_dtype 0 = f32, 1 = bf16.  Supported: Lc = 64, D = 512,
+ * levels <= 3, K <= LSV2_SPARSE_CAP; otherwise LSV2_EUNSUPPORTED (use the two-call path). */
+size_t lsv2_render_decode_scratch_bytes(int32_t levels);
+int lsv2_render_decode(const lsv2_view* view, const lsv2_geom* geom, const lsv2_binning* binning,
+                       const lsv2_features* feat, const lsv2_image* image, const float* codebooks,
+                       int32_t levels, int32_t Lc, int32_t D, int32_t normalize, int32_t out_dtype,
+                       void* out, void* scratch, size_t scratch_bytes, void* stream);
+
 /* autograd of the un-normalised decode (scene/gaussian_model.py:538):
  *   dW[l*Lc+k][p] = sum_d C[l][k][d] dF[l][d][p]   (f32[levels*Lc][HW])
  *   dC[l][k][d]  += sum_p W[l*Lc+k][p] dF[l][d][p] (f32[levels][Lc][D], zero-initialised) */

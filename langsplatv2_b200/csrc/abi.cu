@@ -25,6 +25,11 @@ int launch_decode_backward(int levels, int Lc, int D, int64_t HW, const float* w
 int launch_topk_soft_code(int64_t N, int C, int k, const float* logits, float* dense, float* weights,
                           float* indices, cudaStream_t st);
 
+size_t render_decode_scratch_bytes(int levels);
+int launch_render_decode(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b, const lsv2_features& f,
+                         const lsv2_image& img, const float* codebooks, int levels, int Lc, int D, int normalize,
+                         int out_dtype, void* out, void* scratch, size_t scratch_bytes, cudaStream_t st);
+
 static int tile_bits_for(const lsv2_view& v)
 {
     const int gx = (v.width + TILE - 1) / TILE, gy = (v.height + TILE - 1) / TILE;
@@ -167,6 +172,20 @@ int lsv2_decode(int32_t levels, int32_t Lc, int32_t D, int64_t HW, const float* 
         return launch_decode_tc(levels, Lc, D, HW, wmap, codebooks, normalize, out_dtype, out, scratch,
                                 scratch_bytes, (cudaStream_t)stream);
     return LSV2_EINVAL;
+}
+
+size_t lsv2_render_decode_scratch_bytes(int32_t levels) { return render_decode_scratch_bytes(levels); }
+
+int lsv2_render_decode(const lsv2_view* view, const lsv2_geom* geom, const lsv2_binning* binning,
+                       const lsv2_features* feat, const lsv2_image* image, const float* codebooks, int32_t levels,
+                       int32_t Lc, int32_t D, int32_t normalize, int32_t out_dtype, void* out, void* scratch,
+                       size_t scratch_bytes, void* stream)
+{
+    if (!view_ok(view) || !geom || !binning || !feat || !image || !codebooks || !out) return LSV2_EINVAL;
+    if (!image->color || !image->final_T || !image->n_contrib || !binning->ranges || !binning->status) return LSV2_EINVAL;
+    if (out_dtype != 0 && out_dtype != 1) return LSV2_EINVAL;
+    return launch_render_decode(*view, *geom, *binning, *feat, *image, codebooks, levels, Lc, D, normalize, out_dtype,
+                                out, scratch, scratch_bytes, (cudaStream_t)stream);
 }
 
 int lsv2_decode_backward(int32_t levels, int32_t Lc, int32_t D, int64_t HW, const float* wmap,

@@ -216,7 +216,7 @@ def rasterize_forward(rs: GaussianRasterizationSettings, means3D, opacities, shs
     img["color"] = torch.empty((3, H, W), **f32)
     img["final_T"] = torch.empty((H, W), **f32)
     img["n_contrib"] = torch.empty((H, W), **i32)
-    if mode != MODE_RGB:
+    if mode != MODE_RGB and render:
         img["wmap"] = torch.empty((L, H, W), **f32)
 
     def alloc_binning(cap: int):
@@ -262,6 +262,42 @@ def rasterize_forward(rs: GaussianRasterizationSettings, means3D, opacities, shs
         if mode == MODE_QUICK and int(st.status[STATUS_BAD_INDEX].item()):
             raise _abi.Lsv2Error(f"language_feature_indices outside [0, {L})")
     return st
+
+
+def render_decode(st: FrameState, codebooks: torch.Tensor, normalize: bool = True,
+                  out_dtype: torch.dtype = torch.float32, want_wmap: bool = False) -> torch.Tensor:
+    """Fused blend + codebook decode on a frame that has been preprocessed and binned
+    (``rasterize_forward(..., render=False)``): -> ``[levels, 512, H, W]``; fills ``st.image`` (RGB, final_T,
+    n_contrib, and the weight map when ``want_wmap``).  The L-channel weight map never round-trips HBM."""
+    L_ = _abi.lib()
+    if st.mode == MODE_RGB:
+        raise _abi.Lsv2Error("render_decode needs include_feature / quick_render settings")
+    dev = st.status.device
+    cb = _f32c(codebooks.to(dev), "codebooks")
+    if cb.dim() == 2:
+        cb = cb.unsqueeze(0)
+    levels, Lc, D = (int(x) for x in cb.shape)
+    if levels * Lc != st.L:
+        raise ValueError(f"codebooks give {levels}x{Lc} channels, the frame has L={st.L}")
+    if out_dtype not in (torch.float32, torch.bfloat16):
+        raise ValueError("out_dtype must be float32 or bfloat16")
+    if not want_wmap:
+        st.image.pop("wmap", None)
+    elif "wmap" not in st.image:
+        st.image["wmap"] = torch.empty((st.L, st.H, st.W), dtype=torch.float32, device=dev)
+    out = torch.empty((levels, D, st.H, st.W), dtype=out_dtype, device=dev)
+    nbytes = L_.lsv2_render_decode_scratch_bytes(levels)
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    geom_c, bin_c, feat_c, img_c = st.c_geom(), st.c_binning(), st.c_features(), st.c_image()
+    if st.mode == MODE_DENSE:
+        _abi.check(L_.lsv2_compact_coeff(st.P, C.byref(geom_c), C.byref(feat_c), _abi.stream_ptr(dev)),
+                   "lsv2_compact_coeff")
+    _abi.check(L_.lsv2_render_decode(C.byref(st.view), C.byref(geom_c), C.byref(bin_c), C.byref(feat_c),
+                                     C.byref(img_c), cb.data_ptr(), levels, Lc, D, 1 if normalize else 0,
+                                     0 if out_dtype == torch.float32 else 1, out.data_ptr(), scratch.data_ptr(),
+                                     nbytes, _abi.stream_ptr(dev)), "lsv2_render_decode")
+    st.keep += [cb, scratch]
+    return out
 
 
 #: weight-map channels in quick mode: the callers view the result as (3, 64, H, W)

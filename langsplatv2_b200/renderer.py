@@ -5,6 +5,10 @@ Equivalent of ``render_language_feature_map_quick`` + the model hoisting it need
 loop): the merged top-k weights/indices of all levels and the codebooks stay on the device, each call
 takes a camera and returns the L2-normalised ``[levels, 512, H, W]`` feature map.
 
+``fused=True`` (default) blends and decodes in one kernel (``lsv2_render_decode``: tensor-core accumulation of
+the sparse coefficients, weight map kept in TMEM); ``fused=False`` is the two-call path (blend to an fp32 weight
+map in HBM, then ``lsv2_decode``).
+
 ``bounded=True`` runs a frame with no host synchronisation at all (instance buffers are sized once from
 a measured high-water mark and overflow is flagged on the device); ``bounded=False`` reads the instance
 count back between preprocess and binning like the reference does.
@@ -17,13 +21,14 @@ import torch
 
 from . import _abi
 from .decode import decode_feature_map
-from .rasterizer import GaussianRasterizationSettings, FrameState, rasterize_forward
+from .rasterizer import GaussianRasterizationSettings, FrameState, rasterize_forward, render_decode
 from .sparse import get_weights_and_indices
 
 
 class FeatureRenderer:
     def __init__(self, scene: Dict, topk: int = 4, device="cuda", precision: str = "bf16",
-                 out_dtype: torch.dtype = torch.float32, bounded: bool = True, headroom: float = 1.25):
+                 out_dtype: torch.dtype = torch.float32, bounded: bool = True, headroom: float = 1.25,
+                 fused: bool = True):
         dev = torch.device(device)
         self.device = dev
         self.levels = int(scene["levels"])
@@ -46,6 +51,8 @@ class FeatureRenderer:
         self.precision = precision
         self.out_dtype = out_dtype
         self.bounded = bounded
+        self.fused = fused and self.levels * self.codebook_size <= 192 and self.codebook_size == 64 \
+            and int(self.codebooks.shape[2]) == 512 and topk * self.levels <= _abi.SPARSE_CAP
         self.headroom = headroom
         self.capacity: Optional[int] = None
         self.bg = torch.zeros(3, dtype=torch.float32, device=dev)
@@ -81,6 +88,15 @@ class FeatureRenderer:
         cap = self.capacity if self.bounded else None
         if self.bounded and cap is None:
             cap = self.calibrate([cam])
+        if self.fused:
+            st = self._raster(cam, cap, render=False)
+            self.last_state = st
+            if self.hook:
+                self.hook("decode_begin")
+            out = render_decode(st, self.codebooks, normalize=True, out_dtype=self.out_dtype)
+            if self.hook:
+                self.hook("decode_end")
+            return out
         st = self._raster(cam, cap)
         self.last_state = st
         if self.hook:
