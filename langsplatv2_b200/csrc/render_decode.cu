@@ -22,6 +22,7 @@
 // MMAs, scales and streams the features to HBM.  One level's codebook (64 KB fp16) is resident in shared memory and
 // re-fetched level by level from L2 with bulk async copies.
 #include <cuda_fp16.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "tc_common.cuh"
@@ -58,7 +59,9 @@ struct __align__(16) FdHeader {
 
 constexpr size_t FD_SMEM_RING = 0;
 constexpr size_t FD_SMEM_B = FD_SMEM_RING + (size_t)FD_STAGES * FD_STAGE_BYTES;         // 112 KB
-constexpr size_t FD_SMEM_HDR = FD_SMEM_B + (size_t)FD_CHUNKS * FD_TILE16K;              // +64 KB
+constexpr int FD_G_BYTES = FD_LC * 128;                                                 // Gram tile [64 n][64 k] fp16
+constexpr size_t FD_SMEM_G = FD_SMEM_B + (size_t)FD_CHUNKS * FD_TILE16K;                // +64 KB
+constexpr size_t FD_SMEM_HDR = FD_SMEM_G + (size_t)(FD_MAX_L / FD_LC) * FD_G_BYTES;     // +24 KB
 constexpr size_t FD_SMEM_BAR = FD_SMEM_HDR + FD_STAGES * sizeof(FdHeader);
 constexpr size_t FD_SMEM_TOTAL = FD_SMEM_BAR + 32 * sizeof(uint64_t) + 64 + 1024;       // + alignment slack
 
@@ -81,8 +84,11 @@ struct FdArgs {
     uint32_t* n_contrib;
     uint32_t* status;
     const uint8_t* bimg;         // fp16 codebook image [levels][512 rows][64 k], 128B-swizzled
+    const uint8_t* gimg;         // fp16 Gram images  s_l * C_l C_l^T  [levels][64 n][64 k], 128B-swizzled
+    const float* gscale_inv;     // [levels] 1 / s_l
     void* out;                   // [levels][512][H][W]
     int normalize;
+    int dbg;                     // timing experiments only (LSV2_FD_DEBUG): 1 = no feature stores, 2 = no blend math
     uint32_t* tile_counter;
 };
 
@@ -137,6 +143,77 @@ __global__ void k_fd_prep_b(int levels, const float* __restrict__ codebooks, uin
     *reinterpret_cast<uint4*>(bimg + (size_t)l * (FD_D * 128) + sw128_offset(n, chunk)) = make_uint4(w[0], w[1], w[2], w[3]);
 }
 
+// barrier with an OR reduction over the participating threads (uniform result)
+__device__ __forceinline__ bool named_bar_or(int id, int count, bool pred)
+{
+    uint32_t r;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p, q;\n\t"
+        "setp.ne.u32 q, %3, 0;\n\t"
+        "bar.red.or.pred p, %1, %2, q;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}"
+        : "=r"(r)
+        : "r"(id), "r"(count), "r"((uint32_t)pred)
+        : "memory");
+    return r != 0;
+}
+
+// mbarrier wait for the helper warps (producer, MMA issuer): backs off between polls so the spin does not
+// take issue slots from the pixel warps
+__device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity)
+{
+    while (!mbar_try_wait(bar, parity)) __nanosleep(40);
+}
+
+// everything the producer gathers for one instance (kept in registers one batch ahead)
+struct FdGather {
+    uint32_t g, cnt;
+    float4 r0, r1, r2;
+    float wv[FD_KMAX], iv[FD_KMAX];
+};
+
+template <int MODE>
+__device__ __forceinline__ void fd_gather(const FdArgs& a, uint32_t g, FdGather& o)
+{
+    o.g = g;
+    o.cnt = 0;
+    if (g == 0xFFFFFFFFu) return;
+    o.r0 = __ldg(a.rec + 3 * (size_t)g);
+    o.r1 = __ldg(a.rec + 3 * (size_t)g + 1);
+    o.r2 = __ldg(a.rec + 3 * (size_t)g + 2);
+    if (MODE == LSV2_MODE_QUICK) {
+        o.cnt = (uint32_t)a.K;
+        const float* wsrc = a.wq + (size_t)g * a.K;
+        const float* isrc = a.iq + (size_t)g * a.K;
+        if ((a.K & 3) == 0) {
+#pragma unroll
+            for (int k4 = 0; k4 < FD_KMAX / 4; ++k4)
+                if (k4 * 4 < a.K) {
+                    const float4 w4 = __ldg(reinterpret_cast<const float4*>(wsrc) + k4);
+                    const float4 i4 = __ldg(reinterpret_cast<const float4*>(isrc) + k4);
+                    o.wv[4 * k4] = w4.x; o.wv[4 * k4 + 1] = w4.y; o.wv[4 * k4 + 2] = w4.z; o.wv[4 * k4 + 3] = w4.w;
+                    o.iv[4 * k4] = i4.x; o.iv[4 * k4 + 1] = i4.y; o.iv[4 * k4 + 2] = i4.z; o.iv[4 * k4 + 3] = i4.w;
+                }
+        } else {
+#pragma unroll
+            for (int k = 0; k < FD_KMAX; ++k)
+                if (k < a.K) { o.wv[k] = __ldg(wsrc + k); o.iv[k] = __ldg(isrc + k); }
+        }
+    } else {
+        o.cnt = a.sp_count[g];
+        if (o.cnt != FD_ROW_DENSE) {
+#pragma unroll
+            for (int k = 0; k < FD_KMAX; ++k)
+                if ((uint32_t)k < o.cnt) {
+                    o.wv[k] = a.sp_weight[(size_t)g * FD_KMAX + k];
+                    o.iv[k] = (float)a.sp_index[(size_t)g * FD_KMAX + k];
+                }
+        }
+    }
+}
+
 template <int MODE, bool OUT_BF16>
 __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
 {
@@ -144,6 +221,7 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
     unsigned char* smem = reinterpret_cast<unsigned char*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     unsigned char* ring = smem + FD_SMEM_RING;
     unsigned char* s_b = smem + FD_SMEM_B;
+    unsigned char* s_g = smem + FD_SMEM_G;
     FdHeader* hdrs = reinterpret_cast<FdHeader*>(smem + FD_SMEM_HDR);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + FD_SMEM_BAR);
     uint64_t* full = bars;                        // [2]  producer -> blend, mma     (64 arrivals)
@@ -156,7 +234,10 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
     uint64_t* b_free = bars + 13;                 // [4]  mma done with chunk        (commit)
     uint64_t* f_full = bars + 17;                 // [2]  F slot ready               (commit)
     uint64_t* f_free = bars + 19;                 // [2]  F slot drained             (256 arrivals)
-    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 21);
+    uint64_t* g_full = bars + 21;                 //      Gram images landed         (tx)
+    uint64_t* u_full = bars + 22;                 //      U = W.G ready              (commit)
+    uint64_t* adec2_full = bars + 23;             //      blend -> mma: W rescaled   (256 arrivals)
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 24);
     uint32_t* s_ndone = s_tmem + 1;               // [2]  saturated strips, by tile parity
     int32_t* s_tile = reinterpret_cast<int32_t*>(s_tmem + 3);
 
@@ -175,6 +256,9 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
         mbar_init(w_full, 1);
         mbar_init(adec_full, 32 * FD_BLEND_WARPS);
         mbar_init(ring_free, 1);
+        mbar_init(g_full, 1);
+        mbar_init(u_full, 1);
+        mbar_init(adec2_full, 32 * FD_BLEND_WARPS);
         for (int c = 0; c < FD_CHUNKS; ++c) { mbar_init(b_full + c, 1); mbar_init(b_free + c, 1); }
         s_ndone[0] = 0;
         s_ndone[1] = 0;
@@ -188,6 +272,8 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
 
     if (warp >= FD_BLEND_WARPS && warp < FD_BLEND_WARPS + 2) {
         // ======================================= producer =======================================
+        // The gathers of batch b+1 (ids two batches ahead) are issued before batch b is assembled, so the
+        // global-memory latency is off the per-batch critical path: wait stage -> zero B tile -> scatter -> arrive.
         const int pt = tid - 32 * FD_BLEND_WARPS;       // 0..63 = instance slot of the batch
         const int pw = pt >> 5;
         uint32_t use_g = 0;                             // stage uses so far (global)
@@ -197,102 +283,70 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
             const int tile = *s_tile;
             named_bar_sync(1, FD_PROD_THREADS);
             const bool exit_now = tile >= a.n_tiles;
-            if (t_iter > 0 && !exit_now) mbar_wait(ring_free, (t_iter - 1) & 1);
             uint2 range = make_uint2(0, 0);
             if (!exit_now) range = a.ranges[tile];
             const uint32_t n_inst = range.y - range.x;
             const uint32_t n_batches = (n_inst + FD_BATCH - 1) / FD_BATCH;
             const float y0 = (float)((tile / a.gx) * TILE);
-            uint32_t gid_next = 0xFFFFFFFFu;
-            if (!exit_now && (uint32_t)pt < n_inst) gid_next = a.point_list[range.x + pt];
+            auto load_id = [&](uint32_t b) -> uint32_t {
+                const uint32_t i = b * FD_BATCH + pt;
+                return i < n_inst ? __ldg(a.point_list + range.x + i) : 0xFFFFFFFFu;
+            };
+            FdGather cur, nxt;
+            fd_gather<MODE>(a, load_id(0), cur);
+            uint32_t gid_next = load_id(1);
+            if (t_iter > 0 && !exit_now) mbar_wait_sleep(ring_free, (t_iter - 1) & 1);
             for (uint32_t b = 0;; ++b, ++use_g) {
                 const int s = use_g & 1;
                 const uint32_t use = use_g >> 1;
-                if (use > 0) mbar_wait(stage_free + s, (use - 1) & 1);
+                if (use > 0) mbar_wait_sleep(stage_free + s, (use - 1) & 1);
                 FdHeader& Hd = hdrs[s];
                 const bool stop = exit_now || b >= n_batches ||
                                   *(volatile uint32_t*)(s_ndone + (t_iter & 1)) >= FD_BLEND_WARPS;
-                // `stop` must be uniform across the 64 producer threads: s_ndone is read once and shared
-                if (pt == 0) *s_tile = stop ? 1 : 0;
-                named_bar_sync(1, FD_PROD_THREADS);
-                const bool stop_u = *s_tile != 0;
-                named_bar_sync(1, FD_PROD_THREADS);
-                if (stop_u) {
+                // s_ndone may change between the 64 reads: OR-reduce so the decision is uniform
+                if (named_bar_or(1, FD_PROD_THREADS, stop)) {
                     if (pt == 0) { Hd.count = exit_now ? -2 : -1; Hd.tile = tile; Hd.batches = (int32_t)b; }
                     mbar_arrive(full + s);
                     ++use_g;
                     break;
                 }
-                const uint32_t g = gid_next;
-                {
-                    const uint32_t i = (b + 1) * FD_BATCH + pt;
-                    gid_next = i < n_inst ? a.point_list[range.x + i] : 0xFFFFFFFFu;
-                }
-                // issue the gathers first, zero the B tile while they are in flight
-                float4 r0 = make_float4(0, 0, 0, 0), r1 = r0, r2 = r0;
-                float wv[FD_KMAX], iv[FD_KMAX];
-                uint32_t cnt = 0;
-                if (g != 0xFFFFFFFFu) {
-                    r0 = __ldg(a.rec + 3 * (size_t)g);
-                    r1 = __ldg(a.rec + 3 * (size_t)g + 1);
-                    r2 = __ldg(a.rec + 3 * (size_t)g + 2);
-                    if (MODE == LSV2_MODE_QUICK) {
-                        cnt = (uint32_t)a.K;
-                        const float* wsrc = a.wq + (size_t)g * a.K;
-                        const float* isrc = a.iq + (size_t)g * a.K;
-                        if ((a.K & 3) == 0) {
-#pragma unroll
-                            for (int k4 = 0; k4 < FD_KMAX / 4; ++k4)
-                                if (k4 * 4 < a.K) {
-                                    const float4 w4 = __ldg(reinterpret_cast<const float4*>(wsrc) + k4);
-                                    const float4 i4 = __ldg(reinterpret_cast<const float4*>(isrc) + k4);
-                                    wv[4 * k4] = w4.x; wv[4 * k4 + 1] = w4.y; wv[4 * k4 + 2] = w4.z; wv[4 * k4 + 3] = w4.w;
-                                    iv[4 * k4] = i4.x; iv[4 * k4 + 1] = i4.y; iv[4 * k4 + 2] = i4.z; iv[4 * k4 + 3] = i4.w;
-                                }
-                        } else {
-#pragma unroll
-                            for (int k = 0; k < FD_KMAX; ++k)
-                                if (k < a.K) { wv[k] = __ldg(wsrc + k); iv[k] = __ldg(isrc + k); }
-                        }
-                    } else {
-                        cnt = a.sp_count[g];
-                        if (cnt != FD_ROW_DENSE) {
-#pragma unroll
-                            for (int k = 0; k < FD_KMAX; ++k)
-                                if ((uint32_t)k < cnt) {
-                                    wv[k] = a.sp_weight[(size_t)g * FD_KMAX + k];
-                                    iv[k] = (float)a.sp_index[(size_t)g * FD_KMAX + k];
-                                }
-                        }
-                    }
-                }
                 unsigned char* S = ring + (size_t)s * FD_STAGE_BYTES + 2 * FD_TILE16K;
                 for (int q = pt; q < L * 8; q += FD_PROD_THREADS)
                     reinterpret_cast<uint4*>(S)[q] = make_uint4(0, 0, 0, 0);
+                fd_gather<MODE>(a, gid_next, nxt);          // in flight while this batch is assembled
+                gid_next = load_id(b + 2);
                 named_bar_sync(1, FD_PROD_THREADS);
                 uint32_t m8 = 0;
-                if (g != 0xFFFFFFFFu) {
-                    Hd.g0[pt] = r0;
-                    Hd.g1[pt] = r1;
-                    Hd.g2[pt] = make_float2(r2.x, r2.y);
-                    m8 = fd_strip_mask(r0.y - y0, r0.z, r0.w, r1.x, r1.y);
+                if (cur.g != 0xFFFFFFFFu) {
+                    Hd.g0[pt] = cur.r0;
+                    Hd.g1[pt] = cur.r1;
+                    Hd.g2[pt] = make_float2(cur.r2.x, cur.r2.y);
+                    m8 = fd_strip_mask(cur.r0.y - y0, cur.r0.z, cur.r0.w, cur.r1.x, cur.r1.y);
                     const uint32_t col = (uint32_t)(pt & 7) * 2u, chunk = (uint32_t)pt >> 3;
-                    if (cnt != FD_ROW_DENSE) {
+                    if (cur.cnt != FD_ROW_DENSE) {
+                        bool ascending = true;              // distinct channels: plain stores, no read-modify-write
+#pragma unroll
+                        for (int k = 1; k < FD_KMAX; ++k)
+                            if ((uint32_t)k < cur.cnt) ascending &= cur.iv[k] > cur.iv[k - 1];
 #pragma unroll
                         for (int k = 0; k < FD_KMAX; ++k) {
-                            if ((uint32_t)k < cnt) {
-                                const int c = (int)iv[k];
+                            if ((uint32_t)k < cur.cnt) {
+                                const int c = (int)cur.iv[k];
                                 if (c >= 0 && c < L) {
                                     __half* p = reinterpret_cast<__half*>(S + sw128_offset((uint32_t)c, chunk) + col);
-                                    const float old = __half2float(*p);        // duplicates of a channel add up
-                                    *p = __float2half_rn(old + wv[k]);
+                                    if (ascending) {
+                                        *p = __float2half_rn(cur.wv[k]);
+                                    } else {
+                                        const float old = __half2float(*p);    // duplicates of a channel add up
+                                        *p = __float2half_rn(old + cur.wv[k]);
+                                    }
                                 } else {
                                     a.status[LSV2_STATUS_BAD_INDEX] = 1u;
                                 }
                             }
                         }
                     } else {
-                        const float* row = a.coeff_dense + (size_t)g * L;
+                        const float* row = a.coeff_dense + (size_t)cur.g * L;
                         for (int c = 0; c < L; ++c) {
                             const float v = __ldg(row + c);
                             if (v != 0.0f)
@@ -311,6 +365,7 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
                 }
                 fence_async_smem();
                 mbar_arrive(full + s);
+                cur = nxt;
             }
             if (exit_now) break;
         }
@@ -339,7 +394,7 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
             for (uint32_t use_g = 0;; ++use_g) {
                 const int s = use_g & 1;
                 const uint32_t use = use_g >> 1;
-                mbar_wait(full + s, use & 1);
+                mbar_wait_sleep(full + s, use & 1);
                 const FdHeader& Hd = hdrs[s];
                 const int count = Hd.count;
                 if (count == -2) break;
@@ -364,7 +419,7 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
                 batch_in_tile = 0;
                 mbar_arrive(stage_free + s);
                 if (nb > 0) umma_commit(w_full); else mbar_arrive(w_full);
-                mbar_wait(adec_full, tiles_done & 1);
+                mbar_wait_sleep(adec_full, tiles_done & 1);
                 tc_fence_after();
                 if (nb == 0) {
                     mbar_arrive(ring_free);
@@ -455,12 +510,16 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
                 for (int c = 0; c < 8; ++c) {
                     const uint32_t m8 = (uint32_t)(m >> (8 * c)) & 0xFFu;
                     uint32_t hw[4] = {0u, 0u, 0u, 0u};
-                    if (m8 != 0u) {
+                    if (m8 != 0u && !(a.dbg & 2)) {
 #pragma unroll
                         for (int q4 = 0; q4 < 2; ++q4) {
                             const uint32_t m4 = (m8 >> (4 * q4)) & 0xFu;
                             if (m4 == 0u) continue;
-                            float pw_[4], thr_[4];
+                            // stage 1: the four quadratic forms and alphas are independent (ILP); alpha does not
+                            // depend on T.  stage 2: the short sequential transmittance chain.
+                            float pw_[4], op_[4], cr_[4];
+                            bool hit[4];
+                            bool any = false;
 #pragma unroll
                             for (int u = 0; u < 4; ++u) {
                                 const int j = 8 * c + 4 * q4 + u;
@@ -468,29 +527,26 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
                                 const float4 g1 = Hd.g1[j];
                                 const float dx = g0.x - pxf, dy = g0.y - pyf;
                                 pw_[u] = fmaf(g0.z * dx, dx, fmaf(g1.x * dy, dy, (g0.w * dx) * dy));
-                                thr_[u] = g1.y;
-                            }
-                            bool hit[4];
-                            bool any = false;
-#pragma unroll
-                            for (int u = 0; u < 4; ++u) {
-                                hit[u] = ((m4 >> u) & 1u) && !(pw_[u] > 0.0f || pw_[u] < thr_[u]);
+                                hit[u] = ((m4 >> u) & 1u) && !(pw_[u] > 0.0f || pw_[u] < g1.y);
+                                op_[u] = g1.z;
+                                cr_[u] = g1.w;
                                 any |= hit[u];
                             }
                             float wgt[4] = {0.f, 0.f, 0.f, 0.f};
                             if (any && !done) {
+                                float al[4];
+#pragma unroll
+                                for (int u = 0; u < 4; ++u)
+                                    al[u] = hit[u] ? fminf(ALPHA_MAX, op_[u] * repro_expf(fminf(pw_[u], 0.0f))) : 0.0f;
 #pragma unroll
                                 for (int u = 0; u < 4; ++u) {
-                                    if (!hit[u] || done) continue;
+                                    if (al[u] < ALPHA_MIN || done) continue;
                                     const int j = 8 * c + 4 * q4 + u;
-                                    const float4 g1 = Hd.g1[j];
-                                    const float alpha = fminf(ALPHA_MAX, g1.z * repro_expf(pw_[u]));
-                                    if (alpha < ALPHA_MIN) continue;
-                                    const float test_T = T * (1.0f - alpha);
+                                    const float test_T = T * (1.0f - al[u]);
                                     if (test_T < T_MIN) { done = true; continue; }
-                                    const float w = alpha * T;
+                                    const float w = al[u] * T;
                                     const float2 g2 = Hd.g2[j];
-                                    C0 = fmaf(g1.w, w, C0);
+                                    C0 = fmaf(cr_[u], w, C0);
                                     C1 = fmaf(g2.x, w, C1);
                                     C2 = fmaf(g2.y, w, C2);
                                     wgt[u] = w;
@@ -588,15 +644,11 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
                             ++f_seen[q];
                             tc_fence_after();
                             const uint32_t col0 = (uint32_t)(half * 256 + q * FD_CHUNK_N);
-#pragma unroll 1
-                            for (int cc = 0; cc < FD_CHUNK_N / 32; ++cc) {
-                                uint32_t r[32];
-                                tmem_ld32(lane_base + col0 + cc * 32, r);
-                                tmem_wait_ld();
+                            auto consume = [&](const uint32_t (&r)[32], int cc) {
                                 if (!store) {
 #pragma unroll
                                     for (int i = 0; i < 32; ++i) ss = fmaf(__uint_as_float(r[i]), __uint_as_float(r[i]), ss);
-                                } else if (inside) {
+                                } else if (inside && !(a.dbg & 1)) {
                                     const size_t ch0 = (size_t)l * FD_D + c * FD_CHUNK_N + cc * 32;
                                     if (OUT_BF16) {
                                         __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(a.out) + ch0 * HW + pix;
@@ -609,9 +661,24 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
                                         for (int i = 0; i < 32; ++i) st_stream_f32(o + (size_t)i * HW, __uint_as_float(r[i]) * inv);
                                     }
                                 }
-                            }
+                            };
+                            // two register buffers: the next TMEM read is in flight while 32 columns are consumed
+                            uint32_t ra[32], rb[32];
+                            const uint32_t t0 = lane_base + col0;
+                            tmem_ld32(t0, ra);
+                            tmem_wait_ld();
+                            tmem_ld32(t0 + 32, rb);
+                            consume(ra, 0);
+                            tmem_wait_ld();
+                            tmem_ld32(t0 + 64, ra);
+                            consume(rb, 1);
+                            tmem_wait_ld();
+                            tmem_ld32(t0 + 96, rb);
+                            consume(ra, 2);
+                            tmem_wait_ld();
                             tc_fence_before();
-                            mbar_arrive(f_free + q);
+                            mbar_arrive(f_free + q);              // slot drained: the next MMA may overwrite it
+                            consume(rb, 3);
                         }
                     }
                 }
@@ -666,6 +733,7 @@ int launch_render_decode(const lsv2_view& v, const lsv2_geom& g, const lsv2_binn
     a.color = img.color; a.wmap = img.wmap; a.final_T = img.final_T; a.n_contrib = img.n_contrib;
     a.status = b.status;
     a.bimg = bimg; a.out = out; a.normalize = normalize; a.tile_counter = counter;
+    { const char* e = getenv("LSV2_FD_DEBUG"); a.dbg = e ? atoi(e) : 0; }
     const int grid = min(NUM_SMS, gx * gy);
 #define FD_LAUNCH(M, O)                                                                                          \
     do {                                                                                                         \
