@@ -80,6 +80,26 @@ __device__ __forceinline__ float repro_expf(float x)
     return __int_as_float(__float_as_int(y) + (((int)n) << 23));
 }
 
+// Same operations as repro_expf without the range checks, for callers that already know -87 <= x <= 0
+// (or discard the result otherwise): branch-free, so several evaluations interleave.
+__device__ __forceinline__ float repro_expf_inrange(float x)
+{
+    const float t = __fmul_rn(x, 1.44269504088896341f);
+    const float n = __fsub_rn(__fadd_rn(t, 12582912.0f), 12582912.0f);
+    float r = __fmaf_rn(n, -0.693145751953125f, x);
+    r = __fmaf_rn(n, -1.42860682030941723212e-6f, r);
+    float p = 1.9875691500e-4f;
+    p = __fmaf_rn(p, r, 1.3981999507e-3f);
+    p = __fmaf_rn(p, r, 8.3334519073e-3f);
+    p = __fmaf_rn(p, r, 4.1665795894e-2f);
+    p = __fmaf_rn(p, r, 1.6666665459e-1f);
+    p = __fmaf_rn(p, r, 5.0000001201e-1f);
+    const float r2 = __fmul_rn(r, r);
+    float y = __fmaf_rn(p, r2, r);
+    y = __fadd_rn(y, 1.0f);
+    return __int_as_float(__float_as_int(y) + (((int)n) << 23));
+}
+
 // Power cut-off of a splat: alpha = op*exp(power) < 1/255 for every power below it.  The margin
 // (0.01 in the exponent, ~1 % in alpha) dwarfs the 2-ulp error of repro_expf, so skipping the
 // exponential (or a whole pixel strip) below the cut-off never changes a decision.  A cut-off

@@ -218,10 +218,11 @@ template <int MODE, bool OUT_BF16>
 __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
 {
     extern __shared__ unsigned char smem_raw[];
-    unsigned char* smem = reinterpret_cast<unsigned char*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    // offset arithmetic on the __shared__ symbol (not a uintptr_t round trip) keeps the shared address space
+    // visible to the compiler: LDS/STS instead of generic LD/ST in the blend loop
+    unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     unsigned char* ring = smem + FD_SMEM_RING;
     unsigned char* s_b = smem + FD_SMEM_B;
-    unsigned char* s_g = smem + FD_SMEM_G;
     FdHeader* hdrs = reinterpret_cast<FdHeader*>(smem + FD_SMEM_HDR);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + FD_SMEM_BAR);
     uint64_t* full = bars;                        // [2]  producer -> blend, mma     (64 arrivals)
@@ -378,7 +379,7 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
             const int passes = a.normalize ? 2 : 1;
             uint32_t b_issued[FD_CHUNKS] = {0, 0, 0, 0};     // bulk copies issued per chunk slot
             uint32_t b_used[FD_CHUNKS] = {0, 0, 0, 0};       // b_full phases consumed per chunk slot
-            uint32_t f_fill[2] = {0, 0};                     // fills per F slot
+            uint32_t f_n = 0;                                // F slot fills so far (slots alternate)
             int next_level = 0;                              // level the next codebook fetch belongs to
             auto fetch = [&](int c) {                        // chunk c of level `lvl`
                 mbar_arrive_expect_tx(b_full + c, FD_TILE16K);
@@ -429,8 +430,8 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
                 for (int l = 0; l < levels; ++l) {
                     for (int pass = 0; pass < passes; ++pass) {
                         for (int c = 0; c < FD_CHUNKS; ++c) {
-                            const int q = (int)((f_fill[0] + f_fill[1]) & 1u);
-                            if (f_fill[q] > 0) mbar_wait(f_free + q, (f_fill[q] - 1) & 1);
+                            const int q = (int)(f_n & 1u);
+                            if (f_n >= 2) mbar_wait(f_free + q, ((f_n >> 1) - 1) & 1);
                             if (pass == 0) { mbar_wait(b_full + c, b_used[c] & 1); ++b_used[c]; }
                             tc_fence_after();
 #pragma unroll
@@ -443,7 +444,7 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
                                               ks > 0 ? 1u : 0u);
                             }
                             umma_commit(f_full + q);
-                            ++f_fill[q];
+                            ++f_n;
                             if (pass == passes - 1) {
                                 umma_commit(b_free + c);
                                 // refill the chunk slot released one step ago with the next level's tile
@@ -473,7 +474,7 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
         const int row = (warp & 3) * 32 + lane;                      // A-tile row == TMEM lane
         const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
         const int lx = lane & 15, ly = warp * 2 + (lane >> 4);
-        uint32_t f_seen[2] = {0, 0};
+        uint32_t f_n = 0;                                            // F slots consumed so far (slots alternate)
         uint32_t tiles_done = 0;
         uint32_t use_g = 0;
         for (;;) {
@@ -537,21 +538,29 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
                                 float al[4];
 #pragma unroll
                                 for (int u = 0; u < 4; ++u)
-                                    al[u] = hit[u] ? fminf(ALPHA_MAX, op_[u] * repro_expf(fminf(pw_[u], 0.0f))) : 0.0f;
+                                {   // a hit has cut-off <= power <= 0 (cut-off > -6), so the unchecked exp is exact there;
+                                    // evaluated for all four so the chains interleave, discarded where !hit
+                                    const float e = repro_expf_inrange(fmaxf(fminf(pw_[u], 0.0f), -80.0f));
+                                    al[u] = hit[u] ? fminf(ALPHA_MAX, op_[u] * e) : 0.0f;
+                                }
 #pragma unroll
                                 for (int u = 0; u < 4; ++u) {
-                                    if (al[u] < ALPHA_MIN || done) continue;
+                                    // select-only form of: skip if alpha < 1/255 or done; stop if T' < 1e-4; else blend.
+                                    // A skipped instance adds w = 0 (exact), so the sums match the branching form bit for bit.
                                     const int j = 8 * c + 4 * q4 + u;
+                                    const bool valid = !(al[u] < ALPHA_MIN) && !done;
                                     const float test_T = T * (1.0f - al[u]);
-                                    if (test_T < T_MIN) { done = true; continue; }
-                                    const float w = al[u] * T;
+                                    const bool stop = valid && (test_T < T_MIN);
+                                    const bool use = valid && !stop;
+                                    done = done || stop;
+                                    const float w = use ? al[u] * T : 0.0f;
                                     const float2 g2 = Hd.g2[j];
                                     C0 = fmaf(cr_[u], w, C0);
                                     C1 = fmaf(g2.x, w, C1);
                                     C2 = fmaf(g2.y, w, C2);
                                     wgt[u] = w;
-                                    T = test_T;
-                                    last = (uint32_t)nb * FD_BATCH + (uint32_t)j + 1u;
+                                    T = use ? test_T : T;
+                                    last = use ? (uint32_t)nb * FD_BATCH + (uint32_t)j + 1u : last;
                                 }
                             }
                             hw[2 * q4] = pack_f16x2(wgt[0], wgt[1]);
@@ -639,9 +648,9 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
                         const bool store = pass == passes - 1;
                         if (store && a.normalize) inv = 1.0f / (sqrtf(ss) + 1e-10f);
                         for (int c = 0; c < FD_CHUNKS; ++c) {
-                            const int q = (int)((f_seen[0] + f_seen[1]) & 1u);
-                            mbar_wait(f_full + q, f_seen[q] & 1);
-                            ++f_seen[q];
+                            const int q = (int)(f_n & 1u);
+                            mbar_wait(f_full + q, (f_n >> 1) & 1);
+                            ++f_n;
                             tc_fence_after();
                             const uint32_t col0 = (uint32_t)(half * 256 + q * FD_CHUNK_N);
                             auto consume = [&](const uint32_t (&r)[32], int cc) {
@@ -658,7 +667,7 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
                                     } else {
                                         float* o = reinterpret_cast<float*>(a.out) + ch0 * HW + pix;
 #pragma unroll
-                                        for (int i = 0; i < 32; ++i) st_stream_f32(o + (size_t)i * HW, __uint_as_float(r[i]) * inv);
+                                        for (int i = 0; i < 32; ++i, o += HW) st_stream_f32(o, __uint_as_float(r[i]) * inv);
                                     }
                                 }
                             };
