@@ -27,6 +27,14 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar)
 {
     asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(smem_u32(bar)) : "memory");
 }
+// Arrive without release semantics.  A releasing arrive makes the thread wait until its earlier GLOBAL stores are
+// performed -- a full round trip to L2 per arrive in a loop that streams results out.  Use only where the consumer of
+// the barrier needs nothing this thread wrote to memory (e.g. "TMEM slot drained": the tcgen05.ld results are
+// already in registers after tcgen05.wait::ld).
+__device__ __forceinline__ void mbar_arrive_relaxed(uint64_t* bar)
+{
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.relaxed.cta.shared::cta.b64 st, [%0];\n\t}" ::"r"(smem_u32(bar)) : "memory");
+}
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes)
 {
     asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" ::"r"(smem_u32(bar)),

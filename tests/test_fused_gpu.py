@@ -17,6 +17,17 @@ from tests import helpers as hp
 
 pytestmark = pytest.mark.gpu
 
+
+@pytest.fixture(params=["gen1", "gen2"], autouse=True)
+def fused_generation(request, monkeypatch):
+    """Every test in this file runs against both fused kernels (the launcher reads LSV2_FD_V2 per call):
+    render_decode.cu (default) and render_decode2.cu (blend / decode overlapped, Gram-matrix norm)."""
+    if request.param == "gen2":
+        monkeypatch.setenv("LSV2_FD_V2", "1")
+    else:
+        monkeypatch.delenv("LSV2_FD_V2", raising=False)
+    return request.param
+
 BG = (0.1, 0.2, 0.3)
 W_TOL = 1e-3
 F_TOL = 1e-3
