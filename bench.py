@@ -191,6 +191,50 @@ def kernels_per_frame(W, H, fused: bool) -> int:
     return n
 
 
+TRAIN_WL = dict(N=1_000_000, W=1008, H=756,
+                name="train.py --include_feature step shape: frozen 1M-Gaussian geometry, 1008x756, 1 codebook layer "
+                     "(64 x 512), top-4, normalise + cos loss, Adam on logits [1M,64] + codebook")
+
+
+def run_train(args, dev, rank, world, scene, barrier):
+    """Second half of the metric ("train iter/s"): one iteration = softmax/top-k -> render (include_feature) ->
+    decode -> normalise -> cos loss -> backward -> (N>1: one all-reduce of the flat grad bucket) -> Adam.
+    Weak scaling: every rank renders its own view each iteration (the reference's --accum_iter N)."""
+    from langsplatv2_b200 import synth
+    from langsplatv2_b200.trainer import FeatureTrainer, synthetic_gt
+    W, H = TRAIN_WL["W"], TRAIN_WL["H"]
+    steps = max(1, min(args.steps, args.train_steps))
+    cams = [synth.ring_camera(v, VIEWS, W, H) for v in range(VIEWS)]
+    my_views = [v for v in range(VIEWS) if v % world == rank][:4]
+    cams = {v: {k: (x.to(dev) if torch.is_tensor(x) else x) for k, x in cams[v].items()} for v in my_views}
+    gts = {v: synthetic_gt(H, W, device=dev, seed=2 + v) for v in my_views}
+    tr = FeatureTrainer(scene, topk=TOPK, layers=1, device=dev)
+    loss = None
+    for s in range(3):
+        v = my_views[s % len(my_views)]
+        loss = tr.step(cams[v], *gts[v])
+    barrier()
+    t_b, t_e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_b.record()
+    for s in range(steps):
+        v = my_views[s % len(my_views)]
+        loss = tr.step(cams[v], *gts[v])
+    t_e.record()
+    barrier()
+    ms = t_b.elapsed_time(t_e)
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    return {"metric": "train iter/s", "value": steps / (ms * 1e-3), "unit": "iter/s", "views_per_s": world * steps / (ms * 1e-3),
+            "ms_per_iter": ms / steps, "steps": steps, "warmup": 3, "n_gpus": world, "scaling": "weak",
+            "final_loss": float(loss), "dtype": "f32",
+            "config": {"workload": TRAIN_WL["name"], "views_per_iter": world,
+                       "grad_allreduce_bytes": (tr.bucket.nbytes if tr.bucket is not None else 0),
+                       "optimizer": "torch.optim.Adam(fused=True, eps=1e-15) on logits+codebook (dense, as the reference)"}}
+
+
 def run_gpu(args, wl):
     import torch.distributed as dist
     from langsplatv2_b200.renderer import FeatureRenderer
@@ -294,6 +338,13 @@ def run_gpu(args, wl):
     e2e_ms = max(e_b.elapsed_time(e_e), (time.perf_counter() - w0) * 1e3 * 0.0)
     assert int(host_status[1]) == 0, "instance capacity overflow during the e2e run"
 
+    train = None
+    if not args.no_train:
+        del out
+        r.last_state = None
+        torch.cuda.empty_cache()
+        train = run_train(args, dev, rank, world, scene, barrier)
+
     t = torch.tensor([ms_total, e2e_ms, dom_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -335,6 +386,8 @@ def run_gpu(args, wl):
                          "peak_source": peak_src, "algorithmic_bytes_per_launch": dom_bytes,
                          "avg_launch_ms": dom_ms},
         }
+        if train is not None:
+            line["train"] = train
         if world == 1 and not args.no_cpu_baseline:
             est, sample, threads = cpu_frame_time(scene, cpu_cams[0], wl, budget_s=20.0)
             line["cpu_baseline"] = {"value": 1.0 / est, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample}
@@ -352,6 +405,8 @@ def main():
     ap.add_argument("--workload", default="1080p", choices=sorted(WORKLOADS))
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-train", action="store_true", help="skip the train iter/s measurement")
+    ap.add_argument("--train-steps", type=int, default=20)
     ap.add_argument("--unfused", action="store_true", help="two-call path: blend to an fp32 weight map, then decode")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

@@ -233,6 +233,12 @@ int lsv2_decode_backward(int32_t levels, int32_t Lc, int32_t D, int64_t HW, cons
 int lsv2_topk_soft_code(int64_t N, int32_t C, int32_t k, const float* logits, float* dense,
                         float* weights, float* indices, void* stream);
 
+/* Backward of the dense form (autograd of utils/vq_utils.py:9-24, reached from
+ * scene/gaussian_model.py:510-518 during train.py:173): `dense` is the forward's output
+ * (its non-zeros are the top-k mask), d_dense = dL/d dense, d_logits = dL/d logits, all f32[N][C]. */
+int lsv2_topk_soft_code_backward(int64_t N, int32_t C, const float* logits, const float* dense,
+                                 const float* d_dense, float* d_logits, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

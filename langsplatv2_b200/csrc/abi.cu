@@ -22,6 +22,8 @@ int launch_decode_tc(int levels, int Lc, int D, int64_t HW, const float* wmap, c
 size_t decode_tc_scratch_bytes(int levels, int Lc, int D);
 int launch_decode_backward(int levels, int Lc, int D, int64_t HW, const float* wmap, const float* codebooks,
                            const float* dF, float* dW, float* dC, cudaStream_t st);
+int launch_topk_soft_code_bwd(int64_t N, int C, const float* logits, const float* dense, const float* d_dense,
+                              float* d_logits, cudaStream_t st);
 int launch_topk_soft_code(int64_t N, int C, int k, const float* logits, float* dense, float* weights,
                           float* indices, cudaStream_t st);
 
@@ -201,6 +203,13 @@ int lsv2_topk_soft_code(int64_t N, int32_t C, int32_t k, const float* logits, fl
 {
     if (N < 0 || !logits) return LSV2_EINVAL;
     return launch_topk_soft_code(N, C, k, logits, dense, weights, indices, (cudaStream_t)stream);
+}
+
+int lsv2_topk_soft_code_backward(int64_t N, int32_t C, const float* logits, const float* dense,
+                                 const float* d_dense, float* d_logits, void* stream)
+{
+    if (N < 0 || (N > 0 && (!logits || !dense || !d_dense || !d_logits))) return LSV2_EINVAL;
+    return launch_topk_soft_code_bwd(N, C, logits, dense, d_dense, d_logits, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -322,4 +322,81 @@ int launch_topk_soft_code(int64_t N, int C, int k, const float* logits, float* d
     return LSV2_OK;
 }
 
+// Backward of softmax -> top-k -> renormalise (autograd of utils/vq_utils.py:9-24): one warp per row.
+//   p = softmax(x);  y_i = m_i p_i / s,  s = sum_{j in top-k} p_j + 1e-10   (m = the forward's top-k mask, read back
+//   from the forward's dense output: y_i != 0)
+//   dL/dp_i = m_i (g_i / s - G / s^2),  G = sum_j m_j g_j p_j ;   dL/dx_i = p_i (dL/dp_i - sum_j dL/dp_j p_j)
+__global__ void __launch_bounds__(256)
+k_topk_soft_code_bwd(int64_t N, int C, const float* __restrict__ logits, const float* __restrict__ dense,
+                     const float* __restrict__ d_dense, float* __restrict__ d_logits)
+{
+    const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (row >= N) return;
+    const float* x = logits + (size_t)row * C;
+    const float* y = dense + (size_t)row * C;
+    const float* g = d_dense + (size_t)row * C;
+    float v[8], gm[8];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int c = i * 32 + lane;
+        v[i] = c < C ? x[c] : -INFINITY;
+        gm[i] = (c < C && y[c] != 0.0f) ? g[c] : 0.0f;
+        mx = fmaxf(mx, v[i]);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    float s = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int c = i * 32 + lane;
+        v[i] = c < C ? expf(v[i] - mx) : 0.0f;
+        s += v[i];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    float ts = 0.0f, G = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int c = i * 32 + lane;
+        v[i] = v[i] / s;
+        const bool m = c < C && y[c] != 0.0f;
+        ts += m ? v[i] : 0.0f;
+        G = fmaf(gm[i], v[i], G);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        ts += __shfl_xor_sync(0xffffffffu, ts, o);
+        G += __shfl_xor_sync(0xffffffffu, G, o);
+    }
+    ts += 1e-10f;
+    const float inv = 1.0f / ts, sub = G * inv * inv;
+    float dp[8], D = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int c = i * 32 + lane;
+        const bool m = c < C && y[c] != 0.0f;
+        dp[i] = m ? gm[i] * inv - sub : 0.0f;
+        D = fmaf(dp[i], v[i], D);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) D += __shfl_xor_sync(0xffffffffu, D, o);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int c = i * 32 + lane;
+        if (c < C) d_logits[(size_t)row * C + c] = v[i] * (dp[i] - D);
+    }
+}
+
+int launch_topk_soft_code_bwd(int64_t N, int C, const float* logits, const float* dense, const float* d_dense,
+                              float* d_logits, cudaStream_t st)
+{
+    if (N == 0) return LSV2_OK;
+    if (C <= 0 || C > 256) return LSV2_EUNSUPPORTED;
+    k_topk_soft_code_bwd<<<ceil_div(N * 32, 256), 256, 0, st>>>(N, C, logits, dense, d_dense, d_logits);
+    LSV2_LAUNCH_CHECK("k_topk_soft_code_bwd");
+    return LSV2_OK;
+}
+
 }  // namespace lsv2

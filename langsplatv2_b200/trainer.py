@@ -1,0 +1,133 @@
+"""Feature-stage training step on the B200 op (the "train iter/s" half of the metric).
+
+Mirrors ``train.py --include_feature`` of the reference, one iteration per ``step()``:
+
+    render (include_feature)          /root/reference/train.py:147, gaussian_renderer/__init__.py:95-98,108-119
+      logits -> softmax/top-k/renorm  scene/gaussian_model.py:510-518, utils/vq_utils.py:9-24
+    decode one codebook layer         scene/gaussian_model.py:533-543 (layer_num = 1 in the paper, train.py:154)
+    normalise, cosine (+ L1) loss     train.py:157-167, utils/loss_utils.py:18-25
+    backward                          train.py:173
+    Adam on (logits, codebooks)       scene/gaussian_model.py:235-236,255 ; train.py:261-263
+
+Geometry is frozen (scene/gaussian_model.py:238-243).  Data parallel: each rank renders its own view and the
+gradients of (logits, codebooks) go through ONE flat all-reduce (``dist.GradBucket``), SUM as in the reference's
+``--accum_iter`` (train.py:261-263,348).  The hot kernels (top-k fwd/bwd, preprocess, binning, blend fwd/bwd,
+decode fwd/bwd) are liblsv2's; the loss expression and Adam are PyTorch's, as they are in the reference.
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional
+
+import torch
+import torch.nn.functional as F
+
+from . import dist as lsdist
+from .decode import decode_feature_map
+from .rasterizer import GaussianRasterizationSettings, GaussianRasterizer
+from .sparse import softmax_to_topk_soft_code
+
+
+def cos_loss(network_output: torch.Tensor, gt: torch.Tensor) -> torch.Tensor:
+    """utils/loss_utils.py:24-25."""
+    return 1 - F.cosine_similarity(network_output, gt, dim=0).mean()
+
+
+def l1_loss(network_output: torch.Tensor, gt: torch.Tensor) -> torch.Tensor:
+    """utils/loss_utils.py:18-19."""
+    return torch.abs(network_output - gt).mean()
+
+
+class FeatureTrainer:
+    """Resident scene + the two trainable tensors + Adam; ``step(cam, gt, mask)`` is one train.py iteration."""
+
+    def __init__(self, scene: Dict, topk: int = 4, lr: float = 0.0025, device="cuda", normalize: bool = True,
+                 use_cos: bool = True, use_l1: bool = False, layers: Optional[int] = None, fused_adam: bool = True):
+        dev = torch.device(device)
+        f32 = lambda t: t.to(dev, torch.float32).contiguous()
+        self.dev = dev
+        self.topk = topk
+        self.normalize, self.use_cos, self.use_l1 = normalize, use_cos, use_l1
+        self.xyz, self.opacity = f32(scene["xyz"]), f32(scene["opacity"])
+        self.scales, self.rotations = f32(scene["scaling"]), f32(scene["rotation"])
+        self.shs = f32(scene["features"])
+        self.sh_degree = int(scene.get("sh_degree", 3))
+        cb = f32(scene["codebooks"])
+        self.layers = int(cb.shape[0] if layers is None else layers)
+        self.codebook_size = int(cb.shape[1])
+        self.logits = torch.nn.Parameter(f32(scene["logits"])[:, : self.layers * self.codebook_size].clone())
+        self.codebooks = torch.nn.Parameter(cb[: self.layers].clone())
+        self.bg = torch.zeros(3, dtype=torch.float32, device=dev)
+        self.means2D = torch.zeros_like(self.xyz)                      # grad sink of the reference API; unused here
+        # the reference: torch.optim.Adam(l, lr=0.0, eps=1e-15) with the group lr = language_feature_lr
+        self.optimizer = torch.optim.Adam([{"params": [self.logits, self.codebooks], "lr": lr}], lr=0.0, eps=1e-15,
+                                          fused=fused_adam and dev.type == "cuda")
+        self.bucket = lsdist.GradBucket([self.logits, self.codebooks]) if lsdist.world_info()[1] > 1 else None
+        self.iteration = 0
+
+    # ---- reference: GaussianModel.get_render_weights (scene/gaussian_model.py:510-518) ----
+    def render_weights(self) -> torch.Tensor:
+        cs = self.codebook_size
+        w = [softmax_to_topk_soft_code(self.logits[:, i * cs:(i + 1) * cs], self.topk) for i in range(self.layers)]
+        return w[0] if len(w) == 1 else torch.cat(w, dim=-1)
+
+    def settings(self, cam: Dict) -> GaussianRasterizationSettings:
+        d = self.dev
+        return GaussianRasterizationSettings(
+            image_height=int(cam["image_height"]), image_width=int(cam["image_width"]),
+            tanfovx=float(cam["tanfovx"]), tanfovy=float(cam["tanfovy"]), bg=self.bg, scale_modifier=1.0,
+            viewmatrix=cam["world_view_transform"].to(d, non_blocking=True),
+            projmatrix=cam["full_proj_transform"].to(d, non_blocking=True),
+            sh_degree=self.sh_degree, campos=cam["camera_center"].to(d, non_blocking=True), prefiltered=False, debug=False,
+            include_feature=True, quick_render=False)
+
+    # ---- reference: compute_layer_feature_map (scene/gaussian_model.py:533-543) ----
+    def layer_feature_map(self, wmap: torch.Tensor, layer_idx: int) -> torch.Tensor:
+        cs = self.codebook_size
+        feat = None
+        for i in range(layer_idx + 1):
+            f = decode_feature_map(wmap[i * cs:(i + 1) * cs], self.codebooks[i:i + 1], normalize=False,
+                                   precision="fp32")[0]
+            feat = f if feat is None else f + feat.detach()
+        return feat
+
+    def loss(self, cam: Dict, gt: torch.Tensor, mask: torch.Tensor) -> torch.Tensor:
+        rasterizer = GaussianRasterizer(raster_settings=self.settings(cam))
+        zero = torch.zeros((1,), dtype=torch.float32, device=self.dev)
+        _, wmap, _ = rasterizer(means3D=self.xyz, means2D=self.means2D, shs=self.shs, colors_precomp=None,
+                                language_feature_precomp=self.render_weights(), language_feature_weights_quick=zero,
+                                language_feature_indices=zero, opacities=self.opacity, scales=self.scales,
+                                rotations=self.rotations, cov3D_precomp=None)
+        layer_idx = min(int(self.iteration / 10000 * self.layers), self.layers - 1)       # train.py:155
+        feat = self.layer_feature_map(wmap, layer_idx)
+        if self.normalize:
+            feat = feat / (feat.norm(dim=0, keepdim=True) + 1e-10)
+        loss = 0
+        if self.use_cos:
+            loss = loss + cos_loss(feat * mask, gt * mask)
+        if self.use_l1:
+            loss = loss + l1_loss(feat * mask, gt * mask)
+        return loss
+
+    def step(self, cam: Dict, gt: torch.Tensor, mask: torch.Tensor) -> torch.Tensor:
+        """One iteration; returns the (detached, on-device) loss."""
+        self.iteration += 1
+        loss = self.loss(cam, gt, mask)
+        loss.backward()
+        if self.bucket is not None:
+            self.bucket.sync()                      # ONE all-reduce(SUM) of [d logits || d codebooks]
+        self.optimizer.step()
+        self.optimizer.zero_grad(set_to_none=False if self.bucket is not None else True)
+        return loss.detach()
+
+
+def synthetic_gt(H: int, W: int, feat_dim: int = 512, seed: int = 2, device="cuda"):
+    """piecewise-constant ground truth, seg = (x//32 + 7*(y//32)) % 256, rows of a unit-norm table;
+    mask all true.  -> (gt [feat_dim, H, W], mask [1, H, W])"""
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    table = torch.randn((256, feat_dim), generator=g)
+    table = table / table.norm(dim=1, keepdim=True)
+    ys, xs = torch.meshgrid(torch.arange(H), torch.arange(W), indexing="ij")
+    seg = (xs // 32 + 7 * (ys // 32)) % 256
+    gt = table.to(device)[seg.to(device)].permute(2, 0, 1).contiguous()
+    mask = torch.ones((1, H, W), dtype=torch.float32, device=device)
+    return gt, mask

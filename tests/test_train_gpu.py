@@ -1,0 +1,78 @@
+"""Feature-stage training step (train.py --include_feature) on the CUDA path vs the fp64 PyTorch restatement.
+
+The checker here is oracle/torch_ref.py end to end: softmax/top-k/renorm -> preprocess -> binning -> blend ->
+decode one layer -> normalise -> cosine loss, differentiated by torch autograd in float64.  Stated tolerance for the
+gradients: max-abs <= 2e-3 x max|ref| (fp32 blend + fp32 atomics in the coefficient backward; a pixel whose
+alpha/T threshold flips between fp64 exp and the fp32 polynomial moves one contribution).
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import torch_ref
+from langsplatv2_b200 import softmax_to_topk_soft_code
+from langsplatv2_b200.trainer import FeatureTrainer, cos_loss, synthetic_gt
+from tests import helpers as hp
+
+pytestmark = pytest.mark.gpu
+
+
+def test_topk_soft_code_backward_matches_autograd():
+    rng = np.random.default_rng(3)
+    logits = rng.standard_normal((5000, 64)).astype(np.float32) * 2.0
+    g = rng.standard_normal((5000, 64)).astype(np.float32)
+    x64 = torch.tensor(logits, dtype=torch.float64, requires_grad=True)
+    (torch_ref.topk_soft_code(x64, 4) * torch.tensor(g, dtype=torch.float64)).sum().backward()
+    x = torch.tensor(logits, device="cuda", requires_grad=True)
+    y = softmax_to_topk_soft_code(x, 4)
+    (y * torch.tensor(g, device="cuda")).sum().backward()
+    ref = x64.grad.numpy()
+    got = x.grad.cpu().numpy()
+    assert np.max(np.abs(got - ref)) <= 2e-6 * max(1.0, np.abs(ref).max())
+    # rows sum to ~0 (softmax Jacobian) and the non-selected channels only see the tiny coupling term
+    assert np.abs(got.sum(1)).max() < 1e-5
+
+
+def _reference_grads(scene, cam, gt, mask, topk):
+    t64 = lambda a: torch.as_tensor(np.asarray(a), dtype=torch.float64)
+    osc, view = hp.oracle_scene(scene), hp.oracle_view(cam)
+    W, H = view["W"], view["H"]
+    pre = torch_ref.preprocess(t64(osc["means3d"]), t64(osc["opacities"]), t64(osc["scales"]), t64(osc["rotations"]),
+                               t64(view["viewmatrix"]), t64(view["projmatrix"]), t64(view["campos"]), W, H,
+                               view["tanfovx"], view["tanfovy"], shs=t64(osc["shs"]), sh_degree=3)
+    binned = torch_ref.bin_instances(pre, W, H)
+    logits = scene["logits"][:, :64].double().clone().requires_grad_(True)
+    cb = scene["codebooks"][:1].double().clone().requires_grad_(True)
+    dense = torch_ref.topk_soft_code(logits, topk)
+    out = torch_ref.render(pre, binned, W, H, torch.zeros(3), coeff=dense)
+    feat = torch_ref.decode(out["wmap"], cb, normalize=False)[0]
+    feat = feat / (feat.norm(dim=0, keepdim=True) + 1e-10)
+    loss = cos_loss(feat * mask.double().cpu(), gt.double().cpu() * mask.double().cpu())
+    loss.backward()
+    return float(loss), logits.grad.numpy(), cb.grad.numpy()
+
+
+def test_train_step_gradients_match_fp64_autograd():
+    N, W, H = 3000, 96, 64
+    scene, cam = hp.make_case(N, W, H, seed=11, levels=1, scale_boost=2.5)
+    gt, mask = synthetic_gt(H, W, device="cuda")
+    ref_loss, ref_dl, ref_dc = _reference_grads(scene, cam, gt, mask, 4)
+    tr = FeatureTrainer(scene, topk=4, layers=1)
+    loss = tr.loss(cam, gt, mask)
+    loss.backward()
+    assert abs(float(loss) - ref_loss) <= 1e-4
+    dl = tr.logits.grad.cpu().numpy()
+    dc = tr.codebooks.grad.cpu().numpy()
+    assert np.abs(ref_dl).max() > 0 and np.abs(ref_dc).max() > 0
+    assert np.max(np.abs(dl - ref_dl)) <= 2e-3 * np.abs(ref_dl).max()
+    assert np.max(np.abs(dc - ref_dc)) <= 2e-3 * np.abs(ref_dc).max()
+
+
+def test_train_steps_reduce_the_loss():
+    N, W, H = 20000, 160, 96
+    scene, cam = hp.make_case(N, W, H, seed=12, levels=1, scale_boost=2.5)
+    gt, mask = synthetic_gt(H, W, device="cuda")
+    tr = FeatureTrainer(scene, topk=4, layers=1, lr=0.05)
+    losses = [float(tr.step(cam, gt, mask)) for _ in range(15)]
+    assert all(np.isfinite(losses))
+    assert losses[-1] < losses[0] - 0.05, losses
