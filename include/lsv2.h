@@ -239,6 +239,18 @@ int lsv2_topk_soft_code(int64_t N, int32_t C, int32_t k, const float* logits, fl
 int lsv2_topk_soft_code_backward(int64_t N, int32_t C, const float* logits, const float* dense,
                                  const float* d_dense, float* d_logits, void* stream);
 
+/* ---- feature-stage loss (train.py:157-164, utils/loss_utils.py:24-25) -----------------
+ * loss = 1 - mean_p cos(a_p, b_p),  a = mask * F / (|F| + 1e-10) (normalize != 0) or mask * F,  b = mask * gt,
+ * cos as torch.nn.functional.cosine_similarity (each norm clamped at 1e-8).  F, gt: f32[D][HW]; mask f32[HW]
+ * or NULL (all ones).  forward: partial f32[lsv2_cos_loss_blocks(HW)] receives per-block sums of cos_p
+ * (loss = 1 - sum(partial) / HW) and alpha_beta f32[2][HW] the per-pixel scalars of the gradient.
+ * backward: dF = grad_out * dL/dF (grad_out: device scalar or NULL = 1). */
+int32_t lsv2_cos_loss_blocks(int64_t HW);
+int lsv2_cos_loss_forward(int32_t D, int64_t HW, const float* F, const float* gt, const float* mask,
+                          int32_t normalize, float* alpha_beta, float* partial, void* stream);
+int lsv2_cos_loss_backward(int32_t D, int64_t HW, const float* F, const float* gt, const float* alpha_beta,
+                           const float* grad_out, float* dF, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

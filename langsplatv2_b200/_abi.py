@@ -61,7 +61,7 @@ EXPORTS = [
     "lsv2_abi_version", "lsv2_strerror", "lsv2_last_cuda_error", "lsv2_sort_scratch_bytes",
     "lsv2_preprocess", "lsv2_bin", "lsv2_compact_coeff", "lsv2_render_forward", "lsv2_forward",
     "lsv2_mark_visible", "lsv2_render_backward", "lsv2_decode_scratch_bytes", "lsv2_decode",
-    "lsv2_decode_backward", "lsv2_topk_soft_code", "lsv2_topk_soft_code_backward",
+    "lsv2_decode_backward", "lsv2_topk_soft_code", "lsv2_topk_soft_code_backward", "lsv2_cos_loss_blocks", "lsv2_cos_loss_forward", "lsv2_cos_loss_backward",
     "lsv2_render_decode_scratch_bytes", "lsv2_render_decode",
 ]
 
@@ -105,13 +105,18 @@ def lib() -> C.CDLL:
     L.lsv2_decode_backward.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int64, _vp, _vp, _vp, _vp, _vp, _vp]
     L.lsv2_topk_soft_code.argtypes = [C.c_int64, C.c_int32, C.c_int32, _vp, _vp, _vp, _vp, _vp]
     L.lsv2_topk_soft_code_backward.argtypes = [C.c_int64, C.c_int32, _vp, _vp, _vp, _vp, _vp]
+    L.lsv2_cos_loss_blocks.restype = C.c_int32
+    L.lsv2_cos_loss_blocks.argtypes = [C.c_int64]
+    L.lsv2_cos_loss_forward.argtypes = [C.c_int32, C.c_int64, _vp, _vp, _vp, C.c_int32, _vp, _vp, _vp]
+    L.lsv2_cos_loss_backward.argtypes = [C.c_int32, C.c_int64, _vp, _vp, _vp, _vp, _vp, _vp]
     L.lsv2_render_decode_scratch_bytes.restype = C.c_size_t
     L.lsv2_render_decode_scratch_bytes.argtypes = [C.c_int32]
     L.lsv2_render_decode.argtypes = [P(View), P(Geom), P(Binning), P(Features), P(Image), _vp, C.c_int32,
                                      C.c_int32, C.c_int32, C.c_int32, C.c_int32, _vp, _vp, C.c_size_t, _vp]
     for name in ("lsv2_preprocess", "lsv2_bin", "lsv2_compact_coeff", "lsv2_render_forward", "lsv2_forward",
                  "lsv2_mark_visible", "lsv2_render_backward", "lsv2_decode", "lsv2_decode_backward",
-                 "lsv2_topk_soft_code", "lsv2_topk_soft_code_backward", "lsv2_render_decode"):
+                 "lsv2_topk_soft_code", "lsv2_topk_soft_code_backward", "lsv2_cos_loss_forward", "lsv2_cos_loss_backward",
+                 "lsv2_render_decode"):
         getattr(L, name).restype = C.c_int
     _lib = L
     return L

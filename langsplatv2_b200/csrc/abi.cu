@@ -22,6 +22,10 @@ int launch_decode_tc(int levels, int Lc, int D, int64_t HW, const float* wmap, c
 size_t decode_tc_scratch_bytes(int levels, int Lc, int D);
 int launch_decode_backward(int levels, int Lc, int D, int64_t HW, const float* wmap, const float* codebooks,
                            const float* dF, float* dW, float* dC, cudaStream_t st);
+int launch_cos_loss_forward(int D, int64_t HW, const float* F, const float* gt, const float* mask, int normalize,
+                            float* alpha_beta, float* partial, cudaStream_t st);
+int launch_cos_loss_backward(int D, int64_t HW, const float* F, const float* gt, const float* alpha_beta,
+                             const float* grad_out, float* dF, cudaStream_t st);
 int launch_topk_soft_code_bwd(int64_t N, int C, const float* logits, const float* dense, const float* d_dense,
                               float* d_logits, cudaStream_t st);
 int launch_topk_soft_code(int64_t N, int C, int k, const float* logits, float* dense, float* weights,
@@ -210,6 +214,22 @@ int lsv2_topk_soft_code_backward(int64_t N, int32_t C, const float* logits, cons
 {
     if (N < 0 || (N > 0 && (!logits || !dense || !d_dense || !d_logits))) return LSV2_EINVAL;
     return launch_topk_soft_code_bwd(N, C, logits, dense, d_dense, d_logits, (cudaStream_t)stream);
+}
+
+int32_t lsv2_cos_loss_blocks(int64_t HW) { return (int32_t)((HW + 255) / 256); }
+
+int lsv2_cos_loss_forward(int32_t D, int64_t HW, const float* F, const float* gt, const float* mask,
+                          int32_t normalize, float* alpha_beta, float* partial, void* stream)
+{
+    if (D <= 0 || HW < 0 || (HW > 0 && (!F || !gt || !alpha_beta || !partial))) return LSV2_EINVAL;
+    return launch_cos_loss_forward(D, HW, F, gt, mask, normalize, alpha_beta, partial, (cudaStream_t)stream);
+}
+
+int lsv2_cos_loss_backward(int32_t D, int64_t HW, const float* F, const float* gt, const float* alpha_beta,
+                           const float* grad_out, float* dF, void* stream)
+{
+    if (D <= 0 || HW < 0 || (HW > 0 && (!F || !gt || !alpha_beta || !dF))) return LSV2_EINVAL;
+    return launch_cos_loss_backward(D, HW, F, gt, alpha_beta, grad_out, dF, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -23,6 +23,7 @@ import torch.nn.functional as F
 
 from . import dist as lsdist
 from .decode import decode_feature_map
+from .loss import normalized_cos_loss
 from .rasterizer import GaussianRasterizationSettings, GaussianRasterizer
 from .sparse import softmax_to_topk_soft_code
 
@@ -41,12 +42,14 @@ class FeatureTrainer:
     """Resident scene + the two trainable tensors + Adam; ``step(cam, gt, mask)`` is one train.py iteration."""
 
     def __init__(self, scene: Dict, topk: int = 4, lr: float = 0.0025, device="cuda", normalize: bool = True,
-                 use_cos: bool = True, use_l1: bool = False, layers: Optional[int] = None, fused_adam: bool = True):
+                 use_cos: bool = True, use_l1: bool = False, layers: Optional[int] = None, fused_adam: bool = True,
+                 fused_loss: bool = True):
         dev = torch.device(device)
         f32 = lambda t: t.to(dev, torch.float32).contiguous()
         self.dev = dev
         self.topk = topk
         self.normalize, self.use_cos, self.use_l1 = normalize, use_cos, use_l1
+        self.fused_loss = fused_loss        # cos loss (+ the normalisation) as two kernels instead of torch's ~28 passes
         self.xyz, self.opacity = f32(scene["xyz"]), f32(scene["opacity"])
         self.scales, self.rotations = f32(scene["scaling"]), f32(scene["rotation"])
         self.shs = f32(scene["features"])
@@ -99,6 +102,8 @@ class FeatureTrainer:
                                 rotations=self.rotations, cov3D_precomp=None)
         layer_idx = min(int(self.iteration / 10000 * self.layers), self.layers - 1)       # train.py:155
         feat = self.layer_feature_map(wmap, layer_idx)
+        if self.fused_loss and self.use_cos and not self.use_l1 and mask.numel() == feat[0].numel():
+            return normalized_cos_loss(feat, gt, mask, normalize=self.normalize)
         if self.normalize:
             feat = feat / (feat.norm(dim=0, keepdim=True) + 1e-10)
         loss = 0

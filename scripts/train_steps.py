@@ -1,0 +1,22 @@
+"""Runs a few feature-stage training iterations (for ncu launch lists / timing breakdowns).  GPU box only."""
+import os, sys, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from langsplatv2_b200 import synth
+from langsplatv2_b200.trainer import FeatureTrainer, synthetic_gt
+
+N = int(os.environ.get("N", 1_000_000)); W = int(os.environ.get("W", 1008)); H = int(os.environ.get("H", 756))
+steps = int(os.environ.get("STEPS", 4))
+scene = synth.make_scene(N, seed=0, levels=3)
+cam = synth.ring_camera(0, 64, W, H)
+cam = {k: (v.cuda() if torch.is_tensor(v) else v) for k, v in cam.items()}
+gt, mask = synthetic_gt(H, W)
+tr = FeatureTrainer(scene, topk=4, layers=1)
+for _ in range(2):
+    tr.step(cam, gt, mask)
+torch.cuda.synchronize()
+t0 = time.perf_counter()
+for _ in range(steps):
+    loss = tr.step(cam, gt, mask)
+torch.cuda.synchronize()
+print("ms/iter", (time.perf_counter() - t0) * 1e3 / steps, "loss", float(loss))

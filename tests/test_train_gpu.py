@@ -33,6 +33,29 @@ def test_topk_soft_code_backward_matches_autograd():
     assert np.abs(got.sum(1)).max() < 1e-5
 
 
+@pytest.mark.parametrize("normalize", [True, False])
+def test_fused_cos_loss_matches_torch_autograd(normalize):
+    from langsplatv2_b200.loss import normalized_cos_loss
+    g = torch.Generator(device="cpu").manual_seed(5)
+    D, H, W = 512, 37, 53
+    feat = torch.randn((D, H, W), generator=g) * 3.0
+    gt = torch.randn((D, H, W), generator=g)
+    gt = gt / gt.norm(dim=0, keepdim=True)
+    mask = (torch.rand((1, H, W), generator=g) > 0.3).float()
+    feat[:, 0, 0] = 0.0                                    # a dead pixel: 0 / (0 + 1e-10)
+    f64 = feat.double().requires_grad_(True)
+    x = f64 / (f64.norm(dim=0, keepdim=True) + 1e-10) if normalize else f64
+    ref = cos_loss(x * mask.double(), gt.double() * mask.double())
+    ref.backward()
+    fc = feat.cuda().requires_grad_(True)
+    out = normalized_cos_loss(fc, gt.cuda(), mask.cuda(), normalize=normalize)
+    (out * 2.0).backward()                                 # a non-unit upstream gradient
+    assert abs(float(out) - float(ref)) <= 2e-6
+    got = fc.grad.cpu().numpy() / 2.0
+    want = f64.grad.numpy()
+    assert np.max(np.abs(got - want)) <= 1e-5 * np.abs(want).max() + 1e-12
+
+
 def _reference_grads(scene, cam, gt, mask, topk):
     t64 = lambda a: torch.as_tensor(np.asarray(a), dtype=torch.float64)
     osc, view = hp.oracle_scene(scene), hp.oracle_view(cam)
@@ -52,12 +75,13 @@ def _reference_grads(scene, cam, gt, mask, topk):
     return float(loss), logits.grad.numpy(), cb.grad.numpy()
 
 
-def test_train_step_gradients_match_fp64_autograd():
+@pytest.mark.parametrize("fused_loss", [True, False])
+def test_train_step_gradients_match_fp64_autograd(fused_loss):
     N, W, H = 3000, 96, 64
     scene, cam = hp.make_case(N, W, H, seed=11, levels=1, scale_boost=2.5)
     gt, mask = synthetic_gt(H, W, device="cuda")
     ref_loss, ref_dl, ref_dc = _reference_grads(scene, cam, gt, mask, 4)
-    tr = FeatureTrainer(scene, topk=4, layers=1)
+    tr = FeatureTrainer(scene, topk=4, layers=1, fused_loss=fused_loss)
     loss = tr.loss(cam, gt, mask)
     loss.backward()
     assert abs(float(loss) - ref_loss) <= 1e-4
