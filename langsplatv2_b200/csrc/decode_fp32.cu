@@ -117,40 +117,78 @@ int launch_decode_fp32(int levels, int Lc, int D, int64_t HW, const float* wmap,
 
 // ---- decode backward (fp32) -------------------------------------------------------------
 // dW[l*Lc+k][p] = sum_d C[l][k][d] dF[l][d][p]
-// grid: (ceil(HW/128), levels); thread = (pixel, 32-channel half); dF column chunk staged in smem.
+// grid: (ceil(HW/128), levels).  CTA tile 128 pixels x 64 codes, thread tile 4 pixels x 8 codes (a warp shares its
+// 8 codes, so the codebook reads broadcast and the dF reads are one conflict-free float4 per thread); dF and the
+// codebook are staged 32 features at a time.
 __global__ void __launch_bounds__(256)
 k_decode_bwd_dW(int Lc, int D, int64_t HW, const float* __restrict__ codebooks, const float* __restrict__ dF,
                 float* __restrict__ dW)
 {
-    __shared__ float s_c[32][65];                    // [d chunk][k] (k < 64 per sweep)
+    __shared__ __align__(16) float s_f[32][128];     // [feature][pixel]
+    __shared__ __align__(16) float s_c[32][68];      // [feature][code] (+4 pad)
     const int tid = threadIdx.x;
     const int level = blockIdx.y;
-    const int p = tid & 127, kh = tid >> 7;          // pixel in block, which half of a 64-k sweep
-    const int64_t pix = (int64_t)blockIdx.x * 128 + p;
+    const int pg = tid & 31, kg = tid >> 5;
+    const int64_t pix0 = (int64_t)blockIdx.x * 128;
     const float* C = codebooks + (size_t)level * Lc * D;
     const float* F = dF + (size_t)level * D * HW;
+    const bool vec = (HW & 3) == 0 && pix0 + 128 <= HW;
     for (int k0 = 0; k0 < Lc; k0 += 64) {
-        float acc[32];
+        float acc[4][8];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) acc[i] = 0.0f;
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[i][j] = 0.0f;
         for (int d0 = 0; d0 < D; d0 += 32) {
             __syncthreads();
-            for (int e = tid; e < 64 * 32; e += 256) {
-                const int k = e >> 5, d = e & 31;
-                s_c[d][k] = (k0 + k < Lc && d0 + d < D) ? C[(size_t)(k0 + k) * D + d0 + d] : 0.0f;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int e = tid + i * 256, d = e >> 5, p4 = e & 31;
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (d0 + d < D) {
+                    const float* src = F + (size_t)(d0 + d) * HW + pix0 + p4 * 4;
+                    if (vec) {
+                        v = __ldg(reinterpret_cast<const float4*>(src));
+                    } else {
+                        const int64_t q = pix0 + p4 * 4;
+                        if (q < HW) v.x = src[0];
+                        if (q + 1 < HW) v.y = src[1];
+                        if (q + 2 < HW) v.z = src[2];
+                        if (q + 3 < HW) v.w = src[3];
+                    }
+                }
+                *reinterpret_cast<float4*>(&s_f[d][p4 * 4]) = v;
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int e = tid + i * 256, k = e >> 5, d = e & 31;
+                s_c[d][k] = (k0 + k < Lc && d0 + d < D) ? __ldg(C + (size_t)(k0 + k) * D + d0 + d) : 0.0f;
             }
             __syncthreads();
-            for (int d = 0; d < 32 && d0 + d < D; ++d) {
-                const float f = pix < HW ? F[(size_t)(d0 + d) * HW + pix] : 0.0f;
+#pragma unroll 8
+            for (int d = 0; d < 32; ++d) {
+                const float4 f4 = *reinterpret_cast<const float4*>(&s_f[d][pg * 4]);
+                const float4 ca = *reinterpret_cast<const float4*>(&s_c[d][kg * 8]);
+                const float4 cb = *reinterpret_cast<const float4*>(&s_c[d][kg * 8 + 4]);
+                const float fv[4] = {f4.x, f4.y, f4.z, f4.w};
+                const float cv[8] = {ca.x, ca.y, ca.z, ca.w, cb.x, cb.y, cb.z, cb.w};
 #pragma unroll
-                for (int i = 0; i < 32; ++i) acc[i] = fmaf(s_c[d][kh * 32 + i], f, acc[i]);
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(fv[i], cv[j], acc[i][j]);
             }
         }
-        if (pix < HW) {
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                const int k = k0 + kh * 32 + i;
-                if (k < Lc) dW[((size_t)level * Lc + k) * HW + pix] = acc[i];
+        for (int j = 0; j < 8; ++j) {
+            const int k = k0 + kg * 8 + j;
+            if (k >= Lc) continue;
+            float* dst = dW + ((size_t)level * Lc + k) * HW + pix0 + pg * 4;
+            if (vec) {
+                *reinterpret_cast<float4*>(dst) = make_float4(acc[0][j], acc[1][j], acc[2][j], acc[3][j]);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    if (pix0 + pg * 4 + i < HW) dst[i] = acc[i][j];
             }
         }
     }
@@ -229,6 +267,7 @@ int launch_decode_backward(int levels, int Lc, int D, int64_t HW, const float* w
 // ---- softmax -> top-k -> renormalise (utils/vq_utils.py:9-40) -----------------------------
 // One warp per row; C <= 256.  Ties: the lower channel wins (torch.topk on CPU and the
 // checker agree on that for distinct values; exact ties are measure-zero for real logits).
+template <int NI>   // NI = ceil(C / 32): elements per lane
 __global__ void __launch_bounds__(256)
 k_topk_soft_code(int64_t N, int C, int k, const float* __restrict__ logits, float* __restrict__ dense,
                  float* __restrict__ weights, float* __restrict__ indices)
@@ -237,10 +276,10 @@ k_topk_soft_code(int64_t N, int C, int k, const float* __restrict__ logits, floa
     const int lane = threadIdx.x & 31;
     if (row >= N) return;
     const float* x = logits + (size_t)row * C;
-    float v[8];
+    float v[NI];
     float mx = -INFINITY;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
+    for (int i = 0; i < NI; ++i) {
         const int c = i * 32 + lane;
         v[i] = c < C ? x[c] : -INFINITY;
         mx = fmaxf(mx, v[i]);
@@ -251,7 +290,7 @@ k_topk_soft_code(int64_t N, int C, int k, const float* __restrict__ logits, floa
     // parallel; the sum is taken as a tree (differs from a serial sum in the last ulps).
     float s = 0.0f;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
+    for (int i = 0; i < NI; ++i) {
         const int c = i * 32 + lane;
         v[i] = c < C ? expf(v[i] - mx) : 0.0f;
         s += v[i];
@@ -259,14 +298,14 @@ k_topk_soft_code(int64_t N, int C, int k, const float* __restrict__ logits, floa
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) v[i] = v[i] / s;
+    for (int i = 0; i < NI; ++i) v[i] = v[i] / s;
     uint32_t sel = 0;   // bit i: element i*32+lane selected
     float ts = 0.0f;
     for (int j = 0; j < k; ++j) {
         float best = -1.0f;
         int bc = 0x7fffffff;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
+        for (int i = 0; i < NI; ++i) {
             const int c = i * 32 + lane;
             if (c < C && !((sel >> i) & 1u) && (v[i] > best)) { best = v[i]; bc = c; }
         }
@@ -282,19 +321,21 @@ k_topk_soft_code(int64_t N, int C, int k, const float* __restrict__ logits, floa
     // the checker sums the selected probabilities in channel order
     float tsum = 0.0f;
     {
-        // serial over channels, but only k terms are non-zero: gather them in order
-        for (int i = 0; i < 8; ++i) {
-            for (int l = 0; l < 32; ++l) {
-                const uint32_t bit = __shfl_sync(0xffffffffu, (sel >> i) & 1u, l);
-                if (bit) tsum += __shfl_sync(0xffffffffu, v[i], l);
+        // only k terms are non-zero: walk the set bits of the per-slot ballots in channel order
+#pragma unroll
+        for (int i = 0; i < NI; ++i) {
+            uint32_t m = __ballot_sync(0xffffffffu, (sel >> i) & 1u);
+            while (m) {
+                const int l = __ffs(m) - 1;
+                tsum += __shfl_sync(0xffffffffu, v[i], l);
+                m &= m - 1;
             }
-            if ((i + 1) * 32 >= C) break;
         }
     }
     (void)ts;
     const float den = tsum + 1e-10f;
     int before = 0;   // number of selected channels below this lane's element i
-    for (int i = 0; i < 8; ++i) {
+    for (int i = 0; i < NI; ++i) {
         const int c = i * 32 + lane;
         const uint32_t bits = __ballot_sync(0xffffffffu, (sel >> i) & 1u);
         const int o = before + __popc(bits & ((1u << lane) - 1u));
@@ -308,7 +349,6 @@ k_topk_soft_code(int64_t N, int C, int k, const float* __restrict__ logits, floa
             }
         }
         before += __popc(bits);
-        if ((i + 1) * 32 >= C) break;
     }
 }
 
@@ -317,7 +357,11 @@ int launch_topk_soft_code(int64_t N, int C, int k, const float* logits, float* d
 {
     if (N <= 0) return LSV2_OK;
     if (C <= 0 || C > 256 || k <= 0 || k > C) return LSV2_EUNSUPPORTED;
-    k_topk_soft_code<<<ceil_div(N * 32, 256), 256, 0, st>>>(N, C, k, logits, dense, weights, indices);
+    const unsigned grid = (unsigned)ceil_div(N * 32, 256);
+    if (C <= 32) k_topk_soft_code<1><<<grid, 256, 0, st>>>(N, C, k, logits, dense, weights, indices);
+    else if (C <= 64) k_topk_soft_code<2><<<grid, 256, 0, st>>>(N, C, k, logits, dense, weights, indices);
+    else if (C <= 128) k_topk_soft_code<4><<<grid, 256, 0, st>>>(N, C, k, logits, dense, weights, indices);
+    else k_topk_soft_code<8><<<grid, 256, 0, st>>>(N, C, k, logits, dense, weights, indices);
     LSV2_LAUNCH_CHECK("k_topk_soft_code");
     return LSV2_OK;
 }
@@ -326,6 +370,7 @@ int launch_topk_soft_code(int64_t N, int C, int k, const float* logits, float* d
 //   p = softmax(x);  y_i = m_i p_i / s,  s = sum_{j in top-k} p_j + 1e-10   (m = the forward's top-k mask, read back
 //   from the forward's dense output: y_i != 0)
 //   dL/dp_i = m_i (g_i / s - G / s^2),  G = sum_j m_j g_j p_j ;   dL/dx_i = p_i (dL/dp_i - sum_j dL/dp_j p_j)
+template <int NI>
 __global__ void __launch_bounds__(256)
 k_topk_soft_code_bwd(int64_t N, int C, const float* __restrict__ logits, const float* __restrict__ dense,
                      const float* __restrict__ d_dense, float* __restrict__ d_logits)
@@ -336,10 +381,10 @@ k_topk_soft_code_bwd(int64_t N, int C, const float* __restrict__ logits, const f
     const float* x = logits + (size_t)row * C;
     const float* y = dense + (size_t)row * C;
     const float* g = d_dense + (size_t)row * C;
-    float v[8], gm[8];
+    float v[NI], gm[NI];
     float mx = -INFINITY;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
+    for (int i = 0; i < NI; ++i) {
         const int c = i * 32 + lane;
         v[i] = c < C ? x[c] : -INFINITY;
         gm[i] = (c < C && y[c] != 0.0f) ? g[c] : 0.0f;
@@ -349,7 +394,7 @@ k_topk_soft_code_bwd(int64_t N, int C, const float* __restrict__ logits, const f
     for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
     float s = 0.0f;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
+    for (int i = 0; i < NI; ++i) {
         const int c = i * 32 + lane;
         v[i] = c < C ? expf(v[i] - mx) : 0.0f;
         s += v[i];
@@ -358,7 +403,7 @@ k_topk_soft_code_bwd(int64_t N, int C, const float* __restrict__ logits, const f
     for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
     float ts = 0.0f, G = 0.0f;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
+    for (int i = 0; i < NI; ++i) {
         const int c = i * 32 + lane;
         v[i] = v[i] / s;
         const bool m = c < C && y[c] != 0.0f;
@@ -372,9 +417,9 @@ k_topk_soft_code_bwd(int64_t N, int C, const float* __restrict__ logits, const f
     }
     ts += 1e-10f;
     const float inv = 1.0f / ts, sub = G * inv * inv;
-    float dp[8], D = 0.0f;
+    float dp[NI], D = 0.0f;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
+    for (int i = 0; i < NI; ++i) {
         const int c = i * 32 + lane;
         const bool m = c < C && y[c] != 0.0f;
         dp[i] = m ? gm[i] * inv - sub : 0.0f;
@@ -383,7 +428,7 @@ k_topk_soft_code_bwd(int64_t N, int C, const float* __restrict__ logits, const f
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) D += __shfl_xor_sync(0xffffffffu, D, o);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
+    for (int i = 0; i < NI; ++i) {
         const int c = i * 32 + lane;
         if (c < C) d_logits[(size_t)row * C + c] = v[i] * (dp[i] - D);
     }
@@ -394,7 +439,11 @@ int launch_topk_soft_code_bwd(int64_t N, int C, const float* logits, const float
 {
     if (N == 0) return LSV2_OK;
     if (C <= 0 || C > 256) return LSV2_EUNSUPPORTED;
-    k_topk_soft_code_bwd<<<ceil_div(N * 32, 256), 256, 0, st>>>(N, C, logits, dense, d_dense, d_logits);
+    const unsigned grid = (unsigned)ceil_div(N * 32, 256);
+    if (C <= 32) k_topk_soft_code_bwd<1><<<grid, 256, 0, st>>>(N, C, logits, dense, d_dense, d_logits);
+    else if (C <= 64) k_topk_soft_code_bwd<2><<<grid, 256, 0, st>>>(N, C, logits, dense, d_dense, d_logits);
+    else if (C <= 128) k_topk_soft_code_bwd<4><<<grid, 256, 0, st>>>(N, C, logits, dense, d_dense, d_logits);
+    else k_topk_soft_code_bwd<8><<<grid, 256, 0, st>>>(N, C, logits, dense, d_dense, d_logits);
     LSV2_LAUNCH_CHECK("k_topk_soft_code_bwd");
     return LSV2_OK;
 }
