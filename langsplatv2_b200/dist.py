@@ -77,9 +77,25 @@ class GradBucket:
                 p.grad.copy_(v)
 
     def sync(self) -> None:
+        if self.attached:
+            self.all_reduce()                       # the gradients already live in the bucket
+            return
         self.pack()
         self.all_reduce()
         self.unpack()
+
+    attached = False
+
+    def attach(self) -> None:
+        """Make every parameter's ``.grad`` a view of the flat bucket: backward accumulates straight into it and
+        ``sync()`` is the all-reduce alone (no pack / unpack copies).  Pair with ``zero()`` instead of
+        ``optimizer.zero_grad(set_to_none=True)``."""
+        for p, v in zip(self.params, self.views):
+            p.grad = v
+        self.attached = True
+
+    def zero(self) -> None:
+        self.flat.zero_()
 
 
 def all_reduce_grads(params: Iterable[torch.Tensor]) -> None:

@@ -328,11 +328,12 @@ def rasterize_backward(st: FrameState, grad_wmap: Optional[torch.Tensor], grad_c
 class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, language_feature_precomp, weights_quick, indices_quick,
-                opacities, scales, rotations, cov3Ds_precomp, raster_settings):
+                opacities, scales, rotations, cov3Ds_precomp, raster_settings, capacity=None):
         st = rasterize_forward(raster_settings, means3D, opacities, shs=sh, colors_precomp=colors_precomp,
                                scales=scales, rotations=rotations, cov3D_precomp=cov3Ds_precomp,
                                language_feature_precomp=language_feature_precomp,
-                               language_feature_weights_quick=weights_quick, language_feature_indices=indices_quick)
+                               language_feature_weights_quick=weights_quick, language_feature_indices=indices_quick,
+                               capacity=capacity)
         ctx.state = st
         ctx.color_is_precomp = colors_precomp is not None
         H, W = st.H, st.W
@@ -359,15 +360,20 @@ class _RasterizeGaussians(torch.autograd.Function):
             d_coeff, d_colors = rasterize_backward(st, grad_wmap, gc)
         elif need[3]:
             raise NotImplementedError("colour gradients are produced together with the feature backward only")
-        return (None, None, None, d_colors, d_coeff, None, None, None, None, None, None, None)
+        return (None, None, None, d_colors, d_coeff, None, None, None, None, None, None, None, None)
 
 
 class GaussianRasterizer(nn.Module):
     """Drop-in for ``diff_gaussian_rasterization.GaussianRasterizer``."""
 
-    def __init__(self, raster_settings: GaussianRasterizationSettings):
+    def __init__(self, raster_settings: GaussianRasterizationSettings, capacity: Optional[int] = None):
+        """``capacity`` (extension, default off): an upper bound on the number of (Gaussian, tile) instances.  With it
+        the frame runs without the reference's one blocking device->host read of ``num_rendered``; the true count and
+        an overflow flag stay on the device in ``last_state.status``."""
         super().__init__()
         self.raster_settings = raster_settings
+        self.capacity = capacity
+        self.last_state: Optional[FrameState] = None
 
     def markVisible(self, positions: torch.Tensor) -> torch.Tensor:
         L_ = _abi.lib()
@@ -388,6 +394,9 @@ class GaussianRasterizer(nn.Module):
         if ((scales is None or rotations is None) and cov3D_precomp is None) or \
                 ((scales is not None or rotations is not None) and cov3D_precomp is not None):
             raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
-        return _RasterizeGaussians.apply(means3D, means2D, shs, colors_precomp, language_feature_precomp,
-                                         language_feature_weights_quick, language_feature_indices, opacities,
-                                         scales, rotations, cov3D_precomp, rs)
+        out = _RasterizeGaussians.apply(means3D, means2D, shs, colors_precomp, language_feature_precomp,
+                                        language_feature_weights_quick, language_feature_indices, opacities,
+                                        scales, rotations, cov3D_precomp, rs, self.capacity)
+        fn = out[0].grad_fn
+        self.last_state = getattr(fn, "state", None) if fn is not None else None
+        return out

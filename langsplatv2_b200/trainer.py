@@ -64,8 +64,17 @@ class FeatureTrainer:
         # the reference: torch.optim.Adam(l, lr=0.0, eps=1e-15) with the group lr = language_feature_lr
         self.optimizer = torch.optim.Adam([{"params": [self.logits, self.codebooks], "lr": lr}], lr=0.0, eps=1e-15,
                                           fused=fused_adam and dev.type == "cuda")
-        self.bucket = lsdist.GradBucket([self.logits, self.codebooks]) if lsdist.world_info()[1] > 1 else None
+        self.bucket = None
+        if lsdist.world_info()[1] > 1:
+            self.bucket = lsdist.GradBucket([self.logits, self.codebooks])
+            self.bucket.attach()                    # grads are written into the flat all-reduce buffer directly
         self.iteration = 0
+        # instance capacity: the first `calib_steps` iterations read num_rendered back (the reference's one host sync
+        # per frame); after that the frame runs with a bounded instance buffer and no host sync
+        self.capacity: Optional[int] = None
+        self.calib_steps = 3
+        self._max_seen = 0
+        self._last_state = None
 
     # ---- reference: GaussianModel.get_render_weights (scene/gaussian_model.py:510-518) ----
     def render_weights(self) -> torch.Tensor:
@@ -94,12 +103,13 @@ class FeatureTrainer:
         return feat
 
     def loss(self, cam: Dict, gt: torch.Tensor, mask: torch.Tensor) -> torch.Tensor:
-        rasterizer = GaussianRasterizer(raster_settings=self.settings(cam))
+        rasterizer = GaussianRasterizer(raster_settings=self.settings(cam), capacity=self.capacity)
         zero = torch.zeros((1,), dtype=torch.float32, device=self.dev)
         _, wmap, _ = rasterizer(means3D=self.xyz, means2D=self.means2D, shs=self.shs, colors_precomp=None,
                                 language_feature_precomp=self.render_weights(), language_feature_weights_quick=zero,
                                 language_feature_indices=zero, opacities=self.opacity, scales=self.scales,
                                 rotations=self.rotations, cov3D_precomp=None)
+        self._last_state = rasterizer.last_state
         layer_idx = min(int(self.iteration / 10000 * self.layers), self.layers - 1)       # train.py:155
         feat = self.layer_feature_map(wmap, layer_idx)
         if self.fused_loss and self.use_cos and not self.use_l1 and mask.numel() == feat[0].numel():
@@ -121,7 +131,19 @@ class FeatureTrainer:
         if self.bucket is not None:
             self.bucket.sync()                      # ONE all-reduce(SUM) of [d logits || d codebooks]
         self.optimizer.step()
-        self.optimizer.zero_grad(set_to_none=False if self.bucket is not None else True)
+        if self.bucket is not None:
+            self.bucket.zero()
+        else:
+            self.optimizer.zero_grad(set_to_none=True)
+        st = self._last_state
+        if st is not None:
+            if self.capacity is None:
+                self._max_seen = max(self._max_seen, st.num_rendered)
+                if self.iteration >= self.calib_steps:
+                    self.capacity = int(self._max_seen * 1.5) + 4096
+            elif self.iteration % 64 == 0 and st.overflowed:       # rare check (one small D2H read)
+                raise RuntimeError(f"instance capacity {self.capacity} exceeded; raise FeatureTrainer.capacity")
+        self._last_state = None
         return loss.detach()
 
 

@@ -16,7 +16,11 @@ for _ in range(2):
     tr.step(cam, gt, mask)
 torch.cuda.synchronize()
 t0 = time.perf_counter()
-for _ in range(steps):
+evs = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+evs[0].record()
+for i in range(steps):
     loss = tr.step(cam, gt, mask)
+    evs[i + 1].record()
 torch.cuda.synchronize()
+print("per-step ms", [round(evs[i].elapsed_time(evs[i + 1]), 2) for i in range(steps)], "capacity", tr.capacity)
 print("ms/iter", (time.perf_counter() - t0) * 1e3 / steps, "loss", float(loss))

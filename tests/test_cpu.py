@@ -392,6 +392,15 @@ for v in range(world):
     loss_for(v).backward()
 ok = all(torch.allclose(a, b.grad, rtol=1e-5, atol=1e-7) for a, b in zip(got, [logits, codebook]))
 assert bucket.nbytes == (50 * 64 + 64 * 16) * 4
+# attached mode (what FeatureTrainer uses): .grad tensors are views of the bucket, sync() is the all-reduce alone
+logits.grad = None; codebook.grad = None
+b2 = lsdist.GradBucket([logits, codebook]); b2.attach()
+loss_for(view).backward()
+assert logits.grad.data_ptr() == b2.flat.data_ptr()
+b2.sync()
+ok = ok and all(torch.allclose(a, b.grad, rtol=1e-5, atol=1e-7) for a, b in zip(got, [logits, codebook]))
+b2.zero()
+ok = ok and float(logits.grad.abs().sum()) == 0.0
 dist.barrier()
 dist.destroy_process_group()
 sys.exit(0 if ok else 3)
