@@ -460,7 +460,10 @@ def run_gpu(args, wl):
                     "note": "camera from pinned host memory; RGB render + status read back to the host (double-buffered: frame k's D2H under frame k+1's kernels; host wall clock until the last frame is on the host); the 512-d map stays on the device as in the reference's API"},
             "gpu_launches": kernels_per_frame(W, H, fused) * args.steps,
             "roofline": {"kernel": dom_name, "bound": "hbm", "achieved": achieved,
-                         "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                         "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full of this command at the
+                         # 1080p workload (profiles/r01c_ncu_fused.txt); other workloads: not captured
+                         "traffic": (94.439680e6 + 12.727770e9) if (fused and args.workload == "1080p") else None,
                          "peak_source": peak_src, "algorithmic_bytes_per_launch": dom_bytes,
                          "avg_launch_ms": dom_ms},
         }
