@@ -576,6 +576,11 @@ int launch_render_decode2(const lsv2_view& v, const lsv2_geom& g, const lsv2_bin
                           const lsv2_image& img, const float* codebooks, int levels, int Lc, int D, int normalize,
                           int out_dtype, void* out, void* scratch, size_t scratch_bytes, cudaStream_t st);
 
+size_t render_decode3_scratch_bytes(int levels);
+int launch_render_decode3(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b, const lsv2_features& f,
+                          const lsv2_image& img, const float* codebooks, int levels, int Lc, int D, int normalize,
+                          int out_dtype, void* out, void* scratch, size_t scratch_bytes, cudaStream_t st);
+
 static size_t render_decode1_scratch_bytes(int levels)
 {
     return (size_t)(levels > 0 ? levels : 1) * FD_D * 128 + 512;
@@ -598,6 +603,10 @@ int launch_render_decode(const lsv2_view& v, const lsv2_geom& g, const lsv2_binn
                          const lsv2_image& img, const float* codebooks, int levels, int Lc, int D, int normalize,
                          int out_dtype, void* out, void* scratch, size_t scratch_bytes, cudaStream_t st)
 {
+    const char* e3 = getenv("LSV2_FD_V3");
+    if (e3 && atoi(e3) != 0)
+        return launch_render_decode3(v, g, b, f, img, codebooks, levels, Lc, D, normalize, out_dtype, out, scratch,
+                                     scratch_bytes, st);
     const char* e = getenv("LSV2_FD_V2");
     if (e && atoi(e) != 0)
         return launch_render_decode2(v, g, b, f, img, codebooks, levels, Lc, D, normalize, out_dtype, out, scratch,

@@ -18,14 +18,17 @@ from tests import helpers as hp
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(params=["gen1", "gen2"], autouse=True)
+@pytest.fixture(params=["gen1", "gen2", "gen3"], autouse=True)
 def fused_generation(request, monkeypatch):
     """Every test in this file runs against both fused kernels (the launcher reads LSV2_FD_V2 per call):
-    render_decode.cu (default) and render_decode2.cu (blend / decode overlapped, Gram-matrix norm)."""
+    render_decode.cu, render_decode2.cu (blend / decode overlapped in one CTA, Gram-matrix norm) and
+    render_decode3.cu (half a tile per CTA, two CTAs per SM)."""
+    monkeypatch.delenv("LSV2_FD_V2", raising=False)
+    monkeypatch.delenv("LSV2_FD_V3", raising=False)
     if request.param == "gen2":
         monkeypatch.setenv("LSV2_FD_V2", "1")
-    else:
-        monkeypatch.delenv("LSV2_FD_V2", raising=False)
+    elif request.param == "gen3":
+        monkeypatch.setenv("LSV2_FD_V3", "1")
     return request.param
 
 BG = (0.1, 0.2, 0.3)
