@@ -88,8 +88,12 @@ __device__ __forceinline__ void named_bar_sync(int id, int count)
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
 }
 
-// see render_forward.cu: rows of the tile the alpha cut-off ellipse can reach -> mask over the 8 two-row strips
-__device__ __forceinline__ uint32_t fd_strip_mask(float y_rel, float ax, float b, float az, float thr)
+// see render_forward.cu: rows of the tile the alpha cut-off ellipse can reach -> mask over the 8 two-row strips.
+// x_rel: the splat's x relative to the tile's first column; when the ellipse's bounding box misses the tile's 16
+// columns altogether no pixel of the tile can reach alpha >= 1/255 and the mask is empty (conservative: the same
+// 1.0001 / +0.02 margins as the row test, so no blend decision changes).
+__device__ __forceinline__ uint32_t fd_strip_mask(float y_rel, float ax, float b, float az, float thr,
+                                                  float x_rel = 7.5f)
 {
     if (!(thr < 0.0f)) return 0u;
     const float qa = -2.0f * ax, qc = -2.0f * az;
@@ -97,6 +101,10 @@ __device__ __forceinline__ uint32_t fd_strip_mask(float y_rel, float ax, float b
     float dy = 1e30f;
     if (det > 0.0f && qa > 0.0f) dy = sqrtf((-2.0f * thr) * (qa / det)) * 1.0001f + 0.02f;
     if (!(dy == dy)) dy = 1e30f;
+    if (det > 0.0f && qc > 0.0f) {
+        const float dx = sqrtf((-2.0f * thr) * (qc / det)) * 1.0001f + 0.02f;
+        if (dx == dx && (x_rel + dx < 0.0f || x_rel - dx > 15.0f)) return 0u;
+    }
     const float lo_f = ceilf(y_rel - dy), hi_f = floorf(y_rel + dy);
     if (!(hi_f >= 0.0f) || !(lo_f <= 15.0f)) {
         if (lo_f != lo_f || hi_f != hi_f) return 0xFFu;

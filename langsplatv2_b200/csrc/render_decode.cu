@@ -159,7 +159,7 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
             if (!exit_now) range = a.ranges[tile];
             const uint32_t n_inst = range.y - range.x;
             const uint32_t n_batches = (n_inst + FD_BATCH - 1) / FD_BATCH;
-            const float y0 = (float)((tile / a.gx) * TILE);
+            const float y0 = (float)((tile / a.gx) * TILE), x0 = (float)((tile % a.gx) * TILE);
             auto load_id = [&](uint32_t b) -> uint32_t {
                 const uint32_t i = b * FD_BATCH + pt;
                 return i < n_inst ? __ldg(a.point_list + range.x + i) : 0xFFFFFFFFu;
@@ -193,7 +193,7 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
                     Hd.g0[pt] = cur.r0;
                     Hd.g1[pt] = cur.r1;
                     Hd.g2[pt] = make_float2(cur.r2.x, cur.r2.y);
-                    m8 = fd_strip_mask(cur.r0.y - y0, cur.r0.z, cur.r0.w, cur.r1.x, cur.r1.y);
+                    m8 = fd_strip_mask(cur.r0.y - y0, cur.r0.z, cur.r0.w, cur.r1.x, cur.r1.y, cur.r0.x - x0);
                     const uint32_t col = (uint32_t)(pt & 7) * 2u, chunk = (uint32_t)pt >> 3;
                     if (cur.cnt != FD_ROW_DENSE) {
                         bool ascending = true;              // distinct channels: plain stores, no read-modify-write
@@ -524,21 +524,34 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
                             ++f_n;
                             tc_fence_after();
                             const uint32_t col0 = (uint32_t)(half * 256 + q * FD_CHUNK_N);
-                            auto consume = [&](const uint32_t (&r)[32], int cc) {
+                            auto consume = [&](uint32_t (&r)[32], int cc) {
                                 if (!store) {
 #pragma unroll
                                     for (int i = 0; i < 32; ++i) ss = fmaf(__uint_as_float(r[i]), __uint_as_float(r[i]), ss);
                                 } else if (inside && !(a.dbg & 1)) {
+                                    // scale in place, then 32 stores through four independent running addresses
+#pragma unroll
+                                    for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * inv);
+                                    const uint64_t esz = OUT_BF16 ? 2u : 4u;
+                                    const uint64_t stride = (uint64_t)HW * esz;
                                     const size_t ch0 = (size_t)l * FD_D + c * FD_CHUNK_N + cc * 32;
-                                    if (OUT_BF16) {
-                                        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(a.out) + ch0 * HW + pix;
+                                    uint64_t p[4];
+                                    p[0] = (uint64_t)(uintptr_t)a.out + (ch0 * HW + pix) * esz;
+                                    p[1] = p[0] + stride; p[2] = p[1] + stride; p[3] = p[2] + stride;
+                                    const uint64_t s4 = 4 * stride;
 #pragma unroll
-                                        for (int i = 0; i < 32; ++i)
-                                            o[(size_t)i * HW] = __float2bfloat16_rn(__uint_as_float(r[i]) * inv);
-                                    } else {
-                                        float* o = reinterpret_cast<float*>(a.out) + ch0 * HW + pix;
+                                    for (int i = 0; i < 32; i += 4) {
 #pragma unroll
-                                        for (int i = 0; i < 32; ++i, o += HW) st_stream_f32(o, __uint_as_float(r[i]) * inv);
+                                        for (int u = 0; u < 4; ++u) {
+                                            if (OUT_BF16) {
+                                                const unsigned short v =
+                                                    __bfloat16_as_ushort(__float2bfloat16_rn(__uint_as_float(r[i + u])));
+                                                asm volatile("st.global.cs.u16 [%0], %1;" ::"l"(p[u]), "h"(v) : "memory");
+                                            } else {
+                                                asm volatile("st.global.cs.b32 [%0], %1;" ::"l"(p[u]), "r"(r[i + u]) : "memory");
+                                            }
+                                            p[u] += s4;
+                                        }
                                     }
                                 }
                             };

@@ -165,7 +165,7 @@ __global__ void __launch_bounds__(F2_THREADS, 1) k_render_decode2(FdArgs a)
             if (!exit_now) range = a.ranges[tile];
             const uint32_t n_inst = range.y - range.x;
             const uint32_t n_batches = (n_inst + FD_BATCH - 1) / FD_BATCH;
-            const float y0 = (float)((tile / a.gx) * TILE);
+            const float y0 = (float)((tile / a.gx) * TILE), x0 = (float)((tile % a.gx) * TILE);
             auto load_id = [&](uint32_t b) -> uint32_t {
                 const uint32_t i = b * FD_BATCH + pt;
                 return i < n_inst ? __ldg(a.point_list + range.x + i) : 0xFFFFFFFFu;
@@ -199,7 +199,7 @@ __global__ void __launch_bounds__(F2_THREADS, 1) k_render_decode2(FdArgs a)
                     Hd.g0[pt] = cur.r0;
                     Hd.g1[pt] = cur.r1;
                     Hd.g2[pt] = make_float2(cur.r2.x, cur.r2.y);
-                    m8 = fd_strip_mask(cur.r0.y - y0, cur.r0.z, cur.r0.w, cur.r1.x, cur.r1.y);
+                    m8 = fd_strip_mask(cur.r0.y - y0, cur.r0.z, cur.r0.w, cur.r1.x, cur.r1.y, cur.r0.x - x0);
                     const uint32_t col = (uint32_t)(pt & 7) * 2u, chunk = (uint32_t)pt >> 3;
                     if (cur.bad) a.status[LSV2_STATUS_BAD_INDEX] = 1u;
                     if (cur.cnt != FD_ROW_DENSE) {
