@@ -251,6 +251,19 @@ int lsv2_cos_loss_forward(int32_t D, int64_t HW, const float* F, const float* gt
 int lsv2_cos_loss_backward(int32_t D, int64_t HW, const float* F, const float* gt, const float* alpha_beta,
                            const float* grad_out, float* dF, void* stream);
 
+/* The same loss straight from the weight map, the feature map never materialised (decode + normalise + cos loss of
+ * train.py:156-164 in one step; scene/gaussian_model.py:533-543 for one layer).  With F = C^T w:
+ *   h = C gt  f32[Lc][HW]  (lsv2_decode_backward(..., dF = gt, dW = h)),  G = C C^T f32[Lc][Lc],  g2 = |gt_p|^2 f32[HW]
+ *   (lsv2_colsumsq).  forward: u = G w f32[Lc][HW], alpha_beta f32[2][HW], partial as lsv2_cos_loss_forward.
+ *   backward: dw = dL/d wmap, aw = (go alpha) w, bw = (go beta) w, all f32[Lc][HW];
+ *   dL/dC = aw gt^T + (bw w^T) C  (two calls of lsv2_decode_backward's dC form).  Lc must be 64. */
+int lsv2_gram_loss_forward(int32_t Lc, int64_t HW, const float* wmap, const float* h, const float* g2,
+                           const float* mask, const float* G, int32_t normalize, float* u, float* alpha_beta,
+                           float* partial, void* stream);
+int lsv2_gram_loss_backward(int32_t Lc, int64_t HW, const float* wmap, const float* h, const float* u,
+                            const float* alpha_beta, const float* grad_out, float* dw, float* aw, float* bw, void* stream);
+int lsv2_colsumsq(int32_t D, int64_t HW, const float* x, float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -26,6 +26,12 @@ int launch_cos_loss_forward(int D, int64_t HW, const float* F, const float* gt, 
                             float* alpha_beta, float* partial, cudaStream_t st);
 int launch_cos_loss_backward(int D, int64_t HW, const float* F, const float* gt, const float* alpha_beta,
                              const float* grad_out, float* dF, cudaStream_t st);
+int launch_gram_loss_forward(int Lc, int64_t HW, const float* wmap, const float* h, const float* g2, const float* mask,
+                             const float* G, int normalize, float* u, float* alpha_beta, float* partial, cudaStream_t st);
+int launch_gram_loss_backward(int Lc, int64_t HW, const float* wmap, const float* h, const float* u,
+                              const float* alpha_beta, const float* grad_out, float* dw, float* aw, float* bw,
+                              cudaStream_t st);
+int launch_colsumsq(int D, int64_t HW, const float* x, float* out, cudaStream_t st);
 int launch_topk_soft_code_bwd(int64_t N, int C, const float* logits, const float* dense, const float* d_dense,
                               float* d_logits, cudaStream_t st);
 int launch_topk_soft_code(int64_t N, int C, int k, const float* logits, float* dense, float* weights,
@@ -230,6 +236,27 @@ int lsv2_cos_loss_backward(int32_t D, int64_t HW, const float* F, const float* g
 {
     if (D <= 0 || HW < 0 || (HW > 0 && (!F || !gt || !alpha_beta || !dF))) return LSV2_EINVAL;
     return launch_cos_loss_backward(D, HW, F, gt, alpha_beta, grad_out, dF, (cudaStream_t)stream);
+}
+
+int lsv2_gram_loss_forward(int32_t Lc, int64_t HW, const float* wmap, const float* h, const float* g2,
+                           const float* mask, const float* G, int32_t normalize, float* u, float* alpha_beta,
+                           float* partial, void* stream)
+{
+    if (HW < 0 || (HW > 0 && (!wmap || !h || !g2 || !G || !u || !alpha_beta || !partial))) return LSV2_EINVAL;
+    return launch_gram_loss_forward(Lc, HW, wmap, h, g2, mask, G, normalize, u, alpha_beta, partial, (cudaStream_t)stream);
+}
+
+int lsv2_gram_loss_backward(int32_t Lc, int64_t HW, const float* wmap, const float* h, const float* u,
+                            const float* alpha_beta, const float* grad_out, float* dw, float* aw, float* bw, void* stream)
+{
+    if (HW < 0 || (HW > 0 && (!wmap || !h || !u || !alpha_beta || !dw || !aw || !bw))) return LSV2_EINVAL;
+    return launch_gram_loss_backward(Lc, HW, wmap, h, u, alpha_beta, grad_out, dw, aw, bw, (cudaStream_t)stream);
+}
+
+int lsv2_colsumsq(int32_t D, int64_t HW, const float* x, float* out, void* stream)
+{
+    if (D <= 0 || HW < 0 || (HW > 0 && (!x || !out))) return LSV2_EINVAL;
+    return launch_colsumsq(D, HW, x, out, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -97,4 +97,145 @@ int launch_cos_loss_backward(int D, int64_t HW, const float* F, const float* gt,
     return LSV2_OK;
 }
 
+// ---- the same loss without ever forming the feature map ------------------------------------
+// With F_p = C^T w_p everything the loss needs is a scalar product in code space:
+//   |F_p|^2 = w_p^T G w_p  (G = C C^T, 64 x 64),   F_p . gt_p = w_p . h_p  (h = C gt, one GEMM),   |gt_p|^2 = g2_p
+// and the gradient dL/dF_p = alpha_p gt_p + beta_p F_p pulls back to
+//   dL/dw_p = alpha_p h_p + beta_p G w_p ,      dL/dC = (alpha w) gt^T + ((beta w) w^T) C .
+// k_gram_loss_fwd: one thread per pixel, w_p in registers, G in shared memory; writes u = G w (kept for backward),
+// the two scalars and the per-block sums of cos_p.  k_gram_loss_bwd: the three [Lc][HW] products of the pull-back.
+constexpr int GL_LC = 64;
+
+__device__ __forceinline__ void cos_scalars(float m, float n2, float fg, float g2, int normalize, float& cosv,
+                                            float& alpha, float& beta)
+{
+    const float n = sqrtf(fmaxf(n2, 0.0f));
+    const float s = normalize ? 1.0f / (n + NORM_EPS) : 1.0f;
+    const float na = fabsf(m) * s * n, nb = fabsf(m) * sqrtf(g2);
+    const float ca = fmaxf(na, COS_EPS), cb = fmaxf(nb, COS_EPS);
+    const float icab = 1.0f / (ca * cb);
+    cosv = m * m * s * fg * icab;
+    const float ka = na > COS_EPS ? cosv / (ca * na) : 0.0f;
+    const float qF = m * fg * icab - ka * m * s * n2;
+    alpha = m * m * s * icab;
+    beta = -ka * m * m * s * s;
+    if (normalize && n > 0.0f) beta -= m * qF * s * s / n;
+}
+
+__global__ void __launch_bounds__(LOSS_THREADS)
+k_gram_loss_fwd(int64_t HW, const float* __restrict__ wmap, const float* __restrict__ h, const float* __restrict__ g2,
+                const float* __restrict__ mask, const float* __restrict__ G, int normalize, float* __restrict__ u,
+                float* __restrict__ alpha_beta, float* __restrict__ partial)
+{
+    __shared__ __align__(16) float s_G[GL_LC][GL_LC];
+    __shared__ float s_red[LOSS_THREADS / 32];
+    for (int e = threadIdx.x; e < GL_LC * GL_LC; e += LOSS_THREADS) s_G[e / GL_LC][e % GL_LC] = G[e];
+    __syncthreads();
+    const int64_t p = (int64_t)blockIdx.x * LOSS_THREADS + threadIdx.x;
+    float cosv = 0.0f;
+    if (p < HW) {
+        float w[GL_LC];
+        float fg = 0.0f;
+#pragma unroll
+        for (int k = 0; k < GL_LC; ++k) {
+            w[k] = __ldg(wmap + (size_t)k * HW + p);
+            fg = fmaf(w[k], __ldg(h + (size_t)k * HW + p), fg);
+        }
+        float n2 = 0.0f;
+#pragma unroll
+        for (int k = 0; k < GL_LC; ++k) {
+            float acc = 0.0f;
+#pragma unroll
+            for (int j4 = 0; j4 < GL_LC / 4; ++j4) {
+                const float4 g4 = *reinterpret_cast<const float4*>(&s_G[k][4 * j4]);
+                acc = fmaf(g4.x, w[4 * j4], acc);
+                acc = fmaf(g4.y, w[4 * j4 + 1], acc);
+                acc = fmaf(g4.z, w[4 * j4 + 2], acc);
+                acc = fmaf(g4.w, w[4 * j4 + 3], acc);
+            }
+            u[(size_t)k * HW + p] = acc;
+            n2 = fmaf(w[k], acc, n2);
+        }
+        float alpha, beta;
+        cos_scalars(mask ? mask[p] : 1.0f, n2, fg, g2[p], normalize, cosv, alpha, beta);
+        alpha_beta[p] = alpha;
+        alpha_beta[HW + p] = beta;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) cosv += __shfl_xor_sync(0xffffffffu, cosv, o);
+    if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = cosv;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.0f;
+        for (int i = 0; i < LOSS_THREADS / 32; ++i) t += s_red[i];
+        partial[blockIdx.x] = t;
+    }
+}
+
+__global__ void __launch_bounds__(LOSS_THREADS)
+k_gram_loss_bwd(int64_t HW, const float* __restrict__ wmap, const float* __restrict__ h, const float* __restrict__ u,
+                const float* __restrict__ alpha_beta, const float* __restrict__ grad_out, float* __restrict__ dw,
+                float* __restrict__ aw, float* __restrict__ bw)
+{
+    const int64_t p = (int64_t)blockIdx.x * LOSS_THREADS + threadIdx.x;
+    if (p >= HW) return;
+    const float go = -(grad_out ? grad_out[0] : 1.0f) / (float)HW;
+    const float alpha = alpha_beta[p] * go, beta = alpha_beta[HW + p] * go;
+    const int k0 = blockIdx.y * (GL_LC / gridDim.y), k1 = k0 + GL_LC / gridDim.y;
+#pragma unroll 4
+    for (int k = k0; k < k1; ++k) {
+        const size_t o = (size_t)k * HW + p;
+        const float wv = __ldg(wmap + o);
+        dw[o] = fmaf(alpha, __ldg(h + o), beta * __ldg(u + o));
+        aw[o] = alpha * wv;
+        bw[o] = beta * wv;
+    }
+}
+
+__global__ void __launch_bounds__(LOSS_THREADS)
+k_colsumsq(int D, int64_t HW, const float* __restrict__ x, float* __restrict__ out)
+{
+    const int64_t p = (int64_t)blockIdx.x * LOSS_THREADS + threadIdx.x;
+    if (p >= HW) return;
+    float s = 0.0f;
+#pragma unroll 8
+    for (int d = 0; d < D; ++d) {
+        const float v = __ldg(x + (size_t)d * HW + p);
+        s = fmaf(v, v, s);
+    }
+    out[p] = s;
+}
+
+int launch_gram_loss_forward(int Lc, int64_t HW, const float* wmap, const float* h, const float* g2, const float* mask,
+                             const float* G, int normalize, float* u, float* alpha_beta, float* partial, cudaStream_t st)
+{
+    if (Lc != GL_LC) return LSV2_EUNSUPPORTED;
+    if (HW == 0) return LSV2_OK;
+    const int64_t blocks = (HW + LOSS_THREADS - 1) / LOSS_THREADS;
+    k_gram_loss_fwd<<<(unsigned)blocks, LOSS_THREADS, 0, st>>>(HW, wmap, h, g2, mask, G, normalize, u, alpha_beta, partial);
+    LSV2_LAUNCH_CHECK("k_gram_loss_fwd");
+    return LSV2_OK;
+}
+
+int launch_gram_loss_backward(int Lc, int64_t HW, const float* wmap, const float* h, const float* u,
+                              const float* alpha_beta, const float* grad_out, float* dw, float* aw, float* bw,
+                              cudaStream_t st)
+{
+    if (Lc != GL_LC) return LSV2_EUNSUPPORTED;
+    if (HW == 0) return LSV2_OK;
+    const int64_t blocks = (HW + LOSS_THREADS - 1) / LOSS_THREADS;
+    k_gram_loss_bwd<<<dim3((unsigned)blocks, 4), LOSS_THREADS, 0, st>>>(HW, wmap, h, u, alpha_beta, grad_out, dw, aw, bw);
+    LSV2_LAUNCH_CHECK("k_gram_loss_bwd");
+    return LSV2_OK;
+}
+
+int launch_colsumsq(int D, int64_t HW, const float* x, float* out, cudaStream_t st)
+{
+    if (HW == 0) return LSV2_OK;
+    const int64_t blocks = (HW + LOSS_THREADS - 1) / LOSS_THREADS;
+    k_colsumsq<<<(unsigned)blocks, LOSS_THREADS, 0, st>>>(D, HW, x, out);
+    LSV2_LAUNCH_CHECK("k_colsumsq");
+    return LSV2_OK;
+}
+
 }  // namespace lsv2

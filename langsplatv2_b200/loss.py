@@ -49,3 +49,91 @@ def normalized_cos_loss(language_feature: torch.Tensor, gt: torch.Tensor, mask: 
     """``cos_loss(f * mask, gt * mask)`` with ``f = language_feature / (norm(dim=0) + 1e-10)`` when ``normalize``
     (train.py:157-164); language_feature, gt: [D, H, W]; mask: [1, H, W] or None."""
     return _CosLoss.apply(language_feature, gt, mask, normalize)
+
+
+def _decode_bwd(levels, Lc, D, HW, wmap, codebooks, dF, dW, dC, dev):
+    L_ = _abi.lib()
+    _abi.check(L_.lsv2_decode_backward(levels, Lc, D, HW, _abi.ptr(wmap), _abi.ptr(codebooks), dF.data_ptr(),
+                                       _abi.ptr(dW), _abi.ptr(dC), _abi.stream_ptr(dev)), "lsv2_decode_backward")
+
+
+def column_sumsq(x: torch.Tensor) -> torch.Tensor:
+    """|x_p|^2 per pixel of a [D, ...] map (one streaming kernel)."""
+    L_ = _abi.lib()
+    x = x.contiguous().float()
+    HW = x[0].numel()
+    out = torch.empty(HW, dtype=torch.float32, device=x.device)
+    _abi.check(L_.lsv2_colsumsq(int(x.shape[0]), HW, x.data_ptr(), out.data_ptr(), _abi.stream_ptr(x.device)),
+               "lsv2_colsumsq")
+    return out
+
+
+class _GramCosLoss(torch.autograd.Function):
+    """decode one codebook layer + normalise + cos loss without forming the [512, H, W] feature map
+    (csrc/loss.cu, second half): two 64x512xHW GEMMs per iteration instead of three, no F / dF tensors."""
+
+    @staticmethod
+    def forward(ctx, wmap, codebook, gt, mask, normalize, gt_sumsq):
+        L_ = _abi.lib()
+        _abi.require_cuda(wmap, "language_feature_weight_map")
+        dev = wmap.device
+        w = wmap.contiguous().float()
+        Lc, HW = int(w.shape[0]), w[0].numel()
+        Cb = codebook.contiguous().float().reshape(Lc, -1)
+        D = int(Cb.shape[1])
+        g = gt.contiguous().float()
+        if g.shape[0] != D or g[0].numel() != HW:
+            raise ValueError("gt must be [D, H, W] with the weight map's H, W")
+        m = None
+        if mask is not None:
+            m = mask.to(torch.float32).contiguous()
+            if m.numel() != HW:
+                raise ValueError("mask must be [1, H, W] (one value per pixel)")
+        g2 = gt_sumsq if gt_sumsq is not None else column_sumsq(g)
+        allow = torch.backends.cuda.matmul.allow_tf32
+        torch.backends.cuda.matmul.allow_tf32 = False
+        G = (Cb @ Cb.t()).contiguous()
+        torch.backends.cuda.matmul.allow_tf32 = allow
+        h = torch.empty_like(w)
+        _decode_bwd(1, Lc, D, HW, None, Cb, g, h, None, dev)                       # h = C gt
+        u = torch.empty_like(w)
+        ab = torch.empty((2, HW), dtype=torch.float32, device=dev)
+        partial = torch.empty(L_.lsv2_cos_loss_blocks(HW), dtype=torch.float32, device=dev)
+        _abi.check(L_.lsv2_gram_loss_forward(Lc, HW, w.data_ptr(), h.data_ptr(), g2.data_ptr(), _abi.ptr(m),
+                                             G.data_ptr(), 1 if normalize else 0, u.data_ptr(), ab.data_ptr(),
+                                             partial.data_ptr(), _abi.stream_ptr(dev)), "lsv2_gram_loss_forward")
+        ctx.save_for_backward(w, h, u, ab, g, Cb)
+        ctx.cb_shape = codebook.shape
+        return 1.0 - partial.sum() / HW
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        L_ = _abi.lib()
+        w, h, u, ab, g, Cb = ctx.saved_tensors
+        dev = w.device
+        Lc, HW, D = int(w.shape[0]), w[0].numel(), int(Cb.shape[1])
+        go = grad_out.reshape(1).contiguous().float()
+        dw, aw, bw = torch.empty_like(w), torch.empty_like(w), torch.empty_like(w)
+        _abi.check(L_.lsv2_gram_loss_backward(Lc, HW, w.data_ptr(), h.data_ptr(), u.data_ptr(), ab.data_ptr(),
+                                              go.data_ptr(), dw.data_ptr(), aw.data_ptr(), bw.data_ptr(),
+                                              _abi.stream_ptr(dev)), "lsv2_gram_loss_backward")
+        dC = None
+        if ctx.needs_input_grad[1]:
+            dC = torch.zeros_like(Cb)
+            _decode_bwd(1, Lc, D, HW, aw, None, g, None, dC, dev)                  # (alpha w) gt^T
+            M = torch.zeros((Lc, Lc), dtype=torch.float32, device=dev)
+            _decode_bwd(1, Lc, Lc, HW, bw, None, w, None, M, dev)                  # (beta w) w^T
+            allow = torch.backends.cuda.matmul.allow_tf32
+            torch.backends.cuda.matmul.allow_tf32 = False
+            dC = (dC + M @ Cb).reshape(ctx.cb_shape)
+            torch.backends.cuda.matmul.allow_tf32 = allow
+        return (dw if ctx.needs_input_grad[0] else None), dC, None, None, None, None
+
+
+def decode_cos_loss(weight_map: torch.Tensor, codebook: torch.Tensor, gt: torch.Tensor,
+                    mask: Optional[torch.Tensor] = None, normalize: bool = True,
+                    gt_sumsq: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``cos_loss(normalise(codebook^T @ weight_map) * mask, gt * mask)`` (train.py:156-164 with one codebook layer)
+    without the feature map.  weight_map [64, H, W]; codebook [64, 512] or [1, 64, 512]; gt [512, H, W];
+    ``gt_sumsq`` = ``column_sumsq(gt)`` may be passed when the same gt is reused across iterations."""
+    return _GramCosLoss.apply(weight_map, codebook, gt, mask, normalize, gt_sumsq)

@@ -23,7 +23,7 @@ import torch.nn.functional as F
 
 from . import dist as lsdist
 from .decode import decode_feature_map
-from .loss import normalized_cos_loss
+from .loss import column_sumsq, decode_cos_loss, normalized_cos_loss
 from .rasterizer import GaussianRasterizationSettings, GaussianRasterizer
 from .sparse import softmax_to_topk_soft_code
 
@@ -43,13 +43,15 @@ class FeatureTrainer:
 
     def __init__(self, scene: Dict, topk: int = 4, lr: float = 0.0025, device="cuda", normalize: bool = True,
                  use_cos: bool = True, use_l1: bool = False, layers: Optional[int] = None, fused_adam: bool = True,
-                 fused_loss: bool = True):
+                 fused_loss: bool = True, gram_loss: bool = True):
         dev = torch.device(device)
         f32 = lambda t: t.to(dev, torch.float32).contiguous()
         self.dev = dev
         self.topk = topk
         self.normalize, self.use_cos, self.use_l1 = normalize, use_cos, use_l1
         self.fused_loss = fused_loss        # cos loss (+ the normalisation) as two kernels instead of torch's ~28 passes
+        self.gram_loss = gram_loss          # ... and, for a single layer, without forming the [512, H, W] feature map
+        self._g2_cache = {}                 # |gt_p|^2 per ground-truth tensor (constant across iterations of a view)
         self.xyz, self.opacity = f32(scene["xyz"]), f32(scene["opacity"])
         self.scales, self.rotations = f32(scene["scaling"]), f32(scene["rotation"])
         self.shs = f32(scene["features"])
@@ -111,6 +113,16 @@ class FeatureTrainer:
                                 rotations=self.rotations, cov3D_precomp=None)
         self._last_state = rasterizer.last_state
         layer_idx = min(int(self.iteration / 10000 * self.layers), self.layers - 1)       # train.py:155
+        cs = self.codebook_size
+        if (self.gram_loss and self.fused_loss and layer_idx == 0 and cs == 64 and self.use_cos and not self.use_l1
+                and mask.numel() == wmap[0].numel()):
+            key = (gt.data_ptr(), tuple(gt.shape))
+            g2 = self._g2_cache.get(key)
+            if g2 is None:
+                if len(self._g2_cache) > 64:
+                    self._g2_cache.clear()
+                g2 = self._g2_cache[key] = column_sumsq(gt)
+            return decode_cos_loss(wmap[:cs], self.codebooks[0:1], gt, mask, normalize=self.normalize, gt_sumsq=g2)
         feat = self.layer_feature_map(wmap, layer_idx)
         if self.fused_loss and self.use_cos and not self.use_l1 and mask.numel() == feat[0].numel():
             return normalized_cos_loss(feat, gt, mask, normalize=self.normalize)

@@ -56,6 +56,39 @@ def test_fused_cos_loss_matches_torch_autograd(normalize):
     assert np.max(np.abs(got - want)) <= 1e-5 * np.abs(want).max() + 1e-12
 
 
+@pytest.mark.parametrize("normalize", [True, False])
+def test_gram_decode_cos_loss_matches_torch_autograd(normalize):
+    """decode + normalise + cos loss without the feature map (lsv2_gram_loss_*) vs fp64 autograd of the reference's
+    expressions (scene/gaussian_model.py:538, train.py:157-164)."""
+    from langsplatv2_b200.loss import decode_cos_loss
+    g = torch.Generator(device="cpu").manual_seed(8)
+    H, W = 29, 41
+    wmap = torch.rand((64, H, W), generator=g) * (torch.rand((64, H, W), generator=g) > 0.6)
+    wmap[:, 0, 0] = 0.0                                     # dead pixel
+    cb = torch.randn((1, 64, 512), generator=g)
+    gt = torch.randn((512, H, W), generator=g)
+    gt = gt / gt.norm(dim=0, keepdim=True)
+    mask = (torch.rand((1, H, W), generator=g) > 0.3).float()
+    w64 = wmap.double().requires_grad_(True)
+    c64 = cb.double().requires_grad_(True)
+    feat = (c64[0].T @ w64.view(64, -1)).view(512, H, W)
+    if normalize:
+        feat = feat / (feat.norm(dim=0, keepdim=True) + 1e-10)
+    ref = cos_loss(feat * mask.double(), gt.double() * mask.double())
+    ref.backward()
+    wc = wmap.cuda().requires_grad_(True)
+    cc = cb.cuda().requires_grad_(True)
+    out = decode_cos_loss(wc, cc, gt.cuda(), mask.cuda(), normalize=normalize)
+    (out * 3.0).backward()
+    assert abs(float(out.detach()) - float(ref.detach())) <= 5e-6
+    live = torch.ones((H, W), dtype=torch.bool)
+    live[0, 0] = False                                      # the dead pixel's gradient is ~1e18 on both sides
+    gw, rw = wc.grad.cpu().numpy()[:, live.numpy()] / 3.0, w64.grad.numpy()[:, live.numpy()]
+    assert np.max(np.abs(gw - rw)) <= 2e-5 * np.abs(rw).max()
+    gc, rc = cc.grad.cpu().numpy() / 3.0, c64.grad.numpy()
+    assert np.max(np.abs(gc - rc)) <= 2e-5 * np.abs(rc).max()
+
+
 def _reference_grads(scene, cam, gt, mask, topk):
     t64 = lambda a: torch.as_tensor(np.asarray(a), dtype=torch.float64)
     osc, view = hp.oracle_scene(scene), hp.oracle_view(cam)
@@ -75,13 +108,13 @@ def _reference_grads(scene, cam, gt, mask, topk):
     return float(loss), logits.grad.numpy(), cb.grad.numpy()
 
 
-@pytest.mark.parametrize("fused_loss", [True, False])
-def test_train_step_gradients_match_fp64_autograd(fused_loss):
+@pytest.mark.parametrize("fused_loss,gram_loss", [(True, True), (True, False), (False, False)])
+def test_train_step_gradients_match_fp64_autograd(fused_loss, gram_loss):
     N, W, H = 3000, 96, 64
     scene, cam = hp.make_case(N, W, H, seed=11, levels=1, scale_boost=2.5)
     gt, mask = synthetic_gt(H, W, device="cuda")
     ref_loss, ref_dl, ref_dc = _reference_grads(scene, cam, gt, mask, 4)
-    tr = FeatureTrainer(scene, topk=4, layers=1, fused_loss=fused_loss)
+    tr = FeatureTrainer(scene, topk=4, layers=1, fused_loss=fused_loss, gram_loss=gram_loss)
     loss = tr.loss(cam, gt, mask)
     loss.backward()
     assert abs(float(loss) - ref_loss) <= 1e-4
