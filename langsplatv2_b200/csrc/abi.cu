@@ -86,7 +86,8 @@ size_t lsv2_sort_scratch_bytes(uint64_t capacity, int32_t P)
 {
     const size_t a = sort_scratch_bytes(capacity);
     const size_t b = scan_scratch_bytes(P);
-    return (a > b ? a : b) + 256;
+    const size_t c = depth_order_scratch_bytes(P);
+    return (a > b ? (a > c ? a : c) : (b > c ? b : c)) + 256;
 }
 
 int lsv2_preprocess(const lsv2_view* view, const lsv2_scene* scene, const lsv2_geom* geom,
@@ -111,13 +112,19 @@ int lsv2_bin(const lsv2_view* view, int32_t P, const lsv2_geom* geom, const lsv2
         return LSV2_EINVAL;
     cudaStream_t st = (cudaStream_t)stream;
     const int tb = tile_bits_for(*view);
-    const int npass = sort_num_passes(DEPTH_KEY_BITS, tb);
+    // Gaussians in depth order first (P pairs), then the instances on the tile word alone (R pairs): the same
+    // list as one stable sort on (tile | depth), see radix_sort.cu
+    const uint32_t *order = nullptr, *offsets = geom->offsets;
+    int rc = launch_depth_order(P, *geom, DEPTH_KEY_BITS, binning->scratch, binning->scratch_bytes, &order, &offsets,
+                                st);
+    if (rc) return rc;
+    const int npass = sort_num_passes(0, tb);
     // emit the unsorted pairs into the buffer from which an npass ping-pong ends in (keys, point_list)
     lsv2_binning emit = *binning;
     if (!(npass & 1)) { emit.keys_alt = binning->keys; emit.vals_alt = binning->point_list; }
-    int rc = launch_duplicate(*view, P, *geom, emit, st);
+    rc = launch_duplicate(*view, P, *geom, emit, order, offsets, st);
     if (rc) return rc;
-    rc = launch_sort(*binning, DEPTH_KEY_BITS, tb, binning->scratch, binning->scratch_bytes, st);
+    rc = launch_sort(*binning, 0, tb, binning->scratch, binning->scratch_bytes, st);
     if (rc) return rc;
     return launch_ranges(*view, *binning, st);
 }

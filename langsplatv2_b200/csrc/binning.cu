@@ -1,43 +1,69 @@
 // binning.cu -- K3 duplicateWithKeys and K5 identifyTileRanges.
 // key = (tile_id << 32) | float_bits(depth); value = Gaussian id; emission order inside one
-// Gaussian is y-major over its tile rectangle.  The instance count lives on the device
+// Gaussian is y-major over its tile rectangle; the Gaussians emit in depth order (radix_sort.cu,
+// launch_depth_order) so that the instance sort only has the tile word left to do.  The instance count lives on the device
 // (status[NUM_RENDERED]); every kernel clamps to `capacity`.
 #include "common.cuh"
 
 namespace lsv2 {
 
+// Slot i of the emission order is Gaussian order[i] (its depth rank; order == nullptr: i itself) and owns the
+// instance range [offsets[i-1], offsets[i]).  A warp emits the ranges of its 32 slots one after the other with the
+// lanes striding over the instances, so the key/value stores are contiguous runs.
 __global__ void __launch_bounds__(256)
 k_duplicate(int P, int gx, int gy, const int32_t* __restrict__ radii, const float2* __restrict__ xy,
-            const float* __restrict__ depth, const uint32_t* __restrict__ offsets, uint64_t capacity,
+            const float* __restrict__ depth, const uint32_t* __restrict__ order,
+            const uint32_t* __restrict__ offsets, uint64_t capacity,
             uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t* __restrict__ status)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= P) return;
-    const int r = radii[i];
-    if (r <= 0) return;
-    uint64_t off = (i == 0) ? 0u : offsets[i - 1];
-    const uint32_t end = offsets[i];
-    if ((uint64_t)end > capacity) status[LSV2_STATUS_OVERFLOW] = 1u;
-    const float2 p = xy[i];
-    int minx, miny, maxx, maxy;
-    tile_rect(p.x, p.y, (float)r, gx, gy, minx, miny, maxx, maxy);
-    const uint64_t dbits = (uint64_t)__float_as_uint(depth[i]);
-    for (int y = miny; y < maxy; ++y)
-        for (int x = minx; x < maxx; ++x) {
-            if (off < capacity) {
-                keys[off] = ((uint64_t)(uint32_t)(y * gx + x) << 32) | dbits;
-                vals[off] = (uint32_t)i;
-            }
-            ++off;
+    const int lane = threadIdx.x & 31;
+    uint32_t gid = 0, off = 0, cnt = 0, dbits = 0;
+    int minx = 0, miny = 0, w = 1;
+    if (i < P) {
+        gid = order ? order[i] : (uint32_t)i;
+        const int r = radii[gid];
+        if (r > 0) {
+            off = (i == 0) ? 0u : offsets[i - 1];
+            const uint32_t end = offsets[i];
+            if ((uint64_t)end > capacity) status[LSV2_STATUS_OVERFLOW] = 1u;
+            const float2 p = xy[gid];
+            int maxx, maxy;
+            tile_rect(p.x, p.y, (float)r, gx, gy, minx, miny, maxx, maxy);
+            w = max(maxx - minx, 1);
+            cnt = end - off;                      // == (maxx - minx) * (maxy - miny) = tiles_touched
+            dbits = __float_as_uint(depth[gid]);
         }
+    }
+    uint32_t todo = __ballot_sync(0xffffffffu, cnt > 0);
+    while (todo) {
+        const int src = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const uint32_t c = __shfl_sync(0xffffffffu, cnt, src);
+        const uint32_t o = __shfl_sync(0xffffffffu, off, src);
+        const uint32_t g = __shfl_sync(0xffffffffu, gid, src);
+        const uint32_t db = __shfl_sync(0xffffffffu, dbits, src);
+        const int x0 = __shfl_sync(0xffffffffu, minx, src);
+        const int y0 = __shfl_sync(0xffffffffu, miny, src);
+        const int ww = __shfl_sync(0xffffffffu, w, src);
+        for (uint32_t k = lane; k < c; k += 32) {
+            const uint64_t dst = (uint64_t)o + k;
+            if (dst < capacity) {
+                const int y = y0 + (int)k / ww, x = x0 + (int)k % ww;      // y-major over the rectangle
+                keys[dst] = ((uint64_t)(uint32_t)(y * gx + x) << 32) | db;
+                vals[dst] = g;
+            }
+        }
+    }
 }
 
-int launch_duplicate(const lsv2_view& v, int P, const lsv2_geom& g, const lsv2_binning& b, cudaStream_t st)
+int launch_duplicate(const lsv2_view& v, int P, const lsv2_geom& g, const lsv2_binning& b, const uint32_t* order,
+                     const uint32_t* offsets, cudaStream_t st)
 {
     if (P <= 0) return LSV2_OK;
     const int gx = (v.width + TILE - 1) / TILE, gy = (v.height + TILE - 1) / TILE;
     k_duplicate<<<ceil_div(P, 256), 256, 0, st>>>(P, gx, gy, g.radii, reinterpret_cast<const float2*>(g.xy),
-                                                  g.depth, g.offsets, b.capacity, b.keys_alt, b.vals_alt,
+                                                  g.depth, order, offsets, b.capacity, b.keys_alt, b.vals_alt,
                                                   b.status);
     LSV2_LAUNCH_CHECK("k_duplicate");
     return LSV2_OK;

@@ -139,7 +139,11 @@ int launch_preprocess(const lsv2_view& v, const lsv2_scene& s, const lsv2_geom& 
 int launch_scan(int P, const uint32_t* in, uint32_t* out_inclusive, uint32_t* total_out,
                 void* scratch, size_t scratch_bytes, cudaStream_t st);
 size_t scan_scratch_bytes(int P);
-int launch_duplicate(const lsv2_view& v, int P, const lsv2_geom& g, const lsv2_binning& b, cudaStream_t st);
+int launch_duplicate(const lsv2_view& v, int P, const lsv2_geom& g, const lsv2_binning& b, const uint32_t* order,
+                     const uint32_t* offsets, cudaStream_t st);
+size_t depth_order_scratch_bytes(int P);
+int launch_depth_order(int P, const lsv2_geom& g, int depth_bits, void* scratch, size_t scratch_bytes,
+                       const uint32_t** order, const uint32_t** offsets, cudaStream_t st);
 int launch_ranges(const lsv2_view& v, const lsv2_binning& b, cudaStream_t st);
 size_t sort_scratch_bytes(uint64_t capacity);
 // sorts (keys_alt, vals_alt)[0..*n) on key bits selected by (lo_bits of the low word, hi_bits of

@@ -62,18 +62,20 @@ size_t sort_scratch_bytes(uint64_t capacity)
     return rs_header_bytes() + (size_t)RS_MAX_PASSES * rs_tiles(capacity) * RS_RADIX * sizeof(uint32_t);
 }
 
-__device__ __forceinline__ uint64_t clamp_count(const uint32_t* status, uint64_t capacity)
+// `count` points at the device word that holds the number of pairs (status[NUM_RENDERED] for the
+// instance list, a scratch word for the per-Gaussian depth sort)
+__device__ __forceinline__ uint64_t clamp_count(const uint32_t* count, uint64_t capacity)
 {
-    return min((uint64_t)status[LSV2_STATUS_NUM_RENDERED], capacity);
+    return min((uint64_t)count[0], capacity);
 }
 
 // ---- all-pass digit histogram ------------------------------------------------------------
 __global__ void __launch_bounds__(RS_THREADS)
-k_rs_histogram(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ status, uint64_t capacity,
+k_rs_histogram(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ count, uint64_t capacity,
                SortPlan plan, uint32_t* __restrict__ g_hist)
 {
     __shared__ uint32_t s_hist[RS_MAX_PASSES * RS_RADIX];
-    const uint64_t n = clamp_count(status, capacity);
+    const uint64_t n = clamp_count(count, capacity);
     for (int i = threadIdx.x; i < plan.npass * RS_RADIX; i += RS_THREADS) s_hist[i] = 0;
     __syncthreads();
     const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
@@ -98,7 +100,7 @@ k_rs_histogram(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ s
 __global__ void __launch_bounds__(RS_THREADS)
 k_rs_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
               uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
-              const uint32_t* __restrict__ status, uint64_t capacity, int shift, int bits,
+              const uint32_t* __restrict__ n_ptr, uint64_t capacity, int shift, int bits,
               const uint32_t* __restrict__ g_hist /*[256] of this pass*/, uint32_t* counter,
               volatile uint32_t* lookback /*[tiles][256] of this pass*/)
 {
@@ -110,7 +112,7 @@ k_rs_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__
     __shared__ uint32_t s_tile;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint64_t n = clamp_count(status, capacity);
+    const uint64_t n = clamp_count(n_ptr, capacity);
     if (tid == 0) s_tile = atomicAdd(counter, 1u);
 #pragma unroll
     for (int w = 0; w < RS_WARPS; ++w) s_hist[w][tid] = 0;
@@ -250,13 +252,14 @@ k_rs_onesweep(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__
     }
 }
 
-int launch_sort(const lsv2_binning& b, int depth_bits, int tile_bits, void* scratch, size_t scratch_bytes,
-                cudaStream_t st)
+// Sorts `count[0]` (<= capacity) pairs.  The input lives in (k_a, v_a) when the plan has an even number of
+// passes and in (k_b, v_b) when odd, so the result always ends in (k_a, v_a).
+static int sort_pairs(uint64_t* k_a, uint32_t* v_a, uint64_t* k_b, uint32_t* v_b, const uint32_t* count,
+                      uint64_t capacity, const SortPlan& plan, void* scratch, size_t scratch_bytes, cudaStream_t st)
 {
-    if (b.capacity == 0) return LSV2_OK;
-    if (b.capacity >= (1ull << 30)) return LSV2_EUNSUPPORTED;
-    const SortPlan plan = make_plan(depth_bits, tile_bits);
-    const size_t tiles = rs_tiles(b.capacity);
+    if (capacity == 0 || plan.npass == 0) return LSV2_OK;
+    if (capacity >= (1ull << 30)) return LSV2_EUNSUPPORTED;
+    const size_t tiles = rs_tiles(capacity);
     const size_t need = rs_header_bytes() + (size_t)plan.npass * tiles * RS_RADIX * sizeof(uint32_t);
     if (scratch_bytes < need) return LSV2_ENOSPC;
     LSV2_CUDA_TRY(cudaMemsetAsync(scratch, 0, need, st));
@@ -264,20 +267,18 @@ int launch_sort(const lsv2_binning& b, int depth_bits, int tile_bits, void* scra
     uint32_t* counters = g_hist + RS_MAX_PASSES * RS_RADIX;
     uint32_t* lookback = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(scratch) + rs_header_bytes());
 
-    // the unsorted pairs were emitted into whichever buffer makes the last pass land in
-    // (keys, point_list)
     const bool odd = plan.npass & 1;
-    uint64_t* k_src = odd ? b.keys_alt : b.keys;
-    uint32_t* v_src = odd ? b.vals_alt : b.point_list;
-    uint64_t* k_dst = odd ? b.keys : b.keys_alt;
-    uint32_t* v_dst = odd ? b.point_list : b.vals_alt;
+    uint64_t* k_src = odd ? k_b : k_a;
+    uint32_t* v_src = odd ? v_b : v_a;
+    uint64_t* k_dst = odd ? k_a : k_b;
+    uint32_t* v_dst = odd ? v_a : v_b;
 
     const int hist_grid = (int)min((size_t)NUM_SMS * 8, tiles * (RS_TILE / RS_THREADS));
-    k_rs_histogram<<<hist_grid, RS_THREADS, 0, st>>>(k_src, b.status, b.capacity, plan, g_hist);
+    k_rs_histogram<<<hist_grid, RS_THREADS, 0, st>>>(k_src, count, capacity, plan, g_hist);
     LSV2_LAUNCH_CHECK("k_rs_histogram");
     for (int p = 0; p < plan.npass; ++p) {
         k_rs_onesweep<<<(unsigned)tiles, RS_THREADS, 0, st>>>(
-            k_src, v_src, k_dst, v_dst, b.status, b.capacity, plan.shift[p], plan.bits[p],
+            k_src, v_src, k_dst, v_dst, count, capacity, plan.shift[p], plan.bits[p],
             g_hist + p * RS_RADIX, counters + p, lookback + (size_t)p * tiles * RS_RADIX);
         LSV2_LAUNCH_CHECK("k_rs_onesweep");
         uint64_t* tk = k_src; k_src = k_dst; k_dst = tk;
@@ -286,8 +287,83 @@ int launch_sort(const lsv2_binning& b, int depth_bits, int tile_bits, void* scra
     return LSV2_OK;
 }
 
+// The unsorted pairs were emitted into whichever buffer makes the last pass land in (keys, point_list).
+int launch_sort(const lsv2_binning& b, int depth_bits, int tile_bits, void* scratch, size_t scratch_bytes,
+                cudaStream_t st)
+{
+    return sort_pairs(b.keys, b.point_list, b.keys_alt, b.vals_alt, b.status + LSV2_STATUS_NUM_RENDERED, b.capacity,
+                      make_plan(depth_bits, tile_bits), scratch, scratch_bytes, st);
+}
+
 // number of passes for a (depth_bits, tile_bits) key -- lsv2_bin uses it to pick the buffer
 // the unsorted pairs are emitted into.
 int sort_num_passes(int depth_bits, int tile_bits) { return make_plan(depth_bits, tile_bits).npass; }
+
+// ---- depth order of the Gaussians ----------------------------------------------------------
+// A stable sort of the instance list on (tile | depth) equals: stable-sort the P Gaussians on depth, emit their
+// instances in that order, stable-sort the instances on the tile word alone.  The first sort moves P pairs instead
+// of R (R/P ~ 12 at the metric's size), which takes the 31 depth bits (4 of the 6 passes) off the instance list.
+// Equal (tile, depth) keys keep Gaussian-index order in both formulations.
+__global__ void __launch_bounds__(256)
+k_depth_keys(int P, const int32_t* __restrict__ radii, const float* __restrict__ depth, uint64_t* __restrict__ gk,
+             uint32_t* __restrict__ gv, uint32_t* __restrict__ count)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) count[0] = (uint32_t)P;
+    if (i >= P) return;
+    gk[i] = radii[i] > 0 ? (uint64_t)__float_as_uint(depth[i]) : 0ull;    // culled Gaussians emit nothing: any slot
+    gv[i] = (uint32_t)i;
+}
+
+__global__ void __launch_bounds__(256)
+k_gather_touched(int P, const uint32_t* __restrict__ order, const int32_t* __restrict__ radii,
+                 const uint32_t* __restrict__ tiles_touched, uint32_t* __restrict__ out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const uint32_t g = order[i];
+    out[i] = radii[g] > 0 ? tiles_touched[g] : 0u;
+}
+
+static size_t al256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+size_t depth_order_scratch_bytes(int P)
+{
+    if (P <= 0) return 0;
+    const size_t p = (size_t)P;
+    return al256(sort_scratch_bytes(p)) + 2 * al256(p * 8) + 4 * al256(p * 4) + al256(scan_scratch_bytes(P)) + 256;
+}
+
+int launch_depth_order(int P, const lsv2_geom& g, int depth_bits, void* scratch, size_t scratch_bytes,
+                       const uint32_t** order, const uint32_t** offsets, cudaStream_t st)
+{
+    if (P <= 0) return LSV2_OK;
+    if (scratch_bytes < depth_order_scratch_bytes(P)) return LSV2_ENOSPC;
+    const size_t p = (size_t)P;
+    char* c = reinterpret_cast<char*>(scratch);
+    void* sort_scr = c;                                   c += al256(sort_scratch_bytes(p));
+    uint64_t* gk_a = reinterpret_cast<uint64_t*>(c);      c += al256(p * 8);
+    uint64_t* gk_b = reinterpret_cast<uint64_t*>(c);      c += al256(p * 8);
+    uint32_t* gv_a = reinterpret_cast<uint32_t*>(c);      c += al256(p * 4);
+    uint32_t* gv_b = reinterpret_cast<uint32_t*>(c);      c += al256(p * 4);
+    uint32_t* touched = reinterpret_cast<uint32_t*>(c);   c += al256(p * 4);
+    uint32_t* offs = reinterpret_cast<uint32_t*>(c);      c += al256(p * 4);
+    void* scan_scr = c;                                   c += al256(scan_scratch_bytes(P));
+    uint32_t* count = reinterpret_cast<uint32_t*>(c);     // [0] = P, [1] = total (unused)
+
+    const SortPlan plan = make_plan(depth_bits, 0);
+    const bool odd = plan.npass & 1;
+    k_depth_keys<<<ceil_div(P, 256), 256, 0, st>>>(P, g.radii, g.depth, odd ? gk_b : gk_a, odd ? gv_b : gv_a, count);
+    LSV2_LAUNCH_CHECK("k_depth_keys");
+    int rc = sort_pairs(gk_a, gv_a, gk_b, gv_b, count, p, plan, sort_scr, al256(sort_scratch_bytes(p)), st);
+    if (rc) return rc;
+    k_gather_touched<<<ceil_div(P, 256), 256, 0, st>>>(P, gv_a, g.radii, g.tiles_touched, touched);
+    LSV2_LAUNCH_CHECK("k_gather_touched");
+    rc = launch_scan(P, touched, offs, count + 1, scan_scr, al256(scan_scratch_bytes(P)), st);
+    if (rc) return rc;
+    *order = gv_a;
+    *offsets = offs;
+    return LSV2_OK;
+}
 
 }  // namespace lsv2
