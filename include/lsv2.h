@@ -111,10 +111,11 @@ typedef struct lsv2_geom {
 /* Per-instance state (the reference's binningBuffer) + per-tile ranges. */
 typedef struct lsv2_binning {
     uint64_t capacity;       /* instances addressable in each array below          */
-    uint64_t* keys;          /* u64[capacity]  sorted (tile<<32 | depth bits)      */
+    uint64_t* keys;          /* u64[capacity]  sorted (tile<<32 | Gaussian id), in the order of the reference's
+                                (tile<<32 | depth bits) key == (keys[i] & ~0xffffffff) | bits(depth[id])       */
     uint32_t* point_list;    /* u32[capacity]  sorted Gaussian ids                 */
-    uint64_t* keys_alt;      /* u64[capacity]  unsorted keys / ping-pong buffer    */
-    uint32_t* vals_alt;      /* u32[capacity]                                      */
+    uint64_t* keys_alt;      /* u64[capacity]  ping-pong buffer of the sort        */
+    uint32_t* vals_alt;      /* u32[capacity]  unused since the packed sort; may be NULL */
     uint32_t* ranges;        /* u32[tiles][2]  (start,end) per 16x16 tile          */
     void* scratch;           /* lsv2_sort_scratch_bytes(capacity, P)               */
     size_t scratch_bytes;

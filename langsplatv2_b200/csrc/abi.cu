@@ -14,7 +14,7 @@ void set_cuda_error(cudaError_t e, const char* what)
     snprintf(g_cuda_error, sizeof g_cuda_error, "%s: %s (%s)", what, cudaGetErrorString(e), cudaGetErrorName(e));
 }
 
-int sort_num_passes(int depth_bits, int tile_bits);
+int sort_num_passes(int nbits);
 int launch_decode_fp32(int levels, int Lc, int D, int64_t HW, const float* wmap, const float* codebooks,
                        int normalize, float* out, cudaStream_t st);
 int launch_decode_tc(int levels, int Lc, int D, int64_t HW, const float* wmap, const float* codebooks,
@@ -108,25 +108,28 @@ int lsv2_preprocess(const lsv2_view* view, const lsv2_scene* scene, const lsv2_g
 int lsv2_bin(const lsv2_view* view, int32_t P, const lsv2_geom* geom, const lsv2_binning* binning, void* stream)
 {
     if (!view_ok(view) || !geom || !binning || !binning->status || !binning->ranges) return LSV2_EINVAL;
-    if (binning->capacity > 0 && (!binning->keys || !binning->point_list || !binning->keys_alt || !binning->vals_alt))
+    if (binning->capacity > 0 && (!binning->keys || !binning->point_list || !binning->keys_alt))
         return LSV2_EINVAL;
     cudaStream_t st = (cudaStream_t)stream;
     const int tb = tile_bits_for(*view);
     // Gaussians in depth order first (P pairs), then the instances on the tile word alone (R pairs): the same
     // list as one stable sort on (tile | depth), see radix_sort.cu
-    const uint32_t *order = nullptr, *offsets = geom->offsets;
+    const uint64_t* order = nullptr;
+    const uint32_t* offsets = geom->offsets;
     int rc = launch_depth_order(P, *geom, DEPTH_KEY_BITS, binning->scratch, binning->scratch_bytes, &order, &offsets,
                                 st);
     if (rc) return rc;
-    const int npass = sort_num_passes(0, tb);
+    const int npass = sort_num_passes(tb);
     // emit the unsorted pairs into the buffer from which an npass ping-pong ends in (keys, point_list)
     lsv2_binning emit = *binning;
-    if (!(npass & 1)) { emit.keys_alt = binning->keys; emit.vals_alt = binning->point_list; }
+    if (!(npass & 1)) emit.keys_alt = binning->keys;
     rc = launch_duplicate(*view, P, *geom, emit, order, offsets, st);
     if (rc) return rc;
-    rc = launch_sort(*binning, 0, tb, binning->scratch, binning->scratch_bytes, st);
+    const int n_tiles = ((view->width + TILE - 1) / TILE) * ((view->height + TILE - 1) / TILE);
+    bool ranges_done = false;
+    rc = launch_sort(*binning, tb, n_tiles, &ranges_done, binning->scratch, binning->scratch_bytes, st);
     if (rc) return rc;
-    return launch_ranges(*view, *binning, st);
+    return ranges_done ? LSV2_OK : launch_ranges(*view, *binning, st);
 }
 
 int lsv2_compact_coeff(int32_t P, const lsv2_geom* geom, const lsv2_features* feat, void* stream)

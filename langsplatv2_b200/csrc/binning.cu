@@ -1,7 +1,8 @@
 // binning.cu -- K3 duplicateWithKeys and K5 identifyTileRanges.
-// key = (tile_id << 32) | float_bits(depth); value = Gaussian id; emission order inside one
-// Gaussian is y-major over its tile rectangle; the Gaussians emit in depth order (radix_sort.cu,
-// launch_depth_order) so that the instance sort only has the tile word left to do.  The instance count lives on the device
+// An instance is emitted as ONE packed word (tile_id << 32) | Gaussian id; emission order inside one Gaussian is
+// y-major over its tile rectangle and the Gaussians emit in depth order (radix_sort.cu, launch_depth_order), so the
+// instance sort only has the tile word left to do.  The reference's pair is key = (tile_id << 32) |
+// float_bits(depth), value = Gaussian id: same order, and the key is (word & ~0xffffffff) | bits(depth[id]).  The instance count lives on the device
 // (status[NUM_RENDERED]); every kernel clamps to `capacity`.
 #include "common.cuh"
 
@@ -12,16 +13,15 @@ namespace lsv2 {
 // lanes striding over the instances, so the key/value stores are contiguous runs.
 __global__ void __launch_bounds__(256)
 k_duplicate(int P, int gx, int gy, const int32_t* __restrict__ radii, const float2* __restrict__ xy,
-            const float* __restrict__ depth, const uint32_t* __restrict__ order,
-            const uint32_t* __restrict__ offsets, uint64_t capacity,
-            uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t* __restrict__ status)
+            const uint64_t* __restrict__ order, const uint32_t* __restrict__ offsets, uint64_t capacity,
+            uint64_t* __restrict__ packed, uint32_t* __restrict__ status)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31;
-    uint32_t gid = 0, off = 0, cnt = 0, dbits = 0;
+    uint32_t gid = 0, off = 0, cnt = 0;
     int minx = 0, miny = 0, w = 1;
     if (i < P) {
-        gid = order ? order[i] : (uint32_t)i;
+        gid = order ? (uint32_t)order[i] : (uint32_t)i;
         const int r = radii[gid];
         if (r > 0) {
             off = (i == 0) ? 0u : offsets[i - 1];
@@ -32,7 +32,6 @@ k_duplicate(int P, int gx, int gy, const int32_t* __restrict__ radii, const floa
             tile_rect(p.x, p.y, (float)r, gx, gy, minx, miny, maxx, maxy);
             w = max(maxx - minx, 1);
             cnt = end - off;                      // == (maxx - minx) * (maxy - miny) = tiles_touched
-            dbits = __float_as_uint(depth[gid]);
         }
     }
     uint32_t todo = __ballot_sync(0xffffffffu, cnt > 0);
@@ -42,7 +41,6 @@ k_duplicate(int P, int gx, int gy, const int32_t* __restrict__ radii, const floa
         const uint32_t c = __shfl_sync(0xffffffffu, cnt, src);
         const uint32_t o = __shfl_sync(0xffffffffu, off, src);
         const uint32_t g = __shfl_sync(0xffffffffu, gid, src);
-        const uint32_t db = __shfl_sync(0xffffffffu, dbits, src);
         const int x0 = __shfl_sync(0xffffffffu, minx, src);
         const int y0 = __shfl_sync(0xffffffffu, miny, src);
         const int ww = __shfl_sync(0xffffffffu, w, src);
@@ -50,21 +48,19 @@ k_duplicate(int P, int gx, int gy, const int32_t* __restrict__ radii, const floa
             const uint64_t dst = (uint64_t)o + k;
             if (dst < capacity) {
                 const int y = y0 + (int)k / ww, x = x0 + (int)k % ww;      // y-major over the rectangle
-                keys[dst] = ((uint64_t)(uint32_t)(y * gx + x) << 32) | db;
-                vals[dst] = g;
+                packed[dst] = ((uint64_t)(uint32_t)(y * gx + x) << 32) | g;
             }
         }
     }
 }
 
-int launch_duplicate(const lsv2_view& v, int P, const lsv2_geom& g, const lsv2_binning& b, const uint32_t* order,
+int launch_duplicate(const lsv2_view& v, int P, const lsv2_geom& g, const lsv2_binning& b, const uint64_t* order,
                      const uint32_t* offsets, cudaStream_t st)
 {
     if (P <= 0) return LSV2_OK;
     const int gx = (v.width + TILE - 1) / TILE, gy = (v.height + TILE - 1) / TILE;
     k_duplicate<<<ceil_div(P, 256), 256, 0, st>>>(P, gx, gy, g.radii, reinterpret_cast<const float2*>(g.xy),
-                                                  g.depth, order, offsets, b.capacity, b.keys_alt, b.vals_alt,
-                                                  b.status);
+                                                  order, offsets, b.capacity, b.keys_alt, b.status);
     LSV2_LAUNCH_CHECK("k_duplicate");
     return LSV2_OK;
 }

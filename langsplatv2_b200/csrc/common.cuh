@@ -139,17 +139,17 @@ int launch_preprocess(const lsv2_view& v, const lsv2_scene& s, const lsv2_geom& 
 int launch_scan(int P, const uint32_t* in, uint32_t* out_inclusive, uint32_t* total_out,
                 void* scratch, size_t scratch_bytes, cudaStream_t st);
 size_t scan_scratch_bytes(int P);
-int launch_duplicate(const lsv2_view& v, int P, const lsv2_geom& g, const lsv2_binning& b, const uint32_t* order,
+int launch_duplicate(const lsv2_view& v, int P, const lsv2_geom& g, const lsv2_binning& b, const uint64_t* order,
                      const uint32_t* offsets, cudaStream_t st);
 size_t depth_order_scratch_bytes(int P);
 int launch_depth_order(int P, const lsv2_geom& g, int depth_bits, void* scratch, size_t scratch_bytes,
-                       const uint32_t** order, const uint32_t** offsets, cudaStream_t st);
+                       const uint64_t** order, const uint32_t** offsets, cudaStream_t st);
 int launch_ranges(const lsv2_view& v, const lsv2_binning& b, cudaStream_t st);
 size_t sort_scratch_bytes(uint64_t capacity);
-// sorts (keys_alt, vals_alt)[0..*n) on key bits selected by (lo_bits of the low word, hi_bits of
-// the high word) into (keys, point_list); stable.
-int launch_sort(const lsv2_binning& b, int depth_bits, int tile_bits, void* scratch, size_t scratch_bytes,
-                cudaStream_t st);
+// stable sort of the packed instances (tile << 32 | id) on the tile word into keys; the last pass also writes
+// point_list.  *ranges_done: the tile ranges were derived from the tile counts.
+int launch_sort(const lsv2_binning& b, int tile_bits, int n_tiles, bool* ranges_done, void* scratch,
+                size_t scratch_bytes, cudaStream_t st);
 int launch_compact_coeff(int P, const lsv2_geom& g, const lsv2_features& f, cudaStream_t st);
 int launch_render_forward(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b,
                           const lsv2_features& f, const lsv2_image& img, cudaStream_t st);

@@ -226,7 +226,6 @@ def rasterize_forward(rs: GaussianRasterizationSettings, means3D, opacities, shs
         b["keys"] = torch.empty(n, dtype=torch.int64, device=dev)
         b["point_list"] = torch.empty(n, **i32)
         b["keys_alt"] = torch.empty(n, dtype=torch.int64, device=dev)
-        b["vals_alt"] = torch.empty(n, **i32)
         b["ranges"] = torch.empty((gx * gy, 2), **i32)
         b["scratch"] = torch.empty(L_.lsv2_sort_scratch_bytes(cap, P), dtype=torch.uint8, device=dev)
 

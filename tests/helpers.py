@@ -72,3 +72,13 @@ def u32(t):
 
 def u64(t):
     return t.detach().cpu().numpy().view(np.uint64)
+
+
+def ref_keys(st, R=None):
+    """The reference's sort keys (tile << 32 | depth bits) of the sorted instance list, rebuilt from the packed words
+    (tile << 32 | Gaussian id) the CUDA sort leaves in binning["keys"] (include/lsv2.h, lsv2_binning.keys)."""
+    R = st.num_rendered if R is None else R
+    packed = u64(st.binning["keys"])[:R]
+    depth = st.geom["depth"].detach().cpu().numpy().view(np.uint32)
+    ids = (packed & np.uint64(0xFFFFFFFF)).astype(np.int64)
+    return (packed & np.uint64(0xFFFFFFFF00000000)) | depth[ids].astype(np.uint64)

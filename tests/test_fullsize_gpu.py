@@ -51,7 +51,7 @@ def test_full_size_frame(W, H, stride):
     np.testing.assert_array_equal(ranges, binned["ranges"])
 
     # ---- properties over the whole frame ----
-    keys = hp.u64(st.binning["keys"])[:R]
+    keys = hp.ref_keys(st, R)
     assert np.all(keys[1:] >= keys[:-1]), "keys not sorted"
     assert int(pre["tiles_touched"].astype(np.int64).sum()) == R
     vis = np.nonzero(pre["tiles_touched"])[0]
@@ -110,7 +110,7 @@ def test_config4_forward_backward_adjoint_identity():
     assert abs(float(lhs - rhs)) <= 1e-4 * abs(float(lhs)) + 1e-3, (float(lhs), float(rhs))
     d2, _ = rasterize_backward(st, 2.0 * dW, dense_grad=True)
     assert float((d2 - 2.0 * d_coeff).abs().max()) <= 2e-4 * float(d_coeff.abs().max())
-    keys = st.binning["keys"][: st.num_rendered]
+    keys = torch.as_tensor(hp.ref_keys(st).view(np.int64))
     assert bool((keys[1:] >= keys[:-1]).all())
 
 
@@ -130,7 +130,7 @@ def test_config5_4k_render_properties():
                      debug_buffers=False)
     out = render_decode(st, scene["codebooks"].cuda(), normalize=True)
     R = st.num_rendered
-    keys = st.binning["keys"][:R]
+    keys = torch.as_tensor(hp.ref_keys(st, R).view(np.int64))
     assert bool((keys[1:] >= keys[:-1]).all())
     ranges = st.binning["ranges"].to(torch.int64)
     lens = ranges[:, 1] - ranges[:, 0]

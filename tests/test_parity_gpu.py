@@ -29,7 +29,9 @@ def _check_geom_bin(st, pre, binned):
     np.testing.assert_array_equal(g["clamped"].cpu().numpy(), pre["clamped"])
     R = binned["R"]
     assert st.num_rendered == R and not st.overflowed
-    np.testing.assert_array_equal(hp.u64(st.binning["keys"])[:R], binned["keys"])
+    np.testing.assert_array_equal(hp.ref_keys(st, R), binned["keys"])
+    np.testing.assert_array_equal((hp.u64(st.binning["keys"])[:R] & np.uint64(0xFFFFFFFF)).astype(np.uint32),
+                                  binned["point_list"])
     np.testing.assert_array_equal(hp.u32(st.binning["point_list"])[:R], binned["point_list"])
     np.testing.assert_array_equal(hp.u32(st.binning["ranges"]), binned["ranges"])
 
@@ -121,8 +123,9 @@ def test_sort_large_random_keys_properties():
     scene, cam = hp.make_case(300000, 1008, 756, seed=3)
     st = hp.run_cuda(scene, cam, BG, hp.MODE_RGB)
     R = st.num_rendered
-    keys = hp.u64(st.binning["keys"])[:R]
+    keys = hp.ref_keys(st, R)
     ids = hp.u32(st.binning["point_list"])[:R]
+    assert np.array_equal((hp.u64(st.binning["keys"])[:R] & np.uint64(0xFFFFFFFF)).astype(np.uint32), ids)
     assert np.all(keys[1:] >= keys[:-1])
     same = keys[1:] == keys[:-1]
     assert np.all(ids[1:][same] > ids[:-1][same])           # stable: emission order is id-ascending
