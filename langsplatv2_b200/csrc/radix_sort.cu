@@ -201,6 +201,24 @@ k_rs_onesweep(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ keys_
         key[j] = li < tile_n ? keys_in[tile_base + li] : ~0ull;
     }
 
+    // early per-warp digit counts: the tile's aggregate is published before the ranking, so the look-back of
+    // the following tiles never waits on this tile's ranking
+#pragma unroll
+    for (int j = 0; j < RS_IPT; ++j) atomicAdd(&s_hist[warp][(uint32_t)(key[j] >> shift) & mask], 1u);
+    __syncthreads();
+
+    // thread d: per-warp exclusive offsets inside digit d, tile count of digit d.  Padding items of the last tile
+    // carry the all-ones key; they inflate its count of the top digit, which no later tile ever reads.
+    uint32_t count = 0;
+#pragma unroll
+    for (int w = 0; w < RS_WARPS; ++w) {
+        const uint32_t t = s_hist[w][tid];
+        s_hist[w][tid] = count;
+        count += t;
+    }
+    volatile uint32_t* mine = lookback + (size_t)tile * RS_RADIX + tid;
+    *mine = (tile == 0 ? LB_INC : LB_AGG) | count;
+
     // global exclusive offset of this thread's digit (exclusive scan of the pass histogram)
     uint32_t g_excl;
     {
@@ -219,32 +237,6 @@ k_rs_onesweep(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ keys_
         g_excl = woff + incl - c;
         __syncthreads();
     }
-
-    // rank inside the warp chunk (stable: row j before row j+1, lane order inside a row)
-    uint32_t rank[RS_IPT];
-    const uint32_t lt_mask = (1u << lane) - 1u;
-#pragma unroll
-    for (int j = 0; j < RS_IPT; ++j) {
-        const uint32_t d = (uint32_t)(key[j] >> shift) & mask;
-        const uint32_t peers = __match_any_sync(0xffffffffu, d);
-        const int leader = __ffs(peers) - 1;
-        uint32_t pre = 0;
-        if (lane == leader) pre = s_hist[warp][d];
-        pre = __shfl_sync(0xffffffffu, pre, leader);
-        if (lane == leader) s_hist[warp][d] = pre + __popc(peers);
-        rank[j] = pre + __popc(peers & lt_mask);
-        __syncwarp();
-    }
-    __syncthreads();
-
-    // thread d: per-warp offsets inside digit d, tile count of digit d
-    uint32_t count = 0;
-#pragma unroll
-    for (int w = 0; w < RS_WARPS; ++w) {
-        const uint32_t t = s_hist[w][tid];
-        s_hist[w][tid] = count;
-        count += t;
-    }
     // exclusive scan of the tile's digit counts -> start of each digit run in sorted order
     {
         uint32_t incl = count;
@@ -260,16 +252,36 @@ k_rs_onesweep(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ keys_
         for (int w = 0; w < RS_WARPS; ++w) if (w < warp) woff += s_scan[w];
         s_start[tid] = woff + incl - count;
     }
+    __syncthreads();
 
-    // decoupled look-back for digit `tid`.  Padding items of the last tile carry the all-ones
-    // key; they inflate its count of the top digit, which no later tile ever reads.
+    // rank inside the warp chunk (stable: row j before row j+1, lane order inside a row) and scatter into
+    // tile-sorted order.  The peers of a lane (same digit) come from one ballot per digit bit.
+    const uint32_t lt_mask = (1u << lane) - 1u;
+#pragma unroll
+    for (int j = 0; j < RS_IPT; ++j) {
+        const uint32_t d = (uint32_t)(key[j] >> shift) & mask;
+        uint32_t peers = 0xffffffffu;
+#pragma unroll
+        for (int b = 0; b < 8; ++b) {
+            if (b < bits) {
+                const bool bit = (d >> b) & 1u;
+                const uint32_t v = __ballot_sync(0xffffffffu, bit);
+                peers &= bit ? v : ~v;
+            }
+        }
+        const int leader = __ffs(peers) - 1;
+        uint32_t pre = 0;
+        if (lane == leader) pre = s_hist[warp][d];
+        pre = __shfl_sync(0xffffffffu, pre, leader);
+        if (lane == leader) s_hist[warp][d] = pre + __popc(peers);
+        s_keys[s_start[d] + pre + __popc(peers & lt_mask)] = key[j];
+        __syncwarp();
+    }
+
+    // decoupled look-back for digit `tid`
     {
         uint32_t excl = 0;
-        volatile uint32_t* mine = lookback + (size_t)tile * RS_RADIX + tid;
-        if (tile == 0) {
-            *mine = LB_INC | count;
-        } else {
-            *mine = LB_AGG | count;
+        if (tile != 0) {
             for (int64_t t = (int64_t)tile - 1; t >= 0; --t) {
                 uint32_t s;
                 do { s = lookback[(size_t)t * RS_RADIX + tid]; } while ((s & LB_FLAG) == 0);
@@ -279,14 +291,6 @@ k_rs_onesweep(const uint64_t* __restrict__ keys_in, uint64_t* __restrict__ keys_
             *mine = LB_INC | ((excl + count) & LB_VAL);
         }
         s_gbase[tid] = g_excl + excl - s_start[tid];
-    }
-    __syncthreads();
-
-    // scatter into tile-sorted order, then out in runs
-#pragma unroll
-    for (int j = 0; j < RS_IPT; ++j) {
-        const uint32_t d = (uint32_t)(key[j] >> shift) & mask;
-        s_keys[s_start[d] + s_hist[warp][d] + rank[j]] = key[j];
     }
     __syncthreads();
 #pragma unroll
