@@ -9,8 +9,7 @@
 namespace lsv2 {
 
 // Slot i of the emission order is Gaussian order[i] (its depth rank; order == nullptr: i itself) and owns the
-// instance range [offsets[i-1], offsets[i]).  A warp emits the ranges of its 32 slots one after the other with the
-// lanes striding over the instances, so the key/value stores are contiguous runs.
+// instance range [offsets[i-1], offsets[i]).  A warp emits the ranges of its 32 slots as one contiguous run.
 __global__ void __launch_bounds__(256)
 k_duplicate(int P, int gx, int gy, const int32_t* __restrict__ radii, const float2* __restrict__ xy,
             const uint64_t* __restrict__ order, const uint32_t* __restrict__ offsets, uint64_t capacity,
@@ -34,22 +33,39 @@ k_duplicate(int P, int gx, int gy, const int32_t* __restrict__ radii, const floa
             cnt = end - off;                      // == (maxx - minx) * (maxy - miny) = tiles_touched
         }
     }
-    uint32_t todo = __ballot_sync(0xffffffffu, cnt > 0);
-    while (todo) {
-        const int src = __ffs(todo) - 1;
-        todo &= todo - 1;
-        const uint32_t c = __shfl_sync(0xffffffffu, cnt, src);
-        const uint32_t o = __shfl_sync(0xffffffffu, off, src);
-        const uint32_t g = __shfl_sync(0xffffffffu, gid, src);
-        const int x0 = __shfl_sync(0xffffffffu, minx, src);
-        const int y0 = __shfl_sync(0xffffffffu, miny, src);
-        const int ww = __shfl_sync(0xffffffffu, w, src);
-        for (uint32_t k = lane; k < c; k += 32) {
-            const uint64_t dst = (uint64_t)o + k;
-            if (dst < capacity) {
-                const int y = y0 + (int)k / ww, x = x0 + (int)k % ww;      // y-major over the rectangle
-                packed[dst] = ((uint64_t)(uint32_t)(y * gx + x) << 32) | g;
-            }
+    // The 32 ranges of a warp are adjacent (culled slots are empty), so the warp writes ONE run of `total` words
+    // starting at its first slot's offset; word k belongs to the slot j with excl[j] <= k < incl[j] (binary search
+    // over the warp's inclusive counts).
+    uint32_t incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    const uint32_t excl = incl - cnt;
+    const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+    if (total == 0) return;
+    // offset of word 0 of the run: the start of the first non-empty slot
+    const int first = __ffs(__ballot_sync(0xffffffffu, cnt > 0)) - 1;
+    const uint64_t run = (uint64_t)__shfl_sync(0xffffffffu, off, first);
+    for (uint32_t k0 = 0; k0 < total; k0 += 32) {
+        const uint32_t k = min(k0 + lane, total - 1);
+        int j = 0;
+#pragma unroll
+        for (int step = 16; step >= 1; step >>= 1) {
+            const uint32_t v = __shfl_sync(0xffffffffu, incl, j + step - 1);
+            if (v <= k) j += step;
+        }
+        const uint32_t e = __shfl_sync(0xffffffffu, excl, j);
+        const uint32_t g = __shfl_sync(0xffffffffu, gid, j);
+        const int x0 = __shfl_sync(0xffffffffu, minx, j);
+        const int y0 = __shfl_sync(0xffffffffu, miny, j);
+        const int ww = __shfl_sync(0xffffffffu, w, j);
+        const uint64_t dst = run + k0 + lane;
+        if (k0 + lane < total && dst < capacity) {
+            const int kl = (int)(k - e);
+            const int y = y0 + kl / ww, x = x0 + kl % ww;                  // y-major over the rectangle
+            packed[dst] = ((uint64_t)(uint32_t)(y * gx + x) << 32) | g;
         }
     }
 }

@@ -73,19 +73,21 @@ __device__ __forceinline__ uint64_t clamp_count(const uint32_t* count, uint64_t 
 }
 
 // ---- all-pass digit histogram (+ the per-image-tile counts the tile ranges come from) --------
-__global__ void __launch_bounds__(RS_THREADS)
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
 k_rs_histogram(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ count, uint64_t capacity,
                SortPlan plan, uint32_t* __restrict__ g_hist, uint32_t* __restrict__ g_tiles, int n_tiles)
 {
     __shared__ uint32_t s_hist[RS_MAX_PASSES * RS_RADIX];
     __shared__ uint32_t s_tiles[RS_TILE_HIST];
     const uint64_t n = clamp_count(count, capacity);
-    for (int i = threadIdx.x; i < plan.npass * RS_RADIX; i += RS_THREADS) s_hist[i] = 0;
+    for (int i = threadIdx.x; i < plan.npass * RS_RADIX; i += THREADS) s_hist[i] = 0;
     if (g_tiles)
-        for (int i = threadIdx.x; i < n_tiles; i += RS_THREADS) s_tiles[i] = 0;
+        for (int i = threadIdx.x; i < n_tiles; i += THREADS) s_tiles[i] = 0;
     __syncthreads();
-    const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
-    for (uint64_t i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; i < n; i += stride) {
+    const uint64_t stride = (uint64_t)gridDim.x * THREADS;
+#pragma unroll 4
+    for (uint64_t i = (uint64_t)blockIdx.x * THREADS + threadIdx.x; i < n; i += stride) {
         const uint64_t k = keys[i];
         if (g_tiles) {              // the digit counts follow from the tile counts (k_ranges_from_counts)
             const uint32_t t = (uint32_t)(k >> 32);
@@ -101,12 +103,12 @@ k_rs_histogram(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ c
         }
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < plan.npass * RS_RADIX; i += RS_THREADS) {
+    for (int i = threadIdx.x; i < plan.npass * RS_RADIX; i += THREADS) {
         const uint32_t c = s_hist[i];
         if (c) atomicAdd(&g_hist[i], c);
     }
     if (g_tiles)
-        for (int i = threadIdx.x; i < n_tiles; i += RS_THREADS) {
+        for (int i = threadIdx.x; i < n_tiles; i += THREADS) {
             const uint32_t c = s_tiles[i];
             if (c) atomicAdd(&g_tiles[i], c);
         }
@@ -332,9 +334,14 @@ static int sort_packed(uint64_t* k_a, uint64_t* k_b, uint32_t* vals_out, const u
     uint64_t* k_src = odd ? k_b : k_a;
     uint64_t* k_dst = odd ? k_a : k_b;
 
-    const int hist_grid = (int)min((size_t)NUM_SMS * 8, tiles * (RS_TILE / RS_THREADS));
-    k_rs_histogram<<<hist_grid, RS_THREADS, 0, st>>>(k_src, count, capacity, plan, g_hist, ranges ? g_tiles : nullptr,
-                                                     n_tiles);
+    if (ranges) {
+        // every CTA flushes up to n_tiles counts with global atomics: few, large CTAs
+        const int hist_grid = (int)min((size_t)NUM_SMS, tiles);
+        k_rs_histogram<1024><<<hist_grid, 1024, 0, st>>>(k_src, count, capacity, plan, g_hist, g_tiles, n_tiles);
+    } else {
+        const int hist_grid = (int)min((size_t)NUM_SMS * 8, tiles * (RS_TILE / RS_THREADS));
+        k_rs_histogram<RS_THREADS><<<hist_grid, RS_THREADS, 0, st>>>(k_src, count, capacity, plan, g_hist, nullptr, 0);
+    }
     LSV2_LAUNCH_CHECK("k_rs_histogram");
     if (ranges) {
         k_ranges_from_counts<<<1, 1024, 0, st>>>(g_tiles, n_tiles, ranges, plan, g_hist);
