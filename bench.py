@@ -210,7 +210,8 @@ def run_train(args, dev, rank, world, scene, barrier):
     gts = {v: synthetic_gt(H, W, device=dev, seed=2 + v) for v in my_views}
     tr = FeatureTrainer(scene, topk=TOPK, layers=1, device=dev)
     loss = None
-    for s in range(3):
+    n_warm = tr.calib_steps + 3          # the calibration iterations (host sync, exact capacity) + 3 steady-state ones
+    for s in range(n_warm):
         v = my_views[s % len(my_views)]
         loss = tr.step(cams[v], *gts[v])
     barrier()
@@ -228,7 +229,7 @@ def run_train(args, dev, rank, world, scene, barrier):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
     return {"metric": "train iter/s", "value": steps / (ms * 1e-3), "unit": "iter/s", "views_per_s": world * steps / (ms * 1e-3),
-            "ms_per_iter": ms / steps, "steps": steps, "warmup": 3, "n_gpus": world, "scaling": "weak",
+            "ms_per_iter": ms / steps, "steps": steps, "warmup": n_warm, "n_gpus": world, "scaling": "weak",
             "final_loss": float(loss), "dtype": "f32",
             "config": {"workload": TRAIN_WL["name"], "views_per_iter": world,
                        "grad_allreduce_bytes": (tr.bucket.nbytes if tr.bucket is not None else 0),

@@ -150,6 +150,8 @@ size_t sort_scratch_bytes(uint64_t capacity);
 // point_list.  *ranges_done: the tile ranges were derived from the tile counts.
 int launch_sort(const lsv2_binning& b, int tile_bits, int n_tiles, bool* ranges_done, void* scratch,
                 size_t scratch_bytes, cudaStream_t st);
+bool launch_gemm_nt_tf32x3(const float* X, const float* Y, float* out, int D, int Lc, int64_t HW, cudaStream_t st,
+                           int* rc);
 int launch_compact_coeff(int P, const lsv2_geom& g, const lsv2_features& f, cudaStream_t st);
 int launch_render_forward(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b,
                           const lsv2_features& f, const lsv2_image& img, cudaStream_t st);

@@ -257,9 +257,20 @@ int launch_decode_backward(int levels, int Lc, int D, int64_t HW, const float* w
         LSV2_LAUNCH_CHECK("k_decode_bwd_dW");
     }
     if (dC) {
-        dim3 grid((unsigned)ceil_div(HW, DC_SLAB), (unsigned)ceil_div(D, 64), (unsigned)levels);
-        k_decode_bwd_dC<<<grid, 256, 0, st>>>(Lc, D, HW, wmap, dF, dC);
-        LSV2_LAUNCH_CHECK("k_decode_bwd_dC");
+        // tensor-core path (3xTF32, gemm_tf32x3.cu) level by level; CUDA-core kernel for shapes it does not take
+        bool all_tc = true;
+        for (int l = 0; l < levels && all_tc; ++l) {
+            int rc = LSV2_OK;
+            all_tc = launch_gemm_nt_tf32x3(dF + (size_t)l * D * HW, wmap + (size_t)l * Lc * HW,
+                                           dC + (size_t)l * Lc * D, D, Lc, HW, st, &rc);
+            if (rc) return rc;
+            if (!all_tc && l > 0) return LSV2_ECUDA;      // cannot happen: the shape test does not depend on l
+        }
+        if (!all_tc) {
+            dim3 grid((unsigned)ceil_div(HW, DC_SLAB), (unsigned)ceil_div(D, 64), (unsigned)levels);
+            k_decode_bwd_dC<<<grid, 256, 0, st>>>(Lc, D, HW, wmap, dF, dC);
+            LSV2_LAUNCH_CHECK("k_decode_bwd_dC");
+        }
     }
     return LSV2_OK;
 }

@@ -133,3 +133,26 @@ def test_train_steps_reduce_the_loss():
     losses = [float(tr.step(cam, gt, mask)) for _ in range(15)]
     assert all(np.isfinite(losses))
     assert losses[-1] < losses[0] - 0.05, losses
+
+
+@pytest.mark.parametrize("D,H,W", [(512, 64, 100), (64, 64, 100), (512, 300, 404), (200, 37, 44)])
+def test_codebook_gradient_tensor_core_3xtf32_matches_fp64(D, H, W):
+    """dC[k][d] = sum_p w[k][p] dF[d][p] on the tcgen05 path (csrc/gemm_tf32x3.cu: fp32 operands split hi + lo, three
+    tf32 products, fp32 accumulate) against a float64 product.  Stated tolerance: 2e-6 x sum_p |w||dF| per element
+    (the dropped lo*lo term is <= 2^-20 per product), i.e. fp32-GEMM grade, as the reference's fp32 einsum backward
+    (scene/gaussian_model.py:538).  HW % 4 == 0 on every case here so the tensor-core path is the one that runs; the
+    last case has a ragged row count (200 of 256) and a ragged last 32-pixel step."""
+    from langsplatv2_b200.loss import _decode_bwd
+    g = torch.Generator(device="cuda").manual_seed(D + H)
+    HW = H * W
+    assert HW % 4 == 0
+    w = torch.randn((64, HW), generator=g, device="cuda") * torch.exp(2.0 * torch.randn((64, 1), generator=g, device="cuda"))
+    w = w * (torch.rand((64, HW), generator=g, device="cuda") > 0.5)
+    dF = torch.randn((D, HW), generator=g, device="cuda") * torch.exp(torch.randn((D, 1), generator=g, device="cuda"))
+    dC = torch.zeros((1, 64, D), dtype=torch.float32, device="cuda")
+    _decode_bwd(1, 64, D, HW, w, None, dF, None, dC, w.device)
+    ref = w.double() @ dF.double().T
+    bound = w.double().abs() @ dF.double().abs().T
+    err = (dC[0].double() - ref).abs()
+    assert bool((err <= 2e-6 * bound + 1e-30).all()), float((err / (bound + 1e-30)).max())
+    assert float(err.max()) <= 1e-5 * float(ref.abs().max())
