@@ -24,7 +24,7 @@
 namespace lsv2 {
 using namespace tc;
 
-constexpr int GX_STAGES = 2;
+constexpr int GX_STAGES = 3;                       // raw (-> hi) tiles in flight; the lo tiles have 2 buffers
 constexpr int GX_KSTEP = 32;                       // pixels per stage: 32 fp32 = one 128-byte swizzled row
 constexpr int GX_LOADERS = 128;
 constexpr int gx_threads(int MT) { return GX_LOADERS + 32 + 128 * MT; }   // + MMA warp + 4 epilogue warps per M tile
@@ -34,8 +34,10 @@ constexpr int GX_XT_BYTES = 128 * 128;             // 16 KB per 128-row tile
 
 template <int MT> struct GxLayout {
     static constexpr int X_BYTES = MT * GX_XT_BYTES;
-    static constexpr int STAGE = 2 * X_BYTES + 2 * GX_Y_BYTES;         // X hi | X lo | Y hi | Y lo
-    static constexpr int TOTAL = GX_STAGES * STAGE + 1024 /*align*/ + 128 /*barriers*/;
+    static constexpr int STAGE = X_BYTES + GX_Y_BYTES;                 // X | Y (raw, then hi in place); lo: same shape
+    static constexpr int LO_OFF = GX_STAGES * STAGE;
+    static constexpr int BAR_OFF = LO_OFF + 2 * STAGE;
+    static constexpr int TOTAL = BAR_OFF + 1024 /*align*/ + 128 /*barriers*/;
     static constexpr int TMEM_COLS = 2 * MT * 64;                      // two chunk buffers: 128 or 256 columns
 };
 
@@ -73,9 +75,9 @@ k_gemm_nt_tf32x3(const float* __restrict__ X, const float* __restrict__ Y, float
     using L = GxLayout<MT>;
     extern __shared__ unsigned char smem_raw[];
     unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + GX_STAGES * L::STAGE);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BAR_OFF);
     uint64_t* full = bars;                          // [GX_STAGES] 128 loader arrivals
-    uint64_t* empty = bars + GX_STAGES;             // [GX_STAGES] MMA commit
+    uint64_t* empty = bars + GX_STAGES;             // [GX_STAGES] MMA commit of the step that read the stage
     uint64_t* acc_full = bars + 2 * GX_STAGES;      // [2] MMA commit of a chunk
     uint64_t* acc_free = acc_full + 2;              // [2] 128 * MT epilogue arrivals
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(acc_free + 2);
@@ -112,28 +114,26 @@ k_gemm_nt_tf32x3(const float* __restrict__ X, const float* __restrict__ Y, float
                 const int grow = isx ? d0 + row : row;
                 const bool ok = p < p_end && (!isx || grow < D);
                 const float* src = (isx ? X : Y) + (ok ? (size_t)grow * HW + p : 0);
-                unsigned char* dst = st + (isx ? 0 : 2 * L::X_BYTES) + sw128_offset(row, ch);
+                unsigned char* dst = st + (isx ? 0 : L::X_BYTES) + sw128_offset(row, ch);
                 cp_async16(smem_u32(dst), src, ok ? 16u : 0u);
             }
             cp_async_commit();
         };
         if (nsteps > 0) issue(0);
+        if (nsteps > 1) issue(1);
         for (int s = 0; s < nsteps; ++s) {
-            if (s + 1 < nsteps) {
-                const int u = (s + 1) / GX_STAGES;                      // use count of that stage
-                if (u > 0) mbar_wait(empty + (s + 1) % GX_STAGES, (u - 1) & 1);
-                issue(s + 1);
-                cp_async_wait<1>();
-            } else {
-                cp_async_wait<0>();
-            }
+            if (s + 1 < nsteps) cp_async_wait<1>();
+            else cp_async_wait<0>();
+            // lo buffer s%2 was last read by step s-2
+            if (s >= 2) mbar_wait(empty + (s - 2) % GX_STAGES, ((s - 2) / GX_STAGES) & 1);
             unsigned char* st = smem + (s % GX_STAGES) * L::STAGE;
 #pragma unroll
             for (int i = 0; i < XCH + YCH; ++i) {
                 const bool isx = i < XCH;
                 const int c = tid + GX_LOADERS * (isx ? i : i - XCH);
-                unsigned char* hi = st + (isx ? 0 : 2 * L::X_BYTES) + sw128_offset(c >> 3, c & 7);
-                unsigned char* lo = hi + (isx ? L::X_BYTES : GX_Y_BYTES);
+                const uint32_t off = (isx ? 0 : L::X_BYTES) + sw128_offset(c >> 3, c & 7);
+                unsigned char* hi = st + off;
+                unsigned char* lo = smem + L::LO_OFF + (s & 1) * L::STAGE + off;
                 const float4 v = *reinterpret_cast<const float4*>(hi);
                 float4 h, l;
                 h.x = __uint_as_float(__float_as_uint(v.x) & 0xffffe000u); l.x = v.x - h.x;
@@ -145,6 +145,11 @@ k_gemm_nt_tf32x3(const float* __restrict__ X, const float* __restrict__ Y, float
             }
             fence_async_smem();
             mbar_arrive(full + s % GX_STAGES);
+            // step s-1's MMAs (running under the split above) done: stage (s+2)%3 == (s-1)%3 takes the next loads
+            if (s + 2 < nsteps) {
+                if (s >= 1) mbar_wait(empty + (s - 1) % GX_STAGES, ((s - 1) / GX_STAGES) & 1);
+                issue(s + 2);
+            }
         }
     } else if (warp > 4) {
         // ---- epilogue warps: TMEM lane = X row inside the tile, column = k ---------------------------
@@ -188,10 +193,11 @@ k_gemm_nt_tf32x3(const float* __restrict__ X, const float* __restrict__ Y, float
             mbar_wait(full + s % GX_STAGES, (s / GX_STAGES) & 1);
             tc_fence_after();
             const uint32_t st = smem_u32(smem + (s % GX_STAGES) * L::STAGE);
-            const uint32_t y_hi = st + 2 * L::X_BYTES, y_lo = y_hi + GX_Y_BYTES;
+            const uint32_t lo = smem_u32(smem + L::LO_OFF + (s & 1) * L::STAGE);
+            const uint32_t y_hi = st + L::X_BYTES, y_lo = lo + L::X_BYTES;
 #pragma unroll
             for (int m = 0; m < MT; ++m) {
-                const uint32_t x_hi = st + m * GX_XT_BYTES, x_lo = x_hi + L::X_BYTES;
+                const uint32_t x_hi = st + m * GX_XT_BYTES, x_lo = lo + m * GX_XT_BYTES;
 #pragma unroll
                 for (int k8 = 0; k8 < GX_KSTEP / 8; ++k8) {
                     const uint64_t koff = (uint64_t)((k8 * 32) >> 4);
