@@ -152,6 +152,8 @@ int launch_sort(const lsv2_binning& b, int tile_bits, int n_tiles, bool* ranges_
                 size_t scratch_bytes, cudaStream_t st);
 bool launch_gemm_nt_tf32x3(const float* X, const float* Y, float* out, int D, int Lc, int64_t HW, cudaStream_t st,
                            int* rc);
+bool launch_gemm_h_tf32x3(const float* C, const float* gt, float* h, int D, int Lc, int64_t HW, cudaStream_t st,
+                          int* rc);
 int launch_compact_coeff(int P, const lsv2_geom& g, const lsv2_features& f, cudaStream_t st);
 int launch_render_forward(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b,
                           const lsv2_features& f, const lsv2_image& img, cudaStream_t st);

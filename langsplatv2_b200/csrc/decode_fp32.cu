@@ -252,9 +252,18 @@ int launch_decode_backward(int levels, int Lc, int D, int64_t HW, const float* w
 {
     if (levels <= 0 || HW <= 0) return LSV2_OK;
     if (dW) {
-        dim3 grid((unsigned)ceil_div(HW, 128), (unsigned)levels);
-        k_decode_bwd_dW<<<grid, 256, 0, st>>>(Lc, D, HW, codebooks, dF, dW);
-        LSV2_LAUNCH_CHECK("k_decode_bwd_dW");
+        bool all_tc = true;
+        for (int l = 0; l < levels && all_tc; ++l) {
+            int rc = LSV2_OK;
+            all_tc = launch_gemm_h_tf32x3(codebooks + (size_t)l * Lc * D, dF + (size_t)l * D * HW,
+                                          dW + (size_t)l * Lc * HW, D, Lc, HW, st, &rc);
+            if (rc) return rc;
+        }
+        if (!all_tc) {
+            dim3 grid((unsigned)ceil_div(HW, 128), (unsigned)levels);
+            k_decode_bwd_dW<<<grid, 256, 0, st>>>(Lc, D, HW, codebooks, dF, dW);
+            LSV2_LAUNCH_CHECK("k_decode_bwd_dW");
+        }
     }
     if (dC) {
         // tensor-core path (3xTF32, gemm_tf32x3.cu) level by level; CUDA-core kernel for shapes it does not take

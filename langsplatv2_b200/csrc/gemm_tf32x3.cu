@@ -220,6 +220,209 @@ k_gemm_nt_tf32x3(const float* __restrict__ X, const float* __restrict__ Y, float
     }
 }
 
+// ---- h[k][p] = sum_d C[k][d] * gt[d][p]  (k < 64, d < D, p < HW) ---------------------------------------
+// The other 64 x D x HW product of the training step (dL/dW = C dF of scene/gaussian_model.py:538's backward; h = C gt
+// of the feature-map-free loss).  The contraction runs over the feature axis, so the big operand gt[d][p] is
+// MN-major (pixels contiguous): A = gt tile, M = 128 pixels, MN-major 128B-swizzled panels of 32 pixels x 8 d;
+// B = codebook tile [64 codes][32 d], K-major.  Same 3xTF32 split, same 2-step TMEM chunks drained into registers;
+// a CTA walks its pixel tiles with the 16 d-steps of a tile as the inner loop and stores h at the end of each tile.
+constexpr int GH_A_BYTES = 32 * 512;               // 32 d rows x 128 pixels fp32 = 4 panels of 4 KB
+constexpr int GH_B_BYTES = 64 * 128;               // 64 codes x 32 d
+constexpr int GH_STAGE = GH_A_BYTES + GH_B_BYTES;  // 24 KB
+constexpr int GH_LO_OFF = GX_STAGES * GH_STAGE;
+constexpr int GH_BAR_OFF = GH_LO_OFF + 2 * GH_STAGE;
+constexpr int GH_TOTAL = GH_BAR_OFF + 1024 + 128;
+constexpr int GH_THREADS = GX_LOADERS + 32 + 128;
+
+// MN-major operand of 32-bit elements: layout type 1 = SWIZZLE_128B_BASE32B (the plain 128B swizzle yields zeros for
+// an MN-major tf32 operand).  Atom = 128-byte rows (32 fp32 along MN) x 4 k; inside an atom the 32-byte unit index is
+// XORed with the row (byte-address bits [7,9) into [5,7)).  `lbo` = bytes between the 32-element MN blocks, `sbo` =
+// bytes between 4-k groups.
+__device__ __forceinline__ uint64_t umma_desc_mn_sw128_32b(uint32_t smem_addr, uint32_t lbo, uint32_t sbo)
+{
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);
+    d |= (uint64_t)(lbo >> 4) << 16;
+    d |= (uint64_t)(sbo >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)1 << 61;
+    return d;
+}
+// byte offset of (k row, 16-byte chunk) inside a [rows][128 B] panel with that swizzle
+__device__ __forceinline__ uint32_t sw128_32b_offset(uint32_t row, uint32_t chunk)
+{
+    return row * 128u + ((((chunk >> 1) ^ (row & 3u)) << 5) | ((chunk & 1u) << 4));
+}
+
+__global__ void __launch_bounds__(GH_THREADS, 1)
+k_gemm_h_tf32x3(const float* __restrict__ C, const float* __restrict__ gt, float* __restrict__ h, int D, int64_t HW,
+                int ntiles, uint32_t lbo, uint32_t sbo)
+{
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + GH_BAR_OFF);
+    uint64_t* full = bars;
+    uint64_t* empty = bars + GX_STAGES;
+    uint64_t* acc_full = bars + 2 * GX_STAGES;
+    uint64_t* acc_free = acc_full + 2;
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(acc_free + 2);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int dsteps = D / GX_KSTEP;                                     // 16 for D = 512 (even, see the launcher)
+    int my_tiles = 0;
+    for (int t = blockIdx.x; t < ntiles; t += gridDim.x) ++my_tiles;
+    const int nsteps = my_tiles * dsteps;
+
+    if (tid == 0) {
+        for (int s = 0; s < GX_STAGES; ++s) { mbar_init(full + s, GX_LOADERS); mbar_init(empty + s, 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(acc_full + b, 1); mbar_init(acc_free + b, 128); }
+        mbar_fence_init();
+    }
+    if (warp == 4) tmem_alloc(s_tmem, 128);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *s_tmem;
+
+    if (warp < 4) {
+        auto issue = [&](int s) {
+            unsigned char* st = smem + (s % GX_STAGES) * GH_STAGE;
+            const int64_t p0 = ((int64_t)blockIdx.x + (int64_t)(s / dsteps) * gridDim.x) * 128;
+            const int d0 = (s % dsteps) * GX_KSTEP;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {                                // A: row d = c >> 5, 16-byte chunk c & 31
+                const int c = tid + GX_LOADERS * i;
+                const int row = c >> 5, ch = c & 31;
+                const int64_t p = p0 + ch * 4;
+                const bool ok = p < HW;
+                const float* src = gt + (ok ? (size_t)(d0 + row) * HW + p : 0);
+                unsigned char* dst = st + (ch >> 3) * 4096 + sw128_32b_offset(row, ch & 7);
+                cp_async16(smem_u32(dst), src, ok ? 16u : 0u);
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {                                // B: row k = c >> 3, chunk c & 7
+                const int c = tid + GX_LOADERS * i;
+                const int row = c >> 3, ch = c & 7;
+                cp_async16(smem_u32(st + GH_A_BYTES + sw128_offset(row, ch)), C + (size_t)row * D + d0 + ch * 4, 16u);
+            }
+            cp_async_commit();
+        };
+        if (nsteps > 0) issue(0);
+        if (nsteps > 1) issue(1);
+        for (int s = 0; s < nsteps; ++s) {
+            if (s + 1 < nsteps) cp_async_wait<1>();
+            else cp_async_wait<0>();
+            if (s >= 2) mbar_wait(empty + (s - 2) % GX_STAGES, ((s - 2) / GX_STAGES) & 1);
+            unsigned char* st = smem + (s % GX_STAGES) * GH_STAGE;
+            unsigned char* lo_st = smem + GH_LO_OFF + (s & 1) * GH_STAGE;
+#pragma unroll
+            for (int i = 0; i < 12; ++i) {
+                const int c = tid + GX_LOADERS * (i < 8 ? i : i - 8);
+                const uint32_t off = i < 8 ? (uint32_t)((c & 31) >> 3) * 4096u + sw128_32b_offset(c >> 5, c & 7)
+                                           : (uint32_t)GH_A_BYTES + sw128_offset(c >> 3, c & 7);
+                const float4 v = *reinterpret_cast<const float4*>(st + off);
+                float4 hh, ll;
+                hh.x = __uint_as_float(__float_as_uint(v.x) & 0xffffe000u); ll.x = v.x - hh.x;
+                hh.y = __uint_as_float(__float_as_uint(v.y) & 0xffffe000u); ll.y = v.y - hh.y;
+                hh.z = __uint_as_float(__float_as_uint(v.z) & 0xffffe000u); ll.z = v.z - hh.z;
+                hh.w = __uint_as_float(__float_as_uint(v.w) & 0xffffe000u); ll.w = v.w - hh.w;
+                *reinterpret_cast<float4*>(st + off) = hh;
+                *reinterpret_cast<float4*>(lo_st + off) = ll;
+            }
+            fence_async_smem();
+            mbar_arrive(full + s % GX_STAGES);
+            if (s + 2 < nsteps) {
+                if (s >= 1) mbar_wait(empty + (s - 1) % GX_STAGES, ((s - 1) / GX_STAGES) & 1);
+                issue(s + 2);
+            }
+        }
+    } else if (warp > 4) {
+        const int q = warp & 3;
+        const int nchunks = nsteps / GX_CHUNK;                           // dsteps is even: chunks never straddle tiles
+        const int chunks_per_tile = dsteps / GX_CHUNK;
+        float acc[64];
+#pragma unroll
+        for (int k = 0; k < 64; ++k) acc[k] = 0.0f;
+        for (int c = 0; c < nchunks; ++c) {
+            const int bsel = c & 1;
+            mbar_wait(acc_full + bsel, (c >> 1) & 1);
+            tc_fence_after();
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                uint32_t r[32];
+                tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + bsel * 64 + half * 32, r);
+                tmem_wait_ld();
+#pragma unroll
+                for (int k = 0; k < 32; ++k) acc[half * 32 + k] += __uint_as_float(r[k]);
+            }
+            tc_fence_before();
+            mbar_arrive(acc_free + bsel);
+            if ((c + 1) % chunks_per_tile == 0) {
+                const int64_t p = ((int64_t)blockIdx.x + (int64_t)(c / chunks_per_tile) * gridDim.x) * 128 + q * 32 + lane;
+                if (p < HW) {
+#pragma unroll
+                    for (int k = 0; k < 64; ++k) h[(size_t)k * HW + p] = acc[k];
+                }
+#pragma unroll
+                for (int k = 0; k < 64; ++k) acc[k] = 0.0f;
+            }
+        }
+    } else if (lane == 0) {
+        // A: MN-major (bit 15 of the instruction descriptor), B: K-major
+        const uint32_t idesc = umma_idesc_tf32_f32(128, 64) | (1u << 15);
+        for (int s = 0; s < nsteps; ++s) {
+            const int c = s / GX_CHUNK, bsel = c & 1;
+            const bool first = s % GX_CHUNK == 0;
+            if (first && c >= 2) {
+                mbar_wait(acc_free + bsel, ((c >> 1) - 1) & 1);
+                tc_fence_after();
+            }
+            mbar_wait(full + s % GX_STAGES, (s / GX_STAGES) & 1);
+            tc_fence_after();
+            const uint32_t st = smem_u32(smem + (s % GX_STAGES) * GH_STAGE);
+            const uint32_t lo = smem_u32(smem + GH_LO_OFF + (s & 1) * GH_STAGE);
+#pragma unroll
+            for (int k8 = 0; k8 < GX_KSTEP / 8; ++k8) {
+                const uint64_t a_hi = umma_desc_mn_sw128_32b(st + k8 * 1024, lbo, sbo);
+                const uint64_t a_lo = umma_desc_mn_sw128_32b(lo + k8 * 1024, lbo, sbo);
+                const uint64_t koff = (uint64_t)((k8 * 32) >> 4);
+                const uint64_t b_hi = umma_desc_k_sw128(st + GH_A_BYTES) + koff;
+                const uint64_t b_lo = umma_desc_k_sw128(lo + GH_A_BYTES) + koff;
+                const uint32_t d_t = tmem + bsel * 64;
+                umma_tf32(d_t, a_lo, b_hi, idesc, (!first || k8 > 0) ? 1u : 0u);
+                umma_tf32(d_t, a_hi, b_lo, idesc, 1u);
+                umma_tf32(d_t, a_hi, b_hi, idesc, 1u);
+            }
+            umma_commit(empty + s % GX_STAGES);
+            if (s % GX_CHUNK == GX_CHUNK - 1) umma_commit(acc_full + bsel);
+        }
+    }
+    __syncthreads();
+    if (warp == 4) {
+        tc_fence_after();
+        tmem_dealloc(tmem, 128);
+    }
+}
+
+bool launch_gemm_h_tf32x3(const float* C, const float* gt, float* h, int D, int Lc, int64_t HW, cudaStream_t st, int* rc)
+{
+    static const bool off = [] { const char* e = getenv("LSV2_DC_SIMT"); return e && e[0] == '1'; }();
+    static const int dbg = [] { const char* e = getenv("LSV2_GH_DESC"); return e ? atoi(e) : 0; }();
+    *rc = LSV2_OK;
+    if (off || Lc != 64 || D < 64 || D % 64 != 0 || HW < 128 || (HW & 3) != 0 ||
+        (reinterpret_cast<uintptr_t>(C) & 15) != 0 || (reinterpret_cast<uintptr_t>(gt) & 15) != 0)
+        return false;
+    const int ntiles = (int)ceil_div(HW, (int64_t)128);
+    const int grid = min(ntiles, NUM_SMS);
+    // panels of 32 pixels x 32 d (4 KB) side by side; 4-d groups 512 B apart inside a panel
+    uint32_t lbo = 4096, sbo = 512;
+    if (dbg == 1) { lbo = 512; sbo = 4096; }
+    cudaError_t e = cudaFuncSetAttribute(k_gemm_h_tf32x3, cudaFuncAttributeMaxDynamicSharedMemorySize, GH_TOTAL);
+    if (e == cudaSuccess) k_gemm_h_tf32x3<<<grid, GH_THREADS, GH_TOTAL, st>>>(C, gt, h, D, HW, ntiles, lbo, sbo);
+    if (e != cudaSuccess || cudaGetLastError() != cudaSuccess) *rc = LSV2_ECUDA;
+    return true;
+}
+
 // true when the tensor-core path took the product; false -> the caller runs its CUDA-core kernel
 bool launch_gemm_nt_tf32x3(const float* X, const float* Y, float* out, int D, int Lc, int64_t HW, cudaStream_t st,
                            int* rc)

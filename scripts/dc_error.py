@@ -23,3 +23,20 @@ for D, HW in [(512, 6400), (512, 121200), (512, 762048), (64, 762048)]:
         _decode_bwd(1, 64, D, HW, w, None, dF, None, dC, w.device)
     t1.record(); torch.cuda.synchronize()
     print("   ms per call %.3f" % (t0.elapsed_time(t1) / 5))
+
+print("h = C gt (dW product)")
+for D, HW in [(512, 6400), (512, 762048), (512, 1189 * 4)]:
+    g = torch.Generator(device="cuda").manual_seed(2)
+    C = torch.randn((1, 64, D), generator=g, device="cuda")
+    gt = torch.randn((D, HW), generator=g, device="cuda")
+    h = torch.full((64, HW), float("nan"), device="cuda")
+    _decode_bwd(1, 64, D, HW, None, C, gt, h, None, gt.device)
+    ref = C[0].double() @ gt.double()
+    err = (h.double() - ref).abs()
+    print(D, HW, "max err / max|ref| %.3e" % float(err.max() / ref.abs().max()), "nan", int(torch.isnan(h).sum()))
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for _ in range(5):
+        _decode_bwd(1, 64, D, HW, None, C, gt, h, None, gt.device)
+    t1.record(); torch.cuda.synchronize()
+    print("   ms per call %.3f" % (t0.elapsed_time(t1) / 5))
