@@ -14,9 +14,9 @@
 // each chunk into round-to-nearest fp32 register accumulators while the next chunk runs into the other TMEM
 // buffer -- measured error then equals the CUDA-core fp32 kernel's.
 //
-// One CTA = a slab of pixels x MT*128 rows of X.  Warps 0-3 stream 32-pixel steps of X and Y into 128B-swizzled
+// One CTA = a slab of pixels x MT*128 rows of X.  Warps 0-7 stream 32-pixel steps of X and Y into 128B-swizzled
 // tiles with 16-byte async copies, split the chunks they copied themselves (no cross-thread hand-off), and
-// arrive on the stage's barrier; warp 4 issues the MMAs (2 x MT x [128 x 64] fp32 in TMEM); 4 warps per M tile
+// arrive on the stage's barrier; the next warp issues the MMAs (2 x MT x [128 x 64] fp32 in TMEM); 4 warps per M tile
 // accumulate the chunks and at the end add their registers to `out` (split-K over the slabs: fp32 atomics).
 #include "common.cuh"
 #include "tc_common.cuh"
@@ -26,7 +26,8 @@ using namespace tc;
 
 constexpr int GX_STAGES = 3;                       // raw (-> hi) tiles in flight; the lo tiles have 2 buffers
 constexpr int GX_KSTEP = 32;                       // pixels per stage: 32 fp32 = one 128-byte swizzled row
-constexpr int GX_LOADERS = 128;
+constexpr int GX_LOADERS = 256;                    // 8 warps copy + split (they are the critical path of a step)
+constexpr int GX_LW = GX_LOADERS / 32;             // the MMA warp id
 constexpr int gx_threads(int MT) { return GX_LOADERS + 32 + 128 * MT; }   // + MMA warp + 4 epilogue warps per M tile
 constexpr int GX_CHUNK = 2;                        // steps accumulated in TMEM before the registers take over
 constexpr int GX_Y_BYTES = 64 * 128;               // 8 KB
@@ -93,15 +94,15 @@ k_gemm_nt_tf32x3(const float* __restrict__ X, const float* __restrict__ Y, float
         for (int b = 0; b < 2; ++b) { mbar_init(acc_full + b, 1); mbar_init(acc_free + b, 128 * MT); }
         mbar_fence_init();
     }
-    if (warp == 4) tmem_alloc(s_tmem, L::TMEM_COLS);
+    if (warp == GX_LW) tmem_alloc(s_tmem, L::TMEM_COLS);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *s_tmem;
 
-    if (warp < 4) {
+    if (warp < GX_LW) {
         // ---- loaders: chunk c = tid + 128*i of a tile -> row c>>3, 16-byte chunk c&7 -----------------
-        constexpr int XCH = MT * 8, YCH = 4;
+        constexpr int XCH = MT * 1024 / GX_LOADERS, YCH = 512 / GX_LOADERS;
         auto issue = [&](int s) {
             unsigned char* st = smem + (s % GX_STAGES) * L::STAGE;
             const int64_t p0 = p_beg + (int64_t)s * GX_KSTEP;
@@ -151,10 +152,10 @@ k_gemm_nt_tf32x3(const float* __restrict__ X, const float* __restrict__ Y, float
                 issue(s + 2);
             }
         }
-    } else if (warp > 4) {
+    } else if (warp > GX_LW) {
         // ---- epilogue warps: TMEM lane = X row inside the tile, column = k ---------------------------
         // warp 5 + 4*m + j drains M tile m; a warp may only read the TMEM lane quarter (warp id % 4)
-        const int q = warp & 3, m = (warp - 5) >> 2;
+        const int q = warp & 3, m = (warp - GX_LW - 1) >> 2;
         const int nchunks = (nsteps + GX_CHUNK - 1) / GX_CHUNK;
         float acc[64];
 #pragma unroll
@@ -214,7 +215,7 @@ k_gemm_nt_tf32x3(const float* __restrict__ X, const float* __restrict__ Y, float
         }
     }
     __syncthreads();
-    if (warp == 4) {
+    if (warp == GX_LW) {
         tc_fence_after();
         tmem_dealloc(tmem, L::TMEM_COLS);
     }
@@ -233,6 +234,7 @@ constexpr int GH_LO_OFF = GX_STAGES * GH_STAGE;
 constexpr int GH_BAR_OFF = GH_LO_OFF + 2 * GH_STAGE;
 constexpr int GH_TOTAL = GH_BAR_OFF + 1024 + 128;
 constexpr int GH_THREADS = GX_LOADERS + 32 + 128;
+constexpr int GH_ACH = 1024 / GX_LOADERS, GH_BCH = 512 / GX_LOADERS;   // 16-byte chunks per loader thread and step
 
 // MN-major operand of 32-bit elements: layout type 1 = SWIZZLE_128B_BASE32B (the plain 128B swizzle yields zeros for
 // an MN-major tf32 operand).  Atom = 128-byte rows (32 fp32 along MN) x 4 k; inside an atom the 32-byte unit index is
@@ -278,19 +280,19 @@ k_gemm_h_tf32x3(const float* __restrict__ C, const float* __restrict__ gt, float
         for (int b = 0; b < 2; ++b) { mbar_init(acc_full + b, 1); mbar_init(acc_free + b, 128); }
         mbar_fence_init();
     }
-    if (warp == 4) tmem_alloc(s_tmem, 128);
+    if (warp == GX_LW) tmem_alloc(s_tmem, 128);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *s_tmem;
 
-    if (warp < 4) {
+    if (warp < GX_LW) {
         auto issue = [&](int s) {
             unsigned char* st = smem + (s % GX_STAGES) * GH_STAGE;
             const int64_t p0 = ((int64_t)blockIdx.x + (int64_t)(s / dsteps) * gridDim.x) * 128;
             const int d0 = (s % dsteps) * GX_KSTEP;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {                                // A: row d = c >> 5, 16-byte chunk c & 31
+            for (int i = 0; i < GH_ACH; ++i) {                           // A: row d = c >> 5, 16-byte chunk c & 31
                 const int c = tid + GX_LOADERS * i;
                 const int row = c >> 5, ch = c & 31;
                 const int64_t p = p0 + ch * 4;
@@ -300,7 +302,7 @@ k_gemm_h_tf32x3(const float* __restrict__ C, const float* __restrict__ gt, float
                 cp_async16(smem_u32(dst), src, ok ? 16u : 0u);
             }
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {                                // B: row k = c >> 3, chunk c & 7
+            for (int i = 0; i < GH_BCH; ++i) {                           // B: row k = c >> 3, chunk c & 7
                 const int c = tid + GX_LOADERS * i;
                 const int row = c >> 3, ch = c & 7;
                 cp_async16(smem_u32(st + GH_A_BYTES + sw128_offset(row, ch)), C + (size_t)row * D + d0 + ch * 4, 16u);
@@ -316,9 +318,9 @@ k_gemm_h_tf32x3(const float* __restrict__ C, const float* __restrict__ gt, float
             unsigned char* st = smem + (s % GX_STAGES) * GH_STAGE;
             unsigned char* lo_st = smem + GH_LO_OFF + (s & 1) * GH_STAGE;
 #pragma unroll
-            for (int i = 0; i < 12; ++i) {
-                const int c = tid + GX_LOADERS * (i < 8 ? i : i - 8);
-                const uint32_t off = i < 8 ? (uint32_t)((c & 31) >> 3) * 4096u + sw128_32b_offset(c >> 5, c & 7)
+            for (int i = 0; i < GH_ACH + GH_BCH; ++i) {
+                const int c = tid + GX_LOADERS * (i < GH_ACH ? i : i - GH_ACH);
+                const uint32_t off = i < GH_ACH ? (uint32_t)((c & 31) >> 3) * 4096u + sw128_32b_offset(c >> 5, c & 7)
                                            : (uint32_t)GH_A_BYTES + sw128_offset(c >> 3, c & 7);
                 const float4 v = *reinterpret_cast<const float4*>(st + off);
                 float4 hh, ll;
@@ -336,7 +338,7 @@ k_gemm_h_tf32x3(const float* __restrict__ C, const float* __restrict__ gt, float
                 issue(s + 2);
             }
         }
-    } else if (warp > 4) {
+    } else if (warp > GX_LW) {
         const int q = warp & 3;
         const int nchunks = nsteps / GX_CHUNK;                           // dsteps is even: chunks never straddle tiles
         const int chunks_per_tile = dsteps / GX_CHUNK;
@@ -398,7 +400,7 @@ k_gemm_h_tf32x3(const float* __restrict__ C, const float* __restrict__ gt, float
         }
     }
     __syncthreads();
-    if (warp == 4) {
+    if (warp == GX_LW) {
         tc_fence_after();
         tmem_dealloc(tmem, 128);
     }
