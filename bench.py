@@ -185,8 +185,9 @@ def kernels_per_frame(W, H, fused: bool) -> int:
     """liblsv2 kernels launched per frame (torch's own fill kernels are not counted)."""
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
     tb = max(1, math.ceil(math.log2(tiles)))
-    sort_passes = (31 + tb + 7) // 8
-    n = 1 + 1 + 1 + 1 + sort_passes + 1     # preprocess, scan, duplicate, histogram, onesweep passes, ranges
+    # preprocess, scan | depth keys, histogram, 4 depth passes over the Gaussians, gather, scan | duplicate, tile
+    # histogram, ranges, tile passes over the instances
+    n = 1 + 1 + (1 + 1 + (31 + 7) // 8 + 1 + 1) + (1 + 1 + 1 + (tb + 7) // 8)
     n += 2 if fused else 3                  # codebook prep + fused blend/decode | blend + codebook prep + decode
     return n
 
