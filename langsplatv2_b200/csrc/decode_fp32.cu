@@ -372,11 +372,100 @@ k_topk_soft_code(int64_t N, int C, int k, const float* __restrict__ logits, floa
     }
 }
 
+// C == 64 (the LangSplatV2 codebook size): 8 lanes per row, 8 consecutive channels per lane (two 16-byte loads and
+// stores), 3-step reductions, 4 rows per warp -- half the instructions per row of the one-warp-per-row kernel.
+__device__ __forceinline__ float group8_sum_in_order(float loc, int lane)
+{
+    float t = 0.0f;
+#pragma unroll
+    for (int l = 0; l < 8; ++l) t += __shfl_sync(0xffffffffu, loc, (lane & ~7) + l);
+    return t;
+}
+
+__global__ void __launch_bounds__(256)
+k_topk_soft_code_c64(int64_t N, int k, const float* __restrict__ logits, float* __restrict__ dense,
+                     float* __restrict__ weights, float* __restrict__ indices)
+{
+    const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+    const int lane = threadIdx.x & 31, sub = threadIdx.x & 7;
+    const bool live = row < N;
+    const int64_t r = live ? row : N - 1;                      // every lane stays in the shuffles
+    const float4* x4 = reinterpret_cast<const float4*>(logits + (size_t)r * 64 + sub * 8);
+    const float4 a = x4[0], b = x4[1];
+    float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    float mx = v[0];
+#pragma unroll
+    for (int i = 1; i < 8; ++i) mx = fmaxf(mx, v[i]);
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    float s = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { v[i] = expf(v[i] - mx); s += v[i]; }
+    s = group8_sum_in_order(s, lane);                          // channel order up to the 8-wide partials
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] = v[i] / s;
+    uint32_t sel = 0;                                          // bit i: channel sub*8 + i selected
+    for (int j = 0; j < k; ++j) {
+        float best = -1.0f;
+        int bc = 0x7fffffff;
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+            if (!((sel >> i) & 1u) && v[i] > best) { best = v[i]; bc = sub * 8 + i; }
+#pragma unroll
+        for (int o = 4; o > 0; o >>= 1) {
+            const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+            const int oc = __shfl_xor_sync(0xffffffffu, bc, o);
+            if (ob > best || (ob == best && oc < bc)) { best = ob; bc = oc; }
+        }
+        if ((bc >> 3) == sub && bc < 64) sel |= 1u << (bc & 7);
+    }
+    float loc = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) loc += ((sel >> i) & 1u) ? v[i] : 0.0f;
+    const float den = group8_sum_in_order(loc, lane) + 1e-10f;
+    // rank of this lane's first selected channel among the row's selected ones
+    const int cnt = __popc(sel);
+    int before = 0;
+#pragma unroll
+    for (int l = 0; l < 8; ++l) {
+        const int c = __shfl_sync(0xffffffffu, cnt, (lane & ~7) + l);
+        if (l < sub) before += c;
+    }
+    if (!live) return;
+    float y[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) y[i] = ((sel >> i) & 1u) ? v[i] / den : 0.0f;
+    if (dense) {
+        float4* d4 = reinterpret_cast<float4*>(dense + (size_t)row * 64 + sub * 8);
+        d4[0] = make_float4(y[0], y[1], y[2], y[3]);
+        d4[1] = make_float4(y[4], y[5], y[6], y[7]);
+    }
+    if (weights || indices) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            if ((sel >> i) & 1u) {
+                const int o = before + __popc(sel & ((1u << i) - 1u));
+                if (o < k) {
+                    if (weights) weights[(size_t)row * k + o] = y[i];
+                    if (indices) indices[(size_t)row * k + o] = (float)(sub * 8 + i);
+                }
+            }
+        }
+    }
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
 int launch_topk_soft_code(int64_t N, int C, int k, const float* logits, float* dense, float* weights,
                           float* indices, cudaStream_t st)
 {
     if (N <= 0) return LSV2_OK;
     if (C <= 0 || C > 256 || k <= 0 || k > C) return LSV2_EUNSUPPORTED;
+    if (C == 64 && aligned16(logits) && aligned16(dense)) {
+        k_topk_soft_code_c64<<<(unsigned)ceil_div(N * 8, 256), 256, 0, st>>>(N, k, logits, dense, weights, indices);
+        LSV2_LAUNCH_CHECK("k_topk_soft_code_c64");
+        return LSV2_OK;
+    }
     const unsigned grid = (unsigned)ceil_div(N * 32, 256);
     if (C <= 32) k_topk_soft_code<1><<<grid, 256, 0, st>>>(N, C, k, logits, dense, weights, indices);
     else if (C <= 64) k_topk_soft_code<2><<<grid, 256, 0, st>>>(N, C, k, logits, dense, weights, indices);
@@ -454,11 +543,71 @@ k_topk_soft_code_bwd(int64_t N, int C, const float* __restrict__ logits, const f
     }
 }
 
+// C == 64 version of the backward: same 8-lanes-per-row layout as k_topk_soft_code_c64
+__global__ void __launch_bounds__(256)
+k_topk_soft_code_bwd_c64(int64_t N, const float* __restrict__ logits, const float* __restrict__ dense,
+                         const float* __restrict__ d_dense, float* __restrict__ d_logits)
+{
+    const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+    const int sub = threadIdx.x & 7;
+    const bool live = row < N;
+    const int64_t r = live ? row : N - 1;
+    const size_t base = (size_t)r * 64 + sub * 8;
+    const float4 xa = *reinterpret_cast<const float4*>(logits + base), xb = *reinterpret_cast<const float4*>(logits + base + 4);
+    const float4 ya = *reinterpret_cast<const float4*>(dense + base), yb = *reinterpret_cast<const float4*>(dense + base + 4);
+    const float4 ga = *reinterpret_cast<const float4*>(d_dense + base), gb = *reinterpret_cast<const float4*>(d_dense + base + 4);
+    float v[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
+    const float y[8] = {ya.x, ya.y, ya.z, ya.w, yb.x, yb.y, yb.z, yb.w};
+    const float g[8] = {ga.x, ga.y, ga.z, ga.w, gb.x, gb.y, gb.z, gb.w};
+    float mx = v[0];
+#pragma unroll
+    for (int i = 1; i < 8; ++i) mx = fmaxf(mx, v[i]);
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    float s = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { v[i] = expf(v[i] - mx); s += v[i]; }
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    float ts = 0.0f, G = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        v[i] = v[i] / s;
+        const bool m = y[i] != 0.0f;
+        ts += m ? v[i] : 0.0f;
+        G = fmaf(m ? g[i] : 0.0f, v[i], G);
+    }
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) {
+        ts += __shfl_xor_sync(0xffffffffu, ts, o);
+        G += __shfl_xor_sync(0xffffffffu, G, o);
+    }
+    ts += 1e-10f;
+    const float inv = 1.0f / ts, sub2 = G * inv * inv;
+    float dp[8], Dd = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        dp[i] = (y[i] != 0.0f) ? g[i] * inv - sub2 : 0.0f;
+        Dd = fmaf(dp[i], v[i], Dd);
+    }
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) Dd += __shfl_xor_sync(0xffffffffu, Dd, o);
+    if (!live) return;
+    float4* o4 = reinterpret_cast<float4*>(d_logits + (size_t)row * 64 + sub * 8);
+    o4[0] = make_float4(v[0] * (dp[0] - Dd), v[1] * (dp[1] - Dd), v[2] * (dp[2] - Dd), v[3] * (dp[3] - Dd));
+    o4[1] = make_float4(v[4] * (dp[4] - Dd), v[5] * (dp[5] - Dd), v[6] * (dp[6] - Dd), v[7] * (dp[7] - Dd));
+}
+
 int launch_topk_soft_code_bwd(int64_t N, int C, const float* logits, const float* dense, const float* d_dense,
                               float* d_logits, cudaStream_t st)
 {
     if (N == 0) return LSV2_OK;
     if (C <= 0 || C > 256) return LSV2_EUNSUPPORTED;
+    if (C == 64 && aligned16(logits) && aligned16(dense) && aligned16(d_dense) && aligned16(d_logits)) {
+        k_topk_soft_code_bwd_c64<<<(unsigned)ceil_div(N * 8, 256), 256, 0, st>>>(N, logits, dense, d_dense, d_logits);
+        LSV2_LAUNCH_CHECK("k_topk_soft_code_bwd_c64");
+        return LSV2_OK;
+    }
     const unsigned grid = (unsigned)ceil_div(N * 32, 256);
     if (C <= 32) k_topk_soft_code_bwd<1><<<grid, 256, 0, st>>>(N, C, logits, dense, d_dense, d_logits);
     else if (C <= 64) k_topk_soft_code_bwd<2><<<grid, 256, 0, st>>>(N, C, logits, dense, d_dense, d_logits);
