@@ -97,6 +97,42 @@ class GradBucket:
     def zero(self) -> None:
         self.flat.zero_()
 
+    # ---- all-reduce overlapped with the producer of the gradient (attached buckets) ----
+    def begin_overlap(self) -> None:
+        self._works = []
+        if self.flat.is_cuda and getattr(self, "_side", None) is None:
+            self._side = torch.cuda.Stream(device=self.flat.device)
+
+    def reduce_slice(self, a: int, b: int) -> None:
+        """Flat elements [a, b) are final on the current stream: start their all-reduce(SUM) now, on a side stream, so
+        it runs under whatever the current stream does next."""
+        if not (dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1) or b <= a:
+            return
+        if not self.flat.is_cuda:
+            dist.all_reduce(self.flat[a:b], op=dist.ReduceOp.SUM)
+            return
+        ev = torch.cuda.Event()
+        ev.record()
+        with torch.cuda.stream(self._side):
+            self._side.wait_event(ev)
+            self._works.append(dist.all_reduce(self.flat[a:b], op=dist.ReduceOp.SUM, async_op=True))
+
+    def wait_slice(self, i: int) -> None:
+        """Make the current stream wait for the i-th ``reduce_slice`` of this step (no-op on CPU: it was synchronous)."""
+        if i < len(self._works) and self._works[i] is not None:
+            self._works[i].wait()
+            self._works[i] = None
+
+    def finish_overlap(self, done_upto: int) -> None:
+        """Reduce what ``reduce_slice`` has not covered ([done_upto, numel)) and make the current stream wait for
+        every slice."""
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1 and done_upto < self.flat.numel():
+            dist.all_reduce(self.flat[done_upto:], op=dist.ReduceOp.SUM)
+        for w in getattr(self, "_works", []):
+            if w is not None:
+                w.wait()
+        self._works = []
+
 
 def all_reduce_grads(params: Iterable[torch.Tensor]) -> None:
     """One-shot helper (allocates a bucket); training loops should hold a GradBucket instead."""

@@ -16,6 +16,25 @@ def _topk_dense(x: torch.Tensor, k: int) -> torch.Tensor:
     return dense
 
 
+class GradSink:
+    """Where ``_TopkSoftCode.backward`` writes d logits when a trainer wants the gradient chunk by chunk (N > 1 ranks:
+    the all-reduce of chunk i runs under the kernel of chunk i + 1, ``dist.GradBucket.reduce_slice``).  ``target`` is
+    the [N, C] view of the flat gradient bucket that already IS ``logits.grad``; ``on_chunk(a, b)`` is called with the
+    flat element range that has just been written on the current stream."""
+
+    def __init__(self, target: torch.Tensor, row_blocks, on_chunk):
+        self.target, self.row_blocks, self.on_chunk = target, list(row_blocks), on_chunk
+        self.used_upto = 0
+
+
+_GRAD_SINK = None
+
+
+def set_grad_sink(sink) -> None:
+    global _GRAD_SINK
+    _GRAD_SINK = sink
+
+
 class _TopkSoftCode(torch.autograd.Function):
     """One kernel forward, one kernel backward (the reference's autograd graph holds ~6 [N, C] temporaries)."""
 
@@ -31,6 +50,16 @@ class _TopkSoftCode(torch.autograd.Function):
         L_ = _abi.lib()
         x, dense = ctx.saved_tensors
         g = g.contiguous().float()
+        sink = _GRAD_SINK
+        if sink is not None and sink.target.shape == x.shape and sink.target.is_contiguous():
+            N, C = x.shape
+            for a, b in sink.row_blocks:
+                _abi.check(L_.lsv2_topk_soft_code_backward(b - a, C, x[a:].data_ptr(), dense[a:].data_ptr(),
+                                                           g[a:].data_ptr(), sink.target[a:].data_ptr(),
+                                                           _abi.stream_ptr(x.device)), "lsv2_topk_soft_code_backward")
+                sink.on_chunk(a * C, b * C)
+            sink.used_upto = N * C
+            return None, None            # the gradient already sits in logits.grad (the bucket view)
         dx = torch.empty_like(x)
         _abi.check(L_.lsv2_topk_soft_code_backward(x.shape[0], x.shape[1], x.data_ptr(), dense.data_ptr(),
                                                    g.data_ptr(), dx.data_ptr(), _abi.stream_ptr(x.device)),

@@ -10,12 +10,14 @@ Mirrors ``train.py --include_feature`` of the reference, one iteration per ``ste
     Adam on (logits, codebooks)       scene/gaussian_model.py:235-236,255 ; train.py:261-263
 
 Geometry is frozen (scene/gaussian_model.py:238-243).  Data parallel: each rank renders its own view and the
-gradients of (logits, codebooks) go through ONE flat all-reduce (``dist.GradBucket``), SUM as in the reference's
-``--accum_iter`` (train.py:261-263,348).  The hot kernels (top-k fwd/bwd, preprocess, binning, blend fwd/bwd,
+gradients of (logits, codebooks) are summed over the ranks in ONE flat bucket (``dist.GradBucket``; reduced in 4 row
+slices pipelined with the top-k backward and per-slice Adam steps), SUM as in the reference's ``--accum_iter``
+(train.py:261-263,348).  The hot kernels (top-k fwd/bwd, preprocess, binning, blend fwd/bwd,
 decode fwd/bwd) are liblsv2's; the loss expression and Adam are PyTorch's, as they are in the reference.
 """
 from __future__ import annotations
 
+import os
 from typing import Dict, Optional
 
 import torch
@@ -25,6 +27,7 @@ from . import dist as lsdist
 from .decode import decode_feature_map
 from .loss import column_sumsq, decode_cos_loss, normalized_cos_loss
 from .rasterizer import GaussianRasterizationSettings, GaussianRasterizer
+from . import sparse as lssparse
 from .sparse import softmax_to_topk_soft_code
 
 
@@ -67,9 +70,30 @@ class FeatureTrainer:
         self.optimizer = torch.optim.Adam([{"params": [self.logits, self.codebooks], "lr": lr}], lr=0.0, eps=1e-15,
                                           fused=fused_adam and dev.type == "cuda")
         self.bucket = None
+        self.overlap_chunks = int(os.environ.get("LSV2_OVERLAP_CHUNKS", "4"))
+        self._chunk_rows = None
+        self._chunk_opts = None
+        self.keep_last_grad = False
+        self.last_grad = None
         if lsdist.world_info()[1] > 1:
             self.bucket = lsdist.GradBucket([self.logits, self.codebooks])
             self.bucket.attach()                    # grads are written into the flat all-reduce buffer directly
+            if self.layers == 1 and dev.type == "cuda":
+                # row blocks of the logits: block i's gradient leaves the top-k backward, is all-reduced on a side
+                # stream, and gets its own (elementwise-identical) Adam step while block i + 1 is still in flight
+                n = self.logits.shape[0]
+                rows = -(-(-(-n // self.overlap_chunks)) // 1024) * 1024
+                self._chunk_rows = [(a, min(n, a + rows)) for a in range(0, n, rows)]
+                gview = self.bucket.views[0]
+                self._chunk_opts = []
+                for a, b in self._chunk_rows:
+                    p = self.logits.detach()[a:b]                   # leaf view of the same storage
+                    p.grad = gview[a:b]
+                    self._chunk_opts.append(torch.optim.Adam([{"params": [p], "lr": lr}], lr=0.0, eps=1e-15,
+                                                             fused=fused_adam))
+                cb = self.codebooks.detach()
+                cb.grad = self.bucket.views[1]
+                self._cb_opt = torch.optim.Adam([{"params": [cb], "lr": lr}], lr=0.0, eps=1e-15, fused=fused_adam)
         self.iteration = 0
         # instance capacity: the first `calib_steps` iterations read num_rendered back (the reference's one host sync
         # per frame); after that the frame runs with a bounded instance buffer and no host sync
@@ -139,11 +163,42 @@ class FeatureTrainer:
         """One iteration; returns the (detached, on-device) loss."""
         self.iteration += 1
         loss = self.loss(cam, gt, mask)
-        loss.backward()
+        if self._chunk_opts is not None and self.overlap_chunks > 1:
+            # the flat bucket [d logits || d codebooks] is reduced in slices: d logits leaves the top-k backward in
+            # row blocks, block i's all-reduce runs under block i + 1's kernel and under block i - 1's Adam
+            self.bucket.begin_overlap()
+            sink = lssparse.GradSink(self.bucket.views[0], self._chunk_rows, self.bucket.reduce_slice)
+            lssparse.set_grad_sink(sink)
+            try:
+                loss.backward()
+            finally:
+                lssparse.set_grad_sink(None)
+            if sink.used_upto == self.logits.numel():
+                self.bucket.reduce_slice(sink.used_upto, self.bucket.flat.numel())      # the codebook part
+                for i, opt in enumerate(self._chunk_opts):
+                    self.bucket.wait_slice(i)
+                    opt.step()
+                self.bucket.wait_slice(len(self._chunk_opts))
+                self._cb_opt.step()
+                self.bucket.finish_overlap(self.bucket.flat.numel())
+            else:                                   # the sink was not taken (shape mismatch): classic path
+                self.bucket.finish_overlap(0)
+                for opt in self._chunk_opts:
+                    opt.step()
+                self._cb_opt.step()
+        else:
+            loss.backward()
+            if self.bucket is not None:
+                self.bucket.sync()                  # ONE all-reduce(SUM) of [d logits || d codebooks]
+            if self._chunk_opts is not None:
+                for opt in self._chunk_opts:
+                    opt.step()
+                self._cb_opt.step()
+            else:
+                self.optimizer.step()
         if self.bucket is not None:
-            self.bucket.sync()                      # ONE all-reduce(SUM) of [d logits || d codebooks]
-        self.optimizer.step()
-        if self.bucket is not None:
+            if self.keep_last_grad:
+                self.last_grad = self.bucket.flat.clone()           # the all-reduced gradient of this step (tests)
             self.bucket.zero()
         else:
             self.optimizer.zero_grad(set_to_none=True)

@@ -401,6 +401,15 @@ b2.sync()
 ok = ok and all(torch.allclose(a, b.grad, rtol=1e-5, atol=1e-7) for a, b in zip(got, [logits, codebook]))
 b2.zero()
 ok = ok and float(logits.grad.abs().sum()) == 0.0
+# sliced reduction (FeatureTrainer at N > 1: the top-k backward hands d logits over in row blocks, each block's
+# all-reduce starts as soon as it is written; the codebook part goes with finish_overlap)
+loss_for(view).backward()
+b2.begin_overlap()
+n_log = logits.numel()
+for a in range(0, n_log, 1024):
+    b2.reduce_slice(a, min(n_log, a + 1024))
+b2.finish_overlap(n_log)
+ok = ok and all(torch.allclose(a, b.grad, rtol=1e-5, atol=1e-7) for a, b in zip(got, [logits, codebook]))
 dist.barrier()
 dist.destroy_process_group()
 sys.exit(0 if ok else 3)
