@@ -211,7 +211,9 @@ def run_train(args, dev, rank, world, scene, barrier):
     gts = {v: synthetic_gt(H, W, device=dev, seed=2 + v) for v in my_views}
     tr = FeatureTrainer(scene, topk=TOPK, layers=1, device=dev)
     loss = None
-    n_warm = tr.calib_steps + 3          # the calibration iterations (host sync, exact capacity) + 3 steady-state ones
+    # the calibration iterations (host sync, exact capacity) + steady-state ones (more at N > 1: the first sliced
+    # all-reduces on a fresh box set up NCCL connections lazily)
+    n_warm = tr.calib_steps + (3 if world == 1 else 10)
     for s in range(n_warm):
         v = my_views[s % len(my_views)]
         loss = tr.step(cams[v], *gts[v])
@@ -234,6 +236,9 @@ def run_train(args, dev, rank, world, scene, barrier):
             "final_loss": float(loss), "dtype": "f32",
             "config": {"workload": TRAIN_WL["name"], "views_per_iter": world,
                        "grad_allreduce_bytes": (tr.bucket.nbytes if tr.bucket is not None else 0),
+                       "grad_allreduce": ("none" if tr.bucket is None else
+                                          "flat bucket reduced in %d row slices, pipelined with the top-k backward and "
+                                          "per-slice Adam" % len(tr._chunk_rows or [0])),
                        "optimizer": "torch.optim.Adam(fused=True, eps=1e-15) on logits+codebook (dense, as the reference)"}}
 
 
