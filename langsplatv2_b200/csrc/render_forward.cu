@@ -404,11 +404,61 @@ k_compact_coeff(int P, int L, const int32_t* __restrict__ radii, const float* __
     if (lane == 0) sp_count[g] = count > RF_KMAX ? ROW_DENSE : count;
 }
 
+// L == 64: 8 lanes per row, 8 consecutive channels per lane (two 16-byte loads), 4 rows per warp
+__global__ void __launch_bounds__(256)
+k_compact_coeff_c64(int P, const int32_t* __restrict__ radii, const float* __restrict__ coeff,
+                    uint32_t* __restrict__ sp_count, uint16_t* __restrict__ sp_index, float* __restrict__ sp_weight)
+{
+    const int g = (int)(((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3);
+    const int sub = threadIdx.x & 7;
+    const bool live = g < P && radii[min(g, P - 1)] > 0;
+    float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (live) {
+        const float4* r4 = reinterpret_cast<const float4*>(coeff + (size_t)g * 64 + sub * 8);
+        const float4 a = r4[0], b = r4[1];
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    }
+    uint32_t nz = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) nz |= (v[i] != 0.0f ? 1u : 0u) << i;
+    const uint32_t cnt = __popc(nz);
+    uint32_t incl = cnt;                                      // inclusive prefix inside the 8-lane group
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o, 8);
+        if (sub >= o) incl += t;
+    }
+    const uint32_t total = __shfl_sync(0xffffffffu, incl, 7, 8);
+    if (g >= P) return;
+    if (!live) {
+        if (sub == 0) sp_count[g] = 0;
+        return;
+    }
+    uint32_t pos = incl - cnt;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        if ((nz >> i) & 1u) {
+            if (pos < RF_KMAX) {
+                sp_index[(size_t)g * RF_KMAX + pos] = (uint16_t)(sub * 8 + i);
+                sp_weight[(size_t)g * RF_KMAX + pos] = v[i];
+            }
+            ++pos;
+        }
+    }
+    if (sub == 0) sp_count[g] = total > RF_KMAX ? ROW_DENSE : total;
+}
+
 int launch_compact_coeff(int P, const lsv2_geom& g, const lsv2_features& f, cudaStream_t st)
 {
     if (P <= 0) return LSV2_OK;
     if (f.mode != LSV2_MODE_DENSE) return LSV2_OK;
     if (!f.coeff_dense || !f.sparse_count || !f.sparse_index || !f.sparse_weight || f.L <= 0) return LSV2_EINVAL;
+    if (f.L == 64 && (reinterpret_cast<uintptr_t>(f.coeff_dense) & 15) == 0) {
+        k_compact_coeff_c64<<<ceil_div((int64_t)P * 8, 256), 256, 0, st>>>(P, g.radii, f.coeff_dense, f.sparse_count,
+                                                                          f.sparse_index, f.sparse_weight);
+        LSV2_LAUNCH_CHECK("k_compact_coeff_c64");
+        return LSV2_OK;
+    }
     k_compact_coeff<<<ceil_div((int64_t)P * 32, 256), 256, 0, st>>>(P, f.L, g.radii, f.coeff_dense, f.sparse_count,
                                                                    f.sparse_index, f.sparse_weight);
     LSV2_LAUNCH_CHECK("k_compact_coeff");
