@@ -265,6 +265,21 @@ int lsv2_gram_loss_backward(int32_t Lc, int64_t HW, const float* wmap, const flo
                             const float* alpha_beta, const float* grad_out, float* dw, float* aw, float* bw, void* stream);
 int lsv2_colsumsq(int32_t D, int64_t HW, const float* x, float* out, void* stream);
 
+/* The same two calls for a ground truth given as gt = table[seg] (/root/reference/scene/cameras.py:59-96: the
+ * loader's form before it expands it; seg < 0 = unlabelled = masked out): CE = C table^T f32[Lc][nseg] stands in for
+ * h (h_p = CE[:, seg_p]), e2 f32[nseg] = |table_s|^2 for g2, seg i32[HW] for the mask. */
+int lsv2_gram_loss_forward_seg(int32_t Lc, int64_t HW, int32_t nseg, const float* wmap, const float* CE, const float* e2,
+                               const int32_t* seg, const float* G, int32_t normalize, float* u, float* alpha_beta,
+                               float* partial, void* stream);
+int lsv2_gram_loss_backward_seg(int32_t Lc, int64_t HW, int32_t nseg, const float* wmap, const float* CE,
+                                const int32_t* seg, const float* u, const float* alpha_beta, const float* grad_out,
+                                float* dw, float* aw, float* bw, void* stream);
+
+/* out[k][s] += sum_{p : seg[p] == s} x[k][p]   (x f32[Lc][HW], seg i32[HW] (< 0: skipped), out f32[Lc][nseg], caller
+ * zeroes out).  The feature stage's ground truth is table[seg] (/root/reference/scene/cameras.py:59-96), so the
+ * codebook gradient (alpha w) gt^T of lsv2_gram_loss_backward equals (segment sums of alpha w) . table. */
+int lsv2_segment_sum(int32_t Lc, int64_t HW, int32_t nseg, const float* x, const int32_t* seg, float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -62,7 +62,8 @@ EXPORTS = [
     "lsv2_preprocess", "lsv2_bin", "lsv2_compact_coeff", "lsv2_render_forward", "lsv2_forward",
     "lsv2_mark_visible", "lsv2_render_backward", "lsv2_decode_scratch_bytes", "lsv2_decode",
     "lsv2_decode_backward", "lsv2_topk_soft_code", "lsv2_topk_soft_code_backward", "lsv2_cos_loss_blocks", "lsv2_cos_loss_forward", "lsv2_cos_loss_backward",
-    "lsv2_gram_loss_forward", "lsv2_gram_loss_backward", "lsv2_colsumsq",
+    "lsv2_gram_loss_forward", "lsv2_gram_loss_backward", "lsv2_colsumsq", "lsv2_segment_sum",
+    "lsv2_gram_loss_forward_seg", "lsv2_gram_loss_backward_seg",
     "lsv2_render_decode_scratch_bytes", "lsv2_render_decode",
 ]
 
@@ -113,6 +114,10 @@ def lib() -> C.CDLL:
     L.lsv2_gram_loss_forward.argtypes = [C.c_int32, C.c_int64, _vp, _vp, _vp, _vp, _vp, C.c_int32, _vp, _vp, _vp, _vp]
     L.lsv2_gram_loss_backward.argtypes = [C.c_int32, C.c_int64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]
     L.lsv2_colsumsq.argtypes = [C.c_int32, C.c_int64, _vp, _vp, _vp]
+    L.lsv2_segment_sum.argtypes = [C.c_int32, C.c_int64, C.c_int32, _vp, _vp, _vp, _vp]
+    L.lsv2_gram_loss_forward_seg.argtypes = [C.c_int32, C.c_int64, C.c_int32, _vp, _vp, _vp, _vp, _vp, C.c_int32, _vp, _vp,
+                                             _vp, _vp]
+    L.lsv2_gram_loss_backward_seg.argtypes = [C.c_int32, C.c_int64, C.c_int32] + [_vp] * 10
     L.lsv2_render_decode_scratch_bytes.restype = C.c_size_t
     L.lsv2_render_decode_scratch_bytes.argtypes = [C.c_int32]
     L.lsv2_render_decode.argtypes = [P(View), P(Geom), P(Binning), P(Features), P(Image), _vp, C.c_int32,
@@ -120,7 +125,7 @@ def lib() -> C.CDLL:
     for name in ("lsv2_preprocess", "lsv2_bin", "lsv2_compact_coeff", "lsv2_render_forward", "lsv2_forward",
                  "lsv2_mark_visible", "lsv2_render_backward", "lsv2_decode", "lsv2_decode_backward",
                  "lsv2_topk_soft_code", "lsv2_topk_soft_code_backward", "lsv2_cos_loss_forward", "lsv2_cos_loss_backward",
-                 "lsv2_gram_loss_forward", "lsv2_gram_loss_backward", "lsv2_colsumsq", "lsv2_render_decode"):
+                 "lsv2_gram_loss_forward", "lsv2_gram_loss_backward", "lsv2_colsumsq", "lsv2_segment_sum", "lsv2_render_decode"):
         getattr(L, name).restype = C.c_int
     _lib = L
     return L

@@ -15,6 +15,7 @@ void set_cuda_error(cudaError_t e, const char* what)
 }
 
 int sort_num_passes(int nbits);
+int launch_segment_sum(int Lc, int64_t HW, int nseg, const float* x, const int32_t* seg, float* out, cudaStream_t st);
 int launch_decode_fp32(int levels, int Lc, int D, int64_t HW, const float* wmap, const float* codebooks,
                        int normalize, float* out, cudaStream_t st);
 int launch_decode_tc(int levels, int Lc, int D, int64_t HW, const float* wmap, const float* codebooks,
@@ -27,10 +28,11 @@ int launch_cos_loss_forward(int D, int64_t HW, const float* F, const float* gt, 
 int launch_cos_loss_backward(int D, int64_t HW, const float* F, const float* gt, const float* alpha_beta,
                              const float* grad_out, float* dF, cudaStream_t st);
 int launch_gram_loss_forward(int Lc, int64_t HW, const float* wmap, const float* h, const float* g2, const float* mask,
-                             const float* G, int normalize, float* u, float* alpha_beta, float* partial, cudaStream_t st);
+                             const float* G, int normalize, float* u, float* alpha_beta, float* partial,
+                             const int32_t* seg, int nseg, cudaStream_t st);
 int launch_gram_loss_backward(int Lc, int64_t HW, const float* wmap, const float* h, const float* u,
                               const float* alpha_beta, const float* grad_out, float* dw, float* aw, float* bw,
-                              cudaStream_t st);
+                              const int32_t* seg, int nseg, cudaStream_t st);
 int launch_colsumsq(int D, int64_t HW, const float* x, float* out, cudaStream_t st);
 int launch_topk_soft_code_bwd(int64_t N, int C, const float* logits, const float* dense, const float* d_dense,
                               float* d_logits, cudaStream_t st);
@@ -253,14 +255,42 @@ int lsv2_gram_loss_forward(int32_t Lc, int64_t HW, const float* wmap, const floa
                            float* partial, void* stream)
 {
     if (HW < 0 || (HW > 0 && (!wmap || !h || !g2 || !G || !u || !alpha_beta || !partial))) return LSV2_EINVAL;
-    return launch_gram_loss_forward(Lc, HW, wmap, h, g2, mask, G, normalize, u, alpha_beta, partial, (cudaStream_t)stream);
+    return launch_gram_loss_forward(Lc, HW, wmap, h, g2, mask, G, normalize, u, alpha_beta, partial, nullptr, 0,
+                                    (cudaStream_t)stream);
+}
+
+int lsv2_gram_loss_forward_seg(int32_t Lc, int64_t HW, int32_t nseg, const float* wmap, const float* CE, const float* e2,
+                               const int32_t* seg, const float* G, int32_t normalize, float* u, float* alpha_beta,
+                               float* partial, void* stream)
+{
+    if (HW < 0 || nseg <= 0 || (HW > 0 && (!wmap || !CE || !e2 || !seg || !G || !u || !alpha_beta || !partial)))
+        return LSV2_EINVAL;
+    return launch_gram_loss_forward(Lc, HW, wmap, CE, e2, nullptr, G, normalize, u, alpha_beta, partial, seg, nseg,
+                                    (cudaStream_t)stream);
 }
 
 int lsv2_gram_loss_backward(int32_t Lc, int64_t HW, const float* wmap, const float* h, const float* u,
                             const float* alpha_beta, const float* grad_out, float* dw, float* aw, float* bw, void* stream)
 {
     if (HW < 0 || (HW > 0 && (!wmap || !h || !u || !alpha_beta || !dw || !aw || !bw))) return LSV2_EINVAL;
-    return launch_gram_loss_backward(Lc, HW, wmap, h, u, alpha_beta, grad_out, dw, aw, bw, (cudaStream_t)stream);
+    return launch_gram_loss_backward(Lc, HW, wmap, h, u, alpha_beta, grad_out, dw, aw, bw, nullptr, 0,
+                                     (cudaStream_t)stream);
+}
+
+int lsv2_gram_loss_backward_seg(int32_t Lc, int64_t HW, int32_t nseg, const float* wmap, const float* CE,
+                                const int32_t* seg, const float* u, const float* alpha_beta, const float* grad_out,
+                                float* dw, float* aw, float* bw, void* stream)
+{
+    if (HW < 0 || nseg <= 0 || (HW > 0 && (!wmap || !CE || !seg || !u || !alpha_beta || !dw || !aw || !bw)))
+        return LSV2_EINVAL;
+    return launch_gram_loss_backward(Lc, HW, wmap, CE, u, alpha_beta, grad_out, dw, aw, bw, seg, nseg,
+                                     (cudaStream_t)stream);
+}
+
+int lsv2_segment_sum(int32_t Lc, int64_t HW, int32_t nseg, const float* x, const int32_t* seg, float* out, void* stream)
+{
+    if (Lc < 0 || HW < 0 || nseg < 0 || (HW > 0 && Lc > 0 && nseg > 0 && (!x || !seg || !out))) return LSV2_EINVAL;
+    return launch_segment_sum(Lc, HW, nseg, x, seg, out, (cudaStream_t)stream);
 }
 
 int lsv2_colsumsq(int32_t D, int64_t HW, const float* x, float* out, void* stream)

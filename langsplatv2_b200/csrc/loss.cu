@@ -122,10 +122,13 @@ __device__ __forceinline__ void cos_scalars(float m, float n2, float fg, float g
     if (normalize && n > 0.0f) beta -= m * qF * s * s / n;
 }
 
+// SEG: the ground truth is table[seg]; h is then (C table^T)[k][seg_p] (`h` = that [Lc][nseg] matrix), g2 the
+// per-segment |table_s|^2 and the mask is seg_p >= 0.
+template <bool SEG>
 __global__ void __launch_bounds__(LOSS_THREADS)
 k_gram_loss_fwd(int64_t HW, const float* __restrict__ wmap, const float* __restrict__ h, const float* __restrict__ g2,
                 const float* __restrict__ mask, const float* __restrict__ G, int normalize, float* __restrict__ u,
-                float* __restrict__ alpha_beta, float* __restrict__ partial)
+                float* __restrict__ alpha_beta, float* __restrict__ partial, const int32_t* __restrict__ seg, int nseg)
 {
     __shared__ __align__(16) float s_G[GL_LC][GL_LC];
     __shared__ float s_red[LOSS_THREADS / 32];
@@ -136,10 +139,13 @@ k_gram_loss_fwd(int64_t HW, const float* __restrict__ wmap, const float* __restr
     if (p < HW) {
         float w[GL_LC];
         float fg = 0.0f;
+        int sp = 0;
+        if (SEG) { sp = seg[p]; if (sp >= nseg) sp = -1; }
+        const int sc = max(sp, 0);
 #pragma unroll
         for (int k = 0; k < GL_LC; ++k) {
             w[k] = __ldg(wmap + (size_t)k * HW + p);
-            fg = fmaf(w[k], __ldg(h + (size_t)k * HW + p), fg);
+            fg = fmaf(w[k], SEG ? __ldg(h + (size_t)k * nseg + sc) : __ldg(h + (size_t)k * HW + p), fg);
         }
         float n2 = 0.0f;
 #pragma unroll
@@ -157,7 +163,8 @@ k_gram_loss_fwd(int64_t HW, const float* __restrict__ wmap, const float* __restr
             n2 = fmaf(w[k], acc, n2);
         }
         float alpha, beta;
-        cos_scalars(mask ? mask[p] : 1.0f, n2, fg, g2[p], normalize, cosv, alpha, beta);
+        if (SEG) cos_scalars(sp >= 0 ? 1.0f : 0.0f, n2, fg, g2[sc], normalize, cosv, alpha, beta);
+        else cos_scalars(mask ? mask[p] : 1.0f, n2, fg, g2[p], normalize, cosv, alpha, beta);
         alpha_beta[p] = alpha;
         alpha_beta[HW + p] = beta;
     }
@@ -172,13 +179,16 @@ k_gram_loss_fwd(int64_t HW, const float* __restrict__ wmap, const float* __restr
     }
 }
 
+template <bool SEG>
 __global__ void __launch_bounds__(LOSS_THREADS)
 k_gram_loss_bwd(int64_t HW, const float* __restrict__ wmap, const float* __restrict__ h, const float* __restrict__ u,
                 const float* __restrict__ alpha_beta, const float* __restrict__ grad_out, float* __restrict__ dw,
-                float* __restrict__ aw, float* __restrict__ bw)
+                float* __restrict__ aw, float* __restrict__ bw, const int32_t* __restrict__ seg, int nseg)
 {
     const int64_t p = (int64_t)blockIdx.x * LOSS_THREADS + threadIdx.x;
     if (p >= HW) return;
+    int sc = 0;
+    if (SEG) { sc = seg[p]; sc = (sc < 0 || sc >= nseg) ? 0 : sc; }
     const float go = -(grad_out ? grad_out[0] : 1.0f) / (float)HW;
     const float alpha = alpha_beta[p] * go, beta = alpha_beta[HW + p] * go;
     const int k0 = blockIdx.y * (GL_LC / gridDim.y), k1 = k0 + GL_LC / gridDim.y;
@@ -186,7 +196,7 @@ k_gram_loss_bwd(int64_t HW, const float* __restrict__ wmap, const float* __restr
     for (int k = k0; k < k1; ++k) {
         const size_t o = (size_t)k * HW + p;
         const float wv = __ldg(wmap + o);
-        dw[o] = fmaf(alpha, __ldg(h + o), beta * __ldg(u + o));
+        dw[o] = fmaf(alpha, SEG ? __ldg(h + (size_t)k * nseg + sc) : __ldg(h + o), beta * __ldg(u + o));
         aw[o] = alpha * wv;
         bw[o] = beta * wv;
     }
@@ -207,25 +217,74 @@ k_colsumsq(int D, int64_t HW, const float* __restrict__ x, float* __restrict__ o
 }
 
 int launch_gram_loss_forward(int Lc, int64_t HW, const float* wmap, const float* h, const float* g2, const float* mask,
-                             const float* G, int normalize, float* u, float* alpha_beta, float* partial, cudaStream_t st)
+                             const float* G, int normalize, float* u, float* alpha_beta, float* partial,
+                             const int32_t* seg, int nseg, cudaStream_t st)
 {
     if (Lc != GL_LC) return LSV2_EUNSUPPORTED;
     if (HW == 0) return LSV2_OK;
     const int64_t blocks = (HW + LOSS_THREADS - 1) / LOSS_THREADS;
-    k_gram_loss_fwd<<<(unsigned)blocks, LOSS_THREADS, 0, st>>>(HW, wmap, h, g2, mask, G, normalize, u, alpha_beta, partial);
+    if (seg)
+        k_gram_loss_fwd<true><<<(unsigned)blocks, LOSS_THREADS, 0, st>>>(HW, wmap, h, g2, mask, G, normalize, u,
+                                                                         alpha_beta, partial, seg, nseg);
+    else
+        k_gram_loss_fwd<false><<<(unsigned)blocks, LOSS_THREADS, 0, st>>>(HW, wmap, h, g2, mask, G, normalize, u,
+                                                                          alpha_beta, partial, nullptr, 0);
     LSV2_LAUNCH_CHECK("k_gram_loss_fwd");
     return LSV2_OK;
 }
 
 int launch_gram_loss_backward(int Lc, int64_t HW, const float* wmap, const float* h, const float* u,
                               const float* alpha_beta, const float* grad_out, float* dw, float* aw, float* bw,
-                              cudaStream_t st)
+                              const int32_t* seg, int nseg, cudaStream_t st)
 {
     if (Lc != GL_LC) return LSV2_EUNSUPPORTED;
     if (HW == 0) return LSV2_OK;
     const int64_t blocks = (HW + LOSS_THREADS - 1) / LOSS_THREADS;
-    k_gram_loss_bwd<<<dim3((unsigned)blocks, 4), LOSS_THREADS, 0, st>>>(HW, wmap, h, u, alpha_beta, grad_out, dw, aw, bw);
+    if (seg)
+        k_gram_loss_bwd<true><<<dim3((unsigned)blocks, 4), LOSS_THREADS, 0, st>>>(HW, wmap, h, u, alpha_beta, grad_out, dw,
+                                                                                  aw, bw, seg, nseg);
+    else
+        k_gram_loss_bwd<false><<<dim3((unsigned)blocks, 4), LOSS_THREADS, 0, st>>>(HW, wmap, h, u, alpha_beta, grad_out, dw,
+                                                                                   aw, bw, nullptr, 0);
     LSV2_LAUNCH_CHECK("k_gram_loss_bwd");
+    return LSV2_OK;
+}
+
+// out[k][s] += sum over the pixels p with seg[p] == s of x[k][p]  (k < Lc; seg < 0: pixel skipped).
+// The ground truth of the feature stage is a per-segment table gathered through a segmentation map
+// (scene/cameras.py:59-96: point_feature = feature_map[seg]), so (alpha w) gt^T = (segment sums of alpha w) . table.
+// A warp takes 32 consecutive pixels; when they share one segment (the common case) it adds ONE value per k.
+__global__ void __launch_bounds__(LOSS_THREADS)
+k_segment_sum(int Lc, int64_t HW, int nseg, const float* __restrict__ x, const int32_t* __restrict__ seg,
+              float* __restrict__ out)
+{
+    const int64_t p = (int64_t)blockIdx.x * LOSS_THREADS + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    int s = p < HW ? seg[p] : -1;
+    if (s >= nseg) s = -1;
+    const int s0 = __shfl_sync(0xffffffffu, s, 0);
+    const bool uniform = __all_sync(0xffffffffu, s == s0);
+    if (uniform && s0 < 0) return;
+    const int k0 = blockIdx.y * (Lc / gridDim.y), k1 = k0 + Lc / gridDim.y;
+    for (int k = k0; k < k1; ++k) {
+        float v = s >= 0 ? __ldg(x + (size_t)k * HW + p) : 0.0f;
+        if (uniform) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if (lane == 0 && v != 0.0f) atomicAdd(out + (size_t)k * nseg + s0, v);
+        } else if (s >= 0 && v != 0.0f) {
+            atomicAdd(out + (size_t)k * nseg + s, v);
+        }
+    }
+}
+
+int launch_segment_sum(int Lc, int64_t HW, int nseg, const float* x, const int32_t* seg, float* out, cudaStream_t st)
+{
+    if (HW == 0 || Lc <= 0 || nseg <= 0) return LSV2_OK;
+    const int64_t blocks = (HW + LOSS_THREADS - 1) / LOSS_THREADS;
+    const int ky = (Lc % 4 == 0) ? 4 : 1;
+    k_segment_sum<<<dim3((unsigned)blocks, ky), LOSS_THREADS, 0, st>>>(Lc, HW, nseg, x, seg, out);
+    LSV2_LAUNCH_CHECK("k_segment_sum");
     return LSV2_OK;
 }
 

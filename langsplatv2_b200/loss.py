@@ -130,6 +130,76 @@ class _GramCosLoss(torch.autograd.Function):
         return (dw if ctx.needs_input_grad[0] else None), dC, None, None, None, None
 
 
+class _GramCosLossSeg(torch.autograd.Function):
+    """``_GramCosLoss`` for the ground truth as the reference's data path holds it: a per-segment feature table gathered
+    through a segmentation map (scene/cameras.py:59-96, ``point_feature = feature_map[seg]``; seg < 0 = unlabelled,
+    which is also the mask).  With gt_p = E[seg_p] the two 64 x 512 x HW products collapse:
+    h = C gt = (C E^T)[:, seg]  (a 64 x 512 x S product and a gather), and
+    (alpha w) gt^T = (segment sums of alpha w) . E  (``lsv2_segment_sum`` + a 64 x S x 512 product)."""
+
+    @staticmethod
+    def forward(ctx, wmap, codebook, seg, table, normalize):
+        L_ = _abi.lib()
+        _abi.require_cuda(wmap, "language_feature_weight_map")
+        dev = wmap.device
+        w = wmap.contiguous().float()
+        Lc, HW = int(w.shape[0]), w[0].numel()
+        Cb = codebook.contiguous().float().reshape(Lc, -1)
+        E = table.contiguous().float()
+        sg = seg.reshape(-1).to(torch.int32).contiguous()
+        if sg.numel() != HW or E.shape[1] != Cb.shape[1]:
+            raise ValueError("seg must be [H, W] and table [S, D] with the codebook's D")
+        S = int(E.shape[0])
+        allow = torch.backends.cuda.matmul.allow_tf32
+        torch.backends.cuda.matmul.allow_tf32 = False
+        G = (Cb @ Cb.t()).contiguous()
+        h = (Cb @ E.t()).contiguous()                                # C table^T, [Lc, S]: h_p = h[:, seg_p]
+        torch.backends.cuda.matmul.allow_tf32 = allow
+        e2 = (E * E).sum(1).contiguous()
+        u = torch.empty_like(w)
+        ab = torch.empty((2, HW), dtype=torch.float32, device=dev)
+        partial = torch.empty(L_.lsv2_cos_loss_blocks(HW), dtype=torch.float32, device=dev)
+        _abi.check(L_.lsv2_gram_loss_forward_seg(Lc, HW, S, w.data_ptr(), h.data_ptr(), e2.data_ptr(), sg.data_ptr(),
+                                                 G.data_ptr(), 1 if normalize else 0, u.data_ptr(), ab.data_ptr(),
+                                                 partial.data_ptr(), _abi.stream_ptr(dev)),
+                   "lsv2_gram_loss_forward_seg")
+        ctx.save_for_backward(w, h, u, ab, sg, E, Cb)
+        ctx.cb_shape = codebook.shape
+        return 1.0 - partial.sum() / HW
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        L_ = _abi.lib()
+        w, h, u, ab, sg, E, Cb = ctx.saved_tensors
+        dev = w.device
+        Lc, HW, S = int(w.shape[0]), w[0].numel(), int(E.shape[0])
+        go = grad_out.reshape(1).contiguous().float()
+        dw, aw, bw = torch.empty_like(w), torch.empty_like(w), torch.empty_like(w)
+        _abi.check(L_.lsv2_gram_loss_backward_seg(Lc, HW, S, w.data_ptr(), h.data_ptr(), sg.data_ptr(), u.data_ptr(),
+                                                  ab.data_ptr(), go.data_ptr(), dw.data_ptr(), aw.data_ptr(),
+                                                  bw.data_ptr(), _abi.stream_ptr(dev)), "lsv2_gram_loss_backward_seg")
+        dC = None
+        if ctx.needs_input_grad[1]:
+            Sm = torch.zeros((Lc, S), dtype=torch.float32, device=dev)
+            _abi.check(L_.lsv2_segment_sum(Lc, HW, S, aw.data_ptr(), sg.data_ptr(), Sm.data_ptr(),
+                                           _abi.stream_ptr(dev)), "lsv2_segment_sum")
+            M = torch.zeros((Lc, Lc), dtype=torch.float32, device=dev)
+            _decode_bwd(1, Lc, Lc, HW, bw, None, w, None, M, dev)                  # (beta w) w^T
+            allow = torch.backends.cuda.matmul.allow_tf32
+            torch.backends.cuda.matmul.allow_tf32 = False
+            dC = (Sm @ E + M @ Cb).reshape(ctx.cb_shape)
+            torch.backends.cuda.matmul.allow_tf32 = allow
+        return (dw if ctx.needs_input_grad[0] else None), dC, None, None, None
+
+
+def decode_cos_loss_segments(weight_map: torch.Tensor, codebook: torch.Tensor, seg: torch.Tensor, table: torch.Tensor,
+                             normalize: bool = True) -> torch.Tensor:
+    """``decode_cos_loss`` with the ground truth given as (seg [H, W] int, table [S, 512]): gt = table[seg], mask =
+    seg >= 0 -- the form the reference's loader has before it expands it (scene/cameras.py:59-96).  Same value and
+    gradients as the dense call; neither 64 x 512 x HW product is computed."""
+    return _GramCosLossSeg.apply(weight_map, codebook, seg, table, normalize)
+
+
 def decode_cos_loss(weight_map: torch.Tensor, codebook: torch.Tensor, gt: torch.Tensor,
                     mask: Optional[torch.Tensor] = None, normalize: bool = True,
                     gt_sumsq: Optional[torch.Tensor] = None) -> torch.Tensor:

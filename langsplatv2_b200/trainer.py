@@ -25,7 +25,7 @@ import torch.nn.functional as F
 
 from . import dist as lsdist
 from .decode import decode_feature_map
-from .loss import column_sumsq, decode_cos_loss, normalized_cos_loss
+from .loss import column_sumsq, decode_cos_loss, decode_cos_loss_segments, normalized_cos_loss
 from .rasterizer import GaussianRasterizationSettings, GaussianRasterizer
 from . import sparse as lssparse
 from .sparse import softmax_to_topk_soft_code
@@ -138,6 +138,14 @@ class FeatureTrainer:
         self._last_state = rasterizer.last_state
         layer_idx = min(int(self.iteration / 10000 * self.layers), self.layers - 1)       # train.py:155
         cs = self.codebook_size
+        if isinstance(gt, (tuple, list)):
+            # ground truth as (seg [H, W] int, table [S, 512]) -- scene/cameras.py:59-96 before the expansion
+            seg, table = gt
+            if self.gram_loss and layer_idx == 0 and cs == 64 and self.use_cos and not self.use_l1:
+                return decode_cos_loss_segments(wmap[:cs], self.codebooks[0:1], seg, table, normalize=self.normalize)
+            valid = (seg >= 0)
+            gt = table[seg.clamp(min=0).long()].permute(2, 0, 1).contiguous() * valid.unsqueeze(0)
+            mask = valid.unsqueeze(0).to(torch.float32)
         if (self.gram_loss and self.fused_loss and layer_idx == 0 and cs == 64 and self.use_cos and not self.use_l1
                 and mask.numel() == wmap[0].numel()):
             key = (gt.data_ptr(), tuple(gt.shape))
@@ -212,6 +220,16 @@ class FeatureTrainer:
                 raise RuntimeError(f"instance capacity {self.capacity} exceeded; raise FeatureTrainer.capacity")
         self._last_state = None
         return loss.detach()
+
+
+def synthetic_gt_segments(H: int, W: int, feat_dim: int = 512, seed: int = 2, device="cuda"):
+    """The same ground truth as ``synthetic_gt`` in the loader's form: (seg [H, W] int32, table [256, feat_dim])."""
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    table = torch.randn((256, feat_dim), generator=g)
+    table = table / table.norm(dim=1, keepdim=True)
+    ys, xs = torch.meshgrid(torch.arange(H), torch.arange(W), indexing="ij")
+    seg = ((xs // 32 + 7 * (ys // 32)) % 256).to(torch.int32)
+    return seg.to(device), table.to(device)
 
 
 def synthetic_gt(H: int, W: int, feat_dim: int = 512, seed: int = 2, device="cuda"):

@@ -3,7 +3,7 @@ import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from langsplatv2_b200 import synth
-from langsplatv2_b200.trainer import FeatureTrainer, synthetic_gt
+from langsplatv2_b200.trainer import FeatureTrainer, synthetic_gt, synthetic_gt_segments
 
 N = int(os.environ.get("N", 1_000_000)); W = int(os.environ.get("W", 1008)); H = int(os.environ.get("H", 756))
 steps = int(os.environ.get("STEPS", 4))
@@ -11,6 +11,8 @@ scene = synth.make_scene(N, seed=0, levels=3)
 cam = synth.ring_camera(0, 64, W, H)
 cam = {k: (v.cuda() if torch.is_tensor(v) else v) for k, v in cam.items()}
 gt, mask = synthetic_gt(H, W)
+if os.environ.get("SEGMENTS") == "1":          # ground truth as (seg, table): loss.decode_cos_loss_segments
+    gt, mask = synthetic_gt_segments(H, W), None
 tr = FeatureTrainer(scene, topk=4, layers=1)
 for _ in range(2):
     tr.step(cam, gt, mask)

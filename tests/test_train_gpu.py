@@ -156,3 +156,40 @@ def test_codebook_gradient_tensor_core_3xtf32_matches_fp64(D, H, W):
     err = (dC[0].double() - ref).abs()
     assert bool((err <= 2e-6 * bound + 1e-30).all()), float((err / (bound + 1e-30)).max())
     assert float(err.max()) <= 1e-5 * float(ref.abs().max())
+
+
+@pytest.mark.parametrize("normalize", [True, False])
+def test_segment_ground_truth_loss_equals_dense(normalize):
+    """loss.decode_cos_loss_segments (gt = table[seg], unlabelled pixels seg = -1; scene/cameras.py:59-96) against fp64
+    autograd of the reference's dense expressions -- same tolerance as the dense Gram path."""
+    from langsplatv2_b200.loss import decode_cos_loss_segments
+    g = torch.Generator(device="cpu").manual_seed(21)
+    H, W, S = 40, 52, 23
+    wmap = torch.rand((64, H, W), generator=g) * (torch.rand((64, H, W), generator=g) > 0.6)
+    cb = torch.randn((1, 64, 512), generator=g)
+    table = torch.randn((S, 512), generator=g)
+    table = table / table.norm(dim=1, keepdim=True)
+    ys, xs = torch.meshgrid(torch.arange(H), torch.arange(W), indexing="ij")
+    seg = ((xs // 9 + 5 * (ys // 7)) % S).to(torch.int32)
+    seg[torch.rand((H, W), generator=g) < 0.1] = -1                     # unlabelled pixels
+    seg[3, 5:40] = torch.randint(0, S, (35,), generator=g).to(torch.int32)   # a row with mixed segments inside warps
+    valid = seg >= 0
+    gt = table[seg.clamp(min=0).long()].permute(2, 0, 1) * valid
+    mask = valid.unsqueeze(0).double()
+    w64 = wmap.double().requires_grad_(True)
+    c64 = cb.double().requires_grad_(True)
+    feat = (c64[0].T @ w64.view(64, -1)).view(512, H, W)
+    if normalize:
+        feat = feat / (feat.norm(dim=0, keepdim=True) + 1e-10)
+    ref = cos_loss(feat * mask, gt.double() * mask)
+    ref.backward()
+    wc = wmap.cuda().requires_grad_(True)
+    cc = cb.cuda().requires_grad_(True)
+    out = decode_cos_loss_segments(wc, cc, seg.cuda(), table.cuda(), normalize=normalize)
+    (out * 2.0).backward()
+    assert abs(float(out.detach()) - float(ref.detach())) <= 5e-6
+    live = (wmap.abs().sum(0) > 0).numpy()
+    gw, rw = wc.grad.cpu().numpy()[:, live] / 2.0, w64.grad.numpy()[:, live]
+    assert np.max(np.abs(gw - rw)) <= 2e-5 * np.abs(rw).max()
+    gc, rc = cc.grad.cpu().numpy() / 2.0, c64.grad.numpy()
+    assert np.max(np.abs(gc - rc)) <= 2e-5 * np.abs(rc).max()
