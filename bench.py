@@ -202,7 +202,7 @@ def run_train(args, dev, rank, world, scene, barrier):
     decode -> normalise -> cos loss -> backward -> (N>1: one all-reduce of the flat grad bucket) -> Adam.
     Weak scaling: every rank renders its own view each iteration (the reference's --accum_iter N)."""
     from langsplatv2_b200 import synth
-    from langsplatv2_b200.trainer import FeatureTrainer, synthetic_gt
+    from langsplatv2_b200.trainer import FeatureTrainer, synthetic_gt, synthetic_gt_segments
     W, H = TRAIN_WL["W"], TRAIN_WL["H"]
     steps = max(1, min(args.steps, args.train_steps))
     cams = [synth.ring_camera(v, VIEWS, W, H) for v in range(VIEWS)]
@@ -231,7 +231,29 @@ def run_train(args, dev, rank, world, scene, barrier):
         import torch.distributed as dist
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
-    return {"metric": "train iter/s", "value": steps / (ms * 1e-3), "unit": "iter/s", "views_per_s": world * steps / (ms * 1e-3),
+    # the same iterations with the ground truth in the reference loader's own form (segmentation map + per-segment
+    # table, scene/cameras.py:59-96) instead of the expanded [512, H, W] tensor: loss.decode_cos_loss_segments
+    segs = {v: synthetic_gt_segments(H, W, device=dev, seed=2 + v) for v in my_views}
+    for s in range(3):
+        v = my_views[s % len(my_views)]
+        tr.step(cams[v], segs[v], None)
+    barrier()
+    s_b, s_e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s_b.record()
+    for s in range(steps):
+        v = my_views[s % len(my_views)]
+        loss_seg = tr.step(cams[v], segs[v], None)
+    s_e.record()
+    barrier()
+    t2 = torch.tensor([s_b.elapsed_time(s_e)], dtype=torch.float64, device=dev)
+    if world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+    ms_seg = float(t2.item())
+    seg_line = {"value": steps / (ms_seg * 1e-3), "unit": "iter/s", "ms_per_iter": ms_seg / steps,
+                "final_loss": float(loss_seg),
+                "what": "same step with gt given as (seg map, per-segment table) -- no 64x512xHW product"}
+    return {"metric": "train iter/s", "segments_gt": seg_line, "value": steps / (ms * 1e-3), "unit": "iter/s", "views_per_s": world * steps / (ms * 1e-3),
             "ms_per_iter": ms / steps, "steps": steps, "warmup": n_warm, "n_gpus": world, "scaling": "weak",
             "final_loss": float(loss), "dtype": "f32",
             "config": {"workload": TRAIN_WL["name"], "views_per_iter": world,
