@@ -165,10 +165,25 @@ __global__ void __launch_bounds__(PRE_THREADS) k_preprocess(PreArgs a)
         __syncthreads();
         const int warp = tid >> 5, lane = tid & 31;
         const size_t base = (size_t)blockIdx.x * PRE_THREADS;
-        for (int r = warp; r < PRE_THREADS; r += PRE_THREADS / 32) {
-            if (!s_vis[r]) continue;
-            const float* src = a.shs + (base + r) * row;
-            for (int k = lane; k < used; k += 32) s_sh[r * SH_ROW_STRIDE + k] = __ldg(src + k);
+        if ((row & 3) == 0 && (reinterpret_cast<uintptr_t>(a.shs) & 15) == 0) {
+            // the CTA's rows are one contiguous block: 16-byte loads, independent of each other, skipping culled rows
+            const int f4_per_row = row >> 2;
+            const int total = min(PRE_THREADS, a.P - (int)base) * f4_per_row;
+            const float4* src4 = reinterpret_cast<const float4*>(a.shs + base * row);
+#pragma unroll 4
+            for (int e = tid; e < total; e += PRE_THREADS) {
+                const int r = e / f4_per_row, q = e - r * f4_per_row;
+                if (!s_vis[r]) continue;
+                const float4 v = __ldg(src4 + e);
+                float* d = s_sh + r * SH_ROW_STRIDE + 4 * q;
+                d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+            }
+        } else {
+            for (int r = warp; r < PRE_THREADS; r += PRE_THREADS / 32) {
+                if (!s_vis[r]) continue;
+                const float* src = a.shs + (base + r) * row;
+                for (int k = lane; k < used; k += 32) s_sh[r * SH_ROW_STRIDE + k] = __ldg(src + k);
+            }
         }
         __syncthreads();
         if (vis) {
