@@ -86,14 +86,23 @@ k_rs_histogram(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ c
         for (int i = threadIdx.x; i < n_tiles; i += THREADS) s_tiles[i] = 0;
     __syncthreads();
     const uint64_t stride = (uint64_t)gridDim.x * THREADS;
-#pragma unroll 4
-    for (uint64_t i = (uint64_t)blockIdx.x * THREADS + threadIdx.x; i < n; i += stride) {
-        const uint64_t k = keys[i];
-        if (g_tiles) {              // the digit counts follow from the tile counts (k_ranges_from_counts)
-            const uint32_t t = (uint32_t)(k >> 32);
-            if (t < (uint32_t)n_tiles) atomicAdd(&s_tiles[t], 1u);
-            continue;
+    uint64_t i = (uint64_t)blockIdx.x * THREADS + threadIdx.x;
+    if (g_tiles) {                  // the digit counts follow from the tile counts (k_ranges_from_counts)
+        for (; i + 3 * stride < n; i += 4 * stride) {          // four loads in flight per thread
+            const uint32_t t0 = (uint32_t)(keys[i] >> 32), t1 = (uint32_t)(keys[i + stride] >> 32);
+            const uint32_t t2 = (uint32_t)(keys[i + 2 * stride] >> 32), t3 = (uint32_t)(keys[i + 3 * stride] >> 32);
+            if (t0 < (uint32_t)n_tiles) atomicAdd(&s_tiles[t0], 1u);
+            if (t1 < (uint32_t)n_tiles) atomicAdd(&s_tiles[t1], 1u);
+            if (t2 < (uint32_t)n_tiles) atomicAdd(&s_tiles[t2], 1u);
+            if (t3 < (uint32_t)n_tiles) atomicAdd(&s_tiles[t3], 1u);
         }
+        for (; i < n; i += stride) {
+            const uint32_t t = (uint32_t)(keys[i] >> 32);
+            if (t < (uint32_t)n_tiles) atomicAdd(&s_tiles[t], 1u);
+        }
+    }
+    for (; i < n; i += stride) {
+        const uint64_t k = keys[i];
 #pragma unroll
         for (int p = 0; p < RS_MAX_PASSES; ++p) {
             if (p < plan.npass) {
