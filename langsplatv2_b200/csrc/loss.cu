@@ -253,7 +253,7 @@ int launch_gram_loss_backward(int Lc, int64_t HW, const float* wmap, const float
 // out[k][s] += sum over the pixels p with seg[p] == s of x[k][p]  (k < Lc; seg < 0: pixel skipped).
 // The ground truth of the feature stage is a per-segment table gathered through a segmentation map
 // (scene/cameras.py:59-96: point_feature = feature_map[seg]), so (alpha w) gt^T = (segment sums of alpha w) . table.
-// A warp takes 32 consecutive pixels; when they share one segment (the common case) it adds ONE value per k.
+// A warp takes 32 consecutive pixels, which belong to one or a few segments: it adds ONE value per (segment, k).
 __global__ void __launch_bounds__(LOSS_THREADS)
 k_segment_sum(int Lc, int64_t HW, int nseg, const float* __restrict__ x, const int32_t* __restrict__ seg,
               float* __restrict__ out)
@@ -262,18 +262,53 @@ k_segment_sum(int Lc, int64_t HW, int nseg, const float* __restrict__ x, const i
     const int lane = threadIdx.x & 31;
     int s = p < HW ? seg[p] : -1;
     if (s >= nseg) s = -1;
-    const int s0 = __shfl_sync(0xffffffffu, s, 0);
-    const bool uniform = __all_sync(0xffffffffu, s == s0);
-    if (uniform && s0 < 0) return;
-    const int k0 = blockIdx.y * (Lc / gridDim.y), k1 = k0 + Lc / gridDim.y;
-    for (int k = k0; k < k1; ++k) {
-        float v = s >= 0 ? __ldg(x + (size_t)k * HW + p) : 0.0f;
-        if (uniform) {
+    // the (few) distinct segments of this warp: up to SS_GROUPS are reduced with shuffles, lanes of any further
+    // segment add on their own
+    constexpr int SS_GROUPS = 4;
+    const uint32_t peers = __match_any_sync(0xffffffffu, s);
+    uint32_t leaders = __ballot_sync(0xffffffffu, s >= 0 && lane == __ffs(peers) - 1);
+    if (leaders == 0u) return;
+    uint32_t gmask[SS_GROUPS];
+    int gseg[SS_GROUPS];
+    uint32_t covered = 0;
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-            if (lane == 0 && v != 0.0f) atomicAdd(out + (size_t)k * nseg + s0, v);
-        } else if (s >= 0 && v != 0.0f) {
-            atomicAdd(out + (size_t)k * nseg + s, v);
+    for (int g = 0; g < SS_GROUPS; ++g) {
+        gmask[g] = 0; gseg[g] = 0;
+        if (leaders) {
+            const int l = __ffs(leaders) - 1;
+            leaders &= leaders - 1;
+            gmask[g] = __shfl_sync(0xffffffffu, peers, l);
+            gseg[g] = __shfl_sync(0xffffffffu, s, l);
+            covered |= gmask[g];
+        }
+    }
+    const bool own = s >= 0 && !((covered >> lane) & 1u);
+    const int k0 = blockIdx.y * (Lc / gridDim.y), k1 = k0 + Lc / gridDim.y;      // (k1 - k0) % 4 == 0 (launcher)
+    const bool hi16 = lane & 16, hi8 = lane & 8;
+    for (int k = k0; k < k1; k += 4) {
+        float v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[j] = s >= 0 ? __ldg(x + (size_t)(k + j) * HW + p) : 0.0f;
+#pragma unroll
+        for (int g = 0; g < SS_GROUPS; ++g) {
+            if (gmask[g] == 0u) break;                                            // warp-uniform
+            const bool in = (gmask[g] >> lane) & 1u;
+            const float a0 = in ? v[0] : 0.0f, a1 = in ? v[1] : 0.0f, a2 = in ? v[2] : 0.0f, a3 = in ? v[3] : 0.0f;
+            // transposing butterfly: lane 8q ends with the warp sum of channel k + q
+            float b0 = hi16 ? a2 : a0, b1 = hi16 ? a3 : a1;
+            b0 += __shfl_xor_sync(0xffffffffu, hi16 ? a0 : a2, 16);
+            b1 += __shfl_xor_sync(0xffffffffu, hi16 ? a1 : a3, 16);
+            float t = hi8 ? b1 : b0;
+            t += __shfl_xor_sync(0xffffffffu, hi8 ? b0 : b1, 8);
+            t += __shfl_xor_sync(0xffffffffu, t, 4);
+            t += __shfl_xor_sync(0xffffffffu, t, 2);
+            t += __shfl_xor_sync(0xffffffffu, t, 1);
+            if ((lane & 7) == 0 && t != 0.0f) atomicAdd(out + (size_t)(k + (lane >> 3)) * nseg + gseg[g], t);
+        }
+        if (own) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (v[j] != 0.0f) atomicAdd(out + (size_t)(k + j) * nseg + s, v[j]);
         }
     }
 }
@@ -282,7 +317,8 @@ int launch_segment_sum(int Lc, int64_t HW, int nseg, const float* x, const int32
 {
     if (HW == 0 || Lc <= 0 || nseg <= 0) return LSV2_OK;
     const int64_t blocks = (HW + LOSS_THREADS - 1) / LOSS_THREADS;
-    const int ky = (Lc % 4 == 0) ? 4 : 1;
+    if (Lc % 16 != 0) return LSV2_EUNSUPPORTED;      // 4 row blocks of a multiple of 4 channels
+    const int ky = 4;
     k_segment_sum<<<dim3((unsigned)blocks, ky), LOSS_THREADS, 0, st>>>(Lc, HW, nseg, x, seg, out);
     LSV2_LAUNCH_CHECK("k_segment_sum");
     return LSV2_OK;
