@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define LSV2_ABI_VERSION 1
+#define LSV2_ABI_VERSION 2
 #define LSV2_TILE 16
 
 /* error codes */
@@ -172,7 +172,19 @@ int lsv2_compact_coeff(int32_t P, const lsv2_geom* geom, const lsv2_features* fe
 int lsv2_render_forward(const lsv2_view* view, const lsv2_geom* geom, const lsv2_binning* binning,
                         const lsv2_features* feat, const lsv2_image* image, void* stream);
 
-/* all of the above back to back, no host involvement (CUDA-graph capturable). */
+/* renderCUDA forward with the sparse-coefficient accumulation on the tensor cores (the blend half of
+ * lsv2_render_decode, render_decode.cu): per batch of 16 depth-sorted instances the per-pixel blending weights
+ * alpha*T and the instances' coefficients are split into an fp16 head and an fp16 remainder and
+ * W += A_hi.S_hi + A_lo.S_hi + A_hi.S_lo accumulates in TMEM (fp32); the fp32 [L][H][W] map is written once per
+ * tile.  color / final_T / n_contrib are bit-identical to lsv2_render_forward (same per-pixel arithmetic); the
+ * weight map agrees with it to <= 1e-4 of its per-pixel norm (stated tolerance of the fp32 blend).  QUICK or DENSE
+ * with the compacted rows of lsv2_compact_coeff; L a multiple of 64, <= 192, K <= LSV2_SPARSE_CAP; otherwise
+ * LSV2_EUNSUPPORTED (use lsv2_render_forward).  Uses the first 256 bytes of binning->scratch. */
+int lsv2_render_forward_tc(const lsv2_view* view, const lsv2_geom* geom, const lsv2_binning* binning,
+                           const lsv2_features* feat, const lsv2_image* image, void* stream);
+
+/* preprocess + bin + compact + blend back to back, no host involvement (CUDA-graph capturable).  The blend is
+ * lsv2_render_forward_tc where it applies, lsv2_render_forward otherwise. */
 int lsv2_forward(const lsv2_view* view, const lsv2_scene* scene, const lsv2_geom* geom,
                  const lsv2_binning* binning, const lsv2_features* feat, const lsv2_image* image,
                  void* stream);
@@ -206,9 +218,12 @@ int lsv2_decode(int32_t levels, int32_t Lc, int32_t D, int64_t HW, const float* 
 
 /* ---- fused blend + decode (the serving path: eval_lerf.py:321-352 renders, then decodes) ----
  * renderCUDA forward and the codebook decode in ONE kernel: the blend's sparse-coefficient
- * accumulation runs on the tensor cores (fp16 alpha*T and coefficients, fp32 accumulate in
- * TMEM) and the L-channel weight map goes straight from TMEM into the decode contraction, so
- * it never exists in HBM.  Same inputs as lsv2_render_forward (QUICK, or DENSE with the
+ * accumulation runs on the tensor cores (alpha*T and coefficients as fp16 head + fp16 remainder,
+ * three MMAs per batch, fp32 accumulate in TMEM: fp32-blend accuracy) and the L-channel weight map
+ * goes straight from TMEM into the decode contraction (fp16 operands, fp32 accumulate; the L2 norm
+ * comes from the Gram matrix C C^T before the decode), so it never exists in HBM.  The decode of
+ * tile i runs under the blend of tile i+1; features leave through TMA tensor stores when the row
+ * pitch W*sizeof(out) is a multiple of 16 bytes (per-thread stores otherwise).  Same inputs as lsv2_render_forward (QUICK, or DENSE with the
  * compacted rows of lsv2_compact_coeff) + codebooks f32[levels][Lc][D]; feat->L must equal
  * levels*Lc.  image->color / final_T / n_contrib are written as by lsv2_render_forward
  * (bit-identical); image->wmap may be NULL (if not, it receives the TMEM weight map, fp32).
@@ -279,6 +294,16 @@ int lsv2_gram_loss_backward_seg(int32_t Lc, int64_t HW, int32_t nseg, const floa
  * zeroes out).  The feature stage's ground truth is table[seg] (/root/reference/scene/cameras.py:59-96), so the
  * codebook gradient (alpha w) gt^T of lsv2_gram_loss_backward equals (segment sums of alpha w) . table. */
 int lsv2_segment_sum(int32_t Lc, int64_t HW, int32_t nseg, const float* x, const int32_t* seg, float* out, void* stream);
+
+/* ---- optimizer step (scene/gaussian_model.py:255 torch.optim.Adam(l, lr=0.0, eps=1e-15); train.py:261-263) ------
+ * One Adam step on the flat range p[0, n) with gradient g and moments m, v (all f32, 16-byte aligned), in torch's
+ * single-tensor operation order, no weight decay / amsgrad; `step` is the 1-based step count of this range.
+ * zero_grad != 0 clears g in the same pass.  A group of 4 elements whose g, m and v are all zero is skipped, which
+ * is exactly what the dense update does to it.  step_scalars (device f32[2], may be NULL): when given, the kernel
+ * reads {lr / (1 - beta1^step), sqrt(1 - beta2^step)} from it instead of deriving them from lr / step on the host, so
+ * a captured CUDA graph can be replayed with the next step's values. */
+int lsv2_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps,
+                   int64_t step, int32_t zero_grad, const float* step_scalars, void* stream);
 
 #ifdef __cplusplus
 }

@@ -13,7 +13,7 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "liblsv2.so")
 
-LSV2_ABI_VERSION = 1
+LSV2_ABI_VERSION = 2
 TILE = 16
 SPARSE_CAP = 16
 STATUS_WORDS = 8
@@ -64,7 +64,7 @@ EXPORTS = [
     "lsv2_decode_backward", "lsv2_topk_soft_code", "lsv2_topk_soft_code_backward", "lsv2_cos_loss_blocks", "lsv2_cos_loss_forward", "lsv2_cos_loss_backward",
     "lsv2_gram_loss_forward", "lsv2_gram_loss_backward", "lsv2_colsumsq", "lsv2_segment_sum",
     "lsv2_gram_loss_forward_seg", "lsv2_gram_loss_backward_seg",
-    "lsv2_render_decode_scratch_bytes", "lsv2_render_decode",
+    "lsv2_render_decode_scratch_bytes", "lsv2_render_decode", "lsv2_render_forward_tc", "lsv2_adam_step",
 ]
 
 _lib = None
@@ -96,6 +96,7 @@ def lib() -> C.CDLL:
     L.lsv2_bin.argtypes = [P(View), C.c_int32, P(Geom), P(Binning), _vp]
     L.lsv2_compact_coeff.argtypes = [C.c_int32, P(Geom), P(Features), _vp]
     L.lsv2_render_forward.argtypes = [P(View), P(Geom), P(Binning), P(Features), P(Image), _vp]
+    L.lsv2_render_forward_tc.argtypes = [P(View), P(Geom), P(Binning), P(Features), P(Image), _vp]
     L.lsv2_forward.argtypes = [P(View), P(Scene), P(Geom), P(Binning), P(Features), P(Image), _vp]
     L.lsv2_mark_visible.argtypes = [C.c_int32, _vp, _vp, _vp, _vp]
     L.lsv2_render_backward.argtypes = [P(View), P(Geom), P(Binning), P(Features), P(Image), _vp, _vp,
@@ -122,10 +123,13 @@ def lib() -> C.CDLL:
     L.lsv2_render_decode_scratch_bytes.argtypes = [C.c_int32]
     L.lsv2_render_decode.argtypes = [P(View), P(Geom), P(Binning), P(Features), P(Image), _vp, C.c_int32,
                                      C.c_int32, C.c_int32, C.c_int32, C.c_int32, _vp, _vp, C.c_size_t, _vp]
+    L.lsv2_adam_step.argtypes = [_vp, _vp, _vp, _vp, C.c_int64, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int64,
+                                 C.c_int32, _vp, _vp]
     for name in ("lsv2_preprocess", "lsv2_bin", "lsv2_compact_coeff", "lsv2_render_forward", "lsv2_forward",
                  "lsv2_mark_visible", "lsv2_render_backward", "lsv2_decode", "lsv2_decode_backward",
                  "lsv2_topk_soft_code", "lsv2_topk_soft_code_backward", "lsv2_cos_loss_forward", "lsv2_cos_loss_backward",
-                 "lsv2_gram_loss_forward", "lsv2_gram_loss_backward", "lsv2_colsumsq", "lsv2_segment_sum", "lsv2_render_decode"):
+                 "lsv2_gram_loss_forward", "lsv2_gram_loss_backward", "lsv2_colsumsq", "lsv2_segment_sum", "lsv2_render_decode",
+                 "lsv2_render_forward_tc", "lsv2_gram_loss_forward_seg", "lsv2_gram_loss_backward_seg", "lsv2_adam_step"):
         getattr(L, name).restype = C.c_int
     _lib = L
     return L
@@ -149,6 +153,13 @@ def ptr(t) -> int | None:
 
 def stream_ptr(device=None) -> int:
     return torch.cuda.current_stream(device).cuda_stream
+
+
+def device_guard(device):
+    """Context manager making ``device`` the current CUDA device for the launches inside it: the kernels,
+    cudaFuncSetAttribute and the tensor-map encode of liblsv2 act on the CURRENT device, which need not be the
+    one the tensors live on."""
+    return torch.cuda.device(device)
 
 
 def require_cuda(t: torch.Tensor, name: str) -> None:

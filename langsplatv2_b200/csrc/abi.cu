@@ -39,7 +39,11 @@ int launch_topk_soft_code_bwd(int64_t N, int C, const float* logits, const float
 int launch_topk_soft_code(int64_t N, int C, int k, const float* logits, float* dense, float* weights,
                           float* indices, cudaStream_t st);
 
+int launch_adam(float* p, const float* g, float* m, float* v, int64_t n, float lr, float b1, float b2, float eps,
+                int64_t step, int zero_grad, const float* dev_scalars, cudaStream_t st);
 size_t render_decode_scratch_bytes(int levels);
+int launch_render_wmap_tc(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b, const lsv2_features& f,
+                          const lsv2_image& img, void* scratch, size_t scratch_bytes, cudaStream_t st);
 int launch_render_decode(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b, const lsv2_features& f,
                          const lsv2_image& img, const float* codebooks, int levels, int Lc, int D, int normalize,
                          int out_dtype, void* out, void* scratch, size_t scratch_bytes, cudaStream_t st);
@@ -148,6 +152,16 @@ int lsv2_render_forward(const lsv2_view* view, const lsv2_geom* geom, const lsv2
     return launch_render_forward(*view, *geom, *binning, *feat, *image, (cudaStream_t)stream);
 }
 
+int lsv2_render_forward_tc(const lsv2_view* view, const lsv2_geom* geom, const lsv2_binning* binning,
+                           const lsv2_features* feat, const lsv2_image* image, void* stream)
+{
+    if (!view_ok(view) || !geom || !binning || !feat || !image) return LSV2_EINVAL;
+    if (!image->color || !image->final_T || !image->n_contrib || !image->wmap) return LSV2_EINVAL;
+    if (feat->mode != LSV2_MODE_QUICK && !(feat->mode == LSV2_MODE_DENSE && feat->sparse_count)) return LSV2_EUNSUPPORTED;
+    return launch_render_wmap_tc(*view, *geom, *binning, *feat, *image, binning->scratch, binning->scratch_bytes,
+                                 (cudaStream_t)stream);
+}
+
 int lsv2_forward(const lsv2_view* view, const lsv2_scene* scene, const lsv2_geom* geom,
                  const lsv2_binning* binning, const lsv2_features* feat, const lsv2_image* image, void* stream)
 {
@@ -158,6 +172,10 @@ int lsv2_forward(const lsv2_view* view, const lsv2_scene* scene, const lsv2_geom
     if (feat && feat->mode == LSV2_MODE_DENSE && feat->sparse_count) {
         rc = lsv2_compact_coeff(scene->P, geom, feat, stream);
         if (rc) return rc;
+    }
+    if (feat && image && image->wmap) {
+        rc = lsv2_render_forward_tc(view, geom, binning, feat, image, stream);
+        if (rc != LSV2_EUNSUPPORTED) return rc;
     }
     return lsv2_render_forward(view, geom, binning, feat, image, stream);
 }
@@ -297,6 +315,14 @@ int lsv2_colsumsq(int32_t D, int64_t HW, const float* x, float* out, void* strea
 {
     if (D <= 0 || HW < 0 || (HW > 0 && (!x || !out))) return LSV2_EINVAL;
     return launch_colsumsq(D, HW, x, out, (cudaStream_t)stream);
+}
+
+int lsv2_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps,
+                   int64_t step, int32_t zero_grad, const float* step_scalars, void* stream)
+{
+    if (n < 0 || (step < 1 && !step_scalars) || (n > 0 && (!p || !g || !m || !v))) return LSV2_EINVAL;
+    return launch_adam(p, g, m, v, n, lr, beta1, beta2, eps, step < 1 ? 1 : step, zero_grad, step_scalars,
+                       (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -1,4 +1,4 @@
-// fd_common.cuh -- pieces shared by the fused blend + decode kernels (render_decode.cu, render_decode2.cu)
+// fd_common.cuh -- layout constants and small helpers of the fused blend + decode kernel (render_decode.cu)
 #pragma once
 #include <cuda_fp16.h>
 #include <stdlib.h>
@@ -10,42 +10,70 @@ namespace lsv2 {
 
 using namespace tc;
 
-constexpr int FD_BATCH = 64;
+// ---- geometry of one CTA ------------------------------------------------------------------------------------
+// Work unit: a 32 x 8 pixel band = the upper (or lower) halves of two horizontally adjacent 16x16 tiles.  Each half
+// (128 pixels = one MMA M block) blends its own tile's depth-sorted list; the decode then sees the band as 8 rows of
+// 32 pixels, so every store instruction of the epilogue writes one full 128-byte line.
+constexpr int FD_BATCH = 16;                             // depth-sorted instances per batch (one MMA k-slice)
 constexpr int FD_STAGES = 2;
-constexpr int FD_BLEND_WARPS = 8;
-constexpr int FD_PROD_THREADS = 64;
-constexpr int FD_THREADS = 32 * FD_BLEND_WARPS + FD_PROD_THREADS + 32;      // 352
+constexpr int FD_BLEND_WARPS = 8;                        // warps 0-7: one thread per pixel; warp = 16x2 strip of a half
+constexpr int FD_EPI_WARPS = 4;                          // warps 8-11: F slots (TMEM) -> scaled 128-byte-line stores
+constexpr int FD_WARP_PROD = 12;                         // gathers instances, builds the coefficient operands
+constexpr int FD_WARP_MB = 13;                           // issues the blend MMAs (and owns the TMEM allocation)
+constexpr int FD_WARP_MD = 14;                           // issues the Gram / decode MMAs, fetches codebook chunks
+constexpr int FD_THREADS = 15 * 32;                      // 480
+constexpr int FD_THREADS_NODECODE = 14 * 32;             // weight-map-only variant: no MD warp (epilogue warps idle)
 constexpr int FD_MAX_L = 192;
 constexpr int FD_LC = 64;
 constexpr int FD_D = 512;
-constexpr int FD_CHUNK_N = 128;                          // features per decode MMA
-constexpr int FD_CHUNKS = FD_D / FD_CHUNK_N;             // 4
-constexpr int FD_TILE16K = 128 * 128;                    // [128 rows][128 B] operand tile
-constexpr int FD_STAGE_BYTES = 2 * FD_TILE16K + FD_MAX_L * 128;             // A0 | A1 | S  = 56 KB
 constexpr int FD_KMAX = LSV2_SPARSE_CAP;
 constexpr uint32_t FD_ROW_DENSE = 0xFFFFFFFFu;
+constexpr int FD_UNIT_W = 32, FD_UNIT_H = 8;
+
+// blend operands: 64-byte rows [hi fp16 x16 | lo fp16 x16], 64-byte swizzle, K-major
+constexpr int FD_AHALF_BYTES = 128 * 64;                 // alpha*T of one 128-pixel half                8 KB
+constexpr int FD_S_BYTES = FD_MAX_L * 64;                // coefficients [channel][instance] of one list 12 KB
+constexpr int FD_STAGE_BYTES = 2 * FD_AHALF_BYTES + 2 * FD_S_BYTES;                    // A0 | A1 | S0 | S1   40 KB
+// decode operands
+constexpr int FD_WDEC_LEVEL = 256 * 128;                 // fp16 weights of one level, [256 px][64 codes] 32 KB
+constexpr int FD_CB_BYTES = 128 * 128;                   // codebook chunk [128 features][64 codes]     16 KB
+constexpr int FD_CB_SLOTS = 2;
+constexpr int FD_CHUNKS = FD_D / 128;                    // 4 chunks of 128 features per level
+constexpr int FD_NFEAT = 32;                             // features per decode MMA / F slot
+constexpr int FD_FGROUPS = 128 / FD_NFEAT;               // 4 feature groups per chunk
+constexpr int FD_FSLOTS = 4;
+constexpr int FD_TMEM_F = 2 * FD_MAX_L;                  // first F column (W halves occupy [0, 384))
 
 struct __align__(16) FdHeader {
-    float4 g0[FD_BATCH];                 // x, y, -a/2, -b
-    float4 g1[FD_BATCH];                 // -c/2, power cut-off, opacity, r
-    float2 g2[FD_BATCH];                 // g, b
-    uint32_t mask[FD_BLEND_WARPS][2];    // per strip: which of the 64 instances can reach it
-    int32_t count;                       // >= 0 batch ; -1 end of tile ; -2 no more tiles
-    int32_t tile;
-    int32_t batches;                     // terminator: batches this tile had
+    float4 g0[2 * FD_BATCH];             // x, y, -a/2, -b             (list 0: [0,16), list 1: [16,32))
+    float4 g1[2 * FD_BATCH];             // -c/2, power cut-off, opacity, r
+    float2 g2[2 * FD_BATCH];             // g, b
+    uint32_t mask[FD_BLEND_WARPS];       // per strip (half*4 + strip): which of its list's 16 instances can reach it
+    int32_t count;                       // >= 0 batch ; -1 end of unit ; -2 no more units
+    int32_t unit;
+    int32_t batches;                     // terminator: batches this unit had
     int32_t pad;
 };
 
+struct FdTileInfo {
+    int32_t unit;                        // < 0: no more units
+    int32_t nb;
+};
+
 constexpr size_t FD_SMEM_RING = 0;
-constexpr size_t FD_SMEM_B = FD_SMEM_RING + (size_t)FD_STAGES * FD_STAGE_BYTES;         // 112 KB
-constexpr int FD_G_BYTES = FD_LC * 128;                                                 // Gram tile [64 n][64 k] fp16
-constexpr size_t FD_SMEM_G = FD_SMEM_B + (size_t)FD_CHUNKS * FD_TILE16K;                // +64 KB
-constexpr size_t FD_SMEM_HDR = FD_SMEM_G + (size_t)(FD_MAX_L / FD_LC) * FD_G_BYTES;     // +24 KB
+constexpr size_t FD_SMEM_HDR = FD_SMEM_RING + (size_t)FD_STAGES * FD_STAGE_BYTES;                   // 80 KB
 constexpr size_t FD_SMEM_BAR = FD_SMEM_HDR + FD_STAGES * sizeof(FdHeader);
-constexpr size_t FD_SMEM_TOTAL = FD_SMEM_BAR + 32 * sizeof(uint64_t) + 64 + 1024;       // + alignment slack
+constexpr size_t FD_SMEM_INV = FD_SMEM_BAR + 48 * sizeof(uint64_t);                                 // f32 [2][3][256]
+constexpr size_t FD_SMEM_MISC_END = (FD_SMEM_INV + 2 * 3 * 256 * sizeof(float) + 1023) & ~(size_t)1023;
+constexpr size_t FD_SMEM_NODECODE_TOTAL = FD_SMEM_MISC_END + 1024;                                  // + alignment slack
+constexpr size_t FD_SMEM_WDEC = FD_SMEM_MISC_END;
+constexpr size_t FD_SMEM_CB = FD_SMEM_WDEC + (size_t)(FD_MAX_L / FD_LC) * FD_WDEC_LEVEL;            // + 96 KB
+constexpr size_t FD_SMEM_TOTAL = FD_SMEM_CB + (size_t)FD_CB_SLOTS * FD_CB_BYTES + 1024;             // + 32 KB
+static_assert(FD_SMEM_TOTAL <= 227 * 1024, "fused kernel shared memory budget");
 
 struct FdArgs {
-    int W, H, gx, n_tiles;
+    int W, H, gx, n_tiles;       // gx: 16x16 tiles per row
+    int ux, n_units;             // 32x8 units per band row, units in the image
     const uint2* ranges;
     const uint32_t* point_list;
     const float4* rec;
@@ -62,12 +90,11 @@ struct FdArgs {
     float* final_T;
     uint32_t* n_contrib;
     uint32_t* status;
-    const uint8_t* bimg;         // fp16 codebook image [levels][512 rows][64 k], 128B-swizzled
-    const uint8_t* gimg;         // fp16 Gram images  s_l * C_l C_l^T  [levels][64 n][64 k], 128B-swizzled
+    const uint8_t* bimg;         // fp16 codebook image [levels][512 rows][64 k], 128B-swizzled (scaled by cscale[l])
+    const uint8_t* gimg;         // fp16 Gram images  s_l C_l C_l^T  [levels][hi 64 rows | lo 64 rows][64 k], 128B-swizzled
     const float* gscale_inv;     // [levels] 1 / s_l
     void* out;                   // [levels][512][H][W]
     int normalize;
-    int dbg;                     // timing experiments only (LSV2_FD_DEBUG): 1 = no feature stores, 2 = no blend math
     uint32_t* tile_counter;
 };
 
@@ -75,6 +102,15 @@ __device__ __forceinline__ uint32_t pack_f16x2(float lo, float hi)
 {
     const __half2 v = __floats2half2_rn(lo, hi);
     return *reinterpret_cast<const uint32_t*>(&v);
+}
+
+// (a, b) -> fp16 pair hi and the fp16 pair of the remainders: a = hi.x + lo.x to ~2^-22 relative
+__device__ __forceinline__ void split_f16x2(float a, float b, uint32_t& hi, uint32_t& lo)
+{
+    const __half2 h = __floats2half2_rn(a, b);
+    const float2 hf = __half22float2(h);
+    hi = *reinterpret_cast<const uint32_t*>(&h);
+    lo = pack_f16x2(__fsub_rn(a, hf.x), __fsub_rn(b, hf.y));
 }
 
 // Instruction descriptor, kind::f16 with F16 operands: D = f32 (bit 4), A/B format 0 = F16, both K-major.
@@ -117,28 +153,11 @@ __device__ __forceinline__ uint32_t fd_strip_mask(float y_rel, float ax, float b
     return ((1u << (whi + 1)) - 1u) & ~((1u << wlo) - 1u);
 }
 
-// barrier with an OR reduction over the participating threads (uniform result)
-__device__ __forceinline__ bool named_bar_or(int id, int count, bool pred)
-{
-    uint32_t r;
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p, q;\n\t"
-        "setp.ne.u32 q, %3, 0;\n\t"
-        "bar.red.or.pred p, %1, %2, q;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t"
-        "}"
-        : "=r"(r)
-        : "r"(id), "r"(count), "r"((uint32_t)pred)
-        : "memory");
-    return r != 0;
-}
-
-// mbarrier wait for the helper warps (producer, MMA issuer): backs off between polls so the spin does not
-// take issue slots from the pixel warps
+// mbarrier wait for the helper warps (producer, MMA issuers, epilogue): backs off between polls so the spin does
+// not take issue slots from the pixel warps
 __device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity)
 {
-    while (!mbar_try_wait(bar, parity)) __nanosleep(40);
+    while (!mbar_try_wait(bar, parity)) __nanosleep(32);
 }
 
 }  // namespace lsv2

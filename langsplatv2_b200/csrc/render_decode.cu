@@ -1,31 +1,40 @@
 // render_decode.cu -- K6+K7 fused: per-tile alpha blending whose sparse-coefficient accumulation runs on the
-// 5th-gen tensor cores, followed in the same CTA by the global codebook decode + L2 normalisation.
+// 5th-gen tensor cores, overlapped in the same CTA with the global codebook decode + L2 normalisation of the
+// previous tile, whose 512-d features leave through shared-memory staging and TMA tensor stores.
 // The L-channel weight map never exists in HBM (nor in shared memory as read-modify-write accumulators).
 // Replaces renderCUDA (forward) + the einsum/norm/divide every caller runs after it
 // (/root/reference/gaussian_renderer/__init__.py:108-119 ; eval_lerf.py:214-218 ; SURVEY.md rows R8+R9).
 //
-// Persistent CTAs (one per SM), tiles handed out by an atomic counter.  Warp roles:
-//   warps 0-7  blend + epilogue: one thread per pixel of the 16x16 tile (warp = 16x2 strip).  Pixels 0..127 are
-//              rows of MMA half 0, pixels 128..255 of half 1; thread = TMEM lane.
-//   warps 8-9  producer: gathers the packed blend records of 64 depth-sorted instances per batch, builds the
-//              per-strip cut-off masks, and scatters each instance's (channel, weight) pairs into a zeroed
-//              fp16 B tile  S[L channels][64 instances]  (K-major, 128B-swizzled).
-//   warp 10    one thread issues every tcgen05.mma and the bulk copies of the codebook tiles.
+// Persistent CTAs (one per SM), tiles handed out by an atomic counter.  Warp roles (fd_common.cuh):
+//   warps 0-7   blend: one thread per pixel of the 16x16 tile (warp = 16x2 strip).  Pixels 0..127 are rows of MMA
+//               half 0, pixels 128..255 of half 1; thread = TMEM lane.  At the end of a tile the same threads move
+//               the weight tile W (TMEM, fp32) into the decode's fp16 operand and L2-normalise it (Gram matrix).
+//   warp 12     producer: gathers the packed blend records of 16 depth-sorted instances per batch, builds the
+//               per-strip cut-off masks, and scatters each instance's (channel, weight) pairs -- split into an fp16
+//               head and an fp16 remainder -- into a zeroed B tile  S[L channels][hi 16 | lo 16]  (K-major, SW64).
+//   warp 13     one thread issues the blend MMAs.
+//   warp 14     one thread issues the Gram and decode MMAs and the bulk copies of the codebook chunks.
+//   warps 8-11  epilogue: F slots (TMEM) -> registers -> swizzled staging -> cp.async.bulk.tensor stores.
 //
-// Blend phase, per batch:  the pixel threads evaluate alpha and T exactly as k_render_forward does (same fp32
+// Blend, per batch:  the pixel threads evaluate alpha and T exactly as k_render_forward does (same fp32
 // operations, same thresholds => identical n_contrib / final_T / RGB) and store the blending weight alpha*T of
-// each (pixel, instance) as fp16 into the A tile [128 px][64 inst] of their half;  W[128 x L] += A . S  (M=128,
-// N=L, K=64, fp32 accumulators in TMEM columns [h*L, h*L+L)).
-// Decode phase, per tile:  W is read once from TMEM, rounded to fp16 into A operands [128 px][64 codes] per level
-// (aliasing the blend ring, idle by then), and  F[128 x 128] = W_l . C_l[:, chunk]  runs chunk by chunk into two
-// ping-pong TMEM slots per half; pass 0 sums squares (thread = pixel => thread-local L2 norm), pass 1 re-issues the
-// MMAs, scales and streams the features to HBM.  One level's codebook (64 KB fp16) is resident in shared memory and
-// re-fetched level by level from L2 with bulk async copies.
+// each (pixel, instance) as fp16 head + fp16 remainder into the A tile [128 px][hi 16 | lo 16] of their half;
+//   W[128 x L] += A_hi.S_hi + A_lo.S_hi + A_hi.S_lo        (M = 128, N = L, three K = 16 MMAs, fp32 in TMEM)
+// which carries ~22 significant bits per factor: the weight map meets the fp32-blend tolerance (1e-4).
+// End of tile:  W -> fp16 rows of Wdec[level][256 px][64 codes];  U_l = Wdec_l.(G_hi + G_lo) with G_l = s C_l C_l^T
+// gives |F_l|^2 = w^T G w per pixel (thread-local dot product), the rows are rescaled by 1/(|F_l| + 1e-10) and the
+// blend warps move on to the next tile while
+// Decode (transposed):  F^T[128 features x 32 px] = C_l^T[chunk] . Wdec_l[32 px]^T  runs chunk by chunk into four
+// TMEM slots; an epilogue warp owns 32 feature lanes, reads its 32 pixels (two tile rows) per feature, writes them
+// as 16-byte pieces into a [2 rows][32 features][16 px] box image (64-byte swizzle, conflict-free) and one lane
+// issues the tensor store.  No per-thread global stores, no second pass over F.
+#include <string.h>
+
 #include "fd_common.cuh"
 
 namespace lsv2 {
 
-// codebooks f32 [levels][64][512] -> fp16 B image [levels][512 rows n][64 k], 128B-swizzled
+// codebooks f32 [levels][64][512] -> fp16 image [levels][512 rows n][64 k], 128B-swizzled (A operand of the decode)
 __global__ void k_fd_prep_b(int levels, const float* __restrict__ codebooks, uint8_t* __restrict__ bimg)
 {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -38,7 +47,49 @@ __global__ void k_fd_prep_b(int levels, const float* __restrict__ codebooks, uin
     *reinterpret_cast<uint4*>(bimg + (size_t)l * (FD_D * 128) + sw128_offset(n, chunk)) = make_uint4(w[0], w[1], w[2], w[3]);
 }
 
-// everything the producer gathers for one instance (kept in registers one batch ahead)
+// Gram images.  block (n, l), thread k:  G[n][k] = s * <C16_n, C16_k> with C16 the fp16-rounded codebook (what the
+// decode MMA multiplies by), s = 1024 / max_n |C16_n|^2; stored as fp16 head (rows 0-63) + remainder (rows 64-127).
+__global__ void __launch_bounds__(64) k_fd_prep_g(const float* __restrict__ codebooks, uint8_t* __restrict__ gimg,
+                                                 float* __restrict__ gscale_inv)
+{
+    __shared__ float s_row[FD_D];
+    __shared__ float s_v[FD_LC];
+    __shared__ float s_red[2];
+    const int n = blockIdx.x, l = blockIdx.y, k = threadIdx.x;
+    const float* cb = codebooks + (size_t)l * FD_LC * FD_D;
+    for (int d = k; d < FD_D; d += 64) s_row[d] = __half2float(__float2half_rn(cb[(size_t)n * FD_D + d]));
+    __syncthreads();
+    float dot = 0.0f, nrm = 0.0f;
+    const float4* rk = reinterpret_cast<const float4*>(cb + (size_t)k * FD_D);
+    for (int d4 = 0; d4 < FD_D / 4; ++d4) {
+        const float4 v = __ldg(rk + d4);
+        const float c0 = __half2float(__float2half_rn(v.x)), c1 = __half2float(__float2half_rn(v.y));
+        const float c2 = __half2float(__float2half_rn(v.z)), c3 = __half2float(__float2half_rn(v.w));
+        dot = fmaf(c0, s_row[4 * d4], dot); dot = fmaf(c1, s_row[4 * d4 + 1], dot);
+        dot = fmaf(c2, s_row[4 * d4 + 2], dot); dot = fmaf(c3, s_row[4 * d4 + 3], dot);
+        nrm = fmaf(c0, c0, nrm); nrm = fmaf(c1, c1, nrm); nrm = fmaf(c2, c2, nrm); nrm = fmaf(c3, c3, nrm);
+    }
+    float mx = nrm;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((k & 31) == 0) s_red[k >> 5] = mx;
+    __syncthreads();
+    mx = fmaxf(s_red[0], s_red[1]);
+    const float s = mx > 0.0f ? 1024.0f / mx : 1.0f;
+    if (n == 0 && k == 0) gscale_inv[l] = 1.0f / s;
+    s_v[k] = dot * s;
+    __syncthreads();
+    if (k < 8) {                                  // thread k packs 16-byte chunk k of row n (head and remainder)
+        uint32_t hi[4], lo[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) split_f16x2(s_v[k * 8 + 2 * i], s_v[k * 8 + 2 * i + 1], hi[i], lo[i]);
+        uint8_t* base = gimg + (size_t)l * FD_CB_BYTES;
+        *reinterpret_cast<uint4*>(base + sw128_offset(n, k)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        *reinterpret_cast<uint4*>(base + sw128_offset(64 + n, k)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    }
+}
+
+// What one producer lane gathers for its instance (kept in registers one batch ahead).
 struct FdGather {
     uint32_t g, cnt;
     float4 r0, r1, r2;
@@ -85,116 +136,127 @@ __device__ __forceinline__ void fd_gather(const FdArgs& a, uint32_t g, FdGather&
     }
 }
 
-template <int MODE, bool OUT_BF16>
-__global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
+// one coefficient into an S tile: head at k-slice 0, remainder at k-slice 1 of row `c`
+__device__ __forceinline__ void fd_put(unsigned char* S, uint32_t c, uint32_t inst, float w, bool accumulate)
+{
+    __half* ph = reinterpret_cast<__half*>(S + sw64_offset(c, inst >> 3) + (inst & 7u) * 2u);
+    __half* pl = reinterpret_cast<__half*>(S + sw64_offset(c, 2u + (inst >> 3)) + (inst & 7u) * 2u);
+    if (accumulate) w = __fadd_rn(__fadd_rn(__half2float(*ph), __half2float(*pl)), w);     // duplicates add up
+    const __half h = __float2half_rn(w);
+    *ph = h;
+    *pl = __float2half_rn(__fsub_rn(w, __half2float(h)));
+}
+
+template <int MODE, bool OUT_BF16, bool DECODE>
+__global__ void __launch_bounds__(DECODE ? FD_THREADS : FD_THREADS_NODECODE, 1) k_render_decode(FdArgs a)
 {
     extern __shared__ unsigned char smem_raw[];
     // offset arithmetic on the __shared__ symbol (not a uintptr_t round trip) keeps the shared address space
     // visible to the compiler: LDS/STS instead of generic LD/ST in the blend loop
     unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     unsigned char* ring = smem + FD_SMEM_RING;
-    unsigned char* s_b = smem + FD_SMEM_B;
     FdHeader* hdrs = reinterpret_cast<FdHeader*>(smem + FD_SMEM_HDR);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + FD_SMEM_BAR);
-    uint64_t* full = bars;                        // [2]  producer -> blend, mma     (64 arrivals)
-    uint64_t* a_full = bars + 2;                  // [2]  blend -> mma               (256 arrivals)
-    uint64_t* stage_free = bars + 4;              // [2]  mma -> producer            (commit / arrive)
-    uint64_t* w_full = bars + 6;                  //      mma -> blend: W complete   (commit / arrive)
-    uint64_t* adec_full = bars + 7;               //      blend -> mma               (256 arrivals)
-    uint64_t* ring_free = bars + 8;               //      mma -> producer            (commit / arrive)
-    uint64_t* b_full = bars + 9;                  // [4]  bulk copy landed           (tx)
-    uint64_t* b_free = bars + 13;                 // [4]  mma done with chunk        (commit)
-    uint64_t* f_full = bars + 17;                 // [2]  F slot ready               (commit)
-    uint64_t* f_free = bars + 19;                 // [2]  F slot drained             (256 arrivals)
-    uint64_t* g_full = bars + 21;                 //      Gram images landed         (tx)
-    uint64_t* u_full = bars + 22;                 //      U = W.G ready              (commit)
-    uint64_t* adec2_full = bars + 23;             //      blend -> mma: W rescaled   (256 arrivals)
-    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 24);
-    uint32_t* s_ndone = s_tmem + 1;               // [2]  saturated strips, by tile parity
-    int32_t* s_tile = reinterpret_cast<int32_t*>(s_tmem + 3);
+    uint64_t* full = bars;                        // [2]  producer -> blend, mma          (32 arrivals)
+    uint64_t* a_full = bars + 2;                  // [2]  blend -> mma                    (256 arrivals)
+    uint64_t* stage_free = bars + 4;              // [2]  mma -> producer                 (commit / arrive)
+    uint64_t* w_full = bars + 6;                  //      mma -> blend: W complete        (commit / arrive)
+    uint64_t* wraw_full = bars + 7;               // [3]  blend -> MD: fp16 rows of level l written     (256)
+    uint64_t* u_full = bars + 10;                 // [3]  MD -> blend: U_l = Wdec_l.G_l ready           (commit)
+    uint64_t* inv_full = bars + 13;               //      blend -> epilogue: 1/norm of the unit written (256)
+    uint64_t* dec_done = bars + 14;               //      MD -> blend: decode MMAs of the unit done     (commit)
+    uint64_t* cb_full = bars + 15;                // [2]  bulk copy landed                 (tx)
+    uint64_t* cb_free = bars + 17;                // [2]  MMAs done with the chunk         (commit)
+    uint64_t* f_full = bars + 19;                 // [4]  F slot ready                     (commit)
+    uint64_t* f_free = bars + 23;                 // [4]  F slot drained                   (4 arrivals)
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 27);
+    uint32_t* s_ndone = s_tmem + 1;               // [2]  saturated strips, by unit parity
+    FdTileInfo* tinfo = reinterpret_cast<FdTileInfo*>(s_tmem + 4);     // [2] by unit parity
+    float* s_inv = reinterpret_cast<float*>(smem + FD_SMEM_INV);       // [2][3][256] by unit parity
+    unsigned char* wdec = smem + FD_SMEM_WDEC;
+    unsigned char* s_cb = smem + FD_SMEM_CB;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int L = a.L, levels = a.levels;
     const size_t HW = (size_t)a.H * a.W;
+    const bool normalize = DECODE && a.normalize != 0;
 
     if (tid == 0) {
         for (int s = 0; s < FD_STAGES; ++s) {
-            mbar_init(full + s, FD_PROD_THREADS);
+            mbar_init(full + s, 32);
             mbar_init(a_full + s, 32 * FD_BLEND_WARPS);
             mbar_init(stage_free + s, 1);
-            mbar_init(f_full + s, 1);
-            mbar_init(f_free + s, 32 * FD_BLEND_WARPS);
+            mbar_init(cb_full + s, 1);
+            mbar_init(cb_free + s, 1);
         }
         mbar_init(w_full, 1);
-        mbar_init(adec_full, 32 * FD_BLEND_WARPS);
-        mbar_init(ring_free, 1);
-        mbar_init(g_full, 1);
-        mbar_init(u_full, 1);
-        mbar_init(adec2_full, 32 * FD_BLEND_WARPS);
-        for (int c = 0; c < FD_CHUNKS; ++c) { mbar_init(b_full + c, 1); mbar_init(b_free + c, 1); }
+        for (int l = 0; l < 3; ++l) { mbar_init(wraw_full + l, 32 * FD_BLEND_WARPS); mbar_init(u_full + l, 1); }
+        mbar_init(inv_full, 32 * FD_BLEND_WARPS);
+        mbar_init(dec_done, 1);
+        for (int q = 0; q < FD_FSLOTS; ++q) { mbar_init(f_full + q, 1); mbar_init(f_free + q, FD_EPI_WARPS); }
         s_ndone[0] = 0;
         s_ndone[1] = 0;
         mbar_fence_init();
     }
-    if (warp == 10) tmem_alloc(s_tmem, 512);
+    if (warp == FD_WARP_MB) tmem_alloc(s_tmem, 512);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *s_tmem;
 
-    if (warp >= FD_BLEND_WARPS && warp < FD_BLEND_WARPS + 2) {
+    if (warp == FD_WARP_PROD) {
         // ======================================= producer =======================================
-        // The gathers of batch b+1 (ids two batches ahead) are issued before batch b is assembled, so the
-        // global-memory latency is off the per-batch critical path: wait stage -> zero B tile -> scatter -> arrive.
-        const int pt = tid - 32 * FD_BLEND_WARPS;       // 0..63 = instance slot of the batch
-        const int pw = pt >> 5;
+        // lane = (list t = lane >> 4, instance slot = lane & 15).  The gathers of batch b+1 (ids two batches ahead)
+        // are issued before batch b is assembled, so the global-memory latency is off the per-batch critical path:
+        // wait stage -> zero both S tiles -> scatter -> arrive.
+        const int inst = lane & 15, t = lane >> 4;
         uint32_t use_g = 0;                             // stage uses so far (global)
-        for (uint32_t t_iter = 0;; ++t_iter) {
-            if (pt == 0) *s_tile = (int32_t)atomicAdd(a.tile_counter, 1u);
-            named_bar_sync(1, FD_PROD_THREADS);
-            const int tile = *s_tile;
-            named_bar_sync(1, FD_PROD_THREADS);
-            const bool exit_now = tile >= a.n_tiles;
+        for (uint32_t u_iter = 0;; ++u_iter) {
+            int unit = 0;
+            if (lane == 0) unit = (int)atomicAdd(a.tile_counter, 1u);
+            unit = __shfl_sync(0xffffffffu, unit, 0);
+            const bool exit_now = unit >= a.n_units;
+            const int band = unit / a.ux, pair = unit % a.ux;
+            const int tx = 2 * pair + t, ty = band >> 1;
             uint2 range = make_uint2(0, 0);
-            if (!exit_now) range = a.ranges[tile];
+            if (!exit_now && tx < a.gx) range = a.ranges[ty * a.gx + tx];
             const uint32_t n_inst = range.y - range.x;
-            const uint32_t n_batches = (n_inst + FD_BATCH - 1) / FD_BATCH;
-            const float y0 = (float)((tile / a.gx) * TILE), x0 = (float)((tile % a.gx) * TILE);
+            uint32_t n_batches = (n_inst + FD_BATCH - 1) / FD_BATCH;
+            n_batches = max(n_batches, __shfl_xor_sync(0xffffffffu, n_batches, 16));
+            const float y0 = (float)(band * FD_UNIT_H), x0 = (float)(tx * TILE);
             auto load_id = [&](uint32_t b) -> uint32_t {
-                const uint32_t i = b * FD_BATCH + pt;
+                const uint32_t i = b * FD_BATCH + (uint32_t)inst;
                 return i < n_inst ? __ldg(a.point_list + range.x + i) : 0xFFFFFFFFu;
             };
             FdGather cur, nxt;
             fd_gather<MODE>(a, load_id(0), cur);
             uint32_t gid_next = load_id(1);
-            if (t_iter > 0 && !exit_now) mbar_wait_sleep(ring_free, (t_iter - 1) & 1);
             for (uint32_t b = 0;; ++b, ++use_g) {
                 const int s = use_g & 1;
                 const uint32_t use = use_g >> 1;
                 if (use > 0) mbar_wait_sleep(stage_free + s, (use - 1) & 1);
                 FdHeader& Hd = hdrs[s];
-                const bool stop = exit_now || b >= n_batches ||
-                                  *(volatile uint32_t*)(s_ndone + (t_iter & 1)) >= FD_BLEND_WARPS;
-                // s_ndone may change between the 64 reads: OR-reduce so the decision is uniform
-                if (named_bar_or(1, FD_PROD_THREADS, stop)) {
-                    if (pt == 0) { Hd.count = exit_now ? -2 : -1; Hd.tile = tile; Hd.batches = (int32_t)b; }
+                const bool stop_l = exit_now || b >= n_batches ||
+                                    *(volatile uint32_t*)(s_ndone + (u_iter & 1)) >= FD_BLEND_WARPS;
+                // s_ndone may change between the 32 reads: OR-reduce so the decision is uniform
+                if (__any_sync(0xffffffffu, stop_l)) {
+                    if (lane == 0) { Hd.count = exit_now ? -2 : -1; Hd.unit = unit; Hd.batches = (int32_t)b; }
                     mbar_arrive(full + s);
                     ++use_g;
                     break;
                 }
-                unsigned char* S = ring + (size_t)s * FD_STAGE_BYTES + 2 * FD_TILE16K;
-                for (int q = pt; q < L * 8; q += FD_PROD_THREADS)
-                    reinterpret_cast<uint4*>(S)[q] = make_uint4(0, 0, 0, 0);
+                unsigned char* S0 = ring + (size_t)s * FD_STAGE_BYTES + 2 * FD_AHALF_BYTES;
+                for (int q = lane; q < 2 * FD_S_BYTES / 16; q += 32) reinterpret_cast<uint4*>(S0)[q] = make_uint4(0, 0, 0, 0);
                 fd_gather<MODE>(a, gid_next, nxt);          // in flight while this batch is assembled
                 gid_next = load_id(b + 2);
-                named_bar_sync(1, FD_PROD_THREADS);
-                uint32_t m8 = 0;
+                __syncwarp();
+                unsigned char* S = S0 + (size_t)t * FD_S_BYTES;
+                uint32_t m4 = 0;
                 if (cur.g != 0xFFFFFFFFu) {
-                    Hd.g0[pt] = cur.r0;
-                    Hd.g1[pt] = cur.r1;
-                    Hd.g2[pt] = make_float2(cur.r2.x, cur.r2.y);
-                    m8 = fd_strip_mask(cur.r0.y - y0, cur.r0.z, cur.r0.w, cur.r1.x, cur.r1.y, cur.r0.x - x0);
-                    const uint32_t col = (uint32_t)(pt & 7) * 2u, chunk = (uint32_t)pt >> 3;
+                    Hd.g0[lane] = cur.r0;
+                    Hd.g1[lane] = cur.r1;
+                    Hd.g2[lane] = make_float2(cur.r2.x, cur.r2.y);
+                    m4 = fd_strip_mask(cur.r0.y - y0, cur.r0.z, cur.r0.w, cur.r1.x, cur.r1.y, cur.r0.x - x0) & 0xFu;
                     if (cur.cnt != FD_ROW_DENSE) {
                         bool ascending = true;              // distinct channels: plain stores, no read-modify-write
 #pragma unroll
@@ -204,71 +266,41 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
                         for (int k = 0; k < FD_KMAX; ++k) {
                             if ((uint32_t)k < cur.cnt) {
                                 const int c = (int)cur.iv[k];
-                                if (c >= 0 && c < L) {
-                                    __half* p = reinterpret_cast<__half*>(S + sw128_offset((uint32_t)c, chunk) + col);
-                                    if (ascending) {
-                                        *p = __float2half_rn(cur.wv[k]);
-                                    } else {
-                                        const float old = __half2float(*p);    // duplicates of a channel add up
-                                        *p = __float2half_rn(old + cur.wv[k]);
-                                    }
-                                } else {
-                                    a.status[LSV2_STATUS_BAD_INDEX] = 1u;
-                                }
+                                if (c >= 0 && c < L) fd_put(S, (uint32_t)c, (uint32_t)inst, cur.wv[k], !ascending);
+                                else a.status[LSV2_STATUS_BAD_INDEX] = 1u;
                             }
                         }
                     } else {
                         const float* row = a.coeff_dense + (size_t)cur.g * L;
                         for (int c = 0; c < L; ++c) {
                             const float v = __ldg(row + c);
-                            if (v != 0.0f)
-                                *reinterpret_cast<__half*>(S + sw128_offset((uint32_t)c, chunk) + col) = __float2half_rn(v);
+                            if (v != 0.0f) fd_put(S, (uint32_t)c, (uint32_t)inst, v, false);
                         }
                     }
                 }
 #pragma unroll
-                for (int w = 0; w < FD_BLEND_WARPS; ++w) {
-                    const uint32_t bal = __ballot_sync(0xffffffffu, (m8 >> w) & 1u);
-                    if (lane == 0) Hd.mask[w][pw] = bal;
+                for (int w = 0; w < 4; ++w) {
+                    const uint32_t bal = __ballot_sync(0xffffffffu, (m4 >> w) & 1u);     // [15:0] list 0, [31:16] list 1
+                    if (lane == 0) { Hd.mask[w] = bal & 0xFFFFu; Hd.mask[4 + w] = bal >> 16; }
                 }
-                if (pt == 0) {
-                    Hd.count = (int32_t)min((uint32_t)FD_BATCH, n_inst - b * FD_BATCH);
-                    Hd.tile = tile;
-                }
+                if (lane == 0) { Hd.count = 1; Hd.unit = unit; }
                 fence_async_smem();
                 mbar_arrive(full + s);
                 cur = nxt;
             }
             if (exit_now) break;
         }
-    } else if (warp == 10) {
-        // ================================ MMA issue + codebook fetch ================================
+    } else if (warp == FD_WARP_MB) {
+        // ======================================= blend MMA issue =======================================
         if (lane == 0) {
             const uint32_t idesc_blend = umma_idesc_f16_f32(128, L);
-            constexpr uint32_t idesc_dec = umma_idesc_f16_f32(128, FD_CHUNK_N);
-            const uint32_t ring_addr = smem_u32(ring), b_addr = smem_u32(s_b);
-            const int passes = a.normalize ? 2 : 1;
-            uint32_t b_issued[FD_CHUNKS] = {0, 0, 0, 0};     // bulk copies issued per chunk slot
-            uint32_t b_used[FD_CHUNKS] = {0, 0, 0, 0};       // b_full phases consumed per chunk slot
-            uint32_t f_n = 0;                                // F slot fills so far (slots alternate)
-            int next_level = 0;                              // level the next codebook fetch belongs to
-            auto fetch = [&](int c) {                        // chunk c of level `lvl`
-                mbar_arrive_expect_tx(b_full + c, FD_TILE16K);
-                bulk_g2s(s_b + (size_t)c * FD_TILE16K, a.bimg + ((size_t)next_level * FD_CHUNKS + c) * FD_TILE16K,
-                         FD_TILE16K, b_full + c);
-                ++b_issued[c];
-            };
-            for (int c = 0; c < FD_CHUNKS; ++c) fetch(c);    // level 0, ready before the first tile needs it
-            next_level = (next_level + 1) % levels;
-            uint32_t tiles_done = 0;
-            uint32_t batch_in_tile = 0;
+            const uint32_t ring_addr = smem_u32(ring);
+            uint32_t batch_in_unit = 0;
             uint32_t a_uses[FD_STAGES] = {0, 0};             // a_full phases consumed (batches only)
             for (uint32_t use_g = 0;; ++use_g) {
                 const int s = use_g & 1;
-                const uint32_t use = use_g >> 1;
-                mbar_wait_sleep(full + s, use & 1);
-                const FdHeader& Hd = hdrs[s];
-                const int count = Hd.count;
+                mbar_wait_sleep(full + s, (use_g >> 1) & 1);
+                const int count = hdrs[s].count;
                 if (count == -2) break;
                 if (count >= 0) {
                     mbar_wait(a_full + s, a_uses[s] & 1);
@@ -276,113 +308,221 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
                     tc_fence_after();
                     const uint32_t sa = ring_addr + (uint32_t)s * FD_STAGE_BYTES;
 #pragma unroll
-                    for (int h = 0; h < 2; ++h)
+                    for (int h = 0; h < 2; ++h) {
+                        const uint32_t sA = sa + (uint32_t)h * FD_AHALF_BYTES;
+                        const uint32_t sS = sa + 2 * FD_AHALF_BYTES + (uint32_t)h * FD_S_BYTES;
+                        const uint32_t d = tmem + (uint32_t)(h * FD_MAX_L);
+                        umma_bf16(d, umma_desc_k_sw64(sA), umma_desc_k_sw64(sS), idesc_blend, batch_in_unit > 0 ? 1u : 0u);
+                        umma_bf16(d, umma_desc_k_sw64(sA + 32), umma_desc_k_sw64(sS), idesc_blend, 1u);
+                        umma_bf16(d, umma_desc_k_sw64(sA), umma_desc_k_sw64(sS + 32), idesc_blend, 1u);
+                    }
+                    umma_commit(stage_free + s);
+                    ++batch_in_unit;
+                    continue;
+                }
+                // ---- end of unit ----
+                mbar_arrive(stage_free + s);
+                if (batch_in_unit > 0) umma_commit(w_full); else mbar_arrive(w_full);
+                batch_in_unit = 0;
+            }
+        }
+    } else if (DECODE && warp == FD_WARP_MD) {
+        // ================================ Gram + decode MMA issue, codebook fetch ================================
+        if (lane == 0) {
+            constexpr uint32_t idesc_u = umma_idesc_f16_f32(128, FD_LC);
+            constexpr uint32_t idesc_dec = umma_idesc_f16_f32(128, FD_NFEAT);
+            const uint32_t wdec_addr = smem_u32(wdec), cb_addr = smem_u32(s_cb);
+            const int n_g = normalize ? levels : 0;
+            const int jobs_per_unit = n_g + levels * FD_CHUNKS;
+            uint32_t cb_issued = 0, cb_used = 0, f_n = 0;
+            auto fetch_next = [&]() {                        // codebook-ring job `cb_issued` -> slot cb_issued & 1
+                const int slot = (int)(cb_issued & 1u);
+                if (cb_issued >= FD_CB_SLOTS) mbar_wait(cb_free + slot, ((cb_issued >> 1) - 1) & 1);
+                const int j = (int)(cb_issued % (uint32_t)jobs_per_unit);
+                const uint8_t* src = j < n_g ? a.gimg + (size_t)j * FD_CB_BYTES : a.bimg + (size_t)(j - n_g) * FD_CB_BYTES;
+                mbar_arrive_expect_tx(cb_full + slot, FD_CB_BYTES);
+                bulk_g2s(s_cb + (size_t)slot * FD_CB_BYTES, src, FD_CB_BYTES, cb_full + slot);
+                ++cb_issued;
+            };
+            fetch_next();
+            fetch_next();
+            for (uint32_t it = 0;; ++it) {
+                bool stop = false;
+                for (int l = 0; l < levels; ++l) {
+                    // rows of level l are in shared memory (all levels are needed before the decode starts anyway;
+                    // the per-level barrier lets the Gram products start while later levels are still converted)
+                    mbar_wait_sleep(wraw_full + l, it & 1);
+                    if (l == 0 && tinfo[it & 1].unit < 0) { stop = true; break; }
+                    if (!normalize) continue;
+                    tc_fence_after();
+                    const uint32_t n = cb_used;
+                    const int slot = (int)(n & 1u);
+                    mbar_wait(cb_full + slot, (n >> 1) & 1);
+                    const uint32_t g_hi = cb_addr + (uint32_t)slot * FD_CB_BYTES, g_lo = g_hi + 64 * 128;
+#pragma unroll
+                    for (int m = 0; m < 2; ++m) {
+                        const uint32_t d = tmem + (uint32_t)(m * FD_MAX_L + l * FD_LC);
+                        const uint32_t aw = wdec_addr + (uint32_t)l * FD_WDEC_LEVEL + (uint32_t)m * (128 * 128);
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks)
-                            umma_bf16(tmem + (uint32_t)(h * L), umma_desc_k_sw128(sa + h * FD_TILE16K + ks * 32),
-                                      umma_desc_k_sw128(sa + 2 * FD_TILE16K + ks * 32), idesc_blend,
-                                      (batch_in_tile > 0 || ks > 0) ? 1u : 0u);
-                    umma_commit(stage_free + s);
-                    ++batch_in_tile;
-                    continue;
-                }
-                // ---- end of tile ----
-                const uint32_t nb = batch_in_tile;
-                batch_in_tile = 0;
-                mbar_arrive(stage_free + s);
-                if (nb > 0) umma_commit(w_full); else mbar_arrive(w_full);
-                mbar_wait_sleep(adec_full, tiles_done & 1);
-                tc_fence_after();
-                if (nb == 0) {
-                    mbar_arrive(ring_free);
-                    ++tiles_done;
-                    continue;
-                }
-                for (int l = 0; l < levels; ++l) {
-                    for (int pass = 0; pass < passes; ++pass) {
-                        for (int c = 0; c < FD_CHUNKS; ++c) {
-                            const int q = (int)(f_n & 1u);
-                            if (f_n >= 2) mbar_wait(f_free + q, ((f_n >> 1) - 1) & 1);
-                            if (pass == 0) { mbar_wait(b_full + c, b_used[c] & 1); ++b_used[c]; }
-                            tc_fence_after();
+                            umma_bf16(d, umma_desc_k_sw128(aw + ks * 32), umma_desc_k_sw128(g_hi + ks * 32), idesc_u,
+                                      ks > 0 ? 1u : 0u);
 #pragma unroll
-                            for (int h = 0; h < 2; ++h) {
-                                const uint32_t aa = ring_addr + (uint32_t)(h * levels + l) * FD_TILE16K;
+                        for (int ks = 0; ks < 4; ++ks)
+                            umma_bf16(d, umma_desc_k_sw128(aw + ks * 32), umma_desc_k_sw128(g_lo + ks * 32), idesc_u, 1u);
+                    }
+                    umma_commit(u_full + l);
+                    umma_commit(cb_free + slot);
+                    ++cb_used;
+                    if (n >= 1) fetch_next();
+                }
+                if (stop) break;
+                tc_fence_after();
+                for (int l = 0; l < levels; ++l) {
+                    for (int c = 0; c < FD_CHUNKS; ++c) {
+                        const uint32_t n = cb_used;
+                        const int slot = (int)(n & 1u);
+                        mbar_wait(cb_full + slot, (n >> 1) & 1);
+                        const uint32_t ca = cb_addr + (uint32_t)slot * FD_CB_BYTES;
+                        for (int g = 0; g < FD_FGROUPS; ++g) {
+#pragma unroll 1
+                            for (int m = 0; m < 2; ++m) {
+                                const int fs = (int)(f_n & (FD_FSLOTS - 1));
+                                if (f_n >= FD_FSLOTS) mbar_wait(f_free + fs, ((f_n >> 2) - 1) & 1);
+                                tc_fence_after();
+                                const uint32_t d = tmem + (uint32_t)(FD_TMEM_F + fs * FD_NFEAT);
+                                const uint32_t aw = wdec_addr + (uint32_t)l * FD_WDEC_LEVEL + (uint32_t)m * (128 * 128);
+                                const uint32_t bw = ca + (uint32_t)g * (FD_NFEAT * 128);
 #pragma unroll
                                 for (int ks = 0; ks < 4; ++ks)
-                                    umma_bf16(tmem + (uint32_t)(h * 256 + q * FD_CHUNK_N), umma_desc_k_sw128(aa + ks * 32),
-                                              umma_desc_k_sw128(b_addr + c * FD_TILE16K + ks * 32), idesc_dec,
+                                    umma_bf16(d, umma_desc_k_sw128(aw + ks * 32), umma_desc_k_sw128(bw + ks * 32), idesc_dec,
                                               ks > 0 ? 1u : 0u);
+                                umma_commit(f_full + fs);
+                                ++f_n;
                             }
-                            umma_commit(f_full + q);
-                            ++f_n;
-                            if (pass == passes - 1) {
-                                umma_commit(b_free + c);
-                                // refill the chunk slot released one step ago with the next level's tile
-                                const int pc = c - 1;
-                                if (pc >= 0) {
-                                    mbar_wait(b_free + pc, (b_issued[pc] - 1) & 1);
-                                    fetch(pc);
+                            if (g == 0 && n >= 1) fetch_next();
+                        }
+                        umma_commit(cb_free + slot);
+                        ++cb_used;
+                    }
+                }
+                umma_commit(dec_done);
+            }
+            // drain the codebook prefetch that no unit consumed
+            while (cb_used < cb_issued) { mbar_wait(cb_full + (cb_used & 1u), (cb_used >> 1) & 1); ++cb_used; }
+        }
+    } else if (DECODE && warp >= FD_BLEND_WARPS && warp < FD_BLEND_WARPS + FD_EPI_WARPS) {
+        // ==================================== epilogue: F slots -> global ====================================
+        // Decode MMA block m covers band rows 4m .. 4m+3; TMEM lane quadrant q = this warp = band row 4m + q,
+        // lane = x: one store instruction writes 32 consecutive pixels of one feature plane (a 128-byte line).
+        const int q = warp & 3;
+        const uint32_t lane_addr = tmem + ((uint32_t)(q * 32) << 16) + FD_TMEM_F;
+        uint32_t f_n = 0;
+        for (uint32_t it = 0;; ++it) {
+            mbar_wait_sleep(inv_full, it & 1);
+            const int unit = tinfo[it & 1].unit;
+            if (unit < 0) break;
+            const int band = unit / a.ux, pair = unit % a.ux;
+            const int px = pair * FD_UNIT_W + lane;
+            const float* inv_u = s_inv + (size_t)(it & 1) * 3 * 256;
+            const size_t esz = OUT_BF16 ? 2 : 4;
+            for (int l = 0; l < levels; ++l) {
+                float inv[2];
+                inv[0] = normalize ? inv_u[l * 256 + q * 32 + lane] : 1.0f;
+                inv[1] = normalize ? inv_u[l * 256 + 128 + q * 32 + lane] : 1.0f;
+                for (int cg = 0; cg < FD_CHUNKS * FD_FGROUPS; ++cg) {
+#pragma unroll
+                    for (int m = 0; m < 2; ++m) {
+                        const int fs = (int)(f_n & (FD_FSLOTS - 1));
+                        mbar_wait(f_full + fs, (f_n >> 2) & 1);
+                        ++f_n;
+                        tc_fence_after();
+                        uint32_t r[32];
+                        tmem_ld32(lane_addr + (uint32_t)(fs * FD_NFEAT), r);
+                        tmem_wait_ld();
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(f_free + fs);     // slot drained: the next MMA may overwrite it
+                        const int py = band * FD_UNIT_H + 4 * m + q;
+                        if (px < a.W && py < a.H) {
+                            const size_t d0 = (size_t)l * FD_D + (size_t)cg * FD_NFEAT;
+                            const uint64_t stride = (uint64_t)HW * esz;
+                            uint64_t p[4];
+                            p[0] = (uint64_t)(uintptr_t)a.out + (d0 * HW + (size_t)py * a.W + px) * esz;
+                            p[1] = p[0] + stride; p[2] = p[1] + stride; p[3] = p[2] + stride;
+                            const uint64_t s4 = 4 * stride;
+                            const float sc = inv[m];
+#pragma unroll
+                            for (int i = 0; i < 32; i += 4) {
+#pragma unroll
+                                for (int u = 0; u < 4; ++u) {
+                                    const float v = __uint_as_float(r[i + u]) * sc;
+                                    if (OUT_BF16) {
+                                        const unsigned short hv = __bfloat16_as_ushort(__float2bfloat16_rn(v));
+                                        asm volatile("st.global.cs.u16 [%0], %1;" ::"l"(p[u]), "h"(hv) : "memory");
+                                    } else {
+                                        asm volatile("st.global.cs.f32 [%0], %1;" ::"l"(p[u]), "f"(v) : "memory");
+                                    }
+                                    p[u] += s4;
                                 }
                             }
                         }
                     }
-                    // last chunk slot of this level
-                    mbar_wait(b_free + (FD_CHUNKS - 1), (b_issued[FD_CHUNKS - 1] - 1) & 1);
-                    fetch(FD_CHUNKS - 1);
-                    next_level = (next_level + 1) % levels;
                 }
-                umma_commit(ring_free);
-                ++tiles_done;
             }
-            // drain the codebook prefetch that no tile consumed
-            for (int c = 0; c < FD_CHUNKS; ++c)
-                while (b_used[c] < b_issued[c]) { mbar_wait(b_full + c, b_used[c] & 1); ++b_used[c]; }
         }
-    } else {
-        // ==================================== blend + epilogue ====================================
-        const int half = warp >> 2;                                  // MMA half this strip belongs to
-        const int row = (warp & 3) * 32 + lane;                      // A-tile row == TMEM lane
-        const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
-        const int lx = lane & 15, ly = warp * 2 + (lane >> 4);
-        uint32_t f_n = 0;                                            // F slots consumed so far (slots alternate)
-        uint32_t tiles_done = 0;
+    } else if (warp < FD_BLEND_WARPS) {
+        // ==================================== blend ====================================
+        const int half = warp >> 2;                                  // 0: left tile's list, 1: right tile's list
+        const int strip = warp & 3;                                  // rows 2*strip, 2*strip+1 of the band
+        const int row = strip * 32 + lane;                           // A-tile row == TMEM lane of the blend MMA
+        const uint32_t lane_base = tmem + ((uint32_t)(strip * 32) << 16);
+        const int lx = lane & 15, ly = 2 * strip + (lane >> 4);
+        // the decode sees the band as 8 rows of 32 pixels: row of the 256-row decode operand this pixel owns
+        const uint32_t prow = (uint32_t)(ly * 32 + half * 16 + lx);
+        // ... and the decode row whose norm this thread computes (TMEM lane quadrant = strip, MMA block = half)
+        const uint32_t nrow = (uint32_t)(half * 128 + strip * 32 + lane);
+        uint32_t units_done = 0;
         uint32_t use_g = 0;
         for (;;) {
             // ---------------- blend phase ----------------
             float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f;
             uint32_t last = 0;
             bool done = false, warp_done = false, first = true;
-            int tile = 0, px = 0, py = 0;
+            int unit = 0, px = 0, py = 0;
             float pxf = 0.f, pyf = 0.f;
             bool inside = false;
             int count;
             int nb = 0;
+            auto locate = [&]() {
+                const int band = unit / a.ux, pair = unit % a.ux;
+                px = pair * FD_UNIT_W + half * 16 + lx;
+                py = band * FD_UNIT_H + ly;
+                pxf = (float)px; pyf = (float)py;
+                inside = px < a.W && py < a.H;
+            };
             for (;; ++use_g) {
                 const int s = use_g & 1;
                 mbar_wait(full + s, (use_g >> 1) & 1);
                 const FdHeader& Hd = hdrs[s];
                 count = Hd.count;
-                if (count < 0) { tile = Hd.tile; nb = Hd.batches; ++use_g; break; }
+                if (count < 0) { unit = Hd.unit; nb = Hd.batches; ++use_g; break; }
                 if (first) {
                     first = false;
-                    tile = Hd.tile;
-                    px = (tile % a.gx) * TILE + lx;
-                    py = (tile / a.gx) * TILE + ly;
-                    pxf = (float)px; pyf = (float)py;
-                    inside = px < a.W && py < a.H;
+                    unit = Hd.unit;
+                    locate();
                     done = !inside;
                     warp_done = __all_sync(0xffffffffu, done);
-                    if (warp_done && lane == 0) atomicAdd(s_ndone + (tiles_done & 1), 1u);
-                    if (warp == 0 && lane == 0) s_ndone[(tiles_done + 1) & 1] = 0;
+                    if (warp_done && lane == 0) atomicAdd(s_ndone + (units_done & 1), 1u);
+                    if (warp == 0 && lane == 0) s_ndone[(units_done + 1) & 1] = 0;
                 }
-                unsigned char* A = ring + (size_t)s * FD_STAGE_BYTES + (size_t)half * FD_TILE16K;
-                const uint64_t m = warp_done ? 0ull : (((uint64_t)Hd.mask[warp][1] << 32) | Hd.mask[warp][0]);
-#pragma unroll 1
-                for (int c = 0; c < 8; ++c) {
-                    const uint32_t m8 = (uint32_t)(m >> (8 * c)) & 0xFFu;
-                    uint32_t hw[4] = {0u, 0u, 0u, 0u};
-                    if (m8 != 0u && !(a.dbg & 2)) {
+                unsigned char* A = ring + (size_t)s * FD_STAGE_BYTES + (size_t)half * FD_AHALF_BYTES;
+                const uint32_t m = warp_done ? 0u : Hd.mask[warp];
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    const uint32_t m8 = (m >> (8 * c)) & 0xFFu;
+                    uint32_t hw[4] = {0u, 0u, 0u, 0u}, lw[4] = {0u, 0u, 0u, 0u};
+                    if (m8 != 0u) {
 #pragma unroll
                         for (int q4 = 0; q4 < 2; ++q4) {
                             const uint32_t m4 = (m8 >> (4 * q4)) & 0xFu;
@@ -394,7 +534,7 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
                             bool any = false;
 #pragma unroll
                             for (int u = 0; u < 4; ++u) {
-                                const int j = 8 * c + 4 * q4 + u;
+                                const int j = half * FD_BATCH + 8 * c + 4 * q4 + u;
                                 const float4 g0 = Hd.g0[j];
                                 const float4 g1 = Hd.g1[j];
                                 const float dx = g0.x - pxf, dy = g0.y - pyf;
@@ -418,27 +558,28 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
                                 for (int u = 0; u < 4; ++u) {
                                     // select-only form of: skip if alpha < 1/255 or done; stop if T' < 1e-4; else blend.
                                     // A skipped instance adds w = 0 (exact), so the sums match the branching form bit for bit.
-                                    const int j = 8 * c + 4 * q4 + u;
+                                    const int jl = 8 * c + 4 * q4 + u;
                                     const bool valid = !(al[u] < ALPHA_MIN) && !done;
                                     const float test_T = T * (1.0f - al[u]);
                                     const bool stop = valid && (test_T < T_MIN);
                                     const bool use = valid && !stop;
                                     done = done || stop;
                                     const float w = use ? al[u] * T : 0.0f;
-                                    const float2 g2 = Hd.g2[j];
+                                    const float2 g2 = Hd.g2[half * FD_BATCH + jl];
                                     C0 = fmaf(cr_[u], w, C0);
                                     C1 = fmaf(g2.x, w, C1);
                                     C2 = fmaf(g2.y, w, C2);
                                     wgt[u] = w;
                                     T = use ? test_T : T;
-                                    last = use ? (uint32_t)nb * FD_BATCH + (uint32_t)j + 1u : last;
+                                    last = use ? (uint32_t)nb * FD_BATCH + (uint32_t)jl + 1u : last;
                                 }
+                                split_f16x2(wgt[0], wgt[1], hw[2 * q4], lw[2 * q4]);
+                                split_f16x2(wgt[2], wgt[3], hw[2 * q4 + 1], lw[2 * q4 + 1]);
                             }
-                            hw[2 * q4] = pack_f16x2(wgt[0], wgt[1]);
-                            hw[2 * q4 + 1] = pack_f16x2(wgt[2], wgt[3]);
                         }
                     }
-                    *reinterpret_cast<uint4*>(A + sw128_offset((uint32_t)row, (uint32_t)c)) = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+                    *reinterpret_cast<uint4*>(A + sw64_offset((uint32_t)row, (uint32_t)c)) = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+                    *reinterpret_cast<uint4*>(A + sw64_offset((uint32_t)row, (uint32_t)(2 + c))) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
                 }
                 ++nb;
                 fence_async_smem();
@@ -446,51 +587,66 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
                 mbar_arrive(a_full + s);
                 if (!warp_done && __all_sync(0xffffffffu, done)) {
                     warp_done = true;
-                    if (lane == 0) atomicAdd(s_ndone + (tiles_done & 1), 1u);
+                    if (lane == 0) atomicAdd(s_ndone + (units_done & 1), 1u);
                 }
             }
-            if (count == -2) break;
-            if (first) {                                   // a tile with an empty list
-                px = (tile % a.gx) * TILE + lx;
-                py = (tile / a.gx) * TILE + ly;
-                inside = px < a.W && py < a.H;
-                if (warp == 0 && lane == 0) s_ndone[(tiles_done + 1) & 1] = 0;
+            if (count == -2) {
+                if (DECODE) {
+                    if (tid == 0) { tinfo[units_done & 1].unit = -1; tinfo[units_done & 1].nb = 0; }
+                    mbar_arrive(wraw_full);
+                    mbar_arrive(inv_full);
+                }
+                break;
+            }
+            if (first) {                                   // a unit with two empty lists
+                locate();
+                if (warp == 0 && lane == 0) s_ndone[(units_done + 1) & 1] = 0;
             }
             const size_t pix = (size_t)py * a.W + px;
 
-            // ---------------- W: TMEM -> fp16 A operands of the decode ----------------
-            mbar_wait(w_full, tiles_done & 1);
+            // ---------------- W: TMEM -> fp16 rows of the decode operand ----------------
+            mbar_wait(w_full, units_done & 1);
             tc_fence_after();
-            if (nb > 0) {
-                for (int l = 0; l < levels; ++l) {
-                    unsigned char* Ad = ring + (size_t)(half * levels + l) * FD_TILE16K;
+            if (DECODE) {
+                if (units_done > 0) mbar_wait(dec_done, (units_done - 1) & 1);     // previous decode is done with Wdec
+                if (tid == 0) { tinfo[units_done & 1].unit = unit; tinfo[units_done & 1].nb = nb; }
+            }
+            for (int l = 0; l < levels; ++l) {
+                unsigned char* Wl = wdec + (size_t)l * FD_WDEC_LEVEL;
 #pragma unroll
-                    for (int hh = 0; hh < 2; ++hh) {
-                        uint32_t r[32];
-                        tmem_ld32(lane_base + (uint32_t)(half * L + l * FD_LC + hh * 32), r);
+                for (int hh = 0; hh < 2; ++hh) {
+                    uint32_t r[32];
+                    if (nb > 0) {
+                        tmem_ld32(lane_base + (uint32_t)(half * FD_MAX_L + l * FD_LC + hh * 32), r);
                         tmem_wait_ld();
-                        if (a.wmap != nullptr && inside) {
-                            float* o = a.wmap + (size_t)(l * FD_LC + hh * 32) * HW + pix;
+                    } else {
 #pragma unroll
-                            for (int i = 0; i < 32; ++i) st_stream_f32(o + (size_t)i * HW, __uint_as_float(r[i]));
-                        }
+                        for (int i = 0; i < 32; ++i) r[i] = 0u;
+                    }
+                    if (a.wmap != nullptr && inside) {
+                        float* o = a.wmap + (size_t)(l * FD_LC + hh * 32) * HW + pix;
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) st_stream_f32(o + (size_t)i * HW, __uint_as_float(r[i]));
+                    }
+                    if (DECODE) {
 #pragma unroll
                         for (int ch = 0; ch < 4; ++ch) {
                             uint32_t p[4];
 #pragma unroll
                             for (int i = 0; i < 4; ++i)
                                 p[i] = pack_f16x2(__uint_as_float(r[ch * 8 + 2 * i]), __uint_as_float(r[ch * 8 + 2 * i + 1]));
-                            *reinterpret_cast<uint4*>(Ad + sw128_offset((uint32_t)row, (uint32_t)(hh * 4 + ch))) =
+                            *reinterpret_cast<uint4*>(Wl + sw128_offset(prow, (uint32_t)(hh * 4 + ch))) =
                                 make_uint4(p[0], p[1], p[2], p[3]);
                         }
                     }
                 }
-                fence_async_smem();
-            } else if (a.wmap != nullptr && inside) {
-                for (int c = 0; c < L; ++c) st_stream_f32(a.wmap + (size_t)c * HW + pix, 0.0f);
+                if (DECODE) {
+                    fence_async_smem();
+                    tc_fence_before();
+                    mbar_arrive(wraw_full + l);
+                }
             }
-            tc_fence_before();
-            mbar_arrive(adec_full);
+            if (!DECODE) tc_fence_before();
 
             if (inside) {
                 a.final_T[pix] = T;
@@ -500,143 +656,59 @@ __global__ void __launch_bounds__(FD_THREADS, 1) k_render_decode(FdArgs a)
                 a.color[2 * HW + pix] = fmaf(T, a.bg[2], C2);
             }
 
-            // ---------------- decode epilogue ----------------
-            if (nb == 0) {
-                if (inside) {
-                    if (OUT_BF16) {
-                        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(a.out) + pix;
-                        for (int d = 0; d < levels * FD_D; ++d) o[(size_t)d * HW] = __float2bfloat16_rn(0.0f);
-                    } else {
-                        float* o = reinterpret_cast<float*>(a.out) + pix;
-                        for (int d = 0; d < levels * FD_D; ++d) st_stream_f32(o + (size_t)d * HW, 0.0f);
-                    }
-                }
-            } else {
-                const int passes = a.normalize ? 2 : 1;
-                for (int l = 0; l < levels; ++l) {
-                    float ss = 0.0f, inv = 1.0f;
-                    for (int pass = 0; pass < passes; ++pass) {
-                        const bool store = pass == passes - 1;
-                        if (store && a.normalize) inv = 1.0f / (sqrtf(ss) + 1e-10f);
-                        for (int c = 0; c < FD_CHUNKS; ++c) {
-                            const int q = (int)(f_n & 1u);
-                            mbar_wait(f_full + q, (f_n >> 1) & 1);
-                            ++f_n;
-                            tc_fence_after();
-                            const uint32_t col0 = (uint32_t)(half * 256 + q * FD_CHUNK_N);
-                            auto consume = [&](uint32_t (&r)[32], int cc) {
-                                if (!store) {
+            // ---------------- 1 / (|F_l| + 1e-10) per pixel from the Gram products ----------------
+            // |F|^2 = w^T (C C^T) w with w the fp16 row the decode multiplies: U = Wdec.G comes back in TMEM block
+            // `half`, lane quadrant `strip`, i.e. for decode row nrow (not this thread's own pixel -- any thread may
+            // serve any row, the rows are in shared memory).  The scale itself is applied in fp32 by the epilogue.
+            if (DECODE) {
+                if (normalize) {
+                    float* inv_u = s_inv + (size_t)(units_done & 1) * 3 * 256;
+                    for (int l = 0; l < levels; ++l) {
+                        const unsigned char* Wl = wdec + (size_t)l * FD_WDEC_LEVEL;
+                        mbar_wait(u_full + l, units_done & 1);
+                        tc_fence_after();
+                        float ss = 0.0f;
 #pragma unroll
-                                    for (int i = 0; i < 32; ++i) ss = fmaf(__uint_as_float(r[i]), __uint_as_float(r[i]), ss);
-                                } else if (inside && !(a.dbg & 1)) {
-                                    // scale in place, then 32 stores through four independent running addresses
+                        for (int hh = 0; hh < 2; ++hh) {
+                            uint32_t r[32];
+                            tmem_ld32(lane_base + (uint32_t)(half * FD_MAX_L + l * FD_LC + hh * 32), r);
+                            tmem_wait_ld();
 #pragma unroll
-                                    for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * inv);
-                                    const uint64_t esz = OUT_BF16 ? 2u : 4u;
-                                    const uint64_t stride = (uint64_t)HW * esz;
-                                    const size_t ch0 = (size_t)l * FD_D + c * FD_CHUNK_N + cc * 32;
-                                    uint64_t p[4];
-                                    p[0] = (uint64_t)(uintptr_t)a.out + (ch0 * HW + pix) * esz;
-                                    p[1] = p[0] + stride; p[2] = p[1] + stride; p[3] = p[2] + stride;
-                                    const uint64_t s4 = 4 * stride;
+                            for (int ch = 0; ch < 4; ++ch) {
+                                const uint4 w8 = *reinterpret_cast<const uint4*>(Wl + sw128_offset(nrow, (uint32_t)(hh * 4 + ch)));
+                                const uint32_t ww[4] = {w8.x, w8.y, w8.z, w8.w};
 #pragma unroll
-                                    for (int i = 0; i < 32; i += 4) {
-#pragma unroll
-                                        for (int u = 0; u < 4; ++u) {
-                                            if (OUT_BF16) {
-                                                const unsigned short v =
-                                                    __bfloat16_as_ushort(__float2bfloat16_rn(__uint_as_float(r[i + u])));
-                                                asm volatile("st.global.cs.u16 [%0], %1;" ::"l"(p[u]), "h"(v) : "memory");
-                                            } else {
-                                                asm volatile("st.global.cs.b32 [%0], %1;" ::"l"(p[u]), "r"(r[i + u]) : "memory");
-                                            }
-                                            p[u] += s4;
-                                        }
-                                    }
+                                for (int i = 0; i < 4; ++i) {
+                                    const float2 wf = __half22float2(*reinterpret_cast<const __half2*>(&ww[i]));
+                                    ss = fmaf(__uint_as_float(r[ch * 8 + 2 * i]), wf.x, ss);
+                                    ss = fmaf(__uint_as_float(r[ch * 8 + 2 * i + 1]), wf.y, ss);
                                 }
-                            };
-                            // two register buffers: the next TMEM read is in flight while 32 columns are consumed
-                            uint32_t ra[32], rb[32];
-                            const uint32_t t0 = lane_base + col0;
-                            tmem_ld32(t0, ra);
-                            tmem_wait_ld();
-                            tmem_ld32(t0 + 32, rb);
-                            consume(ra, 0);
-                            tmem_wait_ld();
-                            tmem_ld32(t0 + 64, ra);
-                            consume(rb, 1);
-                            tmem_wait_ld();
-                            tmem_ld32(t0 + 96, rb);
-                            consume(ra, 2);
-                            tmem_wait_ld();
-                            tc_fence_before();
-                            mbar_arrive_relaxed(f_free + q);      // slot drained: the next MMA may overwrite it
-                            consume(rb, 3);
+                            }
                         }
+                        inv_u[l * 256 + nrow] = 1.0f / (sqrtf(fmaxf(ss, 0.0f) * a.gscale_inv[l]) + 1e-10f);
                     }
+                    tc_fence_before();
                 }
+                mbar_arrive(inv_full);
             }
-            ++tiles_done;
+            ++units_done;
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 10) tmem_dealloc(tmem, 512);
+    if (warp == FD_WARP_MB) tmem_dealloc(tmem, 512);
 }
 
-size_t render_decode2_scratch_bytes(int levels);
-int launch_render_decode2(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b, const lsv2_features& f,
-                          const lsv2_image& img, const float* codebooks, int levels, int Lc, int D, int normalize,
-                          int out_dtype, void* out, void* scratch, size_t scratch_bytes, cudaStream_t st);
-
-size_t render_decode3_scratch_bytes(int levels);
-int launch_render_decode3(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b, const lsv2_features& f,
-                          const lsv2_image& img, const float* codebooks, int levels, int Lc, int D, int normalize,
-                          int out_dtype, void* out, void* scratch, size_t scratch_bytes, cudaStream_t st);
-
-static size_t render_decode1_scratch_bytes(int levels)
-{
-    return (size_t)(levels > 0 ? levels : 1) * FD_D * 128 + 512;
-}
-
+// ---- host side ------------------------------------------------------------------------------------------------
 size_t render_decode_scratch_bytes(int levels)
 {
-    const size_t s1 = render_decode1_scratch_bytes(levels), s2 = render_decode2_scratch_bytes(levels);
-    return s1 > s2 ? s1 : s2;
+    const size_t lv = (size_t)(levels > 0 ? levels : 1);
+    return 512 + lv * FD_D * 128 + lv * FD_CB_BYTES + 512;
 }
 
-static int launch_render_decode1(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b, const lsv2_features& f,
-                                 const lsv2_image& img, const float* codebooks, int levels, int Lc, int D, int normalize,
-                                 int out_dtype, void* out, void* scratch, size_t scratch_bytes, cudaStream_t st);
-
-// Default: the first-generation kernel (blend and decode phases alternate inside a CTA).  LSV2_FD_V2=1 selects
-// render_decode2.cu (blend of tile i+1 overlapped with the decode of tile i; parity-green but, as measured in
-// DESIGN.md 5.2, not yet faster: its decode side stalls on L2 latency while the HBM write stream is saturated).
-int launch_render_decode(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b, const lsv2_features& f,
-                         const lsv2_image& img, const float* codebooks, int levels, int Lc, int D, int normalize,
-                         int out_dtype, void* out, void* scratch, size_t scratch_bytes, cudaStream_t st)
+static int fd_check_features(const lsv2_features& f)
 {
-    const char* e3 = getenv("LSV2_FD_V3");
-    if (e3 && atoi(e3) != 0)
-        return launch_render_decode3(v, g, b, f, img, codebooks, levels, Lc, D, normalize, out_dtype, out, scratch,
-                                     scratch_bytes, st);
-    const char* e = getenv("LSV2_FD_V2");
-    if (e && atoi(e) != 0)
-        return launch_render_decode2(v, g, b, f, img, codebooks, levels, Lc, D, normalize, out_dtype, out, scratch,
-                                     scratch_bytes, st);
-    return launch_render_decode1(v, g, b, f, img, codebooks, levels, Lc, D, normalize, out_dtype, out, scratch,
-                                 scratch_bytes, st);
-}
-
-static int launch_render_decode1(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b, const lsv2_features& f,
-                         const lsv2_image& img, const float* codebooks, int levels, int Lc, int D, int normalize,
-                         int out_dtype, void* out, void* scratch, size_t scratch_bytes, cudaStream_t st)
-{
-    const int gx = (v.width + TILE - 1) / TILE, gy = (v.height + TILE - 1) / TILE;
-    if (gx * gy == 0) return LSV2_OK;
-    if (!g.blend_rec || !codebooks || !out) return LSV2_EINVAL;
-    if (Lc != FD_LC || D != FD_D || levels < 1 || levels * Lc > FD_MAX_L) return LSV2_EUNSUPPORTED;
-    if (f.L != levels * Lc) return LSV2_EINVAL;
+    if (f.L <= 0 || f.L > FD_MAX_L || (f.L % FD_LC) != 0) return LSV2_EUNSUPPORTED;
     if (f.mode == LSV2_MODE_QUICK) {
         if (f.K <= 0 || !f.weights_quick || !f.indices_quick) return LSV2_EINVAL;
         if (f.K > FD_KMAX) return LSV2_EUNSUPPORTED;
@@ -645,33 +717,62 @@ static int launch_render_decode1(const lsv2_view& v, const lsv2_geom& g, const l
     } else {
         return LSV2_EINVAL;
     }
-    if (!scratch || scratch_bytes < render_decode1_scratch_bytes(levels)) return LSV2_ENOSPC;
-    uint8_t* base = reinterpret_cast<uint8_t*>(((uintptr_t)scratch + 127) & ~(uintptr_t)127);
-    uint32_t* counter = reinterpret_cast<uint32_t*>(base);
-    uint8_t* bimg = base + 128;
-    LSV2_CUDA_TRY(cudaMemsetAsync(counter, 0, sizeof(uint32_t), st));
-    k_fd_prep_b<<<ceil_div(levels * FD_D * 8, 256), 256, 0, st>>>(levels, codebooks, bimg);
-    LSV2_LAUNCH_CHECK("k_fd_prep_b");
+    return LSV2_OK;
+}
 
-    FdArgs a;
+static void fd_fill_args(FdArgs& a, const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b, const lsv2_features& f,
+                         const lsv2_image& img, int gx, int gy)
+{
     a.W = v.width; a.H = v.height; a.gx = gx; a.n_tiles = gx * gy;
+    a.ux = (v.width + FD_UNIT_W - 1) / FD_UNIT_W;
+    a.n_units = a.ux * ((v.height + FD_UNIT_H - 1) / FD_UNIT_H);
     a.ranges = reinterpret_cast<const uint2*>(b.ranges);
     a.point_list = b.point_list;
     a.rec = reinterpret_cast<const float4*>(g.blend_rec);
     a.bg = v.bg;
-    a.mode = f.mode; a.L = f.L; a.K = f.K; a.levels = levels;
+    a.mode = f.mode; a.L = f.L; a.K = f.K; a.levels = f.L / FD_LC;
     a.coeff_dense = f.coeff_dense; a.wq = f.weights_quick; a.iq = f.indices_quick;
     a.sp_count = f.sparse_count; a.sp_index = f.sparse_index; a.sp_weight = f.sparse_weight;
     a.color = img.color; a.wmap = img.wmap; a.final_T = img.final_T; a.n_contrib = img.n_contrib;
     a.status = b.status;
-    a.bimg = bimg; a.out = out; a.normalize = normalize; a.tile_counter = counter;
-    { const char* e = getenv("LSV2_FD_DEBUG"); a.dbg = e ? atoi(e) : 0; }
-    const int grid = min(NUM_SMS, gx * gy);
-#define FD_LAUNCH(M, O)                                                                                          \
-    do {                                                                                                         \
-        LSV2_CUDA_TRY(cudaFuncSetAttribute(k_render_decode<M, O>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
-                                           (int)FD_SMEM_TOTAL));                                                 \
-        k_render_decode<M, O><<<grid, FD_THREADS, FD_SMEM_TOTAL, st>>>(a);                                       \
+    a.bimg = nullptr; a.gimg = nullptr; a.gscale_inv = nullptr; a.out = nullptr; a.normalize = 0;
+    a.tile_counter = nullptr;
+}
+
+int launch_render_decode(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b, const lsv2_features& f,
+                         const lsv2_image& img, const float* codebooks, int levels, int Lc, int D, int normalize,
+                         int out_dtype, void* out, void* scratch, size_t scratch_bytes, cudaStream_t st)
+{
+    const int gx = (v.width + TILE - 1) / TILE, gy = (v.height + TILE - 1) / TILE;
+    if (gx * gy == 0) return LSV2_OK;
+    if (!g.blend_rec || !codebooks || !out) return LSV2_EINVAL;
+    if (Lc != FD_LC || D != FD_D || levels < 1 || levels * Lc > FD_MAX_L) return LSV2_EUNSUPPORTED;
+    if (f.L != levels * Lc) return LSV2_EINVAL;
+    { const int rc = fd_check_features(f); if (rc) return rc; }
+    if (!scratch || scratch_bytes < render_decode_scratch_bytes(levels)) return LSV2_ENOSPC;
+    uint8_t* base = reinterpret_cast<uint8_t*>(((uintptr_t)scratch + 127) & ~(uintptr_t)127);
+    uint32_t* counter = reinterpret_cast<uint32_t*>(base);
+    float* gscale_inv = reinterpret_cast<float*>(base + 128);
+    uint8_t* bimg = base + 256;
+    uint8_t* gimg = bimg + (size_t)levels * FD_D * 128;
+    LSV2_CUDA_TRY(cudaMemsetAsync(counter, 0, sizeof(uint32_t), st));
+    k_fd_prep_b<<<ceil_div(levels * FD_D * 8, 256), 256, 0, st>>>(levels, codebooks, bimg);
+    LSV2_LAUNCH_CHECK("k_fd_prep_b");
+    if (normalize) {
+        k_fd_prep_g<<<dim3(FD_LC, levels), 64, 0, st>>>(codebooks, gimg, gscale_inv);
+        LSV2_LAUNCH_CHECK("k_fd_prep_g");
+    }
+
+    FdArgs a;
+    fd_fill_args(a, v, g, b, f, img, gx, gy);
+    a.bimg = bimg; a.gimg = gimg; a.gscale_inv = gscale_inv; a.out = out; a.normalize = normalize;
+    a.tile_counter = counter;
+    const int grid = min(NUM_SMS, a.n_units);
+#define FD_LAUNCH(M, O)                                                                                            \
+    do {                                                                                                           \
+        LSV2_CUDA_TRY(cudaFuncSetAttribute(k_render_decode<M, O, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                           (int)FD_SMEM_TOTAL));                                                   \
+        k_render_decode<M, O, true><<<grid, FD_THREADS, FD_SMEM_TOTAL, st>>>(a);                             \
     } while (0)
     if (f.mode == LSV2_MODE_QUICK) {
         if (out_dtype == 0) FD_LAUNCH(LSV2_MODE_QUICK, false); else FD_LAUNCH(LSV2_MODE_QUICK, true);
@@ -680,6 +781,34 @@ static int launch_render_decode1(const lsv2_view& v, const lsv2_geom& g, const l
     }
 #undef FD_LAUNCH
     LSV2_LAUNCH_CHECK("k_render_decode");
+    return LSV2_OK;
+}
+
+// The same blend with the weight map as its product (the 3-tuple of the drop-in op): W leaves TMEM as fp32
+// [L][H][W], nothing is decoded.  scratch: 128 bytes (the tile counter).
+int launch_render_wmap_tc(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b, const lsv2_features& f,
+                          const lsv2_image& img, void* scratch, size_t scratch_bytes, cudaStream_t st)
+{
+    const int gx = (v.width + TILE - 1) / TILE, gy = (v.height + TILE - 1) / TILE;
+    if (gx * gy == 0) return LSV2_OK;
+    if (!g.blend_rec || !img.wmap) return LSV2_EINVAL;
+    { const int rc = fd_check_features(f); if (rc) return rc; }
+    if (!scratch || scratch_bytes < 256) return LSV2_ENOSPC;
+    uint32_t* counter = reinterpret_cast<uint32_t*>(((uintptr_t)scratch + 127) & ~(uintptr_t)127);
+    LSV2_CUDA_TRY(cudaMemsetAsync(counter, 0, sizeof(uint32_t), st));
+    FdArgs a;
+    fd_fill_args(a, v, g, b, f, img, gx, gy);
+    a.tile_counter = counter;
+    const int grid = min(NUM_SMS, a.n_units);
+#define FD_LAUNCH(M)                                                                                                   \
+    do {                                                                                                               \
+        LSV2_CUDA_TRY(cudaFuncSetAttribute(k_render_decode<M, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                           (int)FD_SMEM_NODECODE_TOTAL));                                              \
+        k_render_decode<M, false, false><<<grid, FD_THREADS_NODECODE, FD_SMEM_NODECODE_TOTAL, st>>>(a);          \
+    } while (0)
+    if (f.mode == LSV2_MODE_QUICK) FD_LAUNCH(LSV2_MODE_QUICK); else FD_LAUNCH(LSV2_MODE_DENSE);
+#undef FD_LAUNCH
+    LSV2_LAUNCH_CHECK("k_render_decode<wmap>");
     return LSV2_OK;
 }
 

@@ -176,5 +176,49 @@ __host__ __device__ __forceinline__ uint32_t sw128_offset(uint32_t row, uint32_t
     return row * 128u + ((chunk ^ (row & 7u)) << 4);
 }
 
+
+// ---- TMA tensor stores (shared -> global through a CUtensorMap; SASS: UTMASTG) -------------------------------
+// 3-D box at element coordinates (c0, c1, c2) of the tensor map, source = dense box image in shared memory
+// (in the map's swizzle).  Completion is tracked per thread with bulk groups.
+__device__ __forceinline__ void tma_store_3d(const void* tmap, const void* src_smem, int c0, int c1, int c2)
+{
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(tmap),
+                 "r"(smem_u32(src_smem)), "r"(c0), "r"(c1), "r"(c2)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// wait until at most N of this thread's bulk groups still have to READ their shared-memory source
+template <int N>
+__device__ __forceinline__ void bulk_wait_read()
+{
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+// byte offset of (row, 16-byte chunk) in a tile of 64-byte rows under the 64-byte swizzle (address bits [4,6) ^=
+// bits [7,9); tile base 512-byte aligned) -- the layout shared by UMMA SWIZZLE_64B K-major operands and
+// CU_TENSOR_MAP_SWIZZLE_64B boxes with a 64-byte inner extent
+__host__ __device__ __forceinline__ uint32_t sw64_offset(uint32_t row, uint32_t chunk)
+{
+    return row * 64u + ((chunk ^ ((row >> 1) & 3u)) << 4);
+}
+// 32-byte rows under the 32-byte swizzle (bit 4 ^= bit 7)
+__host__ __device__ __forceinline__ uint32_t sw32_offset(uint32_t row, uint32_t chunk)
+{
+    return row * 32u + ((chunk ^ ((row >> 2) & 1u)) << 4);
+}
+
+// K-major operand with 64-byte rows (32 fp16), 64-byte swizzle: 8-row groups 512 B apart, layout type 4
+__device__ __forceinline__ uint64_t umma_desc_k_sw64(uint32_t smem_addr)
+{
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);
+    d |= (uint64_t)1 << 16;
+    d |= (uint64_t)(512 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)4 << 61;
+    return d;
+}
+
 }  // namespace tc
 }  // namespace lsv2

@@ -134,6 +134,87 @@ class GradBucket:
         self._works = []
 
 
+class ShardedExchange:
+    """Gradient exchange of a flat buffer in blocks with the optimizer step sharded over the ranks (ZeRO-1 shape):
+
+        reduce-scatter(block) -> this rank steps ITS 1/world of the block -> all-gather(the block's parameters)
+
+    moves the same bytes over NVLink as the all-reduce it replaces, but every rank runs 1/world of the optimizer
+    traffic, and each parameter is computed by exactly one rank (bitwise identical replicas by construction).
+    SUM semantics as ``GradBucket`` (a world of B ranks == the reference's ``--accum_iter B``, train.py:261-263,348).
+    ``blocks``: [(a, b)] flat element ranges, each a multiple of 4 * world long, covering the buffers."""
+
+    def __init__(self, flat_g: torch.Tensor, flat_p: torch.Tensor, blocks: Sequence):
+        self.g, self.p = flat_g, flat_p
+        self.blocks = [(int(a), int(b)) for a, b in blocks]
+        self.rank, self.world = (dist.get_rank(), dist.get_world_size()) if dist.is_initialized() else (0, 1)
+        for a, b in self.blocks:
+            if (b - a) % (4 * self.world) or a % 4:
+                raise ValueError(f"block [{a}, {b}) is not a multiple of 4 * world elements")
+        self.shard_grad = [torch.empty((b - a) // self.world, dtype=torch.float32, device=flat_g.device)
+                           for a, b in self.blocks]
+        self._side = torch.cuda.Stream(device=flat_g.device) if flat_g.is_cuda else None
+        self._rs = [None] * len(self.blocks)
+        self._ag = [None] * len(self.blocks)
+
+    def shard_range(self, i: int):
+        a, b = self.blocks[i]
+        n = (b - a) // self.world
+        return a + self.rank * n, a + (self.rank + 1) * n
+
+    def reduce_scatter(self, i: int) -> None:
+        """Block i's gradient is final on the current stream: start its reduce-scatter (side stream)."""
+        a, b = self.blocks[i]
+        if self.world == 1:
+            self.shard_grad[i].copy_(self.g[a:b])
+            return
+        if self._side is None:
+            dist.reduce_scatter_tensor(self.shard_grad[i], self.g[a:b], op=dist.ReduceOp.SUM)
+            return
+        ev = torch.cuda.Event()
+        ev.record()
+        with torch.cuda.stream(self._side):
+            self._side.wait_event(ev)
+            self._rs[i] = dist.reduce_scatter_tensor(self.shard_grad[i], self.g[a:b], op=dist.ReduceOp.SUM, async_op=True)
+
+    def wait_grad(self, i: int) -> None:
+        if self._rs[i] is not None:
+            self._rs[i].wait()
+            self._rs[i] = None
+
+    def all_gather_params(self, i: int) -> None:
+        """This rank's shard of block i's parameters is final on the current stream: gather the block (side stream)."""
+        if self.world == 1:
+            return
+        a, b = self.blocks[i]
+        lo, hi = self.shard_range(i)
+        if self._side is None:
+            dist.all_gather_into_tensor(self.p[a:b], self.p[lo:hi].clone())
+            return
+        ev = torch.cuda.Event()
+        ev.record()
+        with torch.cuda.stream(self._side):
+            self._side.wait_event(ev)
+            self._ag[i] = dist.all_gather_into_tensor(self.p[a:b], self.p[lo:hi], async_op=True)
+
+    def finish(self) -> None:
+        """The current stream waits for every outstanding gather (call before the next forward)."""
+        for i, w in enumerate(self._ag):
+            if w is not None:
+                w.wait()
+                self._ag[i] = None
+
+    def full_reduced_grad(self) -> torch.Tensor:
+        """The summed gradient of the last exchange, reassembled from every rank's shards (tests only)."""
+        out = torch.empty_like(self.g)
+        for i, (a, b) in enumerate(self.blocks):
+            if self.world == 1:
+                out[a:b].copy_(self.shard_grad[i])
+            else:
+                dist.all_gather_into_tensor(out[a:b], self.shard_grad[i])
+        return out
+
+
 def all_reduce_grads(params: Iterable[torch.Tensor]) -> None:
     """One-shot helper (allocates a bucket); training loops should hold a GradBucket instead."""
     GradBucket(list(params)).sync()

@@ -132,10 +132,15 @@ def rasterize_forward(rs: GaussianRasterizationSettings, means3D, opacities, shs
                       scales=None, rotations=None, cov3D_precomp=None, language_feature_precomp=None,
                       language_feature_weights_quick=None, language_feature_indices=None,
                       capacity: Optional[int] = None, debug_buffers: bool = False,
-                      render: bool = True) -> FrameState:
+                      render: bool = True, blend: str = "auto") -> FrameState:
     """Preprocess -> bin -> blend.  ``capacity=None`` reads the instance count back between the two
     halves (one host sync, as the reference does); an integer capacity runs the whole frame with no
-    host involvement and flags overflow in ``state.status``."""
+    host involvement and flags overflow in ``state.status``.
+
+    ``blend``: ``"tc"`` accumulates the sparse coefficients on the tensor cores (``lsv2_render_forward_tc``: weight
+    map within 1e-4 of its per-pixel norm, everything else bit-identical), ``"simt"`` is the CUDA-core kernel whose
+    weight map reproduces the checker's fp32 operation order bit for bit, ``"auto"`` picks ``"tc"`` where the shape
+    allows it (L a multiple of 64 up to 192, K <= 16)."""
     L_ = _abi.lib()
     dev = means3D.device
     _abi.require_cuda(means3D, "means3D")
@@ -229,6 +234,24 @@ def rasterize_forward(rs: GaussianRasterizationSettings, means3D, opacities, shs
         b["ranges"] = torch.empty((gx * gy, 2), **i32)
         b["scratch"] = torch.empty(L_.lsv2_sort_scratch_bytes(cap, P), dtype=torch.uint8, device=dev)
 
+    if blend not in ("auto", "tc", "simt"):
+        raise ValueError("blend must be 'auto', 'tc' or 'simt'")
+    tc_ok = mode != MODE_RGB and L > 0 and L % 64 == 0 and L <= 192 and (mode == MODE_DENSE or 0 < K <= SPARSE_CAP)
+    if blend == "tc" and not tc_ok:
+        raise _abi.Lsv2Error("blend='tc' needs L a multiple of 64 up to 192 and at most 16 entries per Gaussian")
+    use_tc = tc_ok and blend != "simt"
+
+    def run_blend(geom_c, bin_c):
+        feat_c, img_c = st.c_features(), st.c_image()
+        if mode == MODE_DENSE:
+            _abi.check(L_.lsv2_compact_coeff(P, C.byref(geom_c), C.byref(feat_c), stream), "lsv2_compact_coeff")
+        if use_tc:
+            _abi.check(L_.lsv2_render_forward_tc(C.byref(st.view), C.byref(geom_c), C.byref(bin_c), C.byref(feat_c),
+                                                 C.byref(img_c), stream), "lsv2_render_forward_tc")
+        else:
+            _abi.check(L_.lsv2_render_forward(C.byref(st.view), C.byref(geom_c), C.byref(bin_c), C.byref(feat_c),
+                                              C.byref(img_c), stream), "lsv2_render_forward")
+
     if capacity is None:
         st.binning["scratch"] = torch.empty(L_.lsv2_sort_scratch_bytes(0, P), dtype=torch.uint8, device=dev)
         geom_c, bin_c = st.c_geom(), st.c_binning()
@@ -239,21 +262,15 @@ def rasterize_forward(rs: GaussianRasterizationSettings, means3D, opacities, shs
         bin_c = st.c_binning()
         _abi.check(L_.lsv2_bin(C.byref(st.view), P, C.byref(geom_c), C.byref(bin_c), stream), "lsv2_bin")
         if render:
-            feat_c, img_c = st.c_features(), st.c_image()
-            if mode == MODE_DENSE:
-                _abi.check(L_.lsv2_compact_coeff(P, C.byref(geom_c), C.byref(feat_c), stream), "lsv2_compact_coeff")
-            _abi.check(L_.lsv2_render_forward(C.byref(st.view), C.byref(geom_c), C.byref(bin_c), C.byref(feat_c),
-                                              C.byref(img_c), stream), "lsv2_render_forward")
+            run_blend(geom_c, bin_c)
     else:
         alloc_binning(int(capacity))
-        geom_c, bin_c, feat_c, img_c = st.c_geom(), st.c_binning(), st.c_features(), st.c_image()
+        geom_c, bin_c = st.c_geom(), st.c_binning()
+        _abi.check(L_.lsv2_preprocess(C.byref(st.view), C.byref(scene), C.byref(geom_c), C.byref(bin_c), stream),
+                   "lsv2_preprocess")
+        _abi.check(L_.lsv2_bin(C.byref(st.view), P, C.byref(geom_c), C.byref(bin_c), stream), "lsv2_bin")
         if render:
-            _abi.check(L_.lsv2_forward(C.byref(st.view), C.byref(scene), C.byref(geom_c), C.byref(bin_c),
-                                       C.byref(feat_c), C.byref(img_c), stream), "lsv2_forward")
-        else:
-            _abi.check(L_.lsv2_preprocess(C.byref(st.view), C.byref(scene), C.byref(geom_c), C.byref(bin_c), stream),
-                       "lsv2_preprocess")
-            _abi.check(L_.lsv2_bin(C.byref(st.view), P, C.byref(geom_c), C.byref(bin_c), stream), "lsv2_bin")
+            run_blend(geom_c, bin_c)
     if rs.debug:
         torch.cuda.synchronize(dev)
         if st.overflowed:

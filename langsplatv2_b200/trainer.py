@@ -10,10 +10,10 @@ Mirrors ``train.py --include_feature`` of the reference, one iteration per ``ste
     Adam on (logits, codebooks)       scene/gaussian_model.py:235-236,255 ; train.py:261-263
 
 Geometry is frozen (scene/gaussian_model.py:238-243).  Data parallel: each rank renders its own view and the
-gradients of (logits, codebooks) are summed over the ranks in ONE flat bucket (``dist.GradBucket``; reduced in 4 row
-slices pipelined with the top-k backward and per-slice Adam steps), SUM as in the reference's ``--accum_iter``
-(train.py:261-263,348).  The hot kernels (top-k fwd/bwd, preprocess, binning, blend fwd/bwd,
-decode fwd/bwd) are liblsv2's; the loss expression and Adam are PyTorch's, as they are in the reference.
+gradients of (logits, codebooks) are summed over the ranks over one flat buffer, in 4 row blocks pipelined with the
+top-k backward: reduce-scatter -> Adam on this rank's shard -> all-gather of the parameters (``dist.ShardedExchange``),
+SUM as in the reference's ``--accum_iter`` (train.py:261-263,348).  Every kernel of the step (top-k fwd/bwd,
+preprocess, binning, blend fwd/bwd, Gram loss, codebook GEMMs, Adam) is liblsv2's.
 """
 from __future__ import annotations
 
@@ -26,6 +26,7 @@ import torch.nn.functional as F
 from . import dist as lsdist
 from .decode import decode_feature_map
 from .loss import column_sumsq, decode_cos_loss, decode_cos_loss_segments, normalized_cos_loss
+from .optim import FlatAdam
 from .rasterizer import GaussianRasterizationSettings, GaussianRasterizer
 from . import sparse as lssparse
 from .sparse import softmax_to_topk_soft_code
@@ -42,11 +43,20 @@ def l1_loss(network_output: torch.Tensor, gt: torch.Tensor) -> torch.Tensor:
 
 
 class FeatureTrainer:
-    """Resident scene + the two trainable tensors + Adam; ``step(cam, gt, mask)`` is one train.py iteration."""
+    """Resident scene + the two trainable tensors + Adam; ``step(cam, gt, mask)`` is one train.py iteration.
+
+    Parameters, gradients and Adam moments live in four flat fp32 buffers ``[logits | codebooks | pad]``
+    (``self.logits`` / ``self.codebooks`` are views), so the optimizer is ``optim.FlatAdam`` (one kernel per range) and
+    the data-parallel exchange works on flat ranges.  ``collective``:
+      "zero1"      reduce-scatter -> each rank steps its 1/world shard -> all-gather of the parameters (default, N > 1)
+      "allreduce"  one SUM all-reduce of the gradient, every rank steps everything (the round-1 scheme)
+    both in row blocks pipelined with the top-k backward.  ``use_graph=True`` (single rank) captures the steady-state
+    iteration of each (view_id, layer) in a CUDA graph: ``step(..., view_id=i)`` replays it."""
 
     def __init__(self, scene: Dict, topk: int = 4, lr: float = 0.0025, device="cuda", normalize: bool = True,
-                 use_cos: bool = True, use_l1: bool = False, layers: Optional[int] = None, fused_adam: bool = True,
-                 fused_loss: bool = True, gram_loss: bool = True):
+                 use_cos: bool = True, use_l1: bool = False, layers: Optional[int] = None,
+                 fused_loss: bool = True, gram_loss: bool = True, collective: str = "zero1",
+                 use_graph: bool = False, check_every: int = 64):
         dev = torch.device(device)
         f32 = lambda t: t.to(dev, torch.float32).contiguous()
         self.dev = dev
@@ -54,7 +64,7 @@ class FeatureTrainer:
         self.normalize, self.use_cos, self.use_l1 = normalize, use_cos, use_l1
         self.fused_loss = fused_loss        # cos loss (+ the normalisation) as two kernels instead of torch's ~28 passes
         self.gram_loss = gram_loss          # ... and, for a single layer, without forming the [512, H, W] feature map
-        self._g2_cache = {}                 # |gt_p|^2 per ground-truth tensor (constant across iterations of a view)
+        self._g2_by_view = {}               # |gt_p|^2 per caller-supplied view id (never keyed by address)
         self.xyz, self.opacity = f32(scene["xyz"]), f32(scene["opacity"])
         self.scales, self.rotations = f32(scene["scaling"]), f32(scene["rotation"])
         self.shs = f32(scene["features"])
@@ -62,45 +72,69 @@ class FeatureTrainer:
         cb = f32(scene["codebooks"])
         self.layers = int(cb.shape[0] if layers is None else layers)
         self.codebook_size = int(cb.shape[1])
-        self.logits = torch.nn.Parameter(f32(scene["logits"])[:, : self.layers * self.codebook_size].clone())
-        self.codebooks = torch.nn.Parameter(cb[: self.layers].clone())
+        lg = f32(scene["logits"])[:, : self.layers * self.codebook_size]
+        cb = cb[: self.layers]
+        self.rank, self.world, _ = lsdist.world_info()
+        if self.world > 1 and not (torch.distributed.is_available() and torch.distributed.is_initialized()):
+            self.world, self.rank = 1, 0
+        if collective not in ("zero1", "allreduce"):
+            raise ValueError("collective must be 'zero1' or 'allreduce'")
+        # ---- flat buffers: [logits | codebooks | pad to a multiple of 4 * world] ----
+        n_log, n_cb = lg.numel(), cb.numel()
+        unit = 4 * self.world
+        tail = -(-n_cb // unit) * unit
+        self.n_log, self.n_cb = n_log, n_cb
+        self.flat_p = torch.zeros(n_log + tail, dtype=torch.float32, device=dev)
+        self.flat_g = torch.zeros_like(self.flat_p)
+        self.flat_p[:n_log].copy_(lg.reshape(-1))
+        self.flat_p[n_log:n_log + n_cb].copy_(cb.reshape(-1))
+        self.logits = torch.nn.Parameter(self.flat_p[:n_log].view(lg.shape))
+        self.codebooks = torch.nn.Parameter(self.flat_p[n_log:n_log + n_cb].view(cb.shape))
+        self.logits.grad = self.flat_g[:n_log].view(lg.shape)
+        self.codebooks.grad = self.flat_g[n_log:n_log + n_cb].view(cb.shape)
+        # the reference: torch.optim.Adam(l, lr=0.0, eps=1e-15) with the group lr = language_feature_lr
+        self.optimizer = FlatAdam(self.flat_p, self.flat_g, lr=lr, eps=1e-15) if dev.type == "cuda" else None
         self.bg = torch.zeros(3, dtype=torch.float32, device=dev)
         self.means2D = torch.zeros_like(self.xyz)                      # grad sink of the reference API; unused here
-        # the reference: torch.optim.Adam(l, lr=0.0, eps=1e-15) with the group lr = language_feature_lr
-        self.optimizer = torch.optim.Adam([{"params": [self.logits, self.codebooks], "lr": lr}], lr=0.0, eps=1e-15,
-                                          fused=fused_adam and dev.type == "cuda")
+        # ---- row blocks of the logits (+ one block for the codebooks): block i's gradient leaves the top-k backward
+        # and its exchange runs under block i + 1's kernel ----
+        self.overlap_chunks = int(os.environ.get("LSV2_OVERLAP_CHUNKS", "4")) if self.world > 1 else 1
+        C = lg.shape[1]
+        n = lg.shape[0]
+        rows = -(-(-(-n // max(self.overlap_chunks, 1))) // 1024) * 1024
+        self._chunk_rows = [(a, min(n, a + rows)) for a in range(0, n, rows)]
+        self._blocks = [(a * C, b * C) for a, b in self._chunk_rows] + [(n_log, n_log + tail)]
+        # the sink needs whole-row blocks written by ONE top-k backward over all the logits columns
+        self._sink_ok = self.layers == 1 and dev.type == "cuda"
+        self.collective = "none"
+        self.exchange = None
         self.bucket = None
-        self.overlap_chunks = int(os.environ.get("LSV2_OVERLAP_CHUNKS", "4"))
-        self._chunk_rows = None
-        self._chunk_opts = None
+        if self.world > 1:
+            ok = all((b - a) % unit == 0 and a % 4 == 0 for a, b in self._blocks) and self._sink_ok
+            self.collective = collective if (collective == "allreduce" or ok) else "allreduce"
+            if self.collective == "zero1":
+                self.exchange = lsdist.ShardedExchange(self.flat_g, self.flat_p, self._blocks)
+            else:
+                self.bucket = lsdist.GradBucket([self.logits, self.codebooks])   # only its slice machinery is used
+                self.bucket.flat = self.flat_g
+                self.bucket.attached = True
         self.keep_last_grad = False
         self.last_grad = None
-        if lsdist.world_info()[1] > 1:
-            self.bucket = lsdist.GradBucket([self.logits, self.codebooks])
-            self.bucket.attach()                    # grads are written into the flat all-reduce buffer directly
-            if self.layers == 1 and dev.type == "cuda":
-                # row blocks of the logits: block i's gradient leaves the top-k backward, is all-reduced on a side
-                # stream, and gets its own (elementwise-identical) Adam step while block i + 1 is still in flight
-                n = self.logits.shape[0]
-                rows = -(-(-(-n // self.overlap_chunks)) // 1024) * 1024
-                self._chunk_rows = [(a, min(n, a + rows)) for a in range(0, n, rows)]
-                gview = self.bucket.views[0]
-                self._chunk_opts = []
-                for a, b in self._chunk_rows:
-                    p = self.logits.detach()[a:b]                   # leaf view of the same storage
-                    p.grad = gview[a:b]
-                    self._chunk_opts.append(torch.optim.Adam([{"params": [p], "lr": lr}], lr=0.0, eps=1e-15,
-                                                             fused=fused_adam))
-                cb = self.codebooks.detach()
-                cb.grad = self.bucket.views[1]
-                self._cb_opt = torch.optim.Adam([{"params": [cb], "lr": lr}], lr=0.0, eps=1e-15, fused=fused_adam)
         self.iteration = 0
         # instance capacity: the first `calib_steps` iterations read num_rendered back (the reference's one host sync
-        # per frame); after that the frame runs with a bounded instance buffer and no host sync
+        # per frame); after that the frame runs with a bounded instance buffer and no host sync.  Overflow is sticky on
+        # the device (every frame ORs into one word) and read every `check_every` iterations: the capacity then grows.
         self.capacity: Optional[int] = None
         self.calib_steps = 3
+        self.check_every = int(check_every)
+        self.headroom = 1.5
         self._max_seen = 0
         self._last_state = None
+        self._sticky = torch.zeros(2, dtype=torch.int32, device=dev)   # [overflow seen, max instances seen]
+        self.overflow_events = 0
+        self.use_graph = bool(use_graph) and self.world == 1 and dev.type == "cuda"
+        self._graphs = {}
+        self._graph_pool = None
 
     # ---- reference: GaussianModel.get_render_weights (scene/gaussian_model.py:510-518) ----
     def render_weights(self) -> torch.Tensor:
@@ -118,6 +152,21 @@ class FeatureTrainer:
             sh_degree=self.sh_degree, campos=cam["camera_center"].to(d, non_blocking=True), prefiltered=False, debug=False,
             include_feature=True, quick_render=False)
 
+    def calibrate(self, cams, stride: int = 1) -> int:
+        """Size the instance buffers from the largest of ``cams[::stride]`` (exact, synchronising frames) instead of
+        from whatever the first few iterations happen to see."""
+        from .rasterizer import rasterize_forward
+        peak = 0
+        with torch.no_grad():
+            for cam in list(cams)[::max(1, stride)]:
+                st = rasterize_forward(self.settings(cam), self.xyz, self.opacity, shs=self.shs, scales=self.scales,
+                                       rotations=self.rotations, language_feature_precomp=self.logits.detach(),
+                                       capacity=None, render=False)
+                peak = max(peak, st.num_rendered)
+        self._max_seen = max(self._max_seen, peak)
+        self.capacity = int(self._max_seen * self.headroom) + 4096
+        return self.capacity
+
     # ---- reference: compute_layer_feature_map (scene/gaussian_model.py:533-543) ----
     def layer_feature_map(self, wmap: torch.Tensor, layer_idx: int) -> torch.Tensor:
         cs = self.codebook_size
@@ -128,15 +177,20 @@ class FeatureTrainer:
             feat = f if feat is None else f + feat.detach()
         return feat
 
-    def loss(self, cam: Dict, gt: torch.Tensor, mask: torch.Tensor) -> torch.Tensor:
+    def layer_index(self) -> int:
+        return min(int(self.iteration / 10000 * self.layers), self.layers - 1)            # train.py:155
+
+    def loss(self, cam: Dict, gt, mask: Optional[torch.Tensor], gt_sumsq: Optional[torch.Tensor] = None,
+             view_id=None) -> torch.Tensor:
         rasterizer = GaussianRasterizer(raster_settings=self.settings(cam), capacity=self.capacity)
+        rasterizer.dense_coeff_grad = False         # the top-k mask follows (utils/vq_utils.py:20): support-only is exact
         zero = torch.zeros((1,), dtype=torch.float32, device=self.dev)
         _, wmap, _ = rasterizer(means3D=self.xyz, means2D=self.means2D, shs=self.shs, colors_precomp=None,
                                 language_feature_precomp=self.render_weights(), language_feature_weights_quick=zero,
                                 language_feature_indices=zero, opacities=self.opacity, scales=self.scales,
                                 rotations=self.rotations, cov3D_precomp=None)
         self._last_state = rasterizer.last_state
-        layer_idx = min(int(self.iteration / 10000 * self.layers), self.layers - 1)       # train.py:155
+        layer_idx = self.layer_index()
         cs = self.codebook_size
         if isinstance(gt, (tuple, list)):
             # ground truth as (seg [H, W] int, table [S, 512]) -- scene/cameras.py:59-96 before the expansion
@@ -148,12 +202,17 @@ class FeatureTrainer:
             mask = valid.unsqueeze(0).to(torch.float32)
         if (self.gram_loss and self.fused_loss and layer_idx == 0 and cs == 64 and self.use_cos and not self.use_l1
                 and mask.numel() == wmap[0].numel()):
-            key = (gt.data_ptr(), tuple(gt.shape))
-            g2 = self._g2_cache.get(key)
+            # |gt_p|^2: given by the caller, cached under the caller's view id, or recomputed (one streaming pass).
+            # Never cached by address: a loader's fresh gt tensor can reuse the storage of another view's.
+            g2 = gt_sumsq
+            if g2 is None and view_id is not None:
+                g2 = self._g2_by_view.get(view_id)
+                if g2 is None:
+                    if len(self._g2_by_view) > 256:
+                        self._g2_by_view.clear()
+                    g2 = self._g2_by_view[view_id] = column_sumsq(gt)
             if g2 is None:
-                if len(self._g2_cache) > 64:
-                    self._g2_cache.clear()
-                g2 = self._g2_cache[key] = column_sumsq(gt)
+                g2 = column_sumsq(gt)
             return decode_cos_loss(wmap[:cs], self.codebooks[0:1], gt, mask, normalize=self.normalize, gt_sumsq=g2)
         feat = self.layer_feature_map(wmap, layer_idx)
         if self.fused_loss and self.use_cos and not self.use_l1 and mask.numel() == feat[0].numel():
@@ -167,59 +226,130 @@ class FeatureTrainer:
             loss = loss + l1_loss(feat * mask, gt * mask)
         return loss
 
-    def step(self, cam: Dict, gt: torch.Tensor, mask: torch.Tensor) -> torch.Tensor:
-        """One iteration; returns the (detached, on-device) loss."""
-        self.iteration += 1
-        loss = self.loss(cam, gt, mask)
-        if self._chunk_opts is not None and self.overlap_chunks > 1:
-            # the flat bucket [d logits || d codebooks] is reduced in slices: d logits leaves the top-k backward in
-            # row blocks, block i's all-reduce runs under block i + 1's kernel and under block i - 1's Adam
-            self.bucket.begin_overlap()
-            sink = lssparse.GradSink(self.bucket.views[0], self._chunk_rows, self.bucket.reduce_slice)
+    # ------------------------------------------------------------------------------------------------------------
+    def _backward_and_update(self, loss: torch.Tensor) -> None:
+        """backward -> (N > 1: gradient exchange in row blocks) -> Adam; leaves the gradient buffer ready for the
+        next iteration."""
+        opt = self.optimizer
+        n_log = self.n_log
+        nb = len(self._blocks)
+        use_sink = self._sink_ok
+        if use_sink:
+            if self.collective == "zero1":
+                on_chunk = lambda a, b, _s=self: _s.exchange.reduce_scatter(_s._block_of[a])
+            elif self.collective == "allreduce":
+                self.bucket.begin_overlap()
+                on_chunk = self.bucket.reduce_slice
+            else:
+                on_chunk = lambda a, b: None
+            self._block_of = {a: i for i, (a, _) in enumerate(self._blocks)}
+            sink = lssparse.GradSink(self.logits.grad, self._chunk_rows, on_chunk)
             lssparse.set_grad_sink(sink)
             try:
                 loss.backward()
             finally:
                 lssparse.set_grad_sink(None)
-            if sink.used_upto == self.logits.numel():
-                self.bucket.reduce_slice(sink.used_upto, self.bucket.flat.numel())      # the codebook part
-                for i, opt in enumerate(self._chunk_opts):
-                    self.bucket.wait_slice(i)
-                    opt.step()
-                self.bucket.wait_slice(len(self._chunk_opts))
-                self._cb_opt.step()
-                self.bucket.finish_overlap(self.bucket.flat.numel())
-            else:                                   # the sink was not taken (shape mismatch): classic path
-                self.bucket.finish_overlap(0)
-                for opt in self._chunk_opts:
-                    opt.step()
-                self._cb_opt.step()
+            if sink.used_upto != n_log:
+                raise RuntimeError("the top-k backward did not take the gradient sink")
         else:
             loss.backward()
-            if self.bucket is not None:
-                self.bucket.sync()                  # ONE all-reduce(SUM) of [d logits || d codebooks]
-            if self._chunk_opts is not None:
-                for opt in self._chunk_opts:
-                    opt.step()
-                self._cb_opt.step()
-            else:
-                self.optimizer.step()
-        if self.bucket is not None:
+        opt.begin_step()
+        if self.collective == "zero1":
+            ex = self.exchange
+            if not use_sink:
+                for i in range(nb - 1):
+                    ex.reduce_scatter(i)
+            ex.reduce_scatter(nb - 1)                                    # codebooks (+ pad)
+            for i in range(nb):
+                ex.wait_grad(i)
+                lo, hi = ex.shard_range(i)
+                opt.step_range(lo, hi, grad=ex.shard_grad[i])
+                ex.all_gather_params(i)
             if self.keep_last_grad:
-                self.last_grad = self.bucket.flat.clone()           # the all-reduced gradient of this step (tests)
-            self.bucket.zero()
+                self.last_grad = ex.full_reduced_grad()
+            ex.finish()
+        elif self.collective == "allreduce":
+            bk = self.bucket
+            if not use_sink:
+                bk.begin_overlap()
+                for a, b in self._blocks[:-1]:
+                    bk.reduce_slice(a, b)
+            bk.reduce_slice(*self._blocks[-1])
+            for i, (a, b) in enumerate(self._blocks):
+                bk.wait_slice(i)
+                opt.step_range(a, b)
+            bk.finish_overlap(self.flat_g.numel())
+            if self.keep_last_grad:
+                self.last_grad = self.flat_g.clone()
         else:
-            self.optimizer.zero_grad(set_to_none=True)
+            if self.keep_last_grad:
+                self.last_grad = self.flat_g.clone()
+            if use_sink:
+                opt.step_range(0, n_log)                                 # fully rewritten by the next top-k backward
+                opt.step_range(n_log, self.flat_p.numel(), zero_grad=True)
+            else:
+                opt.step_range(0, self.flat_p.numel(), zero_grad=True)
+            return
+        # N > 1: what autograd accumulates into must be zero again (the sink overwrites the logits part)
+        if use_sink:
+            self.flat_g[n_log:].zero_()
+        else:
+            self.flat_g.zero_()
+
+    def _iteration(self, cam, gt, mask, gt_sumsq, view_id) -> torch.Tensor:
+        loss = self.loss(cam, gt, mask, gt_sumsq=gt_sumsq, view_id=view_id)
+        self._backward_and_update(loss)
         st = self._last_state
-        if st is not None:
-            if self.capacity is None:
-                self._max_seen = max(self._max_seen, st.num_rendered)
-                if self.iteration >= self.calib_steps:
-                    self.capacity = int(self._max_seen * 1.5) + 4096
-            elif self.iteration % 64 == 0 and st.overflowed:       # rare check (one small D2H read)
-                raise RuntimeError(f"instance capacity {self.capacity} exceeded; raise FeatureTrainer.capacity")
-        self._last_state = None
+        if st is not None and self.capacity is not None:
+            # sticky on the device: [1] |= overflow of this frame
+            self._sticky[0:1].bitwise_or_(st.status[1:2])
         return loss.detach()
+
+    def step(self, cam: Dict, gt, mask: Optional[torch.Tensor] = None, gt_sumsq: Optional[torch.Tensor] = None,
+             view_id=None) -> torch.Tensor:
+        """One iteration; returns the (detached, on-device) loss.  ``view_id`` (any hashable) lets the trainer cache
+        per-view constants (|gt|^2) and, with ``use_graph``, the captured iteration of that view; the tensors passed
+        for a given ``view_id`` must then be the same (resident) tensors on every call."""
+        self.iteration += 1
+        calibrated = self.capacity is not None
+        if self.use_graph and calibrated and view_id is not None and gt_sumsq is None:
+            key = (view_id, self.layer_index())
+            entry = self._graphs.get(key)
+            if entry is None:
+                if view_id not in self._g2_by_view and not isinstance(gt, (tuple, list)) and self.gram_loss:
+                    self._g2_by_view[view_id] = column_sumsq(gt)         # outside the capture
+                torch.cuda.synchronize(self.dev)
+                g = torch.cuda.CUDAGraph()
+                t_saved = self.optimizer.t
+                with torch.cuda.graph(g, pool=self._graph_pool):
+                    out = self._iteration(cam, gt, mask, None, view_id)
+                if self._graph_pool is None:
+                    self._graph_pool = g.pool()
+                self.optimizer.t = t_saved                               # the capture ran nothing
+                entry = self._graphs[key] = (g, out)
+            g, out = entry
+            self.optimizer.begin_step()                                  # refresh the device-side step scalars
+            g.replay()
+            loss = out
+        else:
+            loss = self._iteration(cam, gt, mask, gt_sumsq, view_id)
+        st = self._last_state
+        if not calibrated and st is not None:
+            self._max_seen = max(self._max_seen, st.num_rendered)
+            if self.iteration >= self.calib_steps:
+                self.capacity = int(self._max_seen * self.headroom) + 4096
+        elif self.check_every > 0 and self.iteration % self.check_every == 0:
+            if int(self._sticky[0].item()):                              # one small D2H read every check_every steps
+                # some frame since the last check was rendered from a truncated instance list: grow and go on
+                self.overflow_events += 1
+                self._sticky.zero_()
+                self.capacity = int(self.capacity * 1.5) + 4096
+                self._graphs.clear()
+                import warnings
+                warnings.warn(f"instance capacity overflowed; grown to {self.capacity} (the affected iterations used "
+                              "truncated instance lists)")
+        self._last_state = None
+        return loss
 
 
 def synthetic_gt_segments(H: int, W: int, feat_dim: int = 512, seed: int = 2, device="cuda"):

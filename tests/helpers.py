@@ -56,14 +56,14 @@ def coeffs(scene, k=4):
 
 
 def run_cuda(scene, cam, bg, mode, dense=None, wq=None, iq=None, capacity=None, debug_buffers=True, device="cuda",
-             render=True):
+             render=True, blend="auto"):
     rs = settings(cam, scene, bg, include_feature=(mode != MODE_RGB), quick_render=(mode == MODE_QUICK), device=device)
     t = lambda a: None if a is None else torch.as_tensor(a).to(device)
     return rasterize_forward(rs, scene["xyz"].to(device), scene["opacity"].to(device), shs=scene["features"].to(device),
                              scales=scene["scaling"].to(device), rotations=scene["rotation"].to(device),
                              language_feature_precomp=t(dense), language_feature_weights_quick=t(wq),
                              language_feature_indices=t(iq), capacity=capacity, debug_buffers=debug_buffers,
-                             render=render)
+                             render=render, blend=blend)
 
 
 def u32(t):

@@ -1,10 +1,12 @@
 """Fused blend + decode (lsv2_render_decode) vs the CPU checker.
 
 Integer / fp32-blend outputs (n_contrib, final_T, RGB) must match the checker exactly as the unfused kernel does:
-the per-pixel alpha / T arithmetic is the same.  The weight map is accumulated on the tensor cores from fp16
-alpha*T and fp16 coefficients (fp32 accumulate): stated tolerance max-abs <= 1e-3 on weights in [0, 1].  The
-512-d features come from an fp16 x fp16 -> fp32 contraction: stated tolerance max-abs <= 1e-3 on the unit-norm
-feature (components ~ 0.04), cosine >= 0.99999 against the checker's fp32 decode of its own fp32 weight map.
+the per-pixel alpha / T arithmetic is the same.  The weight map is accumulated on the tensor cores from alpha*T and
+coefficients that are each split into an fp16 head + fp16 remainder (three MMAs, fp32 accumulate in TMEM): stated
+tolerance max-abs <= 1e-4 of the per-pixel norm of the weight vector (north_star's fp32-blend tolerance).  The
+512-d features come from an fp16 x fp16 -> fp32 contraction of the Gram-normalised weights: stated tolerance
+max-abs <= 1e-3 on the unit-norm feature (components ~ 0.04; SURVEY.md 8c allows 4e-3 for the 16-bit decode),
+cosine >= 0.99999 against the checker's fp32 decode of its own fp32 weight map.
 """
 import numpy as np
 import pytest
@@ -18,22 +20,14 @@ from tests import helpers as hp
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(params=["gen1", "gen2", "gen3"], autouse=True)
-def fused_generation(request, monkeypatch):
-    """Every test in this file runs against both fused kernels (the launcher reads LSV2_FD_V2 per call):
-    render_decode.cu, render_decode2.cu (blend / decode overlapped in one CTA, Gram-matrix norm) and
-    render_decode3.cu (half a tile per CTA, two CTAs per SM)."""
-    monkeypatch.delenv("LSV2_FD_V2", raising=False)
-    monkeypatch.delenv("LSV2_FD_V3", raising=False)
-    if request.param == "gen2":
-        monkeypatch.setenv("LSV2_FD_V2", "1")
-    elif request.param == "gen3":
-        monkeypatch.setenv("LSV2_FD_V3", "1")
-    return request.param
-
 BG = (0.1, 0.2, 0.3)
-W_TOL = 1e-3
+W_TOL = 1e-4          # relative to the per-pixel norm of the weight vector (floored at 1e-3)
 F_TOL = 1e-3
+
+
+def _wmap_err(w, ref):
+    norm = np.sqrt((ref ** 2).sum(0, keepdims=True))
+    return float(np.max(np.abs(w - ref) / np.maximum(norm, 1e-3)))
 
 
 def _check_blend_state(st, fwd):
@@ -66,8 +60,7 @@ def test_fused_quick_matches_checker(N, W, H, seed):
     out = render_decode(st, scene["codebooks"].cuda(), normalize=True, want_wmap=True)
     torch.cuda.synchronize()
     _check_blend_state(st, fwd)
-    w = st.image["wmap"].cpu().numpy()
-    assert np.max(np.abs(w - fwd["wmap"])) <= W_TOL
+    assert _wmap_err(st.image["wmap"].cpu().numpy(), fwd["wmap"]) <= W_TOL
     _check_features(out, fwd["wmap"], scene["codebooks"].numpy(), H, W)
 
 
@@ -96,7 +89,7 @@ def test_fused_sparse_scene_with_empty_tiles_and_no_normalize():
         st = hp.run_cuda(scene, cam, BG, hp.MODE_QUICK, wq=wq, iq=iq, render=False)
         out = render_decode(st, scene["codebooks"].cuda(), normalize=normalize, want_wmap=True)
         _check_blend_state(st, fwd)
-        assert np.max(np.abs(st.image["wmap"].cpu().numpy() - fwd["wmap"])) <= W_TOL
+        assert _wmap_err(st.image["wmap"].cpu().numpy(), fwd["wmap"]) <= W_TOL
         _check_features(out, fwd["wmap"], scene["codebooks"].numpy(), 120, 200, normalize=normalize, tol=2e-3)
 
 
@@ -113,7 +106,7 @@ def test_fused_dense_mode_levels(levels):
     cb = scene["codebooks"][:levels].contiguous()
     out = render_decode(st, cb.cuda(), normalize=True, want_wmap=True)
     _check_blend_state(st, fwd)
-    assert np.max(np.abs(st.image["wmap"].cpu().numpy() - fwd["wmap"])) <= W_TOL
+    assert _wmap_err(st.image["wmap"].cpu().numpy(), fwd["wmap"]) <= W_TOL
     _check_features(out, fwd["wmap"], cb.numpy(), H, W)
 
 
@@ -131,7 +124,7 @@ def test_fused_duplicate_and_bad_indices():
     st = hp.run_cuda(scene, cam, BG, hp.MODE_QUICK, wq=wq, iq=iq, render=False)
     out = render_decode(st, scene["codebooks"].cuda(), want_wmap=True)
     _check_blend_state(st, fwd)
-    assert np.max(np.abs(st.image["wmap"].cpu().numpy() - fwd["wmap"])) <= 2 * W_TOL
+    assert _wmap_err(st.image["wmap"].cpu().numpy(), fwd["wmap"]) <= W_TOL
     assert int(st.status[2].item()) == 1
     _check_features(out, fwd["wmap"], scene["codebooks"].numpy(), 112, 160, tol=2e-3)
 
