@@ -11,7 +11,8 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "liblsv2.so")
+# LSV2_LIB: developer hook to load an instrumented build (e.g. liblsv2_prof.so, csrc/Makefile target `prof`)
+LIB_PATH = os.environ.get("LSV2_LIB") or os.path.join(_HERE, "liblsv2.so")
 
 LSV2_ABI_VERSION = 2
 TILE = 16

@@ -100,6 +100,40 @@ __device__ __forceinline__ float repro_expf_inrange(float x)
     return __int_as_float(__float_as_int(y) + (((int)n) << 23));
 }
 
+// Four independent evaluations of repro_expf_inrange, written step by step across the four so that the dependent
+// chains interleave (same operations per element, hence bit-identical results).  The empty asm at the end pins the
+// four results as unconditionally computed: without it the compiler sinks each chain under the branch of its only
+// use and the four exponentials run back to back, each a ~20-instruction dependent chain.
+__device__ __forceinline__ void repro_expf_inrange4(const float (&x)[4], float (&y)[4])
+{
+    float t[4], n[4], r[4], p[4], r2[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) t[u] = __fmul_rn(x[u], 1.44269504088896341f);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) n[u] = __fsub_rn(__fadd_rn(t[u], 12582912.0f), 12582912.0f);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) r[u] = __fmaf_rn(n[u], -0.693145751953125f, x[u]);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) r[u] = __fmaf_rn(n[u], -1.42860682030941723212e-6f, r[u]);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) p[u] = __fmaf_rn(1.9875691500e-4f, r[u], 1.3981999507e-3f);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) p[u] = __fmaf_rn(p[u], r[u], 8.3334519073e-3f);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) p[u] = __fmaf_rn(p[u], r[u], 4.1665795894e-2f);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) p[u] = __fmaf_rn(p[u], r[u], 1.6666665459e-1f);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) p[u] = __fmaf_rn(p[u], r[u], 5.0000001201e-1f);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) r2[u] = __fmul_rn(r[u], r[u]);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) y[u] = __fadd_rn(__fmaf_rn(p[u], r2[u], r[u]), 1.0f);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) y[u] = __int_as_float(__float_as_int(y[u]) + (((int)n[u]) << 23));
+    asm volatile("" : "+f"(y[0]), "+f"(y[1]), "+f"(y[2]), "+f"(y[3]));
+}
+
 // Power cut-off of a splat: alpha = op*exp(power) < 1/255 for every power below it.  The margin
 // (0.01 in the exponent, ~1 % in alpha) dwarfs the 2-ulp error of repro_expf, so skipping the
 // exponential (or a whole pixel strip) below the cut-off never changes a decision.  A cut-off

@@ -18,11 +18,12 @@ constexpr int FD_BATCH = 16;                             // depth-sorted instanc
 constexpr int FD_STAGES = 2;
 constexpr int FD_BLEND_WARPS = 8;                        // warps 0-7: one thread per pixel; warp = 16x2 strip of a half
 constexpr int FD_EPI_WARPS = 4;                          // warps 8-11: F slots (TMEM) -> scaled 128-byte-line stores
-constexpr int FD_WARP_PROD = 12;                         // gathers instances, builds the coefficient operands
-constexpr int FD_WARP_MB = 13;                           // issues the blend MMAs (and owns the TMEM allocation)
-constexpr int FD_WARP_MD = 14;                           // issues the Gram / decode MMAs, fetches codebook chunks
-constexpr int FD_THREADS = 15 * 32;                      // 480
-constexpr int FD_THREADS_NODECODE = 14 * 32;             // weight-map-only variant: no MD warp (epilogue warps idle)
+constexpr int FD_WARP_PROD = 12;                         // warps 12, 13: one per tile list -- gather instances, build S
+constexpr int FD_PROD_THREADS = 64;
+constexpr int FD_WARP_MB = 14;                           // issues the blend MMAs (and owns the TMEM allocation)
+constexpr int FD_WARP_MD = 15;                           // issues the Gram / decode MMAs, fetches codebook chunks
+constexpr int FD_THREADS = 16 * 32;                      // 512
+constexpr int FD_THREADS_NODECODE = 15 * 32;             // weight-map-only variant: no MD warp (epilogue warps idle)
 constexpr int FD_MAX_L = 192;
 constexpr int FD_LC = 64;
 constexpr int FD_D = 512;
@@ -39,9 +40,12 @@ constexpr int FD_WDEC_LEVEL = 256 * 128;                 // fp16 weights of one 
 constexpr int FD_CB_BYTES = 128 * 128;                   // codebook chunk [128 features][64 codes]     16 KB
 constexpr int FD_CB_SLOTS = 2;
 constexpr int FD_CHUNKS = FD_D / 128;                    // 4 chunks of 128 features per level
-constexpr int FD_NFEAT = 32;                             // features per decode MMA / F slot
-constexpr int FD_FGROUPS = 128 / FD_NFEAT;               // 4 feature groups per chunk
-constexpr int FD_FSLOTS = 4;
+#ifndef FD_NFEAT_OPT
+#define FD_NFEAT_OPT 32
+#endif
+constexpr int FD_NFEAT = FD_NFEAT_OPT;                   // features per decode MMA / F slot
+constexpr int FD_FGROUPS = 128 / FD_NFEAT;               // feature groups per chunk
+constexpr int FD_FSLOTS = 128 / FD_NFEAT;                // F slots in the 128 spare TMEM columns
 constexpr int FD_TMEM_F = 2 * FD_MAX_L;                  // first F column (W halves occupy [0, 384))
 
 struct __align__(16) FdHeader {
@@ -96,6 +100,7 @@ struct FdArgs {
     void* out;                   // [levels][512][H][W]
     int normalize;
     uint32_t* tile_counter;
+    long long* prof;             // -DFD_PROF builds only: [grid][4 roles][8] cycle counters
 };
 
 __device__ __forceinline__ uint32_t pack_f16x2(float lo, float hi)
@@ -151,6 +156,23 @@ __device__ __forceinline__ uint32_t fd_strip_mask(float y_rel, float ax, float b
     if (hi < lo) return 0u;
     const int wlo = lo >> 1, whi = hi >> 1;
     return ((1u << (whi + 1)) - 1u) & ~((1u << wlo) - 1u);
+}
+
+// barrier with an OR reduction over the participating threads (uniform result)
+__device__ __forceinline__ bool named_bar_or(int id, int count, bool pred)
+{
+    uint32_t r;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p, q;\n\t"
+        "setp.ne.u32 q, %3, 0;\n\t"
+        "bar.red.or.pred p, %1, %2, q;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}"
+        : "=r"(r)
+        : "r"(id), "r"(count), "r"((uint32_t)pred)
+        : "memory");
+    return r != 0;
 }
 
 // mbarrier wait for the helper warps (producer, MMA issuers, epilogue): backs off between polls so the spin does
