@@ -105,7 +105,8 @@ typedef struct lsv2_geom {
     float* cov3d;            /* f32[P][6] or NULL                                  */
     int32_t* rect;           /* i32[P][4] (minx,miny,maxx,maxy) or NULL            */
     float* blend_rec;        /* f32[P][12] packed per-Gaussian record the blend reads:
-                                (x, y, -a/2, -b), (-c/2, power cut-off, opacity, r), (g, b, 0, 0) */
+                                (x, y, -a/2, -b), (-c/2, power cut-off, opacity, r), (g, b, dy, dx) with (dy, dx) the
+                                half-extents of the alpha >= 1/255 ellipse's bounding box (dy < 0: never contributes) */
 } lsv2_geom;
 
 /* Per-instance state (the reference's binningBuffer) + per-tile ranges. */
@@ -135,8 +136,14 @@ typedef struct lsv2_features {
     uint32_t* sparse_count;      /* u32[P]  non-zeros per row, 0xFFFFFFFF = row too dense  */
     uint16_t* sparse_index;      /* u16[P][LSV2_SPARSE_CAP]                                */
     float* sparse_weight;        /* f32[P][LSV2_SPARSE_CAP]                                */
+    /* Tensor-core blend only (lsv2_render_forward_tc, lsv2_render_decode): the coefficients as the kernel's B operand
+     * wants them, written by lsv2_pack_coeff -- per Gaussian LSV2_PACKED_WORDS u32: 16 x (fp16 head | fp16 remainder
+     * << 16), 16 channel bytes, the entry count (0xFFFFFFFF: read the dense row).  Duplicate channels are merged and
+     * out-of-range ones dropped (and flagged) at pack time. */
+    uint32_t* packed;            /* u32[P][LSV2_PACKED_WORDS]                              */
 } lsv2_features;
 #define LSV2_SPARSE_CAP 16
+#define LSV2_PACKED_WORDS 24
 
 /* Per-pixel outputs (rendered image, weight map, and the reference's imgBuffer). */
 typedef struct lsv2_image {
@@ -182,6 +189,12 @@ int lsv2_render_forward(const lsv2_view* view, const lsv2_geom* geom, const lsv2
  * LSV2_EUNSUPPORTED (use lsv2_render_forward).  Uses the first 256 bytes of binning->scratch. */
 int lsv2_render_forward_tc(const lsv2_view* view, const lsv2_geom* geom, const lsv2_binning* binning,
                            const lsv2_features* feat, const lsv2_image* image, void* stream);
+
+/* Fills feat->packed from the QUICK inputs (weights_quick / indices_quick) or, in DENSE mode, from the compacted rows
+ * of lsv2_compact_coeff (call it first; geom->radii selects the rows that exist).  An index outside [0, L) sets
+ * status[LSV2_STATUS_BAD_INDEX] (status may be NULL).  The table depends only on the coefficients, not on the view:
+ * a resident scene packs once. */
+int lsv2_pack_coeff(int32_t P, const lsv2_geom* geom, const lsv2_features* feat, uint32_t* status, void* stream);
 
 /* preprocess + bin + compact + blend back to back, no host involvement (CUDA-graph capturable).  The blend is
  * lsv2_render_forward_tc where it applies, lsv2_render_forward otherwise. */

@@ -17,6 +17,7 @@ LIB_PATH = os.environ.get("LSV2_LIB") or os.path.join(_HERE, "liblsv2.so")
 LSV2_ABI_VERSION = 2
 TILE = 16
 SPARSE_CAP = 16
+PACKED_WORDS = 24
 STATUS_WORDS = 8
 STATUS_NUM_RENDERED, STATUS_OVERFLOW, STATUS_BAD_INDEX = 0, 1, 2
 MODE_RGB, MODE_DENSE, MODE_QUICK = 0, 1, 2
@@ -51,7 +52,7 @@ class Binning(C.Structure):
 class Features(C.Structure):
     _fields_ = [("mode", C.c_int32), ("L", C.c_int32), ("K", C.c_int32), ("coeff_dense", _vp),
                 ("weights_quick", _vp), ("indices_quick", _vp), ("sparse_count", _vp),
-                ("sparse_index", _vp), ("sparse_weight", _vp)]
+                ("sparse_index", _vp), ("sparse_weight", _vp), ("packed", _vp)]
 
 
 class Image(C.Structure):
@@ -65,7 +66,7 @@ EXPORTS = [
     "lsv2_decode_backward", "lsv2_topk_soft_code", "lsv2_topk_soft_code_backward", "lsv2_cos_loss_blocks", "lsv2_cos_loss_forward", "lsv2_cos_loss_backward",
     "lsv2_gram_loss_forward", "lsv2_gram_loss_backward", "lsv2_colsumsq", "lsv2_segment_sum",
     "lsv2_gram_loss_forward_seg", "lsv2_gram_loss_backward_seg",
-    "lsv2_render_decode_scratch_bytes", "lsv2_render_decode", "lsv2_render_forward_tc", "lsv2_adam_step",
+    "lsv2_render_decode_scratch_bytes", "lsv2_render_decode", "lsv2_render_forward_tc", "lsv2_adam_step", "lsv2_pack_coeff",
 ]
 
 _lib = None
@@ -97,6 +98,7 @@ def lib() -> C.CDLL:
     L.lsv2_bin.argtypes = [P(View), C.c_int32, P(Geom), P(Binning), _vp]
     L.lsv2_compact_coeff.argtypes = [C.c_int32, P(Geom), P(Features), _vp]
     L.lsv2_render_forward.argtypes = [P(View), P(Geom), P(Binning), P(Features), P(Image), _vp]
+    L.lsv2_pack_coeff.argtypes = [C.c_int32, P(Geom), P(Features), _vp, _vp]
     L.lsv2_render_forward_tc.argtypes = [P(View), P(Geom), P(Binning), P(Features), P(Image), _vp]
     L.lsv2_forward.argtypes = [P(View), P(Scene), P(Geom), P(Binning), P(Features), P(Image), _vp]
     L.lsv2_mark_visible.argtypes = [C.c_int32, _vp, _vp, _vp, _vp]
@@ -130,7 +132,7 @@ def lib() -> C.CDLL:
                  "lsv2_mark_visible", "lsv2_render_backward", "lsv2_decode", "lsv2_decode_backward",
                  "lsv2_topk_soft_code", "lsv2_topk_soft_code_backward", "lsv2_cos_loss_forward", "lsv2_cos_loss_backward",
                  "lsv2_gram_loss_forward", "lsv2_gram_loss_backward", "lsv2_colsumsq", "lsv2_segment_sum", "lsv2_render_decode",
-                 "lsv2_render_forward_tc", "lsv2_gram_loss_forward_seg", "lsv2_gram_loss_backward_seg", "lsv2_adam_step"):
+                 "lsv2_render_forward_tc", "lsv2_gram_loss_forward_seg", "lsv2_gram_loss_backward_seg", "lsv2_adam_step", "lsv2_pack_coeff"):
         getattr(L, name).restype = C.c_int
     _lib = L
     return L

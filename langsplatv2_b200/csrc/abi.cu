@@ -42,6 +42,7 @@ int launch_topk_soft_code(int64_t N, int C, int k, const float* logits, float* d
 int launch_adam(float* p, const float* g, float* m, float* v, int64_t n, float lr, float b1, float b2, float eps,
                 int64_t step, int zero_grad, const float* dev_scalars, cudaStream_t st);
 size_t render_decode_scratch_bytes(int levels);
+int launch_pack_coeff(int P, const lsv2_geom& g, const lsv2_features& f, uint32_t* status, cudaStream_t st);
 int launch_render_wmap_tc(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b, const lsv2_features& f,
                           const lsv2_image& img, void* scratch, size_t scratch_bytes, cudaStream_t st);
 int launch_render_decode(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b, const lsv2_features& f,
@@ -152,12 +153,19 @@ int lsv2_render_forward(const lsv2_view* view, const lsv2_geom* geom, const lsv2
     return launch_render_forward(*view, *geom, *binning, *feat, *image, (cudaStream_t)stream);
 }
 
+int lsv2_pack_coeff(int32_t P, const lsv2_geom* geom, const lsv2_features* feat, uint32_t* status, void* stream)
+{
+    if (P < 0 || !geom || !feat) return LSV2_EINVAL;
+    return launch_pack_coeff(P, *geom, *feat, status, (cudaStream_t)stream);
+}
+
 int lsv2_render_forward_tc(const lsv2_view* view, const lsv2_geom* geom, const lsv2_binning* binning,
                            const lsv2_features* feat, const lsv2_image* image, void* stream)
 {
     if (!view_ok(view) || !geom || !binning || !feat || !image) return LSV2_EINVAL;
     if (!image->color || !image->final_T || !image->n_contrib || !image->wmap) return LSV2_EINVAL;
-    if (feat->mode != LSV2_MODE_QUICK && !(feat->mode == LSV2_MODE_DENSE && feat->sparse_count)) return LSV2_EUNSUPPORTED;
+    if (feat->mode != LSV2_MODE_QUICK && feat->mode != LSV2_MODE_DENSE) return LSV2_EUNSUPPORTED;
+    if (!feat->packed) return LSV2_EUNSUPPORTED;
     return launch_render_wmap_tc(*view, *geom, *binning, *feat, *image, binning->scratch, binning->scratch_bytes,
                                  (cudaStream_t)stream);
 }
@@ -173,7 +181,9 @@ int lsv2_forward(const lsv2_view* view, const lsv2_scene* scene, const lsv2_geom
         rc = lsv2_compact_coeff(scene->P, geom, feat, stream);
         if (rc) return rc;
     }
-    if (feat && image && image->wmap) {
+    if (feat && image && image->wmap && feat->packed) {
+        rc = lsv2_pack_coeff(scene->P, geom, feat, binning->status, stream);
+        if (rc) return rc;
         rc = lsv2_render_forward_tc(view, geom, binning, feat, image, stream);
         if (rc != LSV2_EUNSUPPORTED) return rc;
     }

@@ -144,6 +144,23 @@ __device__ __forceinline__ float power_cutoff(float op)
     return -__logf(255.0f * op) - 0.01f;
 }
 
+// Half-extents (in pixels, padded: x 1.0001 + 0.02) of the axis-aligned box around the ellipse power >= thr of a
+// splat with conic (a, b, c) given as ax = -a/2, bb = -b, az = -c/2 (the packed blend record): no pixel outside
+// that box can reach alpha >= 1/255.  dy < 0: the splat can never contribute; 1e30: no bound on that axis.
+__device__ __forceinline__ void cutoff_extents(float ax, float bb, float az, float thr, float& dy, float& dx)
+{
+    dy = -1.0f;
+    dx = 1e30f;
+    if (!(thr < 0.0f)) return;
+    const float qa = -2.0f * ax, qc = -2.0f * az;
+    const float det = qa * qc - bb * bb;
+    dy = 1e30f;
+    if (det > 0.0f && qa > 0.0f) dy = sqrtf((-2.0f * thr) * (qa / det)) * 1.0001f + 0.02f;
+    if (!(dy == dy)) dy = 1e30f;
+    if (det > 0.0f && qc > 0.0f) dx = sqrtf((-2.0f * thr) * (qc / det)) * 1.0001f + 0.02f;
+    if (!(dx == dx)) dx = 1e30f;
+}
+
 // Tile rectangle covered by a splat of integer radius `rad` centred at (px, py).
 __device__ __forceinline__ void tile_rect(float px, float py, float rad, int gx, int gy,
                                           int& minx, int& miny, int& maxx, int& maxy)

@@ -30,6 +30,7 @@ constexpr int FD_D = 512;
 constexpr int FD_KMAX = LSV2_SPARSE_CAP;
 constexpr uint32_t FD_ROW_DENSE = 0xFFFFFFFFu;
 constexpr int FD_UNIT_W = 32, FD_UNIT_H = 8;
+constexpr int FD_CREC_WORDS = LSV2_PACKED_WORDS;         // 16 (hi | lo << 16) words, 16 channel bytes, count, pad
 
 // blend operands: 64-byte rows [hi fp16 x16 | lo fp16 x16], 64-byte swizzle, K-major
 constexpr int FD_AHALF_BYTES = 128 * 64;                 // alpha*T of one 128-pixel half                8 KB
@@ -83,12 +84,8 @@ struct FdArgs {
     const float4* rec;
     const float* bg;
     int mode, L, K, levels;
-    const float* coeff_dense;
-    const float* wq;
-    const float* iq;
-    const uint32_t* sp_count;
-    const uint16_t* sp_index;
-    const float* sp_weight;
+    const float* coeff_dense;    // rows whose packed count is FD_ROW_DENSE are read from here
+    const uint32_t* crec;        // packed coefficients u32[P][FD_CREC_WORDS] (lsv2_pack_coeff)
     float* color;
     float* wmap;                 // optional fp32 [L][H][W]
     float* final_T;
@@ -146,6 +143,24 @@ __device__ __forceinline__ uint32_t fd_strip_mask(float y_rel, float ax, float b
         const float dx = sqrtf((-2.0f * thr) * (qc / det)) * 1.0001f + 0.02f;
         if (dx == dx && (x_rel + dx < 0.0f || x_rel - dx > 15.0f)) return 0u;
     }
+    const float lo_f = ceilf(y_rel - dy), hi_f = floorf(y_rel + dy);
+    if (!(hi_f >= 0.0f) || !(lo_f <= 15.0f)) {
+        if (lo_f != lo_f || hi_f != hi_f) return 0xFFu;
+        return 0u;
+    }
+    const int lo = lo_f <= 0.0f ? 0 : (int)lo_f;
+    const int hi = hi_f >= 15.0f ? 15 : (int)hi_f;
+    if (hi < lo) return 0u;
+    const int wlo = lo >> 1, whi = hi >> 1;
+    return ((1u << (whi + 1)) - 1u) & ~((1u << wlo) - 1u);
+}
+
+// Same mask from the extents stored in the blend record (cutoff_extents, common.cuh): a handful of instructions per
+// instance in the producer instead of two divisions and two square roots.
+__device__ __forceinline__ uint32_t fd_strip_mask_ext(float y_rel, float x_rel, float dy, float dx)
+{
+    if (!(dy >= 0.0f)) return 0u;
+    if (x_rel + dx < 0.0f || x_rel - dx > 15.0f) return 0u;
     const float lo_f = ceilf(y_rel - dy), hi_f = floorf(y_rel + dy);
     if (!(hi_f >= 0.0f) || !(lo_f <= 15.0f)) {
         if (lo_f != lo_f || hi_f != hi_f) return 0xFFu;

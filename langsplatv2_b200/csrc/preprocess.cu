@@ -252,12 +252,15 @@ __global__ void __launch_bounds__(PRE_THREADS) k_preprocess(PreArgs a)
         float4* rec = a.blend_rec + 3 * (size_t)i;
         if (vis) {
             rec[0] = make_float4(px, py, -0.5f * con0, -con1);
-            rec[1] = make_float4(-0.5f * con2, power_cutoff(op), op, rgb[0]);
-            rec[2] = make_float4(rgb[1], rgb[2], 0.f, 0.f);
+            const float thr = power_cutoff(op);
+            float ext_y, ext_x;
+            cutoff_extents(-0.5f * con0, -con1, -0.5f * con2, thr, ext_y, ext_x);
+            rec[1] = make_float4(-0.5f * con2, thr, op, rgb[0]);
+            rec[2] = make_float4(rgb[1], rgb[2], ext_y, ext_x);
         } else {
             rec[0] = make_float4(0.f, 0.f, 0.f, 0.f);
             rec[1] = make_float4(0.f, 1.0f, 0.f, 0.f);
-            rec[2] = make_float4(0.f, 0.f, 0.f, 0.f);
+            rec[2] = make_float4(0.f, 0.f, -1.f, 0.f);
         }
     }
     if (a.rect) {

@@ -111,16 +111,98 @@ __global__ void __launch_bounds__(64) k_fd_prep_g(const float* __restrict__ code
     }
 }
 
-// What one producer lane gathers (kept in registers up to two batches ahead).  Two lanes share an instance: lane
-// part p (= lane >> 4) holds entries k = 2q + p of the instance's (weight, channel) list; part 0 also holds the
-// geometry words of the blend record, part 1 its colour word.
+// ---- packed coefficients (lsv2_pack_coeff) -------------------------------------------------------------------------
+// One thread per Gaussian: entries -> (fp16 head | fp16 remainder << 16) words + channel bytes + count.  Duplicate
+// channels are merged (their weights add up, as the blend would add them), channels outside [0, L) are dropped and
+// flagged.  MODE_DENSE reads the compacted rows of lsv2_compact_coeff; a row too dense for them keeps count =
+// FD_ROW_DENSE and the blend reads it from coeff_dense.
+template <int MODE>
+__global__ void __launch_bounds__(256) k_fd_pack(int P, int L, int K, const float* __restrict__ wq, const float* __restrict__ iq,
+                                                 const int32_t* __restrict__ radii, const uint32_t* __restrict__ sp_count,
+                                                 const uint16_t* __restrict__ sp_index, const float* __restrict__ sp_weight,
+                                                 uint32_t* __restrict__ crec, uint32_t* __restrict__ status)
+{
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= P) return;
+    float w[FD_KMAX];
+    int ch[FD_KMAX];
+    uint32_t n = 0;
+    bool bad = false;
+    if (MODE == LSV2_MODE_QUICK) {
+        for (int k = 0; k < K; ++k) {
+            const float wk = wq[(size_t)g * K + k];
+            const int c = (int)iq[(size_t)g * K + k];
+            if (c < 0 || c >= L) { bad = true; continue; }
+            bool merged = false;
+#pragma unroll
+            for (int e = 0; e < FD_KMAX; ++e)
+                if ((uint32_t)e < n && ch[e] == c) { w[e] += wk; merged = true; }
+            if (!merged) {
+#pragma unroll
+                for (int e = 0; e < FD_KMAX; ++e) if ((uint32_t)e == n) { w[e] = wk; ch[e] = c; }
+                ++n;
+            }
+        }
+    } else {
+        if (radii && radii[g] <= 0) return;                 // the compacted row of an invisible Gaussian does not exist
+        n = sp_count[g];
+        if (n != FD_ROW_DENSE) {
+            n = min(n, (uint32_t)FD_KMAX);
+#pragma unroll
+            for (int e = 0; e < FD_KMAX; ++e)
+                if ((uint32_t)e < n) { w[e] = sp_weight[(size_t)g * FD_KMAX + e]; ch[e] = (int)sp_index[(size_t)g * FD_KMAX + e]; }
+        }
+    }
+    uint32_t out[FD_CREC_WORDS];
+#pragma unroll
+    for (int i = 0; i < FD_CREC_WORDS; ++i) out[i] = 0u;
+    if (n != FD_ROW_DENSE) {
+#pragma unroll
+        for (int e = 0; e < FD_KMAX; ++e)
+            if ((uint32_t)e < n) {
+                const __half h = __float2half_rn(w[e]);
+                const __half lo = __float2half_rn(__fsub_rn(w[e], __half2float(h)));
+                out[e] = (uint32_t)__half_as_ushort(h) | ((uint32_t)__half_as_ushort(lo) << 16);
+                out[16 + (e >> 2)] |= (uint32_t)(ch[e] & 0xFF) << (8 * (e & 3));
+            }
+    }
+    out[20] = n;
+    uint4* dst = reinterpret_cast<uint4*>(crec + (size_t)g * FD_CREC_WORDS);
+#pragma unroll
+    for (int i = 0; i < FD_CREC_WORDS / 4; ++i) dst[i] = make_uint4(out[4 * i], out[4 * i + 1], out[4 * i + 2], out[4 * i + 3]);
+    if (bad && status) status[LSV2_STATUS_BAD_INDEX] = 1u;
+}
+
+int launch_pack_coeff(int P, const lsv2_geom& g, const lsv2_features& f, uint32_t* status, cudaStream_t st)
+{
+    if (P <= 0) return LSV2_OK;
+    if (!f.packed || f.L <= 0 || f.L > 256) return LSV2_EINVAL;
+    if (f.mode == LSV2_MODE_QUICK) {
+        if (f.K <= 0 || !f.weights_quick || !f.indices_quick) return LSV2_EINVAL;
+        if (f.K > FD_KMAX) return LSV2_EUNSUPPORTED;
+        k_fd_pack<LSV2_MODE_QUICK><<<ceil_div(P, 256), 256, 0, st>>>(P, f.L, f.K, f.weights_quick, f.indices_quick, nullptr,
+                                                                     nullptr, nullptr, nullptr, f.packed, status);
+    } else if (f.mode == LSV2_MODE_DENSE) {
+        if (!f.sparse_count || !f.sparse_index || !f.sparse_weight) return LSV2_EINVAL;
+        k_fd_pack<LSV2_MODE_DENSE><<<ceil_div(P, 256), 256, 0, st>>>(P, f.L, 0, nullptr, nullptr, g.radii, f.sparse_count,
+                                                                     f.sparse_index, f.sparse_weight, f.packed, status);
+    } else {
+        return LSV2_EINVAL;
+    }
+    LSV2_LAUNCH_CHECK("k_fd_pack");
+    return LSV2_OK;
+}
+
+// What one producer lane gathers (kept in registers one batch ahead).  Two lanes share an instance: lane part p
+// (= lane >> 4) takes the packed entry pairs p, p + 2, p + 4, p + 6 (entries 2(p + 2i), 2(p + 2i) + 1), part 0 also
+// the position / shape / colour words of the blend record, part 1 its cut-off / opacity word.
 struct FdGather {
     uint32_t g, cnt;
-    float4 ra, rb;                       // part 0: rec[0], rec[1] ; part 1: rec[2], -
-    float wv[FD_KMAX / 2], iv[FD_KMAX / 2];
+    float4 ra, rb;                       // part 0: rec[0], rec[2] ; part 1: rec[1], -
+    uint2 hl[4];
+    uint4 ch;
 };
 
-template <int MODE>
 __device__ __forceinline__ void fd_gather(const FdArgs& a, uint32_t g, int part, FdGather& o)
 {
     o.g = g;
@@ -128,32 +210,18 @@ __device__ __forceinline__ void fd_gather(const FdArgs& a, uint32_t g, int part,
     if (g == 0xFFFFFFFFu) return;
     if (part == 0) {
         o.ra = __ldg(a.rec + 3 * (size_t)g);
-        o.rb = __ldg(a.rec + 3 * (size_t)g + 1);
+        o.rb = __ldg(a.rec + 3 * (size_t)g + 2);
     } else {
-        o.ra = __ldg(a.rec + 3 * (size_t)g + 2);
+        o.ra = __ldg(a.rec + 3 * (size_t)g + 1);
     }
-    if (MODE == LSV2_MODE_QUICK) {
-        o.cnt = (uint32_t)a.K;
-        const float* wsrc = a.wq + (size_t)g * a.K + part;
-        const float* isrc = a.iq + (size_t)g * a.K + part;
+    const uint32_t* row = a.crec + (size_t)g * FD_CREC_WORDS;
 #pragma unroll
-        for (int q = 0; q < FD_KMAX / 2; ++q)
-            if (2 * q + part < a.K) { o.wv[q] = __ldg(wsrc + 2 * q); o.iv[q] = __ldg(isrc + 2 * q); }
-    } else {
-        o.cnt = a.sp_count[g];
-        if (o.cnt != FD_ROW_DENSE) {
-#pragma unroll
-            for (int q = 0; q < FD_KMAX / 2; ++q)
-                if ((uint32_t)(2 * q + part) < o.cnt) {
-                    o.wv[q] = a.sp_weight[(size_t)g * FD_KMAX + 2 * q + part];
-                    o.iv[q] = (float)a.sp_index[(size_t)g * FD_KMAX + 2 * q + part];
-                }
-        }
-    }
+    for (int i = 0; i < 4; ++i) o.hl[i] = __ldg(reinterpret_cast<const uint2*>(row) + part + 2 * i);
+    o.ch = __ldg(reinterpret_cast<const uint4*>(row) + 4);
+    o.cnt = __ldg(row + 20);
 }
 
 // pull what fd_gather will read for Gaussian g towards L2 (no registers held)
-template <int MODE>
 __device__ __forceinline__ void fd_prefetch(const FdArgs& a, uint32_t g, int part)
 {
     if (g == 0xFFFFFFFFu) return;
@@ -163,29 +231,23 @@ __device__ __forceinline__ void fd_prefetch(const FdArgs& a, uint32_t g, int par
     if (part == 0) {
         asm volatile("prefetch.global.L2 [%0];" ::"l"(a.rec + 3 * (size_t)g));
         asm volatile("prefetch.global.L2 [%0];" ::"l"(a.rec + 3 * (size_t)g + 2));
-    } else if (MODE == LSV2_MODE_QUICK) {
-        asm volatile("prefetch.global.L2 [%0];" ::"l"(a.wq + (size_t)g * a.K));
-        asm volatile("prefetch.global.L2 [%0];" ::"l"(a.iq + (size_t)g * a.K));
     } else {
-        asm volatile("prefetch.global.L2 [%0];" ::"l"(a.sp_weight + (size_t)g * FD_KMAX));
-        asm volatile("prefetch.global.L2 [%0];" ::"l"(a.sp_index + (size_t)g * FD_KMAX));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(a.crec + (size_t)g * FD_CREC_WORDS));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(a.crec + (size_t)g * FD_CREC_WORDS + 20));
     }
 }
 
-// one coefficient into an S tile: head at k-slice 0, remainder at k-slice 1 of row `c` (the remainder's 16-byte
-// chunk index is the head's with bit 1 flipped, i.e. byte offset ^ 32)
-__device__ __forceinline__ void fd_put(unsigned char* S, uint32_t c, uint32_t inst, float w, bool accumulate)
+// one coefficient of a dense row into an S tile: head at k-slice 0, remainder at k-slice 1 of row `c` (the
+// remainder's 16-byte chunk index is the head's with bit 1 flipped, i.e. byte offset ^ 32)
+__device__ __forceinline__ void fd_put(unsigned char* S, uint32_t c, uint32_t inst, float w)
 {
     const uint32_t off = sw64_offset(c, inst >> 3) + (inst & 7u) * 2u;
-    __half* ph = reinterpret_cast<__half*>(S + off);
-    __half* pl = reinterpret_cast<__half*>(S + (off ^ 32u));
-    if (accumulate) w = __fadd_rn(__fadd_rn(__half2float(*ph), __half2float(*pl)), w);     // duplicates add up
     const __half h = __float2half_rn(w);
-    *ph = h;
-    *pl = __float2half_rn(__fsub_rn(w, __half2float(h)));
+    *reinterpret_cast<__half*>(S + off) = h;
+    *reinterpret_cast<__half*>(S + (off ^ 32u)) = __float2half_rn(__fsub_rn(w, __half2float(h)));
 }
 
-template <int MODE, bool OUT_BF16, bool DECODE>
+template <bool OUT_BF16, bool DECODE>
 __global__ void __launch_bounds__(DECODE ? FD_THREADS : FD_THREADS_NODECODE, 1) k_render_decode(FdArgs a)
 {
     extern __shared__ unsigned char smem_raw[];
@@ -279,12 +341,15 @@ __global__ void __launch_bounds__(DECODE ? FD_THREADS : FD_THREADS_NODECODE, 1) 
                 const uint32_t i0 = load_id(0), i1 = load_id(1);
 #pragma unroll
                 for (int k = 0; k < 5; ++k) idq[k] = load_id(2 + k);
-                fd_gather<MODE>(a, i0, part, cur);
+                fd_gather(a, i0, part, cur);
                 nxt.g = i1;
 #pragma unroll
-                for (int k = 0; k < 3; ++k) fd_prefetch<MODE>(a, idq[k], part);
+                for (int k = 0; k < 3; ++k) fd_prefetch(a, idq[k], part);
             }
             unsigned char* const S_base = ring + 2 * FD_AHALF_BYTES + (size_t)t * FD_S_BYTES;
+            // byte offset of this lane's instance column inside an S row, without the row / chunk-swizzle part
+            const uint32_t col_off = (uint32_t)(inst & 7) * 2u;
+            const uint32_t chunk0 = (uint32_t)inst >> 3;
             // One batch per iteration (single copy of the code: the roles' loops must share the instruction caches).
             // `cur` holds batch b; the register gather of batch b + 1 is issued at the top and lands while this batch
             // is assembled (its lines were pulled into L2 four batches earlier).
@@ -310,73 +375,40 @@ __global__ void __launch_bounds__(DECODE ? FD_THREADS : FD_THREADS_NODECODE, 1) 
                 }
                 unsigned char* S = S_base + (size_t)s * FD_STAGE_BYTES;
                 for (int q = lane; q < FD_S_BYTES / 16; q += 32) reinterpret_cast<uint4*>(S)[q] = make_uint4(0, 0, 0, 0);
-                fd_gather<MODE>(a, nxt.g, part, nxt);       // batch b + 1
-                fd_prefetch<MODE>(a, idq[3], part);          // batch b + 5
+                fd_gather(a, nxt.g, part, nxt);              // batch b + 1
+                fd_prefetch(a, idq[3], part);                // batch b + 5
                 const uint32_t id_new = load_id(b + 7);
                 __syncwarp();
-                const bool live = cur.g != 0xFFFFFFFFu;
-                const bool sparse_row = live && cur.cnt != FD_ROW_DENSE;
-                // channels distinct and ascending across the pair's interleaved entries: plain stores suffice
-                bool asc = true;
-                {
-                    float prev_other = -1.0f;               // entry k = 2q - 1
-#pragma unroll
-                    for (int q = 0; q < FD_KMAX / 2; ++q) {
-                        const float mine = (sparse_row && (uint32_t)(2 * q + part) < cur.cnt) ? cur.iv[q] : 1e30f;
-                        const float other = __shfl_xor_sync(0xffffffffu, mine, 16);
-                        if (part == 0)
-                            asc &= (mine > prev_other || mine == 1e30f) && (other > mine || other == 1e30f);
-                        prev_other = other;
-                    }
-                    asc = __shfl_sync(0xffffffffu, (int)asc, inst) != 0;
-                }
-                const bool any_dup = __any_sync(0xffffffffu, sparse_row && !asc);
                 uint32_t m4 = 0;
-                if (live) {
+                if (cur.g != 0xFFFFFFFFu) {
                     if (part == 0) {
                         Hd.g0[t * FD_BATCH + inst] = cur.ra;
-                        Hd.g1[t * FD_BATCH + inst] = cur.rb;
-                        m4 = fd_strip_mask(cur.ra.y - y0, cur.ra.z, cur.ra.w, cur.rb.x, cur.rb.y, cur.ra.x - x0) & 0xFu;
+                        Hd.g2[t * FD_BATCH + inst] = make_float2(cur.rb.x, cur.rb.y);
+                        m4 = fd_strip_mask_ext(cur.ra.y - y0, cur.ra.x - x0, cur.rb.z, cur.rb.w) & 0xFu;
                     } else {
-                        Hd.g2[t * FD_BATCH + inst] = make_float2(cur.ra.x, cur.ra.y);
+                        Hd.g1[t * FD_BATCH + inst] = cur.ra;
                     }
-                }
-                if (sparse_row && asc) {
+                    if (cur.cnt != FD_ROW_DENSE) {
+                        const uint32_t chw[4] = {cur.ch.x, cur.ch.y, cur.ch.z, cur.ch.w};
 #pragma unroll
-                    for (int q = 0; q < FD_KMAX / 2; ++q)
-                        if ((uint32_t)(2 * q + part) < cur.cnt) {
-                            const int c = (int)cur.iv[q];
-                            if (c >= 0 && c < L) fd_put(S, (uint32_t)c, (uint32_t)inst, cur.wv[q], false);
-                            else a.status[LSV2_STATUS_BAD_INDEX] = 1u;
+                        for (int i = 0; i < 4; ++i) {
+#pragma unroll
+                            for (int j = 0; j < 2; ++j) {
+                                const uint32_t e = 2u * (uint32_t)(part + 2 * i) + (uint32_t)j;
+                                if (e < cur.cnt) {
+                                    const uint32_t c = (chw[i] >> (8u * (2u * (uint32_t)part + (uint32_t)j))) & 0xFFu;
+                                    const uint32_t v = j == 0 ? cur.hl[i].x : cur.hl[i].y;
+                                    const uint32_t off = c * 64u + (((chunk0 ^ (c >> 1)) & 3u) << 4) + col_off;
+                                    *reinterpret_cast<unsigned short*>(S + off) = (unsigned short)(v & 0xFFFFu);
+                                    *reinterpret_cast<unsigned short*>(S + (off ^ 32u)) = (unsigned short)(v >> 16);
+                                }
+                            }
                         }
-                } else if (live && !sparse_row) {
-                    const float* row = a.coeff_dense + (size_t)cur.g * L;
-                    for (int c = part; c < L; c += 2) {
-                        const float v = __ldg(row + c);
-                        if (v != 0.0f) fd_put(S, (uint32_t)c, (uint32_t)inst, v, false);
-                    }
-                }
-                if (any_dup) {
-                    // rare: an instance repeats a channel.  Lane part 0 walks all its entries in order (its own and,
-                    // through shuffles, its partner's) with read-modify-write.
-#pragma unroll 1
-                    for (int q = 0; q < FD_KMAX / 2; ++q) {
-                        float mw = 0.f, mi = 0.f;
-#pragma unroll
-                        for (int qq = 0; qq < FD_KMAX / 2; ++qq) if (qq == q) { mw = cur.wv[qq]; mi = cur.iv[qq]; }
-                        const float ow = __shfl_xor_sync(0xffffffffu, mw, 16);
-                        const float oi = __shfl_xor_sync(0xffffffffu, mi, 16);
-                        if (sparse_row && !asc && part == 0) {
-                            if ((uint32_t)(2 * q) < cur.cnt) {
-                                const int c = (int)mi;
-                                if (c >= 0 && c < L) fd_put(S, (uint32_t)c, (uint32_t)inst, mw, true);
-                                else a.status[LSV2_STATUS_BAD_INDEX] = 1u;
-                            }
-                            if ((uint32_t)(2 * q + 1) < cur.cnt) {
-                                const int c = (int)oi;
-                                if (c >= 0 && c < L) fd_put(S, (uint32_t)c, (uint32_t)inst, ow, true);
-                                else a.status[LSV2_STATUS_BAD_INDEX] = 1u;
-                            }
+                    } else {
+                        const float* row = a.coeff_dense + (size_t)cur.g * L;
+                        for (int c = part; c < L; c += 2) {
+                            const float v = __ldg(row + c);
+                            if (v != 0.0f) fd_put(S, (uint32_t)c, (uint32_t)inst, v);
                         }
                     }
                 }
@@ -477,7 +509,7 @@ __global__ void __launch_bounds__(DECODE ? FD_THREADS : FD_THREADS_NODECODE, 1) 
                     const int slot = (int)(n & 1u);
                     mbar_wait(cb_full + slot, (n >> 1) & 1);
                     const uint64_t g_hi = desc_cb(slot), g_lo = g_hi + (uint64_t)((64 * 128) >> 4);
-#pragma unroll
+#pragma unroll 1
                     for (int m = 0; m < 2; ++m) {
                         const uint32_t d = tmem + (uint32_t)(m * FD_MAX_L + l * FD_LC);
                         const uint64_t da = desc_w(l, m);
@@ -495,17 +527,19 @@ __global__ void __launch_bounds__(DECODE ? FD_THREADS : FD_THREADS_NODECODE, 1) 
                 }
                 if (stop) break;
                 tc_fence_after();
+#pragma unroll 1
                 for (int l = 0; l < levels; ++l) {
+#pragma unroll 1
                     for (int c = 0; c < FD_CHUNKS; ++c) {
                         const uint32_t n = cb_used;
                         const int slot = (int)(n & 1u);
                         FD_TOC(3);
                         mbar_wait(cb_full + slot, (n >> 1) & 1);
                         FD_TOC(1);
-#pragma unroll
+#pragma unroll 1
                         for (int g = 0; g < FD_FGROUPS; ++g) {
                             const uint64_t db = desc_cb(slot) + (uint64_t)(g * ((FD_NFEAT * 128) >> 4));
-#pragma unroll
+#pragma unroll 1
                             for (int m = 0; m < 2; ++m) {
                                 const int fs = (int)(f_n % FD_FSLOTS);
                                 FD_TOC(3);
@@ -880,13 +914,14 @@ static int fd_check_features(const lsv2_features& f)
 {
     if (f.L <= 0 || f.L > FD_MAX_L || (f.L % FD_LC) != 0) return LSV2_EUNSUPPORTED;
     if (f.mode == LSV2_MODE_QUICK) {
-        if (f.K <= 0 || !f.weights_quick || !f.indices_quick) return LSV2_EINVAL;
+        if (f.K <= 0) return LSV2_EINVAL;
         if (f.K > FD_KMAX) return LSV2_EUNSUPPORTED;
     } else if (f.mode == LSV2_MODE_DENSE) {
-        if (!f.coeff_dense || !f.sparse_count || !f.sparse_index || !f.sparse_weight) return LSV2_EINVAL;
+        if (!f.coeff_dense) return LSV2_EINVAL;
     } else {
         return LSV2_EINVAL;
     }
+    if (!f.packed) return LSV2_EINVAL;              // lsv2_pack_coeff first
     return LSV2_OK;
 }
 
@@ -901,8 +936,7 @@ static void fd_fill_args(FdArgs& a, const lsv2_view& v, const lsv2_geom& g, cons
     a.rec = reinterpret_cast<const float4*>(g.blend_rec);
     a.bg = v.bg;
     a.mode = f.mode; a.L = f.L; a.K = f.K; a.levels = f.L / FD_LC;
-    a.coeff_dense = f.coeff_dense; a.wq = f.weights_quick; a.iq = f.indices_quick;
-    a.sp_count = f.sparse_count; a.sp_index = f.sparse_index; a.sp_weight = f.sparse_weight;
+    a.coeff_dense = f.coeff_dense; a.crec = f.packed;
     a.color = img.color; a.wmap = img.wmap; a.final_T = img.final_T; a.n_contrib = img.n_contrib;
     a.status = b.status;
     a.bimg = nullptr; a.gimg = nullptr; a.gscale_inv = nullptr; a.out = nullptr; a.normalize = 0;
@@ -942,17 +976,13 @@ int launch_render_decode(const lsv2_view& v, const lsv2_geom& g, const lsv2_binn
     a.prof = reinterpret_cast<long long*>(gimg + (size_t)levels * FD_CB_BYTES);
 #endif
     const int grid = min(NUM_SMS, a.n_units);
-#define FD_LAUNCH(M, O)                                                                                            \
-    do {                                                                                                           \
-        LSV2_CUDA_TRY(cudaFuncSetAttribute(k_render_decode<M, O, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                           (int)FD_SMEM_TOTAL));                                                   \
-        k_render_decode<M, O, true><<<grid, FD_THREADS, FD_SMEM_TOTAL, st>>>(a);                             \
+#define FD_LAUNCH(O)                                                                                            \
+    do {                                                                                                        \
+        LSV2_CUDA_TRY(cudaFuncSetAttribute(k_render_decode<O, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                           (int)FD_SMEM_TOTAL));                                                \
+        k_render_decode<O, true><<<grid, FD_THREADS, FD_SMEM_TOTAL, st>>>(a);                                   \
     } while (0)
-    if (f.mode == LSV2_MODE_QUICK) {
-        if (out_dtype == 0) FD_LAUNCH(LSV2_MODE_QUICK, false); else FD_LAUNCH(LSV2_MODE_QUICK, true);
-    } else {
-        if (out_dtype == 0) FD_LAUNCH(LSV2_MODE_DENSE, false); else FD_LAUNCH(LSV2_MODE_DENSE, true);
-    }
+    if (out_dtype == 0) FD_LAUNCH(false); else FD_LAUNCH(true);
 #undef FD_LAUNCH
     LSV2_LAUNCH_CHECK("k_render_decode");
     return LSV2_OK;
@@ -974,14 +1004,9 @@ int launch_render_wmap_tc(const lsv2_view& v, const lsv2_geom& g, const lsv2_bin
     fd_fill_args(a, v, g, b, f, img, gx, gy);
     a.tile_counter = counter;
     const int grid = min(NUM_SMS, a.n_units);
-#define FD_LAUNCH(M)                                                                                                   \
-    do {                                                                                                               \
-        LSV2_CUDA_TRY(cudaFuncSetAttribute(k_render_decode<M, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                           (int)FD_SMEM_NODECODE_TOTAL));                                              \
-        k_render_decode<M, false, false><<<grid, FD_THREADS_NODECODE, FD_SMEM_NODECODE_TOTAL, st>>>(a);          \
-    } while (0)
-    if (f.mode == LSV2_MODE_QUICK) FD_LAUNCH(LSV2_MODE_QUICK); else FD_LAUNCH(LSV2_MODE_DENSE);
-#undef FD_LAUNCH
+    LSV2_CUDA_TRY(cudaFuncSetAttribute(k_render_decode<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)FD_SMEM_NODECODE_TOTAL));
+    k_render_decode<false, false><<<grid, FD_THREADS_NODECODE, FD_SMEM_NODECODE_TOTAL, st>>>(a);
     LSV2_LAUNCH_CHECK("k_render_decode<wmap>");
     return LSV2_OK;
 }

@@ -20,7 +20,7 @@ import torch.nn as nn
 
 from . import _abi
 from ._abi import (Binning, Features, Geom, Image, Scene, View, MODE_DENSE, MODE_QUICK, MODE_RGB,
-                   SPARSE_CAP, STATUS_BAD_INDEX, STATUS_NUM_RENDERED, STATUS_OVERFLOW, STATUS_WORDS, TILE)
+                   PACKED_WORDS, SPARSE_CAP, STATUS_BAD_INDEX, STATUS_NUM_RENDERED, STATUS_OVERFLOW, STATUS_WORDS, TILE)
 
 #: strict per-channel gradient for ``language_feature_precomp`` (every channel of every touched
 #: Gaussian) instead of the support-only gradient (channels whose coefficient is non-zero).
@@ -90,7 +90,21 @@ class FrameState:
         f = self.feat
         return Features(self.mode, self.L, self.K, _abi.ptr(f.get("coeff_dense")), _abi.ptr(f.get("weights_quick")),
                         _abi.ptr(f.get("indices_quick")), _abi.ptr(f.get("sparse_count")),
-                        _abi.ptr(f.get("sparse_index")), _abi.ptr(f.get("sparse_weight")))
+                        _abi.ptr(f.get("sparse_index")), _abi.ptr(f.get("sparse_weight")), _abi.ptr(f.get("packed")))
+
+    def ensure_packed(self, geom_c=None) -> None:
+        """The tensor-core blend reads the coefficients from the packed table of ``lsv2_pack_coeff`` (fp16 head /
+        remainder pairs + channel bytes).  Quick mode: depends on the coefficients only -- pass ``packed=`` to
+        ``rasterize_forward`` to reuse one across frames.  Dense mode: built from this frame's compacted rows."""
+        if "packed" in self.feat:
+            return
+        L_ = _abi.lib()
+        dev = self.status.device
+        self.feat["packed"] = torch.empty((self.P, PACKED_WORDS), dtype=torch.int32, device=dev)
+        geom_c = geom_c or self.c_geom()
+        feat_c = self.c_features()
+        _abi.check(L_.lsv2_pack_coeff(self.P, C.byref(geom_c), C.byref(feat_c), _abi.ptr(self.status),
+                                      _abi.stream_ptr(dev)), "lsv2_pack_coeff")
 
     def c_image(self) -> Image:
         i = self.image
@@ -132,7 +146,7 @@ def rasterize_forward(rs: GaussianRasterizationSettings, means3D, opacities, shs
                       scales=None, rotations=None, cov3D_precomp=None, language_feature_precomp=None,
                       language_feature_weights_quick=None, language_feature_indices=None,
                       capacity: Optional[int] = None, debug_buffers: bool = False,
-                      render: bool = True, blend: str = "auto") -> FrameState:
+                      render: bool = True, blend: str = "auto", packed: Optional[torch.Tensor] = None) -> FrameState:
     """Preprocess -> bin -> blend.  ``capacity=None`` reads the instance count back between the two
     halves (one host sync, as the reference does); an integer capacity runs the whole frame with no
     host involvement and flags overflow in ``state.status``.
@@ -190,6 +204,10 @@ def rasterize_forward(rs: GaussianRasterizationSettings, means3D, opacities, shs
         # callers hard-wire 3 levels x 64 codes (eval_lerf.py:215); tolerate other level counts
         L = int(getattr(rs, "quick_channels", 0) or QUICK_CHANNELS)
 
+    if packed is not None and mode == MODE_QUICK:
+        if packed.shape != (P, PACKED_WORDS) or packed.dtype != torch.int32 or not packed.is_contiguous():
+            raise ValueError("packed must be the [P, 24] int32 table of a previous frame's state.feat['packed']")
+        feat["packed"] = packed
     st = FrameState(P=P, H=H, W=W, mode=mode, L=L, K=K)
     st.feat = feat
     st.view = _make_view(rs, dev, st.keep)
@@ -246,6 +264,8 @@ def rasterize_forward(rs: GaussianRasterizationSettings, means3D, opacities, shs
         if mode == MODE_DENSE:
             _abi.check(L_.lsv2_compact_coeff(P, C.byref(geom_c), C.byref(feat_c), stream), "lsv2_compact_coeff")
         if use_tc:
+            st.ensure_packed(geom_c)
+            feat_c = st.c_features()
             _abi.check(L_.lsv2_render_forward_tc(C.byref(st.view), C.byref(geom_c), C.byref(bin_c), C.byref(feat_c),
                                                  C.byref(img_c), stream), "lsv2_render_forward_tc")
         else:
@@ -308,6 +328,8 @@ def render_decode(st: FrameState, codebooks: torch.Tensor, normalize: bool = Tru
     if st.mode == MODE_DENSE:
         _abi.check(L_.lsv2_compact_coeff(st.P, C.byref(geom_c), C.byref(feat_c), _abi.stream_ptr(dev)),
                    "lsv2_compact_coeff")
+    st.ensure_packed(geom_c)
+    feat_c = st.c_features()
     _abi.check(L_.lsv2_render_decode(C.byref(st.view), C.byref(geom_c), C.byref(bin_c), C.byref(feat_c),
                                      C.byref(img_c), cb.data_ptr(), levels, Lc, D, 1 if normalize else 0,
                                      0 if out_dtype == torch.float32 else 1, out.data_ptr(), scratch.data_ptr(),

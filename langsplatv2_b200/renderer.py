@@ -57,6 +57,7 @@ class FeatureRenderer:
         self.capacity: Optional[int] = None
         self.bg = torch.zeros(3, dtype=torch.float32, device=dev)
         self.last_state: Optional[FrameState] = None
+        self.packed: Optional[torch.Tensor] = None     # lsv2_pack_coeff table: depends on the weights only, built once
         self.hook = None                        # optional callable(tag) for event timing in bench.py
 
     def settings(self, cam: Dict) -> GaussianRasterizationSettings:
@@ -80,7 +81,8 @@ class FeatureRenderer:
         return rasterize_forward(self.settings(cam), self.xyz, self.opacity, shs=self.features,
                                  scales=self.scaling, rotations=self.rotation,
                                  language_feature_weights_quick=self.weights,
-                                 language_feature_indices=self.indices, capacity=capacity, render=render)
+                                 language_feature_indices=self.indices, capacity=capacity, render=render,
+                                 packed=self.packed)
 
     @torch.no_grad()
     def render(self, cam: Dict) -> torch.Tensor:
@@ -96,9 +98,11 @@ class FeatureRenderer:
             out = render_decode(st, self.codebooks, normalize=True, out_dtype=self.out_dtype)
             if self.hook:
                 self.hook("decode_end")
+            self.packed = st.feat.get("packed")
             return out
         st = self._raster(cam, cap)
         self.last_state = st
+        self.packed = st.feat.get("packed", self.packed)
         if self.hook:
             self.hook("decode_begin")
         out = decode_feature_map(st.image["wmap"], self.codebooks, normalize=True, precision=self.precision,
