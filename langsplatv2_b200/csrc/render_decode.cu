@@ -435,84 +435,95 @@ __global__ void __launch_bounds__(DECODE ? FD_THREADS : FD_THREADS_NODECODE, 1) 
         if (ptid == 0) FD_PROF_FLUSH(1);
     } else if (warp == FD_WARP_MB) {
         // ======================================= blend MMA issue =======================================
-        if (lane == 0) {
-            const uint32_t idesc_blend = umma_idesc_f16_f32(128, L);
-            const uint32_t ring_addr = smem_u32(ring);
-            uint32_t batch_in_unit = 0;
-            uint32_t a_uses[FD_STAGES] = {0, 0};             // a_full phases consumed
-            for (uint32_t use_g = 0;; ++use_g) {
-                const int s = use_g & 1;
-                mbar_wait_sleep(full + s, (use_g >> 1) & 1);
-                const int count = hdrs[s].count;
-                mbar_wait(a_full + s, a_uses[s] & 1);        // batches: A tiles written; terminators: header read by all
-                ++a_uses[s];
-                if (count == -2) break;
-                if (count >= 0) {
-                    tc_fence_after();
+        // The whole warp runs the loop converged; one elected lane issues (see elect_one, tc_common.cuh).
+        const uint32_t idesc_blend = umma_idesc_f16_f32(128, L);
+        const uint32_t ring_addr = bcast0(smem_u32(ring));
+        const uint32_t tmem_u = bcast0(tmem);
+        uint32_t batch_in_unit = 0;
+#pragma unroll 1
+        for (uint32_t use_g = 0;; ++use_g) {
+            const int s = use_g & 1;
+            const uint32_t par = (use_g >> 1) & 1;
+            mbar_wait_sleep(full + s, par);
+            const int count = (int)bcast0((uint32_t)hdrs[s].count);
+            mbar_wait(a_full + s, par);                  // batches: A tiles written; terminators: header read by all
+            if (count == -2) break;
+            if (count >= 0) {
+                tc_fence_after();
+                if (elect_one()) {
                     const uint32_t sa = ring_addr + (uint32_t)s * FD_STAGE_BYTES;
+                    const uint64_t dA = umma_desc_k_sw64(sa), dS = umma_desc_k_sw64(sa + 2 * FD_AHALF_BYTES);
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
-                        const uint32_t sA = sa + (uint32_t)h * FD_AHALF_BYTES;
-                        const uint32_t sS = sa + 2 * FD_AHALF_BYTES + (uint32_t)h * FD_S_BYTES;
-                        const uint32_t d = tmem + (uint32_t)(h * FD_MAX_L);
-                        umma_bf16(d, umma_desc_k_sw64(sA), umma_desc_k_sw64(sS), idesc_blend, batch_in_unit > 0 ? 1u : 0u);
-                        umma_bf16(d, umma_desc_k_sw64(sA + 32), umma_desc_k_sw64(sS), idesc_blend, 1u);
-                        umma_bf16(d, umma_desc_k_sw64(sA), umma_desc_k_sw64(sS + 32), idesc_blend, 1u);
+                        const uint64_t a0 = dA + (uint64_t)(h * (FD_AHALF_BYTES >> 4)), s0 = dS + (uint64_t)(h * (FD_S_BYTES >> 4));
+                        const uint32_t d = tmem_u + (uint32_t)(h * FD_MAX_L);
+                        umma_bf16(d, a0, s0, idesc_blend, batch_in_unit > 0 ? 1u : 0u);
+                        umma_bf16(d, a0 + 2, s0, idesc_blend, 1u);
+                        umma_bf16(d, a0, s0 + 2, idesc_blend, 1u);
                     }
                     umma_commit(stage_free + s);
-                    ++batch_in_unit;
-                    continue;
                 }
-                // ---- end of unit ----
+                __syncwarp();
+                ++batch_in_unit;
+                continue;
+            }
+            // ---- end of unit ----
+            if (elect_one()) {
                 mbar_arrive(stage_free + s);
                 if (batch_in_unit > 0) umma_commit(w_full); else mbar_arrive(w_full);
-                batch_in_unit = 0;
             }
+            __syncwarp();
+            batch_in_unit = 0;
         }
     } else if (DECODE && warp == FD_WARP_MD) {
         // ================================ Gram + decode MMA issue, codebook fetch ================================
-        if (lane == 0) {
-            constexpr uint32_t idesc_u = umma_idesc_f16_f32(128, FD_LC);
-            constexpr uint32_t idesc_dec = umma_idesc_f16_f32(128, FD_NFEAT);
-            // operand descriptors are built once; a k-step (32 bytes) or a row block only adds to the address field
-            const uint64_t desc_w0 = umma_desc_k_sw128(smem_u32(wdec)), desc_cb0 = umma_desc_k_sw128(smem_u32(s_cb));
-            auto desc_w = [&](int l, int m) { return desc_w0 + (uint64_t)(l * (FD_WDEC_LEVEL >> 4) + m * ((128 * 128) >> 4)); };
-            auto desc_cb = [&](int slot) { return desc_cb0 + (uint64_t)(slot * (FD_CB_BYTES >> 4)); };
-            const int n_g = normalize ? levels : 0;
-            const int jobs_per_unit = n_g + levels * FD_CHUNKS;
-            uint32_t cb_issued = 0, cb_used = 0, f_n = 0;
-            FD_PROF_DECL
-            FD_TIC();
-            auto fetch_next = [&]() {                        // codebook-ring job `cb_issued` -> slot cb_issued & 1
-                const int slot = (int)(cb_issued & 1u);
-                if (cb_issued >= FD_CB_SLOTS) mbar_wait(cb_free + slot, ((cb_issued >> 1) - 1) & 1);
-                const int j = (int)(cb_issued % (uint32_t)jobs_per_unit);
-                const uint8_t* src = j < n_g ? a.gimg + (size_t)j * FD_CB_BYTES : a.bimg + (size_t)(j - n_g) * FD_CB_BYTES;
+        // Converged warp, one elected lane issues.
+        constexpr uint32_t idesc_u = umma_idesc_f16_f32(128, FD_LC);
+        constexpr uint32_t idesc_dec = umma_idesc_f16_f32(128, FD_NFEAT);
+        const uint32_t tmem_u = bcast0(tmem);
+        // operand descriptors are built once; a k-step (32 bytes) or a row block only adds to the address field
+        const uint64_t desc_w0 = umma_desc_k_sw128(bcast0(smem_u32(wdec))), desc_cb0 = umma_desc_k_sw128(bcast0(smem_u32(s_cb)));
+        const int n_g = normalize ? levels : 0;
+        const int jobs_per_unit = n_g + levels * FD_CHUNKS;
+        uint32_t cb_issued = 0, cb_used = 0, f_n = 0;
+        FD_PROF_DECL
+        FD_TIC();
+        auto fetch_next = [&]() {                        // codebook-ring job `cb_issued` -> slot cb_issued & 1
+            const int slot = (int)(cb_issued & 1u);
+            if (cb_issued >= FD_CB_SLOTS) mbar_wait(cb_free + slot, ((cb_issued >> 1) - 1) & 1);
+            const int j = (int)(cb_issued % (uint32_t)jobs_per_unit);
+            const uint8_t* src = j < n_g ? a.gimg + (size_t)j * FD_CB_BYTES : a.bimg + (size_t)(j - n_g) * FD_CB_BYTES;
+            if (elect_one()) {
                 mbar_arrive_expect_tx(cb_full + slot, FD_CB_BYTES);
                 bulk_g2s(s_cb + (size_t)slot * FD_CB_BYTES, src, FD_CB_BYTES, cb_full + slot);
-                ++cb_issued;
-            };
-            fetch_next();
-            fetch_next();
-            for (uint32_t it = 0;; ++it) {
-                bool stop = false;
-                for (int l = 0; l < levels; ++l) {
-                    // rows of level l are in shared memory (all levels are needed before the decode starts anyway;
-                    // the per-level barrier lets the Gram products start while later levels are still converted)
-                    FD_TOC(3);
-                    mbar_wait_sleep(wraw_full + l, it & 1);
-                    FD_TOC(0);
-                    if (l == 0 && tinfo[it & 1].unit < 0) { stop = true; break; }
-                    if (!normalize) continue;
-                    tc_fence_after();
-                    const uint32_t n = cb_used;
-                    const int slot = (int)(n & 1u);
-                    mbar_wait(cb_full + slot, (n >> 1) & 1);
-                    const uint64_t g_hi = desc_cb(slot), g_lo = g_hi + (uint64_t)((64 * 128) >> 4);
+            }
+            __syncwarp();
+            ++cb_issued;
+        };
+        fetch_next();
+        fetch_next();
 #pragma unroll 1
+        for (uint32_t it = 0;; ++it) {
+            bool stop = false;
+#pragma unroll 1
+            for (int l = 0; l < levels; ++l) {
+                // rows of level l are in shared memory (all levels are needed before the decode starts anyway;
+                // the per-level barrier lets the Gram products start while later levels are still converted)
+                FD_TOC(3);
+                mbar_wait_sleep(wraw_full + l, it & 1);
+                FD_TOC(0);
+                if (l == 0 && (int)bcast0((uint32_t)tinfo[it & 1].unit) < 0) { stop = true; break; }
+                if (!normalize) continue;
+                tc_fence_after();
+                const uint32_t n = cb_used;
+                const int slot = (int)(n & 1u);
+                mbar_wait(cb_full + slot, (n >> 1) & 1);
+                if (elect_one()) {
+                    const uint64_t g_hi = desc_cb0 + (uint64_t)(slot * (FD_CB_BYTES >> 4)), g_lo = g_hi + (uint64_t)((64 * 128) >> 4);
+#pragma unroll
                     for (int m = 0; m < 2; ++m) {
-                        const uint32_t d = tmem + (uint32_t)(m * FD_MAX_L + l * FD_LC);
-                        const uint64_t da = desc_w(l, m);
+                        const uint32_t d = tmem_u + (uint32_t)(m * FD_MAX_L + l * FD_LC);
+                        const uint64_t da = desc_w0 + (uint64_t)(l * (FD_WDEC_LEVEL >> 4) + m * ((128 * 128) >> 4));
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks)
                             umma_bf16(d, da + (uint64_t)(2 * ks), g_hi + (uint64_t)(2 * ks), idesc_u, ks > 0 ? 1u : 0u);
@@ -522,50 +533,54 @@ __global__ void __launch_bounds__(DECODE ? FD_THREADS : FD_THREADS_NODECODE, 1) 
                     }
                     umma_commit(u_full + l);
                     umma_commit(cb_free + slot);
-                    ++cb_used;
-                    if (n >= 1) fetch_next();
                 }
-                if (stop) break;
-                tc_fence_after();
-#pragma unroll 1
-                for (int l = 0; l < levels; ++l) {
-#pragma unroll 1
-                    for (int c = 0; c < FD_CHUNKS; ++c) {
-                        const uint32_t n = cb_used;
-                        const int slot = (int)(n & 1u);
-                        FD_TOC(3);
-                        mbar_wait(cb_full + slot, (n >> 1) & 1);
-                        FD_TOC(1);
-#pragma unroll 1
-                        for (int g = 0; g < FD_FGROUPS; ++g) {
-                            const uint64_t db = desc_cb(slot) + (uint64_t)(g * ((FD_NFEAT * 128) >> 4));
-#pragma unroll 1
-                            for (int m = 0; m < 2; ++m) {
-                                const int fs = (int)(f_n % FD_FSLOTS);
-                                FD_TOC(3);
-                                if (f_n >= FD_FSLOTS) mbar_wait(f_free + fs, ((f_n / FD_FSLOTS) - 1) & 1);
-                                FD_TOC(2);
-                                tc_fence_after();
-                                const uint32_t d = tmem + (uint32_t)(FD_TMEM_F + fs * FD_NFEAT);
-                                const uint64_t da = desc_w(l, m);
-#pragma unroll
-                                for (int ks = 0; ks < 4; ++ks)
-                                    umma_bf16(d, da + (uint64_t)(2 * ks), db + (uint64_t)(2 * ks), idesc_dec, ks > 0 ? 1u : 0u);
-                                umma_commit(f_full + fs);
-                                ++f_n;
-                            }
-                            if (g == 0 && n >= 1) fetch_next();
-                        }
-                        umma_commit(cb_free + slot);
-                        ++cb_used;
-                    }
-                }
-                umma_commit(dec_done);
+                __syncwarp();
+                ++cb_used;
+                if (n >= 1) fetch_next();
             }
-            FD_PROF_FLUSH(2);
-            // drain the codebook prefetch that no unit consumed
-            while (cb_used < cb_issued) { mbar_wait(cb_full + (cb_used & 1u), (cb_used >> 1) & 1); ++cb_used; }
+            if (stop) break;
+            tc_fence_after();
+#pragma unroll 1
+            for (int l = 0; l < levels; ++l) {
+#pragma unroll 1
+                for (int c = 0; c < FD_CHUNKS; ++c) {
+                    const uint32_t n = cb_used;
+                    const int slot = (int)(n & 1u);
+                    FD_TOC(3);
+                    mbar_wait(cb_full + slot, (n >> 1) & 1);
+                    FD_TOC(1);
+#pragma unroll 1
+                    for (int gm = 0; gm < 2 * FD_FGROUPS; ++gm) {
+                        const int g = gm >> 1, m = gm & 1;
+                        const int fs = (int)(f_n % FD_FSLOTS);
+                        FD_TOC(3);
+                        if (f_n >= FD_FSLOTS) mbar_wait(f_free + fs, ((f_n / FD_FSLOTS) - 1) & 1);
+                        FD_TOC(2);
+                        tc_fence_after();
+                        if (elect_one()) {
+                            const uint64_t db = desc_cb0 + (uint64_t)(slot * (FD_CB_BYTES >> 4) + g * ((FD_NFEAT * 128) >> 4));
+                            const uint64_t da = desc_w0 + (uint64_t)(l * (FD_WDEC_LEVEL >> 4) + m * ((128 * 128) >> 4));
+                            const uint32_t d = tmem_u + (uint32_t)(FD_TMEM_F + fs * FD_NFEAT);
+#pragma unroll
+                            for (int ks = 0; ks < 4; ++ks)
+                                umma_bf16(d, da + (uint64_t)(2 * ks), db + (uint64_t)(2 * ks), idesc_dec, ks > 0 ? 1u : 0u);
+                            umma_commit(f_full + fs);
+                        }
+                        __syncwarp();
+                        ++f_n;
+                        if (gm == 1 && n >= 1) fetch_next();
+                    }
+                    if (elect_one()) umma_commit(cb_free + slot);
+                    __syncwarp();
+                    ++cb_used;
+                }
+            }
+            if (elect_one()) umma_commit(dec_done);
+            __syncwarp();
         }
+        if (lane == 0) FD_PROF_FLUSH(2);
+        // drain the codebook prefetch that no unit consumed
+        while (cb_used < cb_issued) { mbar_wait(cb_full + (cb_used & 1u), (cb_used >> 1) & 1); ++cb_used; }
     } else if (DECODE && warp >= FD_BLEND_WARPS && warp < FD_BLEND_WARPS + FD_EPI_WARPS) {
         // ==================================== epilogue: F slots -> global ====================================
         // Decode MMA block m covers band rows 4m .. 4m+3; TMEM lane quadrant q = this warp = band row 4m + q,

@@ -86,6 +86,19 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, u
                  : "memory");
 }
 
+// One lane of a converged warp (elect.sync): the issuing lane of tcgen05.mma / commit / bulk copies.  Keeping the
+// surrounding loop converged (all 32 lanes run it, only the issue is predicated) lets ptxas hold descriptors and
+// barrier addresses in uniform registers; under `if (lane == 0)` every UTCHMMA is wrapped in an
+// ELECT / R2UR.BROADCAST / BRA.U.ANY waterfall loop.
+__device__ __forceinline__ bool elect_one()
+{
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
+// value of lane 0, known warp-uniform to the compiler
+__device__ __forceinline__ uint32_t bcast0(uint32_t v) { return __shfl_sync(0xffffffffu, v, 0); }
+
 // ---- TMEM -------------------------------------------------------------------------------
 __device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols)   // one full warp
 {
