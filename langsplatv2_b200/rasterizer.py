@@ -22,11 +22,12 @@ from . import _abi
 from ._abi import (Binning, Features, Geom, Image, Scene, View, MODE_DENSE, MODE_QUICK, MODE_RGB,
                    PACKED_WORDS, SPARSE_CAP, STATUS_BAD_INDEX, STATUS_NUM_RENDERED, STATUS_OVERFLOW, STATUS_WORDS, TILE)
 
-#: strict per-channel gradient for ``language_feature_precomp`` (every channel of every touched
-#: Gaussian) instead of the support-only gradient (channels whose coefficient is non-zero).
-#: The two agree end to end because the reference masks non-top-k channels with ``torch.where``
-#: (utils/vq_utils.py:20); strict mode exists for parity tests at the operator boundary.
-DENSE_COEFF_GRAD = False
+#: Gradient of ``language_feature_precomp`` at the operator boundary: strict (every channel of every touched
+#: Gaussian, what the reference op returns) by default.  The support-only form (channels whose coefficient is
+#: non-zero) is exact only when the caller masks the non-top-k channels afterwards, as the reference's
+#: ``torch.where`` does (utils/vq_utils.py:20); ``FeatureTrainer`` opts into it per rasterizer
+#: (``GaussianRasterizer.dense_coeff_grad = False``).
+DENSE_COEFF_GRAD = True
 
 
 class GaussianRasterizationSettings(NamedTuple):
@@ -73,6 +74,14 @@ class FrameState:
     @property
     def overflowed(self) -> bool:
         return bool(self.status[STATUS_OVERFLOW].item())
+
+    def for_backward(self) -> "FrameState":
+        """Shallow copy without the forward's output tensors (see _RasterizeGaussians.forward)."""
+        b = FrameState(P=self.P, H=self.H, W=self.W, mode=self.mode, L=self.L, K=self.K, view=self.view,
+                       geom=self.geom, binning=self.binning, feat=self.feat, status=self.status,
+                       capacity=self.capacity, keep=self.keep)
+        b.image = {k: v for k, v in self.image.items() if k in ("final_T", "n_contrib")}
+        return b
 
     def c_geom(self) -> Geom:
         g = self.geom
@@ -158,6 +167,15 @@ def rasterize_forward(rs: GaussianRasterizationSettings, means3D, opacities, shs
     L_ = _abi.lib()
     dev = means3D.device
     _abi.require_cuda(means3D, "means3D")
+    if torch.cuda.current_device() != dev.index:
+        # liblsv2 launches on the CURRENT device: make it the tensors' device for the duration of the call
+        with _abi.device_guard(dev):
+            return rasterize_forward(rs, means3D, opacities, shs=shs, colors_precomp=colors_precomp, scales=scales,
+                                     rotations=rotations, cov3D_precomp=cov3D_precomp,
+                                     language_feature_precomp=language_feature_precomp,
+                                     language_feature_weights_quick=language_feature_weights_quick,
+                                     language_feature_indices=language_feature_indices, capacity=capacity,
+                                     debug_buffers=debug_buffers, render=render, blend=blend, packed=packed)
     P = int(means3D.shape[0])
     H, W = int(rs.image_height), int(rs.image_width)
     mode = feature_mode(rs)
@@ -292,12 +310,41 @@ def rasterize_forward(rs: GaussianRasterizationSettings, means3D, opacities, shs
         if render:
             run_blend(geom_c, bin_c)
     if rs.debug:
-        torch.cuda.synchronize(dev)
-        if st.overflowed:
-            raise _abi.Lsv2Error(f"instance capacity {st.capacity} too small for {st.num_rendered} instances")
-        if mode == MODE_QUICK and int(st.status[STATUS_BAD_INDEX].item()):
-            raise _abi.Lsv2Error(f"language_feature_indices outside [0, {L})")
+        # the reference's debug mode: synchronise after the launches, and on failure dump the inputs before
+        # re-raising (snapshot_fw.dump, [LINEAGE] diff_gaussian_rasterization/__init__.py)
+        try:
+            torch.cuda.synchronize(dev)
+            if st.overflowed:
+                raise _abi.Lsv2Error(f"instance capacity {st.capacity} too small for {st.num_rendered} instances")
+            if mode == MODE_QUICK and int(st.status[STATUS_BAD_INDEX].item()):
+                raise _abi.Lsv2Error(f"language_feature_indices outside [0, {L})")
+        except Exception:
+            _dump_snapshot("snapshot_fw.dump", dict(
+                raster_settings=rs._asdict(), means3D=means3D, opacities=opacities, shs=shs,
+                colors_precomp=colors_precomp, scales=scales, rotations=rotations, cov3D_precomp=cov3D_precomp,
+                language_feature_precomp=language_feature_precomp,
+                language_feature_weights_quick=language_feature_weights_quick,
+                language_feature_indices=language_feature_indices))
+            raise
     return st
+
+
+def _dump_snapshot(path: str, items: dict) -> None:
+    """torch.save of the op's inputs (CPU copies), as the reference's debug mode does before re-raising."""
+    def cpu(v):
+        if torch.is_tensor(v):
+            try:
+                return v.detach().cpu()
+            except Exception:
+                return None
+        if isinstance(v, dict):
+            return {k: cpu(x) for k, x in v.items()}
+        return v
+    try:
+        torch.save({k: cpu(v) for k, v in items.items()}, path)
+        print(f"\nAn error occured in the rasterizer. Writing {path} for debugging.")
+    except Exception:
+        pass
 
 
 def render_decode(st: FrameState, codebooks: torch.Tensor, normalize: bool = True,
@@ -364,16 +411,24 @@ def rasterize_backward(st: FrameState, grad_wmap: Optional[torch.Tensor], grad_c
 
 
 class _RasterizeGaussians(torch.autograd.Function):
+    last_state = None          # side channel forward -> GaussianRasterizer.forward (never referenced from ctx)
+
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, language_feature_precomp, weights_quick, indices_quick,
-                opacities, scales, rotations, cov3Ds_precomp, raster_settings, capacity=None):
+                opacities, scales, rotations, cov3Ds_precomp, raster_settings, capacity=None, dense_coeff_grad=None):
         st = rasterize_forward(raster_settings, means3D, opacities, shs=sh, colors_precomp=colors_precomp,
                                scales=scales, rotations=rotations, cov3D_precomp=cov3Ds_precomp,
                                language_feature_precomp=language_feature_precomp,
                                language_feature_weights_quick=weights_quick, language_feature_indices=indices_quick,
                                capacity=capacity)
-        ctx.state = st
+        # what backward needs, WITHOUT the forward's outputs: a state holding `color` / `wmap` on ctx closes the cycle
+        # output -> grad_fn -> ctx -> state -> output through C++ shared_ptrs, which Python's GC cannot collect --
+        # every grad-enabled forward would leak its whole frame
+        ctx.state = st.for_backward()
         ctx.color_is_precomp = colors_precomp is not None
+        ctx.dense_grad = dense_coeff_grad
+        ctx.debug = bool(raster_settings.debug)
+        _RasterizeGaussians.last_state = st
         H, W = st.H, st.W
         wmap = st.image.get("wmap")
         if wmap is None:
@@ -385,6 +440,10 @@ class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def backward(ctx, grad_color, grad_wmap, _grad_radii):
         st = ctx.state
+        ctx.state = None                     # one backward per forward; drop the frame buffers now
+        if st is None:
+            raise RuntimeError("the rasterizer's backward ran twice (retain_graph is not supported: the frame "
+                               "buffers are released after the first pass)")
         need = ctx.needs_input_grad
         # inputs: 0 means3D, 1 means2D, 2 sh, 3 colors_precomp, 4 language_feature_precomp, 5 weights_quick,
         #         6 indices_quick, 7 opacities, 8 scales, 9 rotations, 10 cov3Ds_precomp, 11 settings
@@ -395,10 +454,18 @@ class _RasterizeGaussians(torch.autograd.Function):
         d_coeff = d_colors = None
         if st.mode == MODE_DENSE and need[4]:
             gc = grad_color if (need[3] and ctx.color_is_precomp) else None
-            d_coeff, d_colors = rasterize_backward(st, grad_wmap, gc)
+            try:
+                d_coeff, d_colors = rasterize_backward(st, grad_wmap, gc, dense_grad=ctx.dense_grad)
+                if ctx.debug:
+                    torch.cuda.synchronize(grad_wmap.device)
+            except Exception:
+                if ctx.debug:
+                    _dump_snapshot("snapshot_bw.dump", dict(grad_color=grad_color, grad_wmap=grad_wmap,
+                                                            radii=st.geom.get("radii"), num_rendered=st.capacity))
+                raise
         elif need[3]:
             raise NotImplementedError("colour gradients are produced together with the feature backward only")
-        return (None, None, None, d_colors, d_coeff, None, None, None, None, None, None, None, None)
+        return (None, None, None, d_colors, d_coeff, None, None, None, None, None, None, None, None, None)
 
 
 class GaussianRasterizer(nn.Module):
@@ -411,6 +478,7 @@ class GaussianRasterizer(nn.Module):
         super().__init__()
         self.raster_settings = raster_settings
         self.capacity = capacity
+        self.dense_coeff_grad: Optional[bool] = None     # None: module default DENSE_COEFF_GRAD (strict)
         self.last_state: Optional[FrameState] = None
 
     def markVisible(self, positions: torch.Tensor) -> torch.Tensor:
@@ -434,7 +502,8 @@ class GaussianRasterizer(nn.Module):
             raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
         out = _RasterizeGaussians.apply(means3D, means2D, shs, colors_precomp, language_feature_precomp,
                                         language_feature_weights_quick, language_feature_indices, opacities,
-                                        scales, rotations, cov3D_precomp, rs, self.capacity)
-        fn = out[0].grad_fn
-        self.last_state = getattr(fn, "state", None) if fn is not None else None
+                                        scales, rotations, cov3D_precomp, rs, self.capacity, self.dense_coeff_grad)
+        # the full frame state (outputs included) lives on the module, outside the autograd graph
+        self.last_state = _RasterizeGaussians.last_state
+        _RasterizeGaussians.last_state = None
         return out

@@ -1,0 +1,152 @@
+"""Round-2 pieces around the hot path: the Adam kernel against torch.optim.Adam, the packed coefficient table, and
+the trainer's memory / capacity / CUDA-graph behaviour."""
+import gc
+import warnings
+
+import numpy as np
+import pytest
+import torch
+
+from langsplatv2_b200 import _abi
+from langsplatv2_b200.optim import FlatAdam
+from langsplatv2_b200.trainer import FeatureTrainer, synthetic_gt
+from tests import helpers as hp
+
+pytestmark = pytest.mark.gpu
+
+
+def test_adam_kernel_matches_torch_adam():
+    """lsv2_adam_step vs torch.optim.Adam(lr, eps=1e-15) -- the reference's optimizer (scene/gaussian_model.py:255) --
+    over 25 steps with sparse gradients (rows that are zero for a while, as the logits of unseen Gaussians are).
+    Stated tolerance: 2e-6 relative to max|p| per step count (same operation order; torch contracts a*b+c)."""
+    g = torch.Generator(device="cuda").manual_seed(5)
+    n = 64 * 1003 + 3                                   # not a multiple of 4: exercises the tail
+    p0 = torch.randn(n, generator=g, device="cuda")
+    flat_p = torch.zeros(n + 1, device="cuda")[:n]      # offset view would break 16-byte alignment: keep base aligned
+    flat_p = p0.clone()
+    flat_g = torch.zeros_like(flat_p)
+    opt = FlatAdam(flat_p, flat_g, lr=0.0025, eps=1e-15)
+    ref_p = torch.nn.Parameter(p0.clone())
+    ref = torch.optim.Adam([ref_p], lr=0.0025, eps=1e-15, foreach=False, fused=False)
+    for step in range(25):
+        grad = torch.randn(n, generator=g, device="cuda") * (torch.rand(n, generator=g, device="cuda") < 0.3)
+        if step < 5:
+            grad[: n // 2] = 0.0                         # untouched rows: m = v = g = 0 -> skipped groups
+        flat_g.copy_(grad)
+        ref_p.grad = grad.clone()
+        opt.begin_step()
+        opt.step_range(0, n, zero_grad=(step % 2 == 0))
+        ref.step()
+        if step % 2 == 0:
+            assert float(flat_g.abs().max()) == 0.0      # cleared in the same pass
+        err = float((flat_p - ref_p.detach()).abs().max())
+        assert err <= 2e-6 * float(ref_p.detach().abs().max()), (step, err)
+    st = ref.state[ref_p]
+    assert float((opt.m - st["exp_avg"]).abs().max()) <= 1e-6 * float(st["exp_avg"].abs().max())
+    assert float((opt.v - st["exp_avg_sq"]).abs().max()) <= 1e-6 * float(st["exp_avg_sq"].abs().max())
+
+
+def test_adam_range_steps_equal_one_full_step():
+    g = torch.Generator(device="cuda").manual_seed(6)
+    n = 4096 * 5
+    p = torch.randn(n, generator=g, device="cuda")
+    grad = torch.randn(n, generator=g, device="cuda")
+    a = FlatAdam(p.clone(), grad.clone(), lr=0.01)
+    b = FlatAdam(p.clone(), grad.clone(), lr=0.01)
+    for _ in range(3):
+        a.begin_step(); a.step_range(0, n)
+        b.begin_step()
+        for lo in range(0, n, 4096):
+            b.step_range(lo, lo + 4096)
+    assert torch.equal(a.p, b.p) and torch.equal(a.m, b.m) and torch.equal(a.v, b.v)
+
+
+def test_packed_coefficient_table():
+    """lsv2_pack_coeff: fp16 head + remainder reproduce the fp32 weight to 2^-21, duplicates are merged, channels
+    outside [0, L) dropped and flagged."""
+    import ctypes as C
+    L_ = _abi.lib()
+    rng = np.random.default_rng(0)
+    P, K, Lch = 5000, 12, 192
+    w = rng.random((P, K), dtype=np.float32)
+    idx = np.stack([rng.choice(Lch, K, replace=False) for _ in range(P)]).astype(np.float32)
+    idx[::5, 3] = idx[::5, 0]                            # duplicate channel
+    idx[::7, 6] = 400.0                                  # out of range
+    wt, it = torch.tensor(w).cuda(), torch.tensor(idx).cuda()
+    packed = torch.empty((P, _abi.PACKED_WORDS), dtype=torch.int32, device="cuda")
+    status = torch.zeros(8, dtype=torch.int32, device="cuda")
+    feat = _abi.Features(_abi.MODE_QUICK, Lch, K, None, wt.data_ptr(), it.data_ptr(), None, None, None, packed.data_ptr())
+    geom = _abi.Geom(*([None] * 11))
+    _abi.check(L_.lsv2_pack_coeff(P, C.byref(geom), C.byref(feat), status.data_ptr(), _abi.stream_ptr()), "lsv2_pack_coeff")
+    pk = packed.cpu().numpy().view(np.uint32)
+    assert int(status[2]) == 1
+    for g in range(0, P, 97):
+        want = {}
+        for k in range(K):
+            c = int(idx[g, k])
+            if 0 <= c < Lch:
+                want[c] = want.get(c, np.float32(0)) + w[g, k]
+        n = int(pk[g, 20])
+        assert n == len(want)
+        got = {}
+        for e in range(n):
+            hi = np.array([pk[g, e] & 0xFFFF], np.uint16).view(np.float16)[0]
+            lo = np.array([pk[g, e] >> 16], np.uint16).view(np.float16)[0]
+            c = int((pk[g, 16 + (e >> 2)] >> (8 * (e & 3))) & 0xFF)
+            got[c] = np.float32(hi) + np.float32(lo)
+        assert set(got) == set(want)
+        for c in want:
+            assert abs(got[c] - want[c]) <= 2.0 ** -21 * max(1.0, abs(want[c])) + 6e-8
+
+
+def _small_trainer(**kw):
+    N, W, H = 20000, 160, 96
+    scene, cam = hp.make_case(N, W, H, seed=12, levels=1, scale_boost=2.5)
+    cam = {k: (v.cuda() if torch.is_tensor(v) else v) for k, v in cam.items()}
+    gt, mask = synthetic_gt(H, W, device="cuda")
+    return FeatureTrainer(scene, topk=4, layers=1, lr=0.05, **kw), cam, gt, mask
+
+
+def test_trainer_memory_is_flat_over_steps_and_unused_forwards():
+    """A grad-enabled forward must not pin its frame: no reference cycle through the autograd ctx."""
+    tr, cam, gt, mask = _small_trainer()
+    for _ in range(5):
+        tr.step(cam, gt, mask)
+    torch.cuda.synchronize(); gc.collect()
+    base = torch.cuda.memory_allocated()
+    for _ in range(20):
+        tr.step(cam, gt, mask)
+    torch.cuda.synchronize(); gc.collect()
+    assert torch.cuda.memory_allocated() - base <= 1 << 20
+    for _ in range(10):                                  # forwards that are never backpropagated
+        loss = tr.loss(cam, gt, mask)
+        del loss
+    tr._last_state = None
+    torch.cuda.synchronize(); gc.collect()
+    assert torch.cuda.memory_allocated() - base <= 1 << 20
+
+
+def test_trainer_overflow_is_sticky_and_capacity_grows():
+    tr, cam, gt, mask = _small_trainer(check_every=4)
+    for _ in range(4):
+        tr.step(cam, gt, mask)
+    assert tr.capacity is not None
+    tr.capacity = 1000                                   # far too small: every frame overflows
+    with warnings.catch_warnings(record=True) as w:
+        warnings.simplefilter("always")
+        for _ in range(4):
+            tr.step(cam, gt, mask)                       # iterations 5..8: the check at 8 sees the flag set at 5
+    assert tr.overflow_events == 1 and tr.capacity > 1000
+    assert any("capacity" in str(x.message) for x in w)
+
+
+def test_trainer_cuda_graph_replays_equal_eager_steps():
+    a, cam, gt, mask = _small_trainer()
+    b, _, _, _ = _small_trainer(use_graph=True)
+    la, lb = [], []
+    for i in range(9):
+        la.append(float(a.step(cam, gt, mask, view_id=0)))
+        lb.append(float(b.step(cam, gt, mask, view_id=0)))
+    assert len(b._graphs) == 1                           # captured once (after calibration), replayed afterwards
+    np.testing.assert_allclose(la, lb, rtol=2e-5)
+    assert float((a.flat_p - b.flat_p).abs().max()) <= 2e-5 * float(a.flat_p.abs().max())
