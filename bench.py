@@ -7,11 +7,12 @@ at 1920x1080 (the configuration BASELINE.json's metric is quoted on); ``--worklo
 View-sharded across ranks (weak scaling: every rank renders --steps frames of its own views; no data-path
 collective).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload 1080p|c2|small]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload 1080p|c2|4k|small] [--gaussians N]
+    python bench.py --workload c1|c4 ...      # BASELINE.json configs 1 / 4: forward + backward iterations
 
 ``--impl reference`` times the reference's CPU implementation of the same path -- here the CPU restatement
 in oracle/ (the reference's rasterizer source is absent from the mounted scrape) -- on the
-host cores, on a bounded tile sample of the same frame.
+host cores, on a bounded tile sample of the same frame (the extrapolation factor is stated in the line).
 """
 from __future__ import annotations
 
@@ -37,10 +38,40 @@ UNIT = "frames/s"
 WORKLOADS = {
     "1080p": dict(N=1_000_000, W=1920, H=1080, name="1M synthetic Gaussians, 1920x1080, 3 levels x top-4 of 64, 512-d normalised fp32 feature map (quick render + decode)"),
     "c2": dict(N=1_000_000, W=1008, H=756, name="1M synthetic Gaussians, 1008x756, 3 levels x top-4 of 64, 512-d normalised fp32 feature map (quick render + decode)"),
+    "4k": dict(N=1_000_000, W=3840, H=2160, name="1M synthetic Gaussians, 3840x2160, 3 levels x top-4 of 64, 512-d normalised fp32 feature map (BASELINE.json config 5)"),
     "small": dict(N=100_000, W=640, H=360, name="100k synthetic Gaussians, 640x360, 3 levels (debug size)"),
+    # forward + backward workloads (one FeatureTrainer iteration per step)
+    "c1": dict(N=50_000, W=256, H=256, fwd_bwd=True, name="BASELINE.json config 1: 50k synthetic Gaussians, 256x256, top-4 of 64, 512-d decode, forward + backward + Adam"),
+    "c4": dict(N=4_000_000, W=1600, H=1066, fwd_bwd=True, name="BASELINE.json config 4: 4M synthetic Gaussians, 1600x1066, top-4 of 64, 512-d decode, forward + backward + Adam"),
 }
 VIEWS = 64
 LEVELS, CODES, D, TOPK = 3, 64, 512, 4
+
+
+def ncu_traffic(kernel_substr: str):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel, read at bench time from the
+    newest `ncu --set full` summary committed under profiles/ (profiles/summarize.py output) -- never a literal.
+    -> (bytes or None, "file: kernel line" or None)."""
+    import glob
+    import re
+    best = None
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "r0[2-9]*_ncu_*.txt"))):
+        name, rd, wr = None, None, None
+        for ln in open(path, errors="replace"):
+            if ln.startswith("## "):
+                if name and rd is not None and wr is not None and kernel_substr in name:
+                    best = (rd + wr, f"{os.path.basename(path)}: {name}")
+                name, rd, wr = ln[3:].strip(), None, None
+            m = re.match(r"\s*dram__bytes_(read|write)\.sum\s+([0-9.eE+-]+)\s+(\w+)", ln)
+            if m:
+                v = float(m.group(2)) * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(m.group(3), 1)
+                if m.group(1) == "read":
+                    rd = v
+                else:
+                    wr = v
+        if name and rd is not None and wr is not None and kernel_substr in name:
+            best = (rd + wr, f"{os.path.basename(path)}: {name}")
+    return best if best else (None, None)
 
 
 def peaks():
@@ -155,10 +186,24 @@ def cpu_frame_time(scene, cam, wl, budget_s: float):
     return est, sample, oracle.num_threads()
 
 
+def reference_cuda_rasterizer_status() -> str:
+    """the reference's own CUDA rasterizer would be timed here if a driver had installed it
+    under baseline/_ref (package diff_gaussian_rasterization with its compiled _C).  Its source is absent from the
+    scrape (.SUBMODULES.json: submodules/efficient-langsplat-rasterization missing), so there is nothing to install."""
+    d = os.path.join(ROOT, "baseline", "_ref", "diff_gaussian_rasterization")
+    if os.path.isdir(d) and any(f.startswith("_C") for f in os.listdir(d)):
+        return "present under baseline/_ref (not timed by this harness version)"
+    return "unavailable on this box: the submodule source is absent from the scrape, baseline/_ref holds no build of it"
+
+
 def run_reference(args, wl):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    # torchrun exports OMP_NUM_THREADS=1: the CPU arm is one process on rank 0 and takes every host core
+    os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
+    if wl.get("fwd_bwd"):
+        return run_reference_fwd_bwd(args, wl)
     scene, cams = make_inputs(wl)
     budget = max(5.0, min(40.0, 150.0 / max(args.steps + args.warmup, 1)))
     times, sample, threads = [], "", 1
@@ -171,10 +216,63 @@ def run_reference(args, wl):
     line = {"metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "reference",
-            "config": {"workload": wl["name"], "views": VIEWS, "note": "CPU restatement (oracle/) on host cores; the reference's CUDA rasterizer source is not in the scrape"},
+            "config": {"workload": wl["name"], "views": VIEWS,
+                       "note": "CPU restatement (oracle/) on all host cores of rank 0; blend + decode timed on a tile sample and "
+                               "extrapolated linearly in the tile count (factor in cpu_baseline.sample)",
+                       "reference_cuda_rasterizer": reference_cuda_rasterizer_status()},
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def cpu_fwd_bwd_time(wl, reps: int = 1):
+    """BASELINE.json config 1 verbatim: the pure-PyTorch evaluation of the rasterizer math (oracle/torch_ref.py), forward
+    + backward of one training iteration (top-k soft code -> render -> decode -> normalise -> cos loss), in FULL (no
+    tile sampling), on the host cores.  -> seconds per iteration."""
+    from langsplatv2_b200 import synth
+    from oracle import torch_ref
+    scene = synth.make_scene(wl["N"], seed=0, levels=1, codebook_size=CODES, feat_dim=D, sh_degree=3)
+    cam = synth.ring_camera(0, VIEWS, wl["W"], wl["H"])
+    W, H = wl["W"], wl["H"]
+    g = torch.Generator().manual_seed(2)
+    table = torch.nn.functional.normalize(torch.randn(256, D, generator=g), dim=1)
+    ys, xs = torch.meshgrid(torch.arange(H), torch.arange(W), indexing="ij")
+    gt = table[(xs // 32 + 7 * (ys // 32)) % 256].permute(2, 0, 1).contiguous()
+    times = []
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        logits = scene["logits"][:, :CODES].clone().requires_grad_(True)
+        cb = scene["codebooks"][:1].clone().requires_grad_(True)
+        pre = torch_ref.preprocess(scene["xyz"], scene["opacity"], scene["scaling"], scene["rotation"],
+                                   cam["world_view_transform"], cam["full_proj_transform"], cam["camera_center"], W, H,
+                                   cam["tanfovx"], cam["tanfovy"], shs=scene["features"], sh_degree=3)
+        binned = torch_ref.bin_instances(pre, W, H)
+        dense = torch_ref.topk_soft_code(logits, TOPK)
+        out = torch_ref.render(pre, binned, W, H, torch.zeros(3), coeff=dense)
+        feat = torch_ref.decode(out["wmap"], cb, normalize=False)[0]
+        feat = feat / (feat.norm(dim=0, keepdim=True) + 1e-10)
+        loss = 1 - torch.nn.functional.cosine_similarity(feat, gt, dim=0).mean()
+        loss.backward()
+        times.append(time.perf_counter() - t0)
+    return float(np.mean(times)), torch.get_num_threads()
+
+
+def run_reference_fwd_bwd(args, wl):
+    steps = max(1, min(args.steps, 3))
+    if wl["N"] > 200_000:
+        line = {"impl": "reference", "unavailable": "the pure-PyTorch CPU evaluation is only run in full at BASELINE.json config 1 (50k, 256x256); "
+                                                     "at this size one iteration takes hours"}
+        print(json.dumps(line), flush=True)
+        return
+    sec, threads = cpu_fwd_bwd_time(wl, reps=steps)
+    val = 1.0 / sec
+    line = {"metric": "forward + backward iterations/s", "value": val, "unit": "iter/s", "n_gpus": args.gpus, "steps": steps,
+            "warmup": 0, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "impl": "reference",
+            "config": {"workload": wl["name"], "note": "oracle/torch_ref.py (pure PyTorch, CPU, autograd), whole frame, no sampling"},
+            "cpu_baseline": {"value": val, "unit": "iter/s", "cores": threads, "kind": "port", "sample": "full iteration, no sampling"},
+            "e2e": {"value": val, "unit": "iter/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line), flush=True)
 
 
@@ -188,7 +286,7 @@ def kernels_per_frame(W, H, fused: bool) -> int:
     # preprocess, scan | depth keys, histogram, 4 depth passes over the Gaussians, gather, scan | duplicate, tile
     # histogram, ranges, tile passes over the instances
     n = 1 + 1 + (1 + 1 + (31 + 7) // 8 + 1 + 1) + (1 + 1 + 1 + (tb + 7) // 8)
-    n += 2 if fused else 3                  # codebook prep + fused blend/decode | blend + codebook prep + decode
+    n += 3                                  # codebook image + Gram image + fused blend/decode | blend + codebook prep + decode
     return n
 
 
@@ -197,75 +295,90 @@ TRAIN_WL = dict(N=1_000_000, W=1008, H=756,
                      "(64 x 512), top-4, normalise + cos loss, Adam on logits [1M,64] + codebook")
 
 
-def run_train(args, dev, rank, world, scene, barrier):
+def _timed_iterations(tr, cams, gts, my_views, steps, dev, world, barrier, seg=False):
+    """`steps` iterations, one CUDA event per iteration on the launching stream -> per-iteration ms (max over ranks per
+    iteration at N > 1 is not available without a sync, so the run's total is the max over ranks and the
+    distribution is rank 0's)."""
+    barrier()
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+    evs[0].record()
+    loss = None
+    for s in range(steps):
+        v = my_views[s % len(my_views)]
+        if seg:
+            loss = tr.step(cams[v], gts[v], None, view_id=("seg", v))
+        else:
+            loss = tr.step(cams[v], *gts[v], view_id=v)
+        evs[s + 1].record()
+    barrier()
+    per = [evs[i].elapsed_time(evs[i + 1]) for i in range(steps)]
+    t = torch.tensor([evs[0].elapsed_time(evs[steps])], dtype=torch.float64, device=dev)
+    if world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item()), per, float(loss)
+
+
+def run_train(args, dev, rank, world, scene, barrier, wl=None):
     """Second half of the metric ("train iter/s"): one iteration = softmax/top-k -> render (include_feature) ->
-    decode -> normalise -> cos loss -> backward -> (N>1: one all-reduce of the flat grad bucket) -> Adam.
+    decode -> normalise -> cos loss -> backward -> (N>1: gradient exchange) -> Adam.
     Weak scaling: every rank renders its own view each iteration (the reference's --accum_iter N)."""
     from langsplatv2_b200 import synth
     from langsplatv2_b200.trainer import FeatureTrainer, synthetic_gt, synthetic_gt_segments
-    W, H = TRAIN_WL["W"], TRAIN_WL["H"]
-    steps = max(1, min(args.steps, args.train_steps))
+    wl = wl or TRAIN_WL
+    W, H = wl["W"], wl["H"]
+    steps = max(1, args.train_steps)
     cams = [synth.ring_camera(v, VIEWS, W, H) for v in range(VIEWS)]
     my_views = [v for v in range(VIEWS) if v % world == rank][:4]
     cams = {v: {k: (x.to(dev) if torch.is_tensor(x) else x) for k, x in cams[v].items()} for v in my_views}
     gts = {v: synthetic_gt(H, W, device=dev, seed=2 + v) for v in my_views}
-    tr = FeatureTrainer(scene, topk=TOPK, layers=1, device=dev)
-    loss = None
-    # the calibration iterations (host sync, exact capacity) + steady-state ones (more at N > 1: the first sliced
-    # all-reduces on a fresh box set up NCCL connections lazily)
-    n_warm = tr.calib_steps + (3 if world == 1 else 10)
-    for s in range(n_warm):
-        v = my_views[s % len(my_views)]
-        loss = tr.step(cams[v], *gts[v])
-    # K steps timed twice (max over ranks each time), the better run reported and both listed: at N > 1 a single
-    # host-side stall of one rank (~100 ms, seen once in a while on a fresh box) otherwise lands on all ranks' K steps
-    runs = []
-    for rep in range(2):
-        barrier()
-        t_b, t_e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        t_b.record()
-        for s in range(steps):
+    use_graph = world == 1 and not args.no_graph
+    tr = FeatureTrainer(scene, topk=TOPK, layers=1, device=dev, use_graph=use_graph)
+    tr.calibrate([cams[v] for v in my_views])          # exact instance counts of the views this rank trains on
+    n_warm = (2 * len(my_views) + 2) if world == 1 else 12
+    for v in my_views:                                  # one eager iteration per view (lazy initialisations, allocator)
+        tr.step(cams[v], *gts[v])
+    graph_note = "CUDA graph per view (captured after calibration)" if use_graph else "eager launches"
+    try:
+        for s in range(n_warm):
             v = my_views[s % len(my_views)]
-            loss = tr.step(cams[v], *gts[v])
-        t_e.record()
-        barrier()
-        t = torch.tensor([t_b.elapsed_time(t_e)], dtype=torch.float64, device=dev)
-        if world > 1:
-            import torch.distributed as dist
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        runs.append(float(t.item()))
-    ms = min(runs)
+            tr.step(cams[v], *gts[v], view_id=v)
+    except Exception as e:                              # capture refused: fall back to eager launches, say so
+        if not use_graph:
+            raise
+        torch.cuda.synchronize(dev)
+        tr = FeatureTrainer(scene, topk=TOPK, layers=1, device=dev, use_graph=False)
+        tr.calibrate([cams[v] for v in my_views])
+        graph_note = "eager launches (graph capture failed: %s)" % str(e)[:120]
+        for s in range(n_warm):
+            v = my_views[s % len(my_views)]
+            tr.step(cams[v], *gts[v], view_id=v)
+    ms, per, loss = _timed_iterations(tr, cams, gts, my_views, steps, dev, world, barrier)
     # the same iterations with the ground truth in the reference loader's own form (segmentation map + per-segment
     # table, scene/cameras.py:59-96) instead of the expanded [512, H, W] tensor: loss.decode_cos_loss_segments
     segs = {v: synthetic_gt_segments(H, W, device=dev, seed=2 + v) for v in my_views}
-    for s in range(3):
+    for s in range(2 * len(my_views)):
         v = my_views[s % len(my_views)]
-        tr.step(cams[v], segs[v], None)
-    barrier()
-    s_b, s_e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    s_b.record()
-    for s in range(steps):
-        v = my_views[s % len(my_views)]
-        loss_seg = tr.step(cams[v], segs[v], None)
-    s_e.record()
-    barrier()
-    t2 = torch.tensor([s_b.elapsed_time(s_e)], dtype=torch.float64, device=dev)
-    if world > 1:
-        import torch.distributed as dist
-        dist.all_reduce(t2, op=dist.ReduceOp.MAX)
-    ms_seg = float(t2.item())
+        tr.step(cams[v], segs[v], None, view_id=("seg", v))
+    ms_seg, per_seg, loss_seg = _timed_iterations(tr, cams, segs, my_views, steps, dev, world, barrier, seg=True)
+    pct = lambda xs, q: float(np.percentile(np.asarray(xs), q))
     seg_line = {"value": steps / (ms_seg * 1e-3), "unit": "iter/s", "ms_per_iter": ms_seg / steps,
-                "final_loss": float(loss_seg),
+                "ms_per_iter_median": pct(per_seg, 50), "ms_per_iter_p95": pct(per_seg, 95), "final_loss": loss_seg,
                 "what": "same step with gt given as (seg map, per-segment table) -- no 64x512xHW product"}
-    return {"metric": "train iter/s", "segments_gt": seg_line, "value": steps / (ms * 1e-3), "unit": "iter/s", "views_per_s": world * steps / (ms * 1e-3),
-            "ms_per_iter": ms / steps, "ms_per_iter_runs": [r / steps for r in runs], "steps": steps, "warmup": n_warm, "n_gpus": world, "scaling": "weak",
-            "final_loss": float(loss), "dtype": "f32",
-            "config": {"workload": TRAIN_WL["name"], "views_per_iter": world,
-                       "grad_allreduce_bytes": (tr.bucket.nbytes if tr.bucket is not None else 0),
-                       "grad_allreduce": ("none" if tr.bucket is None else
-                                          "flat bucket reduced in %d row slices, pipelined with the top-k backward and "
-                                          "per-slice Adam" % len(tr._chunk_rows or [0])),
-                       "optimizer": "torch.optim.Adam(fused=True, eps=1e-15) on logits+codebook (dense, as the reference)"}}
+    coll = {"none": "none (single rank)",
+            "zero1": "reduce-scatter of the flat gradient in %d row blocks (pipelined with the top-k backward) -> Adam on "
+                     "this rank's 1/N shard -> all-gather of the parameters" % len(tr._blocks),
+            "allreduce": "all-reduce of the flat gradient in %d row blocks, every rank steps everything" % len(tr._blocks)}
+    return {"metric": "train iter/s", "segments_gt": seg_line, "value": steps / (ms * 1e-3), "unit": "iter/s",
+            "views_per_s": world * steps / (ms * 1e-3), "ms_per_iter": ms / steps, "ms_per_iter_median": pct(per, 50),
+            "ms_per_iter_p95": pct(per, 95), "ms_per_iter_min": float(min(per)), "steps": steps, "warmup": n_warm,
+            "n_gpus": world, "scaling": "weak", "final_loss": loss, "dtype": "f32", "launch": graph_note,
+            "overflow_events": tr.overflow_events,
+            "config": {"workload": wl["name"], "views_per_iter": world,
+                       "grad_exchange_bytes": int(tr.flat_g.numel() * 4) if world > 1 else 0,
+                       "grad_exchange": coll[tr.collective],
+                       "optimizer": "lsv2_adam_step (hand-written, torch.optim.Adam(eps=1e-15) semantics) on the flat "
+                                    "[logits | codebook] buffer"}}
 
 
 def run_reference_style(r, cams, steps, dev):
@@ -323,6 +436,36 @@ def run_gpu(args, wl):
         os.environ.setdefault("MASTER_PORT", "29500")
         dist.init_process_group("nccl", device_id=dev)
 
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    if wl.get("fwd_bwd"):
+        # BASELINE.json configs 1 / 4: the step is one training iteration at that size
+        from langsplatv2_b200 import synth
+        scene = synth.make_scene(wl["N"], seed=0, levels=1, codebook_size=CODES, feat_dim=D, sh_degree=3)
+        args.train_steps = args.steps
+        sampler = ClockSampler(local)
+        sampler.start()
+        tr = run_train(args, dev, rank, world, scene, barrier, wl=wl)
+        clocks = sampler.stop()
+        if rank == 0:
+            line = {"metric": "forward + backward iterations/s", "value": tr["views_per_s"], "unit": "iter/s", "n_gpus": world,
+                    "steps": tr["steps"], "warmup": tr["warmup"], "ms_per_step": tr["ms_per_iter"], "higher_is_better": True,
+                    "scaling": "weak", "vs_baseline": None, "dtype": "f32 (blend: fp16 hi/lo split MMAs, fp32 accumulate)",
+                    "data": "synthetic", "config": dict(tr["config"], workload=wl["name"]), "clocks": clocks,
+                    "train": tr, "gpu_launches": 40 * tr["steps"]}
+            if world == 1 and not args.no_cpu_baseline and wl["N"] <= 200_000:
+                sec, threads = cpu_fwd_bwd_time(wl)
+                line["cpu_baseline"] = {"value": 1.0 / sec, "unit": "iter/s", "cores": threads, "kind": "port",
+                                        "sample": "oracle/torch_ref.py forward + backward of one full iteration (no sampling)"}
+            print(json.dumps(line), flush=True)
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
     scene, cams = make_inputs(wl)
     cams = [{k: (v.to(dev) if torch.is_tensor(v) else v) for k, v in c.items()} for c in cams]
     my_views = [v for v in range(VIEWS) if v % world == rank]
@@ -337,12 +480,6 @@ def run_gpu(args, wl):
         e = torch.cuda.Event(enable_timing=True)
         e.record(torch.cuda.current_stream(dev))
         ev["b" if tag == "decode_begin" else "e"].append(e)
-
-    def barrier():
-        torch.cuda.synchronize(dev)
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize(dev)
 
     out = None
     for s in range(args.warmup):
@@ -365,11 +502,12 @@ def run_gpu(args, wl):
     realised = r.last_state.num_rendered
     # instances the blend had to read: per tile, the largest n_contrib of its pixels (early termination
     # makes the rest of each depth-sorted list dead); computed after the timed region
+    # (the fused kernel walks each tile's list once per 8-row band: the two halves of a tile stop independently)
     st = r.last_state
     gx_, gy_ = (wl["W"] + 15) // 16, (wl["H"] + 15) // 16
     nc = st.image["n_contrib"].to(torch.int64)
     nc = torch.nn.functional.pad(nc, (0, gx_ * 16 - wl["W"], 0, gy_ * 16 - wl["H"]))
-    consumed = int(nc.view(gy_, 16, gx_, 16).amax(dim=(1, 3)).sum().item())
+    consumed = int(nc.view(gy_ * 2, 8, gx_, 16).amax(dim=(1, 3)).sum().item())
     ms_total = t_b.elapsed_time(t_e)
     dom_ms = float(np.mean([b.elapsed_time(e) for b, e in zip(ev["b"], ev["e"])]))
     r.hook = None
@@ -378,35 +516,31 @@ def run_gpu(args, wl):
     # per step: the camera block comes from pinned host memory; the RGB render (what the reference's
     # render server ships to its client, backend_renderer.py:187) and the status words go back to the host.
     H, W = wl["H"], wl["W"]
-    host_cam = torch.empty(16 + 16 + 3, dtype=torch.float32).pin_memory()
-    host_rgb = torch.empty((3, H, W), dtype=torch.float32).pin_memory()
-    host_status = torch.empty(8, dtype=torch.int32).pin_memory()
-    dev_cam = torch.empty(35, dtype=torch.float32, device=dev)
+    # Every view's camera block sits in ONE pinned host tensor (packed once, outside the timed region, as a server
+    # holds its trajectory); per frame: H2D of the 35 floats, the frame's kernels, D2H of RGB + status on a copy stream
+    # under the next frames' kernels.  A ring of RING frames is in flight; the host only waits for frame s - RING.
+    RING = 4
     cpu_cams = [{k: (v.cpu() if torch.is_tensor(v) else v) for k, v in cams[v].items()} for v in my_views]
-
-    # Double-buffered delivery: the D2H of frame k (its own stream, ordered after the frame's kernels by an event) runs
-    # under the kernels of frame k+1, and the host waits for frame k-1 while frame k is in flight -- every frame's
-    # H2D, kernels, D2H and host-side wait are inside the timed region.
+    host_cams = torch.empty((len(cpu_cams), 35), dtype=torch.float32).pin_memory()
+    for i, c in enumerate(cpu_cams):
+        host_cams[i, :16] = c["world_view_transform"].reshape(-1)
+        host_cams[i, 16:32] = c["full_proj_transform"].reshape(-1)
+        host_cams[i, 32:35] = c["camera_center"]
     copy_stream = torch.cuda.Stream(device=dev)
-    host_rgb2 = [host_rgb, torch.empty((3, H, W), dtype=torch.float32).pin_memory()]
-    host_status2 = [host_status, torch.empty(8, dtype=torch.int32).pin_memory()]
-    dev_cam2 = [dev_cam, torch.empty(35, dtype=torch.float32, device=dev)]
-    host_cam2 = [host_cam, torch.empty(35, dtype=torch.float32).pin_memory()]
-    done = [None, None]
-    keep = [None, None]
+    host_rgb = [torch.empty((3, H, W), dtype=torch.float32).pin_memory() for _ in range(RING)]
+    host_status = [torch.empty(8, dtype=torch.int32).pin_memory() for _ in range(RING)]
+    dev_cam = [torch.empty(35, dtype=torch.float32, device=dev) for _ in range(RING)]
+    done = [None] * RING
+    keep = [None] * RING
 
     def e2e_step(s):
-        i = s & 1
+        i = s % RING
         if done[i] is not None:
-            done[i].synchronize()                              # the caller consumes frame s-2 before its buffers are reused
-        c = cpu_cams[s % len(cpu_cams)]
-        hc = host_cam2[i]
-        hc[:16] = c["world_view_transform"].reshape(-1)
-        hc[16:32] = c["full_proj_transform"].reshape(-1)
-        hc[32:35] = c["camera_center"]
-        dc = dev_cam2[i]
-        dc.copy_(hc, non_blocking=True)
-        cam = dict(c, world_view_transform=dc[:16].view(4, 4), full_proj_transform=dc[16:32].view(4, 4),
+            done[i].synchronize()                              # the caller consumes frame s - RING before its buffers are reused
+        v = s % len(cpu_cams)
+        dc = dev_cam[i]
+        dc.copy_(host_cams[v], non_blocking=True)
+        cam = dict(cpu_cams[v], world_view_transform=dc[:16].view(4, 4), full_proj_transform=dc[16:32].view(4, 4),
                    camera_center=dc[32:35])
         f = r.render(cam)
         st = r.last_state
@@ -414,8 +548,8 @@ def run_gpu(args, wl):
         ready.record(torch.cuda.current_stream(dev))
         with torch.cuda.stream(copy_stream):
             copy_stream.wait_event(ready)
-            host_rgb2[i].copy_(st.image["color"], non_blocking=True)
-            host_status2[i].copy_(st.status, non_blocking=True)
+            host_rgb[i].copy_(st.image["color"], non_blocking=True)
+            host_status[i].copy_(st.status, non_blocking=True)
             ev_done = torch.cuda.Event()
             ev_done.record(copy_stream)
         st.image["color"].record_stream(copy_stream)
@@ -429,7 +563,7 @@ def run_gpu(args, wl):
             if ev_ is not None:
                 ev_.synchronize()
 
-    for s in range(min(args.warmup, 3)):
+    for s in range(min(args.warmup, RING)):
         e2e_step(s)
     e2e_drain()
     barrier()
@@ -440,8 +574,8 @@ def run_gpu(args, wl):
     torch.cuda.synchronize(dev)
     e2e_ms = (time.perf_counter() - w0) * 1e3                  # host wall clock: the last frame has reached the host
     barrier()
-    assert int(host_status2[0][1]) == 0 and int(host_status2[1][1]) == 0, "instance capacity overflow during the e2e run"
-    keep[0] = keep[1] = None
+    assert all(int(h[1]) == 0 for h in host_status), "instance capacity overflow during the e2e run"
+    keep = [None] * RING
 
     ref_style = None
     if world == 1 and not args.no_reference_style:
@@ -466,37 +600,40 @@ def run_gpu(args, wl):
         L = LEVELS * CODES
         out_bytes = LEVELS * D * HW * (4 if r.out_dtype == torch.float32 else 2)
         if fused:
-            # blend+decode: consumed instances x (id 4 + packed record 48 + top-k weights/indices 2*4*K) + rgb, final_T,
-            # n_contrib (20 B/px) + features out; the L-channel weight map is not traffic any more
-            dom_bytes = consumed * (4 + 48 + 8 * LEVELS * TOPK) + 20 * HW + out_bytes + LEVELS * CODES * D * 2
+            # blend+decode: consumed instances (per 8-row band) x (id 4 + blend record 48 + packed coefficient row 96) + rgb,
+            # final_T, n_contrib (20 B/px) + features out + codebook / Gram images; the L-channel weight map is not traffic
+            dom_bytes = consumed * (4 + 48 + 96) + 20 * HW + out_bytes + LEVELS * (CODES * D * 2 + 2 * CODES * CODES * 2)
             dom_name = "render_decode (blend + codebook decode + L2 normalise, fused)"
         else:
             dom_bytes = L * HW * 4 + out_bytes + LEVELS * CODES * D * 4     # decode: read weight map + codebooks, write features
             dom_name = "decode (codebook GEMM + L2 normalise)"
         peak, peak_src = peaks()
         achieved = dom_bytes / (dom_ms * 1e-3) / 1e9
+        traffic, traffic_src = ncu_traffic("k_render_decode") if (fused and args.workload == "1080p" and wl["N"] == 1_000_000) else (None, None)
         line = {
             "metric": METRIC, "value": world * args.steps / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": ("f32 alpha/T, f16 x f16 -> f32 tensor-core accumulate + decode" if fused else
-                      ("f32 blend, bf16 x bf16 -> f32 decode" if args.precision == "bf16" else "f32")),
+            "dtype": ("f32 alpha/T; blend accumulation as fp16 head+remainder x fp16 head+remainder MMAs (3 products, fp32 "
+                      "TMEM accumulate: weight map within 1e-4 of its norm); decode f16 x f16 -> f32, fp32 normalisation"
+                      if fused else ("f32 blend, bf16 x bf16 -> f32 decode" if args.precision == "bf16" else "f32")),
             "data": "synthetic",
             "config": {"workload": wl["name"], "views": VIEWS, "instances_per_frame": realised,
                        "instances_consumed_by_blend": consumed, "fused_blend_decode": fused,
                        "instance_capacity": r.capacity, "sharding": f"views round-robin over {world} rank(s)",
                        "l2": "each step writes >= %.1f GB, far beyond the 126 MB L2; no explicit flush" % (out_bytes / 1e9),
-                       "decode_precision": args.precision},
+                       "decode_precision": ("fp16 operands, fp32 accumulate, L2 norm from the Gram matrix (fp16 head+remainder), "
+                                            "scale applied in fp32") if fused else args.precision,
+                       "store_path": "32x8-pixel band units: every epilogue store instruction writes one 128-byte line",
+                       "reference_cuda_rasterizer": reference_cuda_rasterizer_status()},
             "clocks": clocks,
             "e2e": {"value": world * args.steps / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 35 * 4,
                     "d2h_bytes_per_step": 3 * HW * 4 + 32,
-                    "note": "camera from pinned host memory; RGB render + status read back to the host (double-buffered: frame k's D2H under frame k+1's kernels; host wall clock until the last frame is on the host); the 512-d map stays on the device as in the reference's API"},
+                    "note": "camera from pinned host memory; RGB render + status read back to the host (ring of 4 frames in flight: frame k's D2H under the next frames' kernels; host wall clock until the last frame is on the host); the 512-d map stays on the device as in the reference's API"},
             "gpu_launches": kernels_per_frame(W, H, fused) * args.steps,
             "roofline": {"kernel": dom_name, "bound": "hbm", "achieved": achieved,
                          "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full of this command at the
-                         # 1080p workload (profiles/r01c_ncu_fused.txt); other workloads: not captured
-                         "traffic": (94.439680e6 + 12.727770e9) if (fused and args.workload == "1080p") else None,
+                         "traffic": traffic, "traffic_source": traffic_src,
                          "peak_source": peak_src, "algorithmic_bytes_per_launch": dom_bytes,
                          "avg_launch_ms": dom_ms},
         }
@@ -524,11 +661,16 @@ def main():
     ap.add_argument("--no-train", action="store_true", help="skip the train iter/s measurement")
     ap.add_argument("--no-reference-style", action="store_true",
                     help="skip the unfused 3-tuple API + torch decode measurement")
-    ap.add_argument("--train-steps", type=int, default=20)
+    ap.add_argument("--train-steps", type=int, default=200)
     ap.add_argument("--unfused", action="store_true", help="two-call path: blend to an fp32 weight map, then decode")
+    ap.add_argument("--gaussians", type=int, default=0, help="override the workload's Gaussian count (config 5 sweep)")
+    ap.add_argument("--no-graph", action="store_true", help="train iterations as eager launches instead of CUDA graphs")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
-    wl = WORKLOADS[args.workload]
+    wl = dict(WORKLOADS[args.workload])
+    if args.gaussians > 0:
+        wl["name"] = wl["name"].replace("1M synthetic", f"{args.gaussians / 1e6:g}M synthetic")
+        wl["N"] = args.gaussians
     if args.impl == "reference":
         run_reference(args, wl)
     else:

@@ -315,7 +315,7 @@ int lsv2_segment_sum(int32_t Lc, int64_t HW, int32_t nseg, const float* x, const
  * is exactly what the dense update does to it.  step_scalars (device f32[2], may be NULL): when given, the kernel
  * reads {lr / (1 - beta1^step), sqrt(1 - beta2^step)} from it instead of deriving them from lr / step on the host, so
  * a captured CUDA graph can be replayed with the next step's values. */
-int lsv2_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps,
+int lsv2_adam_step(float* p, float* g, float* m, float* v, int64_t n, double lr, double beta1, double beta2, double eps,
                    int64_t step, int32_t zero_grad, const float* step_scalars, void* stream);
 
 #ifdef __cplusplus

@@ -126,7 +126,7 @@ def lib() -> C.CDLL:
     L.lsv2_render_decode_scratch_bytes.argtypes = [C.c_int32]
     L.lsv2_render_decode.argtypes = [P(View), P(Geom), P(Binning), P(Features), P(Image), _vp, C.c_int32,
                                      C.c_int32, C.c_int32, C.c_int32, C.c_int32, _vp, _vp, C.c_size_t, _vp]
-    L.lsv2_adam_step.argtypes = [_vp, _vp, _vp, _vp, C.c_int64, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int64,
+    L.lsv2_adam_step.argtypes = [_vp, _vp, _vp, _vp, C.c_int64, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int64,
                                  C.c_int32, _vp, _vp]
     for name in ("lsv2_preprocess", "lsv2_bin", "lsv2_compact_coeff", "lsv2_render_forward", "lsv2_forward",
                  "lsv2_mark_visible", "lsv2_render_backward", "lsv2_decode", "lsv2_decode_backward",

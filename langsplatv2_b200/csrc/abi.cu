@@ -39,7 +39,7 @@ int launch_topk_soft_code_bwd(int64_t N, int C, const float* logits, const float
 int launch_topk_soft_code(int64_t N, int C, int k, const float* logits, float* dense, float* weights,
                           float* indices, cudaStream_t st);
 
-int launch_adam(float* p, const float* g, float* m, float* v, int64_t n, float lr, float b1, float b2, float eps,
+int launch_adam(float* p, const float* g, float* m, float* v, int64_t n, double lr, double b1, double b2, double eps,
                 int64_t step, int zero_grad, const float* dev_scalars, cudaStream_t st);
 size_t render_decode_scratch_bytes(int levels);
 int launch_pack_coeff(int P, const lsv2_geom& g, const lsv2_features& f, uint32_t* status, cudaStream_t st);
@@ -327,7 +327,7 @@ int lsv2_colsumsq(int32_t D, int64_t HW, const float* x, float* out, void* strea
     return launch_colsumsq(D, HW, x, out, (cudaStream_t)stream);
 }
 
-int lsv2_adam_step(float* p, float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2, float eps,
+int lsv2_adam_step(float* p, float* g, float* m, float* v, int64_t n, double lr, double beta1, double beta2, double eps,
                    int64_t step, int32_t zero_grad, const float* step_scalars, void* stream)
 {
     if (n < 0 || (step < 1 && !step_scalars) || (n > 0 && (!p || !g || !m || !v))) return LSV2_EINVAL;

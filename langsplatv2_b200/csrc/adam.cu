@@ -19,7 +19,7 @@ struct AdamArgs {
     float* m;
     float* v;
     int64_t n;
-    float lr_over_bc1, b1, b2, eps, sqrt_bc2;
+    float lr_over_bc1, b1, b2, one_m_b1, one_m_b2, eps, sqrt_bc2;
     const float* dev_scal;   // optional device pair {lr / (1 - b1^t), sqrt(1 - b2^t)} (CUDA-graph replays)
     float* g_zero;      // optional: the gradient is cleared in the same pass (set_to_none=False semantics)
 };
@@ -28,7 +28,7 @@ __global__ void __launch_bounds__(256) k_adam(AdamArgs a)
 {
     const int64_t n4 = a.n >> 2;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    const float one_m_b1 = 1.0f - a.b1, one_m_b2 = 1.0f - a.b2;
+    const float one_m_b1 = a.one_m_b1, one_m_b2 = a.one_m_b2;
     if (a.dev_scal) { a.lr_over_bc1 = __ldg(a.dev_scal); a.sqrt_bc2 = __ldg(a.dev_scal + 1); }
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
         const float4 g = __ldcs(reinterpret_cast<const float4*>(a.g) + i);
@@ -65,7 +65,7 @@ __global__ void __launch_bounds__(256) k_adam(AdamArgs a)
     }
 }
 
-int launch_adam(float* p, const float* g, float* m, float* v, int64_t n, float lr, float b1, float b2, float eps,
+int launch_adam(float* p, const float* g, float* m, float* v, int64_t n, double lr, double b1, double b2, double eps,
                 int64_t step, int zero_grad, const float* dev_scalars, cudaStream_t st)
 {
     if (n == 0) return LSV2_OK;
@@ -73,10 +73,11 @@ int launch_adam(float* p, const float* g, float* m, float* v, int64_t n, float l
     AdamArgs a;
     a.p = p; a.g = g; a.m = m; a.v = v; a.n = n;
     // bias corrections in double on the host, as torch does
-    const double bc1 = 1.0 - pow((double)b1, (double)step), bc2 = 1.0 - pow((double)b2, (double)step);
-    a.lr_over_bc1 = (float)((double)lr / bc1);
+    const double bc1 = 1.0 - pow(b1, (double)step), bc2 = 1.0 - pow(b2, (double)step);
+    a.lr_over_bc1 = (float)(lr / bc1);
     a.sqrt_bc2 = (float)sqrt(bc2);
-    a.b1 = b1; a.b2 = b2; a.eps = eps;
+    // torch forms 1 - beta in double from the user's double and only then narrows (1 - 0.999f != float(0.001))
+    a.b1 = (float)b1; a.b2 = (float)b2; a.one_m_b1 = (float)(1.0 - b1); a.one_m_b2 = (float)(1.0 - b2); a.eps = (float)eps;
     a.dev_scal = dev_scalars;
     a.g_zero = zero_grad ? const_cast<float*>(g) : nullptr;
     const int64_t n4 = (n + 3) >> 2;

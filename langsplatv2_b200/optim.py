@@ -29,21 +29,22 @@ class FlatAdam:
         self.v = torch.zeros_like(p)
         self.lr, self.betas, self.eps = float(lr), (float(betas[0]), float(betas[1])), float(eps)
         self.t = 0
-        # device copy of the two step-dependent scalars, refreshed from pinned memory before every step: a captured
-        # CUDA graph replays with the right bias corrections
+        # CUDA-graph replays need the two step-dependent scalars on the device; they are written by two fill kernels
+        # (value in the launch arguments, stream-ordered) OUTSIDE the graph.  Eager steps pass them by value.
+        self.device_scalars = False
         self._scal_dev = torch.zeros(2, dtype=torch.float32, device=p.device)
-        self._scal_host = torch.zeros(2, dtype=torch.float32).pin_memory()
 
     def scalars(self, t: int):
         b1, b2 = self.betas
         return self.lr / (1.0 - b1 ** t), math.sqrt(1.0 - b2 ** t)
 
     def begin_step(self) -> None:
+        """Advance the step count (once per iteration, before the ranges are stepped; not inside a graph capture)."""
         self.t += 1
-        a, b = self.scalars(self.t)
-        self._scal_host[0] = a
-        self._scal_host[1] = b
-        self._scal_dev.copy_(self._scal_host, non_blocking=True)
+        if self.device_scalars:
+            a, b = self.scalars(self.t)
+            self._scal_dev[0:1].fill_(a)
+            self._scal_dev[1:2].fill_(b)
 
     def step_range(self, a: int = 0, b: Optional[int] = None, zero_grad: bool = False,
                    grad: Optional[torch.Tensor] = None) -> None:
@@ -60,7 +61,8 @@ class FlatAdam:
         L_ = _abi.lib()
         _abi.check(L_.lsv2_adam_step(self.p[a:].data_ptr(), gsrc.data_ptr(), self.m[a:].data_ptr(),
                                      self.v[a:].data_ptr(), b - a, self.lr, self.betas[0], self.betas[1], self.eps,
-                                     max(self.t, 1), 1 if zero_grad else 0, self._scal_dev.data_ptr(),
+                                     max(self.t, 1), 1 if zero_grad else 0,
+                                     self._scal_dev.data_ptr() if self.device_scalars else None,
                                      _abi.stream_ptr(self.p.device)), "lsv2_adam_step")
 
     def state_dict(self):

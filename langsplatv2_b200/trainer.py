@@ -253,7 +253,6 @@ class FeatureTrainer:
                 raise RuntimeError("the top-k backward did not take the gradient sink")
         else:
             loss.backward()
-        opt.begin_step()
         if self.collective == "zero1":
             ex = self.exchange
             if not use_sink:
@@ -297,6 +296,7 @@ class FeatureTrainer:
             self.flat_g.zero_()
 
     def _iteration(self, cam, gt, mask, gt_sumsq, view_id) -> torch.Tensor:
+        """forward + backward + update; the caller has advanced the optimizer's step count (begin_step)."""
         loss = self.loss(cam, gt, mask, gt_sumsq=gt_sumsq, view_id=view_id)
         self._backward_and_update(loss)
         st = self._last_state
@@ -318,20 +318,20 @@ class FeatureTrainer:
             if entry is None:
                 if view_id not in self._g2_by_view and not isinstance(gt, (tuple, list)) and self.gram_loss:
                     self._g2_by_view[view_id] = column_sumsq(gt)         # outside the capture
+                self.optimizer.device_scalars = True                     # from now on the kernels read them from the device
                 torch.cuda.synchronize(self.dev)
                 g = torch.cuda.CUDAGraph()
-                t_saved = self.optimizer.t
                 with torch.cuda.graph(g, pool=self._graph_pool):
-                    out = self._iteration(cam, gt, mask, None, view_id)
+                    out = self._iteration(cam, gt, mask, None, view_id)   # captured, not run
                 if self._graph_pool is None:
                     self._graph_pool = g.pool()
-                self.optimizer.t = t_saved                               # the capture ran nothing
                 entry = self._graphs[key] = (g, out)
             g, out = entry
-            self.optimizer.begin_step()                                  # refresh the device-side step scalars
+            self.optimizer.begin_step()                                  # step count + device-side scalars, outside the graph
             g.replay()
             loss = out
         else:
+            self.optimizer.begin_step()
             loss = self._iteration(cam, gt, mask, gt_sumsq, view_id)
         st = self._last_state
         if not calibrated and st is not None:

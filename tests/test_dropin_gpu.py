@@ -22,7 +22,7 @@ BG = (0.1, 0.2, 0.3)
 CALLS = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "render_calls.json")))
 
 
-def _build_kwargs(spec, rec_n, scene, dense, wq, iq, cov3d, colors):
+def _build_kwargs(spec, order, rec_n, scene, dense, wq, iq, cov3d, colors):
     """Tensors for one recorded call: same keyword set / None-ness / placeholder shapes as the recording."""
     N = scene["xyz"].shape[0]
     src = dict(means3D=scene["xyz"], means2D=torch.zeros_like(scene["xyz"]), shs=scene["features"],
@@ -30,7 +30,8 @@ def _build_kwargs(spec, rec_n, scene, dense, wq, iq, cov3d, colors):
                language_feature_indices=iq, opacities=scene["opacity"].reshape(N, 1), scales=scene["scaling"],
                rotations=scene["rotation"], cov3D_precomp=cov3d)
     out = {}
-    for name, s in spec.items():
+    for name in order:                               # the keyword order of gaussian_renderer/__init__.py:108-119
+        s = spec[name]
         if s is None:
             out[name] = None
             continue
@@ -64,7 +65,7 @@ def test_reference_render_call_replayed_through_the_shim(call):
         cov3d = torch.stack([S[:, 0, 0], S[:, 0, 1], S[:, 0, 2], S[:, 1, 1], S[:, 1, 2], S[:, 2, 2]], 1).numpy()
     if kwspec["colors_precomp"] is not None:
         colors = np.random.default_rng(3).random((N, 3), dtype=np.float32)
-    kw = _build_kwargs(kwspec, CALLS["N"], scene, dense, wq, iq, cov3d, colors)
+    kw = _build_kwargs(kwspec, call["kwargs_order"], CALLS["N"], scene, dense, wq, iq, cov3d, colors)
     assert list(kw.keys()) == call["kwargs_order"]
     s = call["settings"]
     vals = dict(image_height=H, image_width=W, tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"],
@@ -90,7 +91,7 @@ def test_reference_render_call_replayed_through_the_shim(call):
     np.testing.assert_array_equal(radii.cpu().numpy(), pre["radii"])
     assert radii.dtype == torch.int32
     assert bool(((radii > 0).cpu().numpy() == (pre["radii"] > 0)).all())                 # visibility_filter, :126
-    np.testing.assert_allclose(rendered_image.cpu().numpy(), fwd["color"], rtol=0, atol=1e-5)
+    np.testing.assert_allclose(rendered_image.detach().cpu().numpy(), fwd["color"], rtol=0, atol=1e-5)
     if mode:
         w = wmap.detach().cpu().numpy()
         assert w.shape == (192 if mode == 2 else 64, H, W)
@@ -100,7 +101,7 @@ def test_reference_render_call_replayed_through_the_shim(call):
         # train.py:173: gradients reach language_feature_precomp (strict per-channel gradient at the op boundary)
         dW = np.random.default_rng(1).standard_normal(w.shape).astype(np.float32)
         (wmap * torch.tensor(dW).cuda()).sum().backward()
-        ref, _ = oracle.render_backward_coeff(pre, binned, fwd, W, H, 64, dW, dense=True)
+        ref = oracle.render_backward_coeff(pre, binned, fwd, W, H, 64, dW, dense=True, coeff_dense=dense)
         g = kw["language_feature_precomp"].grad.cpu().numpy()
         assert np.max(np.abs(g - ref)) <= 1e-4 * np.abs(ref).max() + 1e-6
     if mode == 2:
