@@ -240,13 +240,28 @@ int lsv2_decode(int32_t levels, int32_t Lc, int32_t D, int64_t HW, const float* 
  * compacted rows of lsv2_compact_coeff) + codebooks f32[levels][Lc][D]; feat->L must equal
  * levels*Lc.  image->color / final_T / n_contrib are written as by lsv2_render_forward
  * (bit-identical); image->wmap may be NULL (if not, it receives the TMEM weight map, fp32).
- * out: [levels][D][H][W], out_dtype 0 = f32, 1 = bf16.  Supported: Lc = 64, D = 512,
- * levels <= 3, K <= LSV2_SPARSE_CAP; otherwise LSV2_EUNSUPPORTED (use the two-call path). */
+ * out: [levels][D][H][W], out_dtype 0 = f32, 1 = bf16; OR-ing LSV2_OUT_HWC gives the consumers' channels-last
+ * layout [levels][H][W][D] (eval/openclip_encoder.py:116 takes the map that way).  Supported: Lc = 64, D = 512,
+ * levels <= 3, K <= LSV2_SPARSE_CAP, feat->packed set; otherwise LSV2_EUNSUPPORTED (use the two-call path). */
+#define LSV2_OUT_HWC 2
 size_t lsv2_render_decode_scratch_bytes(int32_t levels);
 int lsv2_render_decode(const lsv2_view* view, const lsv2_geom* geom, const lsv2_binning* binning,
                        const lsv2_features* feat, const lsv2_image* image, const float* codebooks,
                        int32_t levels, int32_t Lc, int32_t D, int32_t normalize, int32_t out_dtype,
                        void* out, void* scratch, size_t scratch_bytes, void* stream);
+
+/* ---- fused blend + relevancy query (eval_lerf.py:351-352 / backend_renderer.py:204-210 call
+ *      OpenCLIPNetwork.get_max_across_quick, eval/openclip_encoder.py:114-138, on the decoded map) -------------
+ * Same blend; instead of the 512-d map the kernel produces, per level and positive phrase,
+ *   min over negatives of softmax(10 * [sim_pos, sim_neg])[0],  sim = <F / (|F| + 1e-10), e>,
+ * from sim = w^T (C_l E^T) / |C_l^T w|: the feature map is never formed or written (levels*n_pos*H*W*4 bytes leave the
+ * chip instead of levels*512*H*W*4).  phrase_embeds f32[n_pos + n_neg][D], positives first, n_pos + n_neg <= 64;
+ * out f32[levels][n_pos][H][W].  image->color / final_T / n_contrib as lsv2_render_forward. */
+size_t lsv2_render_query_scratch_bytes(int32_t levels);
+int lsv2_render_query(const lsv2_view* view, const lsv2_geom* geom, const lsv2_binning* binning,
+                      const lsv2_features* feat, const lsv2_image* image, const float* codebooks, int32_t levels,
+                      int32_t Lc, int32_t D, const float* phrase_embeds, int32_t n_pos, int32_t n_neg, float* out,
+                      void* scratch, size_t scratch_bytes, void* stream);
 
 /* autograd of the un-normalised decode (scene/gaussian_model.py:538):
  *   dW[l*Lc+k][p] = sum_d C[l][k][d] dF[l][d][p]   (f32[levels*Lc][HW])

@@ -6,9 +6,9 @@ Public surface (mirrors the reference's operator API):
   softmax_to_topk_soft_code, get_weights_and_indices  -- sparse-coefficient producer
 """
 from .rasterizer import (GaussianRasterizationSettings, GaussianRasterizer, FrameState, rasterize_forward,
-                         rasterize_backward, render_decode)
+                         rasterize_backward, render_decode, render_query)
 from .decode import decode_feature_map
 from .sparse import softmax_to_topk_soft_code, get_weights_and_indices
 
 __all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "FrameState", "rasterize_forward",
-           "rasterize_backward", "render_decode", "decode_feature_map", "softmax_to_topk_soft_code", "get_weights_and_indices"]
+           "rasterize_backward", "render_decode", "render_query", "decode_feature_map", "softmax_to_topk_soft_code", "get_weights_and_indices"]

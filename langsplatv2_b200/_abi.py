@@ -22,6 +22,7 @@ STATUS_WORDS = 8
 STATUS_NUM_RENDERED, STATUS_OVERFLOW, STATUS_BAD_INDEX = 0, 1, 2
 MODE_RGB, MODE_DENSE, MODE_QUICK = 0, 1, 2
 DECODE_FP32, DECODE_BF16 = 0, 1
+OUT_HWC = 2
 
 _vp = C.c_void_p
 
@@ -67,6 +68,7 @@ EXPORTS = [
     "lsv2_gram_loss_forward", "lsv2_gram_loss_backward", "lsv2_colsumsq", "lsv2_segment_sum",
     "lsv2_gram_loss_forward_seg", "lsv2_gram_loss_backward_seg",
     "lsv2_render_decode_scratch_bytes", "lsv2_render_decode", "lsv2_render_forward_tc", "lsv2_adam_step", "lsv2_pack_coeff",
+    "lsv2_render_query_scratch_bytes", "lsv2_render_query",
 ]
 
 _lib = None
@@ -98,6 +100,10 @@ def lib() -> C.CDLL:
     L.lsv2_bin.argtypes = [P(View), C.c_int32, P(Geom), P(Binning), _vp]
     L.lsv2_compact_coeff.argtypes = [C.c_int32, P(Geom), P(Features), _vp]
     L.lsv2_render_forward.argtypes = [P(View), P(Geom), P(Binning), P(Features), P(Image), _vp]
+    L.lsv2_render_query_scratch_bytes.restype = C.c_size_t
+    L.lsv2_render_query_scratch_bytes.argtypes = [C.c_int32]
+    L.lsv2_render_query.argtypes = [P(View), P(Geom), P(Binning), P(Features), P(Image), _vp, C.c_int32, C.c_int32,
+                                    C.c_int32, _vp, C.c_int32, C.c_int32, _vp, _vp, C.c_size_t, _vp]
     L.lsv2_pack_coeff.argtypes = [C.c_int32, P(Geom), P(Features), _vp, _vp]
     L.lsv2_render_forward_tc.argtypes = [P(View), P(Geom), P(Binning), P(Features), P(Image), _vp]
     L.lsv2_forward.argtypes = [P(View), P(Scene), P(Geom), P(Binning), P(Features), P(Image), _vp]
@@ -132,7 +138,7 @@ def lib() -> C.CDLL:
                  "lsv2_mark_visible", "lsv2_render_backward", "lsv2_decode", "lsv2_decode_backward",
                  "lsv2_topk_soft_code", "lsv2_topk_soft_code_backward", "lsv2_cos_loss_forward", "lsv2_cos_loss_backward",
                  "lsv2_gram_loss_forward", "lsv2_gram_loss_backward", "lsv2_colsumsq", "lsv2_segment_sum", "lsv2_render_decode",
-                 "lsv2_render_forward_tc", "lsv2_gram_loss_forward_seg", "lsv2_gram_loss_backward_seg", "lsv2_adam_step", "lsv2_pack_coeff"):
+                 "lsv2_render_forward_tc", "lsv2_gram_loss_forward_seg", "lsv2_gram_loss_backward_seg", "lsv2_adam_step", "lsv2_pack_coeff", "lsv2_render_query"):
         getattr(L, name).restype = C.c_int
     _lib = L
     return L

@@ -47,7 +47,11 @@ int launch_render_wmap_tc(const lsv2_view& v, const lsv2_geom& g, const lsv2_bin
                           const lsv2_image& img, void* scratch, size_t scratch_bytes, cudaStream_t st);
 int launch_render_decode(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b, const lsv2_features& f,
                          const lsv2_image& img, const float* codebooks, int levels, int Lc, int D, int normalize,
-                         int out_dtype, void* out, void* scratch, size_t scratch_bytes, cudaStream_t st);
+                         int out_dtype, int out_hwc, void* out, void* scratch, size_t scratch_bytes, cudaStream_t st);
+size_t render_query_scratch_bytes(int levels);
+int launch_render_query(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b, const lsv2_features& f,
+                        const lsv2_image& img, const float* codebooks, int levels, int Lc, int D, const float* embeds,
+                        int n_pos, int n_neg, float* out, void* scratch, size_t scratch_bytes, cudaStream_t st);
 
 static int tile_bits_for(const lsv2_view& v)
 {
@@ -235,9 +239,23 @@ int lsv2_render_decode(const lsv2_view* view, const lsv2_geom* geom, const lsv2_
 {
     if (!view_ok(view) || !geom || !binning || !feat || !image || !codebooks || !out) return LSV2_EINVAL;
     if (!image->color || !image->final_T || !image->n_contrib || !binning->ranges || !binning->status) return LSV2_EINVAL;
-    if (out_dtype != 0 && out_dtype != 1) return LSV2_EINVAL;
-    return launch_render_decode(*view, *geom, *binning, *feat, *image, codebooks, levels, Lc, D, normalize, out_dtype,
-                                out, scratch, scratch_bytes, (cudaStream_t)stream);
+    if ((out_dtype & ~LSV2_OUT_HWC) != 0 && (out_dtype & ~LSV2_OUT_HWC) != 1) return LSV2_EINVAL;
+    return launch_render_decode(*view, *geom, *binning, *feat, *image, codebooks, levels, Lc, D, normalize,
+                                out_dtype & 1, (out_dtype & LSV2_OUT_HWC) ? 1 : 0, out, scratch, scratch_bytes,
+                                (cudaStream_t)stream);
+}
+
+size_t lsv2_render_query_scratch_bytes(int32_t levels) { return render_query_scratch_bytes(levels); }
+
+int lsv2_render_query(const lsv2_view* view, const lsv2_geom* geom, const lsv2_binning* binning,
+                      const lsv2_features* feat, const lsv2_image* image, const float* codebooks, int32_t levels,
+                      int32_t Lc, int32_t D, const float* phrase_embeds, int32_t n_pos, int32_t n_neg, float* out,
+                      void* scratch, size_t scratch_bytes, void* stream)
+{
+    if (!view_ok(view) || !geom || !binning || !feat || !image || !codebooks || !phrase_embeds || !out) return LSV2_EINVAL;
+    if (!image->color || !image->final_T || !image->n_contrib || !binning->ranges || !binning->status) return LSV2_EINVAL;
+    return launch_render_query(*view, *geom, *binning, *feat, *image, codebooks, levels, Lc, D, phrase_embeds, n_pos,
+                               n_neg, out, scratch, scratch_bytes, (cudaStream_t)stream);
 }
 
 int lsv2_decode_backward(int32_t levels, int32_t Lc, int32_t D, int64_t HW, const float* wmap,

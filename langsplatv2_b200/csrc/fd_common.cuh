@@ -30,6 +30,8 @@ constexpr int FD_D = 512;
 constexpr int FD_KMAX = LSV2_SPARSE_CAP;
 constexpr uint32_t FD_ROW_DENSE = 0xFFFFFFFFu;
 constexpr int FD_UNIT_W = 32, FD_UNIT_H = 8;
+// what follows the blend: nothing (the weight map is the product), the codebook decode, or the relevancy query
+constexpr int FD_PATH_WMAP = 0, FD_PATH_DECODE = 1, FD_PATH_QUERY = 2;
 constexpr int FD_CREC_WORDS = LSV2_PACKED_WORDS;         // 16 (hi | lo << 16) words, 16 channel bytes, count, pad
 
 // blend operands: 64-byte rows [hi fp16 x16 | lo fp16 x16], 64-byte swizzle, K-major
@@ -94,7 +96,11 @@ struct FdArgs {
     const uint8_t* bimg;         // fp16 codebook image [levels][512 rows][64 k], 128B-swizzled (scaled by cscale[l])
     const uint8_t* gimg;         // fp16 Gram images  s_l C_l C_l^T  [levels][hi 64 rows | lo 64 rows][64 k], 128B-swizzled
     const float* gscale_inv;     // [levels] 1 / s_l
-    void* out;                   // [levels][512][H][W]
+    void* out;                   // [levels][512][H][W]  ([levels][H][W][512] when hwc)
+    int hwc;
+    const uint8_t* qimg;         // query: fp16 images of M_l = C_l E^T  [levels][hi 64 rows (phrase) | lo 64 rows][64 k], 128B-swizzled
+    float* qout;                 // query: relevancy [levels][n_pos][H][W]
+    int n_pos, n_neg;
     int normalize;
     uint32_t* tile_counter;
     long long* prof;             // -DFD_PROF builds only: [grid][4 roles][8] cycle counters

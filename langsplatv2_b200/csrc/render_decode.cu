@@ -111,6 +111,32 @@ __global__ void __launch_bounds__(64) k_fd_prep_g(const float* __restrict__ code
     }
 }
 
+// Query images.  block (k, l), thread q:  M_l[k][q] = <C_l[k], E[q]> in fp32, stored as the B operand of
+// sim = Wdec_l . M_l  (row n = phrase q, column k = code) as fp16 head (rows 0-63) + remainder (rows 64-127).
+__global__ void __launch_bounds__(64) k_fd_prep_q(const float* __restrict__ codebooks, const float* __restrict__ embeds, int Q,
+                                                 uint8_t* __restrict__ qimg)
+{
+    __shared__ float s_row[FD_D];
+    const int k = blockIdx.x, l = blockIdx.y, q = threadIdx.x;
+    const float* cb = codebooks + ((size_t)l * FD_LC + k) * FD_D;
+    for (int d = q; d < FD_D; d += 64) s_row[d] = cb[d];
+    __syncthreads();
+    float dot = 0.0f;
+    if (q < Q) {
+        const float4* e = reinterpret_cast<const float4*>(embeds + (size_t)q * FD_D);
+        for (int d4 = 0; d4 < FD_D / 4; ++d4) {
+            const float4 v = __ldg(e + d4);
+            dot = fmaf(v.x, s_row[4 * d4], dot); dot = fmaf(v.y, s_row[4 * d4 + 1], dot);
+            dot = fmaf(v.z, s_row[4 * d4 + 2], dot); dot = fmaf(v.w, s_row[4 * d4 + 3], dot);
+        }
+    }
+    const __half h = __float2half_rn(dot);
+    const __half lo = __float2half_rn(__fsub_rn(dot, __half2float(h)));
+    uint8_t* base = qimg + (size_t)l * FD_CB_BYTES;
+    *reinterpret_cast<__half*>(base + sw128_offset((uint32_t)q, (uint32_t)(k >> 3)) + (k & 7) * 2) = h;
+    *reinterpret_cast<__half*>(base + sw128_offset((uint32_t)(64 + q), (uint32_t)(k >> 3)) + (k & 7) * 2) = lo;
+}
+
 // ---- packed coefficients (lsv2_pack_coeff) -------------------------------------------------------------------------
 // One thread per Gaussian: entries -> (fp16 head | fp16 remainder << 16) words + channel bytes + count.  Duplicate
 // channels are merged (their weights add up, as the blend would add them), channels outside [0, L) are dropped and
@@ -247,9 +273,12 @@ __device__ __forceinline__ void fd_put(unsigned char* S, uint32_t c, uint32_t in
     *reinterpret_cast<__half*>(S + (off ^ 32u)) = __float2half_rn(__fsub_rn(w, __half2float(h)));
 }
 
-template <bool OUT_BF16, bool DECODE>
-__global__ void __launch_bounds__(DECODE ? FD_THREADS : FD_THREADS_NODECODE, 1) k_render_decode(FdArgs a)
+template <bool OUT_BF16, int PATH>
+__global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS_NODECODE, 1) k_render_decode(FdArgs a)
 {
+    constexpr bool DECODE = PATH == FD_PATH_DECODE;     // codebook decode + epilogue warps
+    constexpr bool QUERY = PATH == FD_PATH_QUERY;       // relevancy query, finished by the blend warps themselves
+    constexpr bool WROWS = PATH != FD_PATH_WMAP;        // the blend's W goes into the fp16 operand rows
     extern __shared__ unsigned char smem_raw[];
     // offset arithmetic on the __shared__ symbol (not a uintptr_t round trip) keeps the shared address space
     // visible to the compiler: LDS/STS instead of generic LD/ST in the blend loop
@@ -280,7 +309,7 @@ __global__ void __launch_bounds__(DECODE ? FD_THREADS : FD_THREADS_NODECODE, 1) 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int L = a.L, levels = a.levels;
     const size_t HW = (size_t)a.H * a.W;
-    const bool normalize = DECODE && a.normalize != 0;
+    const bool normalize = QUERY || (DECODE && a.normalize != 0);
 
     if (tid == 0) {
         for (int s = 0; s < FD_STAGES; ++s) {
@@ -294,7 +323,7 @@ __global__ void __launch_bounds__(DECODE ? FD_THREADS : FD_THREADS_NODECODE, 1) 
         for (int l = 0; l < 3; ++l) { mbar_init(wraw_full + l, FD_BLEND_WARPS); mbar_init(u_full + l, 1); }
         mbar_init(inv_full, FD_BLEND_WARPS);
         mbar_init(dec_done, 1);
-        for (int q = 0; q < FD_FSLOTS; ++q) { mbar_init(f_full + q, 1); mbar_init(f_free + q, FD_EPI_WARPS); }
+        for (int q = 0; q < FD_FSLOTS; ++q) { mbar_init(f_full + q, 1); mbar_init(f_free + q, QUERY ? FD_BLEND_WARPS : FD_EPI_WARPS); }
         s_ndone[0] = 0;
         s_ndone[1] = 0;
         mbar_fence_init();
@@ -475,7 +504,7 @@ __global__ void __launch_bounds__(DECODE ? FD_THREADS : FD_THREADS_NODECODE, 1) 
             __syncwarp();
             batch_in_unit = 0;
         }
-    } else if (DECODE && warp == FD_WARP_MD) {
+    } else if (WROWS && warp == FD_WARP_MD) {
         // ================================ Gram + decode MMA issue, codebook fetch ================================
         // Converged warp, one elected lane issues.
         constexpr uint32_t idesc_u = umma_idesc_f16_f32(128, FD_LC);
@@ -484,7 +513,7 @@ __global__ void __launch_bounds__(DECODE ? FD_THREADS : FD_THREADS_NODECODE, 1) 
         // operand descriptors are built once; a k-step (32 bytes) or a row block only adds to the address field
         const uint64_t desc_w0 = umma_desc_k_sw128(bcast0(smem_u32(wdec))), desc_cb0 = umma_desc_k_sw128(bcast0(smem_u32(s_cb)));
         const int n_g = normalize ? levels : 0;
-        const int jobs_per_unit = n_g + levels * FD_CHUNKS;
+        const int jobs_per_unit = QUERY ? 2 * levels : n_g + levels * FD_CHUNKS;
         uint32_t cb_issued = 0, cb_used = 0, f_n = 0;
         FD_PROF_DECL
         FD_TIC();
@@ -492,7 +521,8 @@ __global__ void __launch_bounds__(DECODE ? FD_THREADS : FD_THREADS_NODECODE, 1) 
             const int slot = (int)(cb_issued & 1u);
             if (cb_issued >= FD_CB_SLOTS) mbar_wait(cb_free + slot, ((cb_issued >> 1) - 1) & 1);
             const int j = (int)(cb_issued % (uint32_t)jobs_per_unit);
-            const uint8_t* src = j < n_g ? a.gimg + (size_t)j * FD_CB_BYTES : a.bimg + (size_t)(j - n_g) * FD_CB_BYTES;
+            const uint8_t* src = QUERY ? ((j & 1) ? a.qimg : a.gimg) + (size_t)(j >> 1) * FD_CB_BYTES
+                                       : (j < n_g ? a.gimg + (size_t)j * FD_CB_BYTES : a.bimg + (size_t)(j - n_g) * FD_CB_BYTES);
             if (elect_one()) {
                 mbar_arrive_expect_tx(cb_full + slot, FD_CB_BYTES);
                 bulk_g2s(s_cb + (size_t)slot * FD_CB_BYTES, src, FD_CB_BYTES, cb_full + slot);
@@ -537,8 +567,38 @@ __global__ void __launch_bounds__(DECODE ? FD_THREADS : FD_THREADS_NODECODE, 1) 
                 __syncwarp();
                 ++cb_used;
                 if (n >= 1) fetch_next();
+                if (QUERY) {
+                    // sim_l = Wdec_l . (M_hi + M_lo) into the spare TMEM columns (one level at a time: the blend warps
+                    // drain it before the next level's product may land)
+                    const uint32_t nq = it * (uint32_t)levels + (uint32_t)l;
+                    const uint32_t n2 = cb_used;
+                    const int slot2 = (int)(n2 & 1u);
+                    mbar_wait(cb_full + slot2, (n2 >> 1) & 1);
+                    if (nq >= 1) mbar_wait(f_free, (nq - 1) & 1);
+                    tc_fence_after();
+                    if (elect_one()) {
+                        const uint64_t q_hi = desc_cb0 + (uint64_t)(slot2 * (FD_CB_BYTES >> 4)), q_lo = q_hi + (uint64_t)((64 * 128) >> 4);
+#pragma unroll
+                        for (int m = 0; m < 2; ++m) {
+                            const uint32_t d = tmem_u + (uint32_t)(FD_TMEM_F + m * 64);
+                            const uint64_t da = desc_w0 + (uint64_t)(l * (FD_WDEC_LEVEL >> 4) + m * ((128 * 128) >> 4));
+#pragma unroll
+                            for (int ks = 0; ks < 4; ++ks)
+                                umma_bf16(d, da + (uint64_t)(2 * ks), q_hi + (uint64_t)(2 * ks), idesc_u, ks > 0 ? 1u : 0u);
+#pragma unroll
+                            for (int ks = 0; ks < 4; ++ks)
+                                umma_bf16(d, da + (uint64_t)(2 * ks), q_lo + (uint64_t)(2 * ks), idesc_u, 1u);
+                        }
+                        umma_commit(f_full);
+                        umma_commit(cb_free + slot2);
+                    }
+                    __syncwarp();
+                    ++cb_used;
+                    fetch_next();
+                }
             }
             if (stop) break;
+            if (QUERY) continue;
             tc_fence_after();
 #pragma unroll 1
             for (int l = 0; l < levels; ++l) {
@@ -627,11 +687,25 @@ __global__ void __launch_bounds__(DECODE ? FD_THREADS : FD_THREADS_NODECODE, 1) 
                                 __syncwarp();
                                 if (lane == 0) mbar_arrive(f_free + fs);     // slot drained: the next MMA may overwrite it
                             }
-#ifdef FD_NOSTORE
-                            if (in && r[0] == 0x7fc12345u) {
-#else
-                            if (in) {
-#endif
+                            if (in && a.hwc) {
+                                // channels-last: this thread's 32 features are contiguous
+                                const size_t e0 = (((size_t)l * a.H + py) * a.W + px) * FD_D + (size_t)cg * FD_NFEAT + (size_t)hh * 32;
+                                if (OUT_BF16) {
+                                    uint4* o = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(a.out) + e0);
+#pragma unroll
+                                    for (int i = 0; i < 4; ++i)
+                                        o[i] = make_uint4(pack_bf16x2(__uint_as_float(r[8 * i]) * sc, __uint_as_float(r[8 * i + 1]) * sc),
+                                                          pack_bf16x2(__uint_as_float(r[8 * i + 2]) * sc, __uint_as_float(r[8 * i + 3]) * sc),
+                                                          pack_bf16x2(__uint_as_float(r[8 * i + 4]) * sc, __uint_as_float(r[8 * i + 5]) * sc),
+                                                          pack_bf16x2(__uint_as_float(r[8 * i + 6]) * sc, __uint_as_float(r[8 * i + 7]) * sc));
+                                } else {
+                                    float* o = reinterpret_cast<float*>(a.out) + e0;
+#pragma unroll
+                                    for (int i = 0; i < 8; ++i)
+                                        st_stream_f32x4(o + 4 * i, __uint_as_float(r[4 * i]) * sc, __uint_as_float(r[4 * i + 1]) * sc,
+                                                        __uint_as_float(r[4 * i + 2]) * sc, __uint_as_float(r[4 * i + 3]) * sc);
+                                }
+                            } else if (in) {
                                 const size_t d0 = (size_t)l * FD_D + (size_t)cg * FD_NFEAT + (size_t)hh * 32;
                                 uint64_t p[4];
                                 p[0] = (uint64_t)(uintptr_t)a.out + (d0 * HW + (size_t)py * a.W + px) * esz;
@@ -651,9 +725,6 @@ __global__ void __launch_bounds__(DECODE ? FD_THREADS : FD_THREADS_NODECODE, 1) 
                                         p[u] += s4;
                                     }
                                 }
-#ifdef FD_FENCE_PACE
-                                if ((f_n % FD_FENCE_PACE) == 0) __threadfence();
-#endif
                             }
                         }
                     }
@@ -802,10 +873,18 @@ __global__ void __launch_bounds__(DECODE ? FD_THREADS : FD_THREADS_NODECODE, 1) 
                 FD_TOCB(6);
             }
             if (count == -2) {
-                if (DECODE) {
+                if (WROWS) {
+                    // The terminating arrivals open a NEW phase of inv_full / wraw_full[0]: a warp that is through with the
+                    // last unit must not arrive while slower warps still owe their arrival of that unit's phase (8
+                    // arrivals complete a phase no matter who made them -- the epilogue would be released before the
+                    // slow warps' 1/norm values exist).
+                    if (units_done > 0) {
+                        mbar_wait(wraw_full, (units_done - 1) & 1);
+                        if (DECODE) mbar_wait(inv_full, (units_done - 1) & 1);
+                    }
                     if (tid == 0) { tinfo[units_done & 1].unit = -1; tinfo[units_done & 1].nb = 0; }
                     __syncwarp();
-                    if (lane == 0) { mbar_arrive(wraw_full); mbar_arrive(inv_full); }
+                    if (lane == 0) { mbar_arrive(wraw_full); if (DECODE) mbar_arrive(inv_full); }
                 }
                 break;
             }
@@ -817,8 +896,9 @@ __global__ void __launch_bounds__(DECODE ? FD_THREADS : FD_THREADS_NODECODE, 1) 
             mbar_wait(w_full, units_done & 1);
             FD_TOC(2);
             tc_fence_after();
-            if (DECODE) {
-                if (units_done > 0) mbar_wait(dec_done, (units_done - 1) & 1);     // previous decode is done with Wdec
+            if (WROWS) {
+                // the previous unit's MMAs are done with Wdec (query: its last product was waited for by every thread)
+                if (DECODE && units_done > 0) mbar_wait(dec_done, (units_done - 1) & 1);
                 FD_TOC(3);
                 if (tid == 0) { tinfo[units_done & 1].unit = unit; tinfo[units_done & 1].nb = nb; }
             }
@@ -839,7 +919,7 @@ __global__ void __launch_bounds__(DECODE ? FD_THREADS : FD_THREADS_NODECODE, 1) 
 #pragma unroll
                         for (int i = 0; i < 32; ++i) st_stream_f32(o + (size_t)i * HW, __uint_as_float(r[i]));
                     }
-                    if (DECODE) {
+                    if (WROWS) {
 #pragma unroll
                         for (int ch = 0; ch < 4; ++ch) {
                             uint32_t p[4];
@@ -851,14 +931,14 @@ __global__ void __launch_bounds__(DECODE ? FD_THREADS : FD_THREADS_NODECODE, 1) 
                         }
                     }
                 }
-                if (DECODE) {
+                if (WROWS) {
                     fence_async_smem();
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(wraw_full + l);
                 }
             }
-            if (!DECODE) tc_fence_before();
+            if (!WROWS) tc_fence_before();
             FD_TOC(4);
 
             if (inside) {
@@ -873,9 +953,11 @@ __global__ void __launch_bounds__(DECODE ? FD_THREADS : FD_THREADS_NODECODE, 1) 
             // |F|^2 = w^T (C C^T) w with w the fp16 row the decode multiplies: U = Wdec.G comes back in TMEM block
             // `half`, lane quadrant `strip`, i.e. for decode row nrow (not this thread's own pixel -- any thread may
             // serve any row, the rows are in shared memory).  The scale itself is applied in fp32 by the epilogue.
-            if (DECODE) {
+            if (WROWS) {
                 if (normalize) {
                     float* inv_u = s_inv + (size_t)(units_done & 1) * 3 * 256;
+                    // the decode row nrow is band row (nrow >> 5), column (nrow & 31)
+                    const int qx = (unit % a.ux) * FD_UNIT_W + (int)(nrow & 31u), qy = (unit / a.ux) * FD_UNIT_H + (int)(nrow >> 5);
                     for (int l = 0; l < levels; ++l) {
                         const unsigned char* Wl = wdec + (size_t)l * FD_WDEC_LEVEL;
                         mbar_wait(u_full + l, units_done & 1);
@@ -898,12 +980,46 @@ __global__ void __launch_bounds__(DECODE ? FD_THREADS : FD_THREADS_NODECODE, 1) 
                                 }
                             }
                         }
-                        inv_u[l * 256 + nrow] = 1.0f / (sqrtf(fmaxf(ss, 0.0f) * a.gscale_inv[l]) + 1e-10f);
+                        const float inv = 1.0f / (sqrtf(fmaxf(ss, 0.0f) * a.gscale_inv[l]) + 1e-10f);
+                        if (DECODE) inv_u[l * 256 + nrow] = inv;
+                        if (QUERY) {
+                            // similarities of the normalised feature with every phrase: sim = (w . M) / |F|; then
+                            // min over the negatives of softmax(10 [pos, neg])[0] = 1 / (1 + exp(10 (max neg - pos)))
+                            // (eval/openclip_encoder.py:126-137: the pairwise softmax is monotone in the negative)
+                            const uint32_t nq = units_done * (uint32_t)levels + (uint32_t)l;
+                            mbar_wait(f_full, nq & 1);
+                            tc_fence_after();
+                            uint32_t s0[32], s1[32];
+                            tmem_ld32(lane_base + (uint32_t)(FD_TMEM_F + half * 64), s0);
+                            tmem_ld32(lane_base + (uint32_t)(FD_TMEM_F + half * 64 + 32), s1);
+                            tmem_wait_ld();
+                            tc_fence_before();
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(f_free);             // the next level's product may land
+                            float maxneg = -1e30f;
+#pragma unroll
+                            for (int i = 0; i < 64; ++i) {
+                                const float v = __uint_as_float(i < 32 ? s0[i] : s1[i - 32]) * inv;
+                                if (i >= a.n_pos && i < a.n_pos + a.n_neg) maxneg = fmaxf(maxneg, v);
+                            }
+                            if (qx < a.W && qy < a.H) {
+                                float* o = a.qout + ((size_t)l * a.n_pos * a.H + qy) * a.W + qx;
+#pragma unroll
+                                for (int i = 0; i < 64; ++i) {
+                                    if (i < a.n_pos) {
+                                        const float v = __uint_as_float(i < 32 ? s0[i] : s1[i - 32]) * inv;
+                                        st_stream_f32(o + (size_t)i * HW, 1.0f / (1.0f + expf(10.0f * (maxneg - v))));
+                                    }
+                                }
+                            }
+                        }
                     }
                     tc_fence_before();
                 }
-                __syncwarp();
-                if (lane == 0) mbar_arrive(inv_full);
+                if (DECODE) {
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(inv_full);
+                }
             }
             FD_TOC(5);
             ++units_done;
@@ -955,13 +1071,14 @@ static void fd_fill_args(FdArgs& a, const lsv2_view& v, const lsv2_geom& g, cons
     a.color = img.color; a.wmap = img.wmap; a.final_T = img.final_T; a.n_contrib = img.n_contrib;
     a.status = b.status;
     a.bimg = nullptr; a.gimg = nullptr; a.gscale_inv = nullptr; a.out = nullptr; a.normalize = 0;
+    a.hwc = 0; a.qimg = nullptr; a.qout = nullptr; a.n_pos = 0; a.n_neg = 0;
     a.prof = nullptr;
     a.tile_counter = nullptr;
 }
 
 int launch_render_decode(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b, const lsv2_features& f,
                          const lsv2_image& img, const float* codebooks, int levels, int Lc, int D, int normalize,
-                         int out_dtype, void* out, void* scratch, size_t scratch_bytes, cudaStream_t st)
+                         int out_dtype, int out_hwc, void* out, void* scratch, size_t scratch_bytes, cudaStream_t st)
 {
     const int gx = (v.width + TILE - 1) / TILE, gy = (v.height + TILE - 1) / TILE;
     if (gx * gy == 0) return LSV2_OK;
@@ -985,7 +1102,7 @@ int launch_render_decode(const lsv2_view& v, const lsv2_geom& g, const lsv2_binn
 
     FdArgs a;
     fd_fill_args(a, v, g, b, f, img, gx, gy);
-    a.bimg = bimg; a.gimg = gimg; a.gscale_inv = gscale_inv; a.out = out; a.normalize = normalize;
+    a.bimg = bimg; a.gimg = gimg; a.gscale_inv = gscale_inv; a.out = out; a.normalize = normalize; a.hwc = out_hwc;
     a.tile_counter = counter;
 #ifdef FD_PROF
     a.prof = reinterpret_cast<long long*>(gimg + (size_t)levels * FD_CB_BYTES);
@@ -993,13 +1110,57 @@ int launch_render_decode(const lsv2_view& v, const lsv2_geom& g, const lsv2_binn
     const int grid = min(NUM_SMS, a.n_units);
 #define FD_LAUNCH(O)                                                                                            \
     do {                                                                                                        \
-        LSV2_CUDA_TRY(cudaFuncSetAttribute(k_render_decode<O, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+        LSV2_CUDA_TRY(cudaFuncSetAttribute(k_render_decode<O, FD_PATH_DECODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                            (int)FD_SMEM_TOTAL));                                                \
-        k_render_decode<O, true><<<grid, FD_THREADS, FD_SMEM_TOTAL, st>>>(a);                                   \
+        k_render_decode<O, FD_PATH_DECODE><<<grid, FD_THREADS, FD_SMEM_TOTAL, st>>>(a);                         \
     } while (0)
     if (out_dtype == 0) FD_LAUNCH(false); else FD_LAUNCH(true);
 #undef FD_LAUNCH
     LSV2_LAUNCH_CHECK("k_render_decode");
+    return LSV2_OK;
+}
+
+// Blend + relevancy query (eval/openclip_encoder.py:114-138 on top of eval_lerf.py:214-218): the 512-d map is never
+// formed -- sim = w^T (C E^T) / |C^T w| per level and phrase, then the pairwise softmax / min over the negatives.
+// scratch: counter | 1/s per level | Gram images | query images.
+size_t render_query_scratch_bytes(int levels)
+{
+    const size_t lv = (size_t)(levels > 0 ? levels : 1);
+    return 512 + 2 * lv * FD_CB_BYTES + 512;
+}
+
+int launch_render_query(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b, const lsv2_features& f,
+                        const lsv2_image& img, const float* codebooks, int levels, int Lc, int D, const float* embeds,
+                        int n_pos, int n_neg, float* out, void* scratch, size_t scratch_bytes, cudaStream_t st)
+{
+    const int gx = (v.width + TILE - 1) / TILE, gy = (v.height + TILE - 1) / TILE;
+    if (gx * gy == 0) return LSV2_OK;
+    if (!g.blend_rec || !codebooks || !embeds || !out) return LSV2_EINVAL;
+    if (Lc != FD_LC || D != FD_D || levels < 1 || levels * Lc > FD_MAX_L) return LSV2_EUNSUPPORTED;
+    if (n_pos < 1 || n_neg < 1 || n_pos + n_neg > 64) return LSV2_EUNSUPPORTED;
+    if (f.L != levels * Lc) return LSV2_EINVAL;
+    { const int rc = fd_check_features(f); if (rc) return rc; }
+    if (!scratch || scratch_bytes < render_query_scratch_bytes(levels)) return LSV2_ENOSPC;
+    uint8_t* base = reinterpret_cast<uint8_t*>(((uintptr_t)scratch + 127) & ~(uintptr_t)127);
+    uint32_t* counter = reinterpret_cast<uint32_t*>(base);
+    float* gscale_inv = reinterpret_cast<float*>(base + 128);
+    uint8_t* gimg = base + 256;
+    uint8_t* qimg = gimg + (size_t)levels * FD_CB_BYTES;
+    LSV2_CUDA_TRY(cudaMemsetAsync(counter, 0, sizeof(uint32_t), st));
+    k_fd_prep_g<<<dim3(FD_LC, levels), 64, 0, st>>>(codebooks, gimg, gscale_inv);
+    LSV2_LAUNCH_CHECK("k_fd_prep_g");
+    k_fd_prep_q<<<dim3(FD_LC, levels), 64, 0, st>>>(codebooks, embeds, n_pos + n_neg, qimg);
+    LSV2_LAUNCH_CHECK("k_fd_prep_q");
+    FdArgs a;
+    fd_fill_args(a, v, g, b, f, img, gx, gy);
+    a.gimg = gimg; a.gscale_inv = gscale_inv; a.qimg = qimg; a.qout = out; a.n_pos = n_pos; a.n_neg = n_neg;
+    a.normalize = 1;
+    a.tile_counter = counter;
+    const int grid = min(NUM_SMS, a.n_units);
+    LSV2_CUDA_TRY(cudaFuncSetAttribute(k_render_decode<false, FD_PATH_QUERY>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)FD_SMEM_TOTAL));
+    k_render_decode<false, FD_PATH_QUERY><<<grid, FD_THREADS, FD_SMEM_TOTAL, st>>>(a);
+    LSV2_LAUNCH_CHECK("k_render_decode<query>");
     return LSV2_OK;
 }
 
@@ -1019,9 +1180,9 @@ int launch_render_wmap_tc(const lsv2_view& v, const lsv2_geom& g, const lsv2_bin
     fd_fill_args(a, v, g, b, f, img, gx, gy);
     a.tile_counter = counter;
     const int grid = min(NUM_SMS, a.n_units);
-    LSV2_CUDA_TRY(cudaFuncSetAttribute(k_render_decode<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    LSV2_CUDA_TRY(cudaFuncSetAttribute(k_render_decode<false, FD_PATH_WMAP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)FD_SMEM_NODECODE_TOTAL));
-    k_render_decode<false, false><<<grid, FD_THREADS_NODECODE, FD_SMEM_NODECODE_TOTAL, st>>>(a);
+    k_render_decode<false, FD_PATH_WMAP><<<grid, FD_THREADS_NODECODE, FD_SMEM_NODECODE_TOTAL, st>>>(a);
     LSV2_LAUNCH_CHECK("k_render_decode<wmap>");
     return LSV2_OK;
 }

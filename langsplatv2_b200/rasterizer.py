@@ -348,10 +348,12 @@ def _dump_snapshot(path: str, items: dict) -> None:
 
 
 def render_decode(st: FrameState, codebooks: torch.Tensor, normalize: bool = True,
-                  out_dtype: torch.dtype = torch.float32, want_wmap: bool = False) -> torch.Tensor:
+                  out_dtype: torch.dtype = torch.float32, want_wmap: bool = False,
+                  out_layout: str = "CHW") -> torch.Tensor:
     """Fused blend + codebook decode on a frame that has been preprocessed and binned
-    (``rasterize_forward(..., render=False)``): -> ``[levels, 512, H, W]``; fills ``st.image`` (RGB, final_T,
-    n_contrib, and the weight map when ``want_wmap``).  The L-channel weight map never round-trips HBM."""
+    (``rasterize_forward(..., render=False)``): -> ``[levels, 512, H, W]`` (``out_layout="HWC"``: ``[levels, H, W,
+    512]``, the layout ``OpenCLIPNetwork.get_max_across_quick`` takes); fills ``st.image`` (RGB, final_T, n_contrib,
+    and the weight map when ``want_wmap``).  The L-channel weight map never round-trips HBM."""
     L_ = _abi.lib()
     if st.mode == MODE_RGB:
         raise _abi.Lsv2Error("render_decode needs include_feature / quick_render settings")
@@ -368,7 +370,10 @@ def render_decode(st: FrameState, codebooks: torch.Tensor, normalize: bool = Tru
         st.image.pop("wmap", None)
     elif "wmap" not in st.image:
         st.image["wmap"] = torch.empty((st.L, st.H, st.W), dtype=torch.float32, device=dev)
-    out = torch.empty((levels, D, st.H, st.W), dtype=out_dtype, device=dev)
+    if out_layout not in ("CHW", "HWC"):
+        raise ValueError("out_layout must be 'CHW' or 'HWC'")
+    hwc = out_layout == "HWC"
+    out = torch.empty((levels, st.H, st.W, D) if hwc else (levels, D, st.H, st.W), dtype=out_dtype, device=dev)
     nbytes = L_.lsv2_render_decode_scratch_bytes(levels)
     scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
     geom_c, bin_c, feat_c, img_c = st.c_geom(), st.c_binning(), st.c_features(), st.c_image()
@@ -379,9 +384,46 @@ def render_decode(st: FrameState, codebooks: torch.Tensor, normalize: bool = Tru
     feat_c = st.c_features()
     _abi.check(L_.lsv2_render_decode(C.byref(st.view), C.byref(geom_c), C.byref(bin_c), C.byref(feat_c),
                                      C.byref(img_c), cb.data_ptr(), levels, Lc, D, 1 if normalize else 0,
-                                     0 if out_dtype == torch.float32 else 1, out.data_ptr(), scratch.data_ptr(),
-                                     nbytes, _abi.stream_ptr(dev)), "lsv2_render_decode")
+                                     (0 if out_dtype == torch.float32 else 1) | (_abi.OUT_HWC if hwc else 0),
+                                     out.data_ptr(), scratch.data_ptr(), nbytes, _abi.stream_ptr(dev)),
+               "lsv2_render_decode")
     st.keep += [cb, scratch]
+    return out
+
+
+def render_query(st: FrameState, codebooks: torch.Tensor, phrase_embeds: torch.Tensor, n_pos: int) -> torch.Tensor:
+    """Fused blend + relevancy query on a preprocessed and binned frame: ``phrase_embeds [P + N, 512]`` (positives
+    first, as ``torch.cat([pos_embeds, neg_embeds])`` at eval/openclip_encoder.py:127) -> relevancy ``[levels, P, H, W]``
+    = ``OpenCLIPNetwork.get_max_across_quick`` of the decoded map (:114-138), without ever forming that map."""
+    L_ = _abi.lib()
+    if st.mode == MODE_RGB:
+        raise _abi.Lsv2Error("render_query needs include_feature / quick_render settings")
+    dev = st.status.device
+    cb = _f32c(codebooks.to(dev), "codebooks")
+    if cb.dim() == 2:
+        cb = cb.unsqueeze(0)
+    levels, Lc, D = (int(x) for x in cb.shape)
+    if levels * Lc != st.L:
+        raise ValueError(f"codebooks give {levels}x{Lc} channels, the frame has L={st.L}")
+    e = _f32c(phrase_embeds.to(dev), "phrase_embeds")
+    if e.dim() != 2 or e.shape[1] != D or not (0 < n_pos < e.shape[0]):
+        raise ValueError("phrase_embeds must be [P + N, D] with 0 < n_pos < P + N")
+    n_neg = int(e.shape[0]) - int(n_pos)
+    st.image.pop("wmap", None)
+    out = torch.empty((levels, n_pos, st.H, st.W), dtype=torch.float32, device=dev)
+    nbytes = L_.lsv2_render_query_scratch_bytes(levels)
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    geom_c, bin_c, feat_c, img_c = st.c_geom(), st.c_binning(), st.c_features(), st.c_image()
+    if st.mode == MODE_DENSE:
+        _abi.check(L_.lsv2_compact_coeff(st.P, C.byref(geom_c), C.byref(feat_c), _abi.stream_ptr(dev)),
+                   "lsv2_compact_coeff")
+    st.ensure_packed(geom_c)
+    feat_c = st.c_features()
+    _abi.check(L_.lsv2_render_query(C.byref(st.view), C.byref(geom_c), C.byref(bin_c), C.byref(feat_c),
+                                    C.byref(img_c), cb.data_ptr(), levels, Lc, D, e.data_ptr(), int(n_pos), n_neg,
+                                    out.data_ptr(), scratch.data_ptr(), nbytes, _abi.stream_ptr(dev)),
+               "lsv2_render_query")
+    st.keep += [cb, e, scratch]
     return out
 
 

@@ -21,14 +21,15 @@ import torch
 
 from . import _abi
 from .decode import decode_feature_map
-from .rasterizer import GaussianRasterizationSettings, FrameState, rasterize_forward, render_decode
+from .rasterizer import (GaussianRasterizationSettings, FrameState, rasterize_forward, render_decode,
+                         render_query)
 from .sparse import get_weights_and_indices
 
 
 class FeatureRenderer:
     def __init__(self, scene: Dict, topk: int = 4, device="cuda", precision: str = "bf16",
                  out_dtype: torch.dtype = torch.float32, bounded: bool = True, headroom: float = 1.25,
-                 fused: bool = True):
+                 fused: bool = True, out_layout: str = "CHW"):
         dev = torch.device(device)
         self.device = dev
         self.levels = int(scene["levels"])
@@ -50,6 +51,7 @@ class FeatureRenderer:
         self.indices = torch.cat(idx, dim=1).contiguous()
         self.precision = precision
         self.out_dtype = out_dtype
+        self.out_layout = out_layout            # "HWC": [levels, H, W, 512] (fused path only)
         self.bounded = bounded
         self.fused = fused and self.levels * self.codebook_size <= 192 and self.codebook_size == 64 \
             and int(self.codebooks.shape[2]) == 512 and topk * self.levels <= _abi.SPARSE_CAP
@@ -95,7 +97,8 @@ class FeatureRenderer:
             self.last_state = st
             if self.hook:
                 self.hook("decode_begin")
-            out = render_decode(st, self.codebooks, normalize=True, out_dtype=self.out_dtype)
+            out = render_decode(st, self.codebooks, normalize=True, out_dtype=self.out_dtype,
+                                out_layout=self.out_layout)
             if self.hook:
                 self.hook("decode_end")
             self.packed = st.feat.get("packed")
@@ -109,6 +112,28 @@ class FeatureRenderer:
                                  out_dtype=self.out_dtype)
         if self.hook:
             self.hook("decode_end")
+        return out
+
+    @torch.no_grad()
+    def query(self, cam: Dict, pos_embeds: torch.Tensor, neg_embeds: torch.Tensor) -> torch.Tensor:
+        """Open-vocabulary relevancy of the view for P positive phrases against N canonical negatives ->
+        ``[levels, P, H, W]``: what ``eval_lerf.py:351-352`` / ``backend_renderer.py:204-210`` compute with
+        ``render_language_feature_map_quick`` + ``get_max_across_quick``, in one kernel and without the 512-d map
+        (``lsv2_render_query``).  ``pos_embeds [P, 512]``, ``neg_embeds [N, 512]``: unit-norm CLIP text embeddings."""
+        if not self.fused:
+            raise _abi.Lsv2Error("query() needs the fused kernel's shapes (3 x 64 codes, 512-d)")
+        cap = self.capacity if self.bounded else None
+        if self.bounded and cap is None:
+            cap = self.calibrate([cam])
+        st = self._raster(cam, cap, render=False)
+        self.last_state = st
+        if self.hook:
+            self.hook("decode_begin")
+        e = torch.cat([pos_embeds.to(self.device, torch.float32), neg_embeds.to(self.device, torch.float32)], dim=0)
+        out = render_query(st, self.codebooks, e, int(pos_embeds.shape[0]))
+        if self.hook:
+            self.hook("decode_end")
+        self.packed = st.feat.get("packed")
         return out
 
     def check_overflow(self) -> None:

@@ -215,3 +215,21 @@ def forward(scene: dict, view: dict, mode: int = 0, L: int = 0, coeff_dense=None
     fwd = render_forward(pre, binned, W, H, bg, mode=mode, L=L, coeff_dense=coeff_dense,
                          weights_quick=weights_quick, indices_quick=indices_quick)
     return pre, binned, fwd
+
+
+def relevancy(feature_map, phrase_embeds, n_pos: int):
+    """Restatement of OpenCLIPNetwork.get_max_across_quick (/root/reference/eval/openclip_encoder.py:114-138):
+    feature_map [levels, 512, H, W] (the decoded, normalised map), phrase_embeds [P+N, 512] (positives first) ->
+    relevancy [levels, P, H, W] = min over the negatives of softmax(10 * [pos, neg])[0], in float32 like the
+    reference (einsum, pairwise softmax over the stacked pair, min)."""
+    f = _f32(feature_map)
+    e = _f32(phrase_embeds)
+    levels, D, H, W = f.shape
+    sim = np.einsum("ldn,pd->lnp", f.reshape(levels, D, H * W), e).astype(np.float32)        # [levels, HW, P+N]
+    pos, neg = sim[:, :, :n_pos], sim[:, :, n_pos:]
+    a = (np.float32(10.0) * pos)[:, :, :, None]                                              # [levels, HW, P, 1]
+    b = (np.float32(10.0) * neg)[:, :, None, :]                                              # [levels, HW, 1, N]
+    m = np.maximum(a, b)
+    ea, eb = np.exp(a - m, dtype=np.float32), np.exp(b - m, dtype=np.float32)
+    p0 = ea / (ea + eb)                                                                      # softmax(...)[..., 0]
+    return np.ascontiguousarray(p0.min(axis=-1).transpose(0, 2, 1).reshape(levels, n_pos, H, W))

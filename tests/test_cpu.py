@@ -532,3 +532,17 @@ def test_sharded_exchange_equals_allreduce_gloo(tmp_path):
     for p in procs:
         out, _ = p.communicate(timeout=180)
         assert p.returncode == 0, out.decode()[-2000:]
+
+
+# ------------------------------------------------------------------------------------------------
+# golden vectors: relevancy query (eval/openclip_encoder.py:114-138), generated by running the reference
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("tag", ["a", "b", "c"])
+def test_golden_relevancy_query(tag):
+    Q = np.load(os.path.join(ROOT, "tests", "golden", "reference_query.npz"))
+    sem = Q[f"{tag}_sem"]                                    # [levels, H, W, 512] as the reference takes it
+    embeds = np.concatenate([Q[f"{tag}_pos"], Q[f"{tag}_neg"]], 0)
+    got = oracle.relevancy(np.ascontiguousarray(sem.transpose(0, 3, 1, 2)), embeds, Q[f"{tag}_pos"].shape[0])
+    assert got.shape == Q[f"{tag}_relev"].shape
+    np.testing.assert_allclose(got, Q[f"{tag}_relev"], rtol=0, atol=2e-6)
+    assert np.allclose(got[0, :, 0, 0], 0.5)                 # the empty pixel: every similarity is 0
