@@ -332,13 +332,13 @@ def run_train(args, dev, rank, world, scene, barrier, wl=None):
     my_views = [v for v in range(VIEWS) if v % world == rank][:4]
     cams = {v: {k: (x.to(dev) if torch.is_tensor(x) else x) for k, x in cams[v].items()} for v in my_views}
     gts = {v: synthetic_gt(H, W, device=dev, seed=2 + v) for v in my_views}
-    use_graph = world == 1 and not args.no_graph
+    use_graph = not args.no_graph
     tr = FeatureTrainer(scene, topk=TOPK, layers=1, device=dev, use_graph=use_graph)
     tr.calibrate([cams[v] for v in my_views])          # exact instance counts of the views this rank trains on
     n_warm = (2 * len(my_views) + 2) if world == 1 else 12
     for v in my_views:                                  # one eager iteration per view (lazy initialisations, allocator)
         tr.step(cams[v], *gts[v])
-    graph_note = "CUDA graph per view (captured after calibration)" if use_graph else "eager launches"
+    graph_note = ("CUDA graph per view (captured after calibration%s)" % (", NCCL exchange inside the graph" if world > 1 else "")) if use_graph else "eager launches"
     try:
         for s in range(n_warm):
             v = my_views[s % len(my_views)]
@@ -416,7 +416,24 @@ def run_reference_style(r, cams, steps, dev):
     del out
     torch.backends.cuda.matmul.allow_tf32 = allow
     ms = b.elapsed_time(e) / steps
+    # the op alone (what this repo replaces) vs the reference's own torch decode lines on top of it
+    def op_only(cam):
+        with torch.no_grad():
+            rast = GaussianRasterizer(raster_settings=r.settings(cam))
+            return rast(means3D=r.xyz, means2D=None, shs=r.features, colors_precomp=None, language_feature_precomp=zero,
+                        language_feature_weights_quick=r.weights, language_feature_indices=r.indices, opacities=r.opacity,
+                        scales=r.scaling, rotations=r.rotation, cov3D_precomp=None)[1]
+    op_only(cams[0])
+    torch.cuda.synchronize(dev)
+    b.record()
+    for s in range(steps):
+        wm = op_only(cams[s % len(cams)])
+    e.record()
+    torch.cuda.synchronize(dev)
+    del wm
+    op_ms = b.elapsed_time(e) / steps
     return {"value": 1e3 / ms, "unit": UNIT, "ms_per_step": ms, "steps": steps,
+            "op_ms": op_ms, "op_fps": 1e3 / op_ms, "torch_decode_ms": ms - op_ms,
             "what": "drop-in 3-tuple API (host sync per frame, fp32 weight map) + the reference's torch einsum/norm/divide "
                     "(eval_lerf.py:214-218); rasterizer kernels are this repo's"}
 
@@ -519,7 +536,8 @@ def run_gpu(args, wl):
     # Every view's camera block sits in ONE pinned host tensor (packed once, outside the timed region, as a server
     # holds its trajectory); per frame: H2D of the 35 floats, the frame's kernels, D2H of RGB + status on a copy stream
     # under the next frames' kernels.  A ring of RING frames is in flight; the host only waits for frame s - RING.
-    RING = 4
+    out_bytes_frame = LEVELS * D * H * W * (4 if r.out_dtype == torch.float32 else 2)
+    RING = 4 if 4 * out_bytes_frame < 70e9 else 2          # every captured frame owns its output buffers
     cpu_cams = [{k: (v.cpu() if torch.is_tensor(v) else v) for k, v in cams[v].items()} for v in my_views]
     host_cams = torch.empty((len(cpu_cams), 35), dtype=torch.float32).pin_memory()
     for i, c in enumerate(cpu_cams):
@@ -532,6 +550,22 @@ def run_gpu(args, wl):
     dev_cam = [torch.empty(35, dtype=torch.float32, device=dev) for _ in range(RING)]
     done = [None] * RING
     keep = [None] * RING
+    # one captured frame per ring slot (FeatureRenderer.graphed): the slot's camera tensor is rewritten by the H2D copy,
+    # the frame is ONE graph launch; falls back to eager launches if the capture is refused
+    frames = None
+    if not args.no_graph and RING * out_bytes_frame < 70e9:
+        try:
+            frames = []
+            for i in range(RING):
+                dc = dev_cam[i]
+                dc.copy_(host_cams[0], non_blocking=True)
+                cam_i = dict(cpu_cams[0], world_view_transform=dc[:16].view(4, 4), full_proj_transform=dc[16:32].view(4, 4),
+                             camera_center=dc[32:35])
+                frames.append(r.graphed(cam_i))
+        except Exception as exc:
+            print("bench: frame capture failed, e2e runs eager launches:", str(exc)[:200], file=sys.stderr)
+            frames = None
+            torch.cuda.synchronize(dev)
 
     def e2e_step(s):
         i = s % RING
@@ -540,10 +574,14 @@ def run_gpu(args, wl):
         v = s % len(cpu_cams)
         dc = dev_cam[i]
         dc.copy_(host_cams[v], non_blocking=True)
-        cam = dict(cpu_cams[v], world_view_transform=dc[:16].view(4, 4), full_proj_transform=dc[16:32].view(4, 4),
-                   camera_center=dc[32:35])
-        f = r.render(cam)
-        st = r.last_state
+        if frames is not None:
+            f = frames[i].replay()
+            st = frames[i].state
+        else:
+            cam = dict(cpu_cams[v], world_view_transform=dc[:16].view(4, 4), full_proj_transform=dc[16:32].view(4, 4),
+                       camera_center=dc[32:35])
+            f = r.render(cam)
+            st = r.last_state
         ready = torch.cuda.Event()
         ready.record(torch.cuda.current_stream(dev))
         with torch.cuda.stream(copy_stream):
@@ -552,8 +590,9 @@ def run_gpu(args, wl):
             host_status[i].copy_(st.status, non_blocking=True)
             ev_done = torch.cuda.Event()
             ev_done.record(copy_stream)
-        st.image["color"].record_stream(copy_stream)
-        st.status.record_stream(copy_stream)
+        if frames is None:
+            st.image["color"].record_stream(copy_stream)
+            st.status.record_stream(copy_stream)
         done[i] = ev_done
         keep[i] = f
         return f
@@ -576,6 +615,44 @@ def run_gpu(args, wl):
     barrier()
     assert all(int(h[1]) == 0 for h in host_status), "instance capacity overflow during the e2e run"
     keep = [None] * RING
+    e2e_launch = "one CUDA-graph launch per frame (FeatureRenderer.graphed)" if frames is not None else "eager launches"
+    frames = None
+    torch.cuda.empty_cache()
+
+    # ---- open-vocabulary query: blend + relevancy epilogue, the 512-d map never written ----
+    query = None
+    if fused and not args.no_query:
+        gq = torch.Generator().manual_seed(5)
+        pos = torch.nn.functional.normalize(torch.randn(8, D, generator=gq), dim=-1).to(dev)
+        neg = torch.nn.functional.normalize(torch.randn(4, D, generator=gq), dim=-1).to(dev)
+        qev = {"b": [], "e": []}
+        r.hook = lambda tag: (qev["b" if tag == "decode_begin" else "e"].append(torch.cuda.Event(enable_timing=True)),
+                              qev["b" if tag == "decode_begin" else "e"][-1].record(torch.cuda.current_stream(dev)))
+        for s in range(3):
+            rel = r.query(cams[my_views[s % len(my_views)]], pos, neg)
+        qev["b"].clear(); qev["e"].clear()
+        barrier()
+        q_b, q_e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        q_b.record()
+        for s in range(args.steps):
+            rel = r.query(cams[my_views[s % len(my_views)]], pos, neg)
+        q_e.record()
+        barrier()
+        r.hook = None
+        q_ms = q_b.elapsed_time(q_e)
+        qk_ms = float(np.mean([b.elapsed_time(e) for b, e in zip(qev["b"], qev["e"])]))
+        tq = torch.tensor([q_ms, qk_ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tq, op=dist.ReduceOp.MAX)
+        q_ms, qk_ms = (float(x) for x in tq.tolist())
+        q_bytes = consumed * (4 + 48 + 96) + 20 * H * W + LEVELS * 8 * H * W * 4
+        query = {"metric": "open-vocabulary relevancy FPS (8 phrases vs 4 negatives, 3 levels)", "value": world * args.steps / (q_ms * 1e-3),
+                 "unit": UNIT, "ms_per_step": q_ms / args.steps, "kernel_ms": qk_ms,
+                 "what": "FeatureRenderer.query(): blend -> sim = w^T (C E^T) / |C^T w| -> pairwise softmax / min over negatives "
+                         "(eval/openclip_encoder.py:114-138) in the blend kernel; output [3, 8, H, W] fp32, no 512-d map",
+                 "roofline": {"bound": "latency / issue of the blend (the 12.7 GB feature write is gone)", "algorithmic_bytes_per_launch": q_bytes,
+                              "achieved": q_bytes / (qk_ms * 1e-3) / 1e9, "unit": "GB/s"}}
+        del rel
 
     ref_style = None
     if world == 1 and not args.no_reference_style:
@@ -629,7 +706,8 @@ def run_gpu(args, wl):
             "clocks": clocks,
             "e2e": {"value": world * args.steps / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 35 * 4,
                     "d2h_bytes_per_step": 3 * HW * 4 + 32,
-                    "note": "camera from pinned host memory; RGB render + status read back to the host (ring of 4 frames in flight: frame k's D2H under the next frames' kernels; host wall clock until the last frame is on the host); the 512-d map stays on the device as in the reference's API"},
+                    "launch": e2e_launch,
+                    "note": "camera from pinned host memory; RGB render + status read back to the host (ring of %d frames in flight: frame k's D2H under the next frames' kernels; host wall clock until the last frame is on the host); the 512-d map stays on the device as in the reference's API" % RING},
             "gpu_launches": kernels_per_frame(W, H, fused) * args.steps,
             "roofline": {"kernel": dom_name, "bound": "hbm", "achieved": achieved,
                          "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -641,6 +719,8 @@ def run_gpu(args, wl):
             line["train"] = train
         if ref_style is not None:
             line["reference_style"] = ref_style
+        if query is not None:
+            line["query"] = query
         if world == 1 and not args.no_cpu_baseline:
             est, sample, threads = cpu_frame_time(scene, cpu_cams[0], wl, budget_s=20.0)
             line["cpu_baseline"] = {"value": 1.0 / est, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample}
@@ -664,6 +744,7 @@ def main():
     ap.add_argument("--train-steps", type=int, default=200)
     ap.add_argument("--unfused", action="store_true", help="two-call path: blend to an fp32 weight map, then decode")
     ap.add_argument("--gaussians", type=int, default=0, help="override the workload's Gaussian count (config 5 sweep)")
+    ap.add_argument("--no-query", action="store_true", help="skip the relevancy-query measurement")
     ap.add_argument("--no-graph", action="store_true", help="train iterations as eager launches instead of CUDA graphs")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

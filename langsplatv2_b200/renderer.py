@@ -136,8 +136,41 @@ class FeatureRenderer:
         self.packed = st.feat.get("packed")
         return out
 
+    def graphed(self, cam: Dict) -> "GraphedFrame":
+        """Capture one frame of this renderer as a CUDA graph bound to ``cam``'s device tensors: write a new camera into
+        those tensors (e.g. an H2D copy on the same stream), call ``.replay()``, read ``.out`` / ``.state``.  A bounded,
+        calibrated frame makes no host decision, so the whole frame -- ~20 launches and their allocations -- becomes
+        one launch; outputs are static buffers owned by the graph."""
+        return GraphedFrame(self, cam)
+
     def check_overflow(self) -> None:
         st = self.last_state
         if st is not None and st.overflowed:
             raise _abi.Lsv2Error(f"instance capacity {st.capacity} overflowed ({st.num_rendered} needed); "
                                  "call calibrate() with representative views")
+
+
+class GraphedFrame:
+    """One captured frame (see ``FeatureRenderer.graphed``).  The camera matrices are read from the device tensors of
+    the ``cam`` dict given at capture time on every replay; intrinsics and image size are baked in."""
+
+    def __init__(self, renderer: FeatureRenderer, cam: Dict):
+        if not renderer.bounded:
+            raise _abi.Lsv2Error("a captured frame needs bounded=True (no host read of the instance count)")
+        if renderer.capacity is None:
+            renderer.calibrate([cam])
+        for k in ("world_view_transform", "full_proj_transform", "camera_center"):
+            if not (torch.is_tensor(cam[k]) and cam[k].is_cuda):
+                raise _abi.Lsv2Error(f"cam['{k}'] must be a CUDA tensor that stays alive and is rewritten in place")
+        self.renderer, self.cam = renderer, cam
+        renderer.render(cam)                               # eager once: packed table, lazy initialisations
+        torch.cuda.synchronize(renderer.device)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.out = renderer.render(cam)
+        self.state = renderer.last_state
+
+    def replay(self) -> torch.Tensor:
+        self.graph.replay()
+        self.renderer.last_state = self.state
+        return self.out

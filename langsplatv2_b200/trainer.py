@@ -132,7 +132,8 @@ class FeatureTrainer:
         self._last_state = None
         self._sticky = torch.zeros(2, dtype=torch.int32, device=dev)   # [overflow seen, max instances seen]
         self.overflow_events = 0
-        self.use_graph = bool(use_graph) and self.world == 1 and dev.type == "cuda"
+        # at N > 1 the captured iteration contains the NCCL reduce-scatter / all-gather (side stream, joined back)
+        self.use_graph = bool(use_graph) and dev.type == "cuda"
         self._graphs = {}
         self._graph_pool = None
 
