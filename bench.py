@@ -537,7 +537,8 @@ def run_gpu(args, wl):
     # holds its trajectory); per frame: H2D of the 35 floats, the frame's kernels, D2H of RGB + status on a copy stream
     # under the next frames' kernels.  A ring of RING frames is in flight; the host only waits for frame s - RING.
     out_bytes_frame = LEVELS * D * H * W * (4 if r.out_dtype == torch.float32 else 2)
-    RING = 4 if 4 * out_bytes_frame < 70e9 else 2          # every captured frame owns its output buffers
+    RING = 4 if 4 * out_bytes_frame < 70e9 else (2 if 4 * out_bytes_frame < 140e9 else 1)   # frames in flight hold their outputs
+    out = None
     cpu_cams = [{k: (v.cpu() if torch.is_tensor(v) else v) for k, v in cams[v].items()} for v in my_views]
     host_cams = torch.empty((len(cpu_cams), 35), dtype=torch.float32).pin_memory()
     for i, c in enumerate(cpu_cams):
