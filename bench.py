@@ -93,12 +93,38 @@ class ClockSampler:
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         self.p = None
 
-    def start(self):
+    def start(self, wait_first: float = 10.0):
+        """Starts nvidia-smi and waits until its first line is out (its start-up takes longer than a short timed
+        region), so that every later line is a sample under whatever the GPU is doing then."""
         try:
             self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                       "-lms", "200", "-i", str(self.gpu)], stdout=self.f, stderr=subprocess.DEVNULL)
+                                       "-lms", "100", "-i", str(self.gpu)], stdout=self.f, stderr=subprocess.DEVNULL)
         except Exception:
             self.p = None
+            return
+        t0 = time.perf_counter()
+        while self.lines() == 0 and time.perf_counter() - t0 < wait_first and self.p.poll() is None:
+            time.sleep(0.02)
+        self.skip = self.lines()          # samples before the load starts are not counted
+
+    def lines(self) -> int:
+        try:
+            with open(self.f.name) as fh:
+                return sum(1 for _ in fh)
+        except OSError:
+            return 0
+
+    def samples_under_load(self) -> int:
+        return max(0, self.lines() - getattr(self, "skip", 0))
+
+    def keep_loaded(self, step_fn, want: int = 3, limit_s: float = 3.0) -> None:
+        """A timed region shorter than a few sampling periods: keep the SAME load running, untimed, until ``want``
+        samples exist (the clocks line is about the load, not about the stopwatch)."""
+        if self.p is None:
+            return
+        t0 = time.perf_counter()
+        while self.samples_under_load() < want and time.perf_counter() - t0 < limit_s:
+            step_fn()
 
     def stop(self):
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
@@ -113,7 +139,7 @@ class ClockSampler:
         self.f.seek(0)
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for line in self.f.read().splitlines():
+        for line in self.f.read().splitlines()[getattr(self, "skip", 0):]:
             parts = [x.strip() for x in line.split(",")]
             if len(parts) < 9:
                 continue
@@ -505,8 +531,8 @@ def run_gpu(args, wl):
     # ---- device-resident throughput ("value") ----
     r.hook = hook
     sampler = ClockSampler(local)
-    barrier()
     sampler.start()
+    barrier()
     t_b, t_e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t_b.record()
     realised = 0
@@ -514,6 +540,11 @@ def run_gpu(args, wl):
         out = r.render(cams[my_views[s % len(my_views)]])
     t_e.record()
     barrier()
+
+    def _same_load():
+        r.render(cams[my_views[0]])
+        torch.cuda.synchronize(dev)
+    sampler.keep_loaded(_same_load)
     clocks = sampler.stop()
     r.check_overflow()
     realised = r.last_state.num_rendered
@@ -618,6 +649,10 @@ def run_gpu(args, wl):
     keep = [None] * RING
     e2e_launch = "one CUDA-graph launch per frame (FeatureRenderer.graphed)" if frames is not None else "eager launches"
     frames = None
+    out = None                                                 # the last frame's map (51 GB at 4k) and the graph pools
+    import gc
+    gc.collect()
+    torch.cuda.empty_cache()
     torch.cuda.empty_cache()
 
     # ---- open-vocabulary query: blend + relevancy epilogue, the 512-d map never written ----
@@ -659,7 +694,13 @@ def run_gpu(args, wl):
     if world == 1 and not args.no_reference_style:
         del out
         torch.cuda.empty_cache()
-        ref_style = run_reference_style(r, [cams[v] for v in my_views], min(args.steps, 10), dev)
+        try:
+            ref_style = run_reference_style(r, [cams[v] for v in my_views], min(args.steps, 10), dev)
+        except torch.OutOfMemoryError as ex:
+            # the reference's decode lines hold the un-normalised map, its norm and the result at once (2 x 51 GB at 4k)
+            ref_style = {"unavailable": "the reference's torch decode (einsum + norm + divide) ran out of device memory "
+                                        "at this size: " + str(ex).split(".")[0]}
+            torch.cuda.empty_cache()
         out = None
     train = None
     if not args.no_train:

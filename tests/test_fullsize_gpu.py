@@ -87,6 +87,10 @@ def test_full_size_frame(W, H, stride):
         assert torch.equal(st.image[k], un.image[k]), k
     wm = un.image["wmap"][:, torch.as_tensor(mask, device="cuda")].cpu().numpy()
     assert np.max(np.abs(wm - fwd["wmap"][:, mask])) <= 1e-5
+    # conservation over the whole frame: each level's top-k coefficients sum to 1 per Gaussian, so the 64 channels of
+    # a level sum to the blended opacity sum_i alpha_i T_i = 1 - T_final
+    lvl = un.image["wmap"].view(3, 64, H, W).sum(dim=1)
+    assert float((lvl - (1.0 - un.image["final_T"]).unsqueeze(0)).abs().max()) <= 2e-4
 
 
 def test_config4_forward_backward_adjoint_identity():
