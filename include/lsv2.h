@@ -218,6 +218,37 @@ int lsv2_render_backward(const lsv2_view* view, const lsv2_geom* geom, const lsv
                          const float* dL_dwmap, const float* dL_dcolor, int32_t dense_grad,
                          float* dL_dcoeff, float* dL_dcolors, void* stream);
 
+/* ---- RGB-stage backward (replaces _C.rasterize_gaussians_backward for train.py WITHOUT --include_feature:
+ *      train.py:169-172 l1 + ssim on the RGB render, :247-258 optimizer / densification;
+ *      gradients reach means3D, means2D, shs / colors_precomp, opacities, scales, rotations / cov3D_precomp
+ *      exactly as gaussian_renderer/__init__.py:108-119 passes them) ----------------------------------------
+ * Step 1, lsv2_render_backward_rgb: per-Gaussian sums over all pixels the Gaussian contributed to,
+ *   acc f32[P][LSV2_GEOM_ACC], ZERO-initialised by the caller:
+ *   [0..2] sum w dL/dC_rgb            (w = alpha T)            -> dL/d rgb
+ *   [3]    sum q                      (q = G dL/dalpha)        -> dL/d opacity
+ *   [4..5] sum q dx, sum q dy         (d = mean2D - pixel)
+ *   [6..8] sum q dx^2, q dx dy, q dy^2
+ *   image->color must be the forward's output (background included), image->n_contrib its contributor counts.
+ * Step 2, lsv2_preprocess_backward: pulls acc through conic -> cov2D -> cov3D -> scale / rotation, the projection
+ *   and SH -> RGB.  Every non-NULL array of lsv2_geom_grads is fully written (zeros for culled Gaussians).
+ *   means2d receives (dL/dpx * W/2, dL/dpy * H/2, 0): the gradient with respect to the NDC-scaled screen point,
+ *   which is what the callers read as a densification statistic (scene/gaussian_model.py:506-508). */
+#define LSV2_GEOM_ACC 12
+typedef struct lsv2_geom_grads {
+    float* means3d;     /* f32[P][3]     */
+    float* means2d;     /* f32[P][3]     */
+    float* opacities;   /* f32[P]        */
+    float* scales;      /* f32[P][3]     (scales / rotations path)  */
+    float* rotations;   /* f32[P][4]     16-byte aligned            */
+    float* cov3d;       /* f32[P][6]     (cov3d_precomp path)       */
+    float* shs;         /* f32[P][M][3]  (shs path)                 */
+    float* colors;      /* f32[P][3]     (colors_precomp path)      */
+} lsv2_geom_grads;
+int lsv2_render_backward_rgb(const lsv2_view* view, const lsv2_geom* geom, const lsv2_binning* binning,
+                             const lsv2_image* image, const float* dL_dcolor, float* acc, void* stream);
+int lsv2_preprocess_backward(const lsv2_view* view, const lsv2_scene* scene, const lsv2_geom* geom,
+                             const float* acc, const lsv2_geom_grads* grads, void* stream);
+
 /* ---- global codebook decode (eval_lerf.py:214-218; scene/gaussian_model.py:533-549) ---
  * wmap f32[levels*Lc][HW], codebooks f32[levels][Lc][D] -> out [levels][D][HW]
  * out = C_l^T W_l, optionally divided by (||.||_2 over D + 1e-10).

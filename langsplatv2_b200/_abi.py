@@ -60,6 +60,14 @@ class Image(C.Structure):
     _fields_ = [("color", _vp), ("wmap", _vp), ("final_T", _vp), ("n_contrib", _vp)]
 
 
+class GeomGrads(C.Structure):
+    _fields_ = [("means3d", _vp), ("means2d", _vp), ("opacities", _vp), ("scales", _vp), ("rotations", _vp),
+                ("cov3d", _vp), ("shs", _vp), ("colors", _vp)]
+
+
+GEOM_ACC = 12
+
+
 EXPORTS = [
     "lsv2_abi_version", "lsv2_strerror", "lsv2_last_cuda_error", "lsv2_sort_scratch_bytes",
     "lsv2_preprocess", "lsv2_bin", "lsv2_compact_coeff", "lsv2_render_forward", "lsv2_forward",
@@ -69,6 +77,7 @@ EXPORTS = [
     "lsv2_gram_loss_forward_seg", "lsv2_gram_loss_backward_seg",
     "lsv2_render_decode_scratch_bytes", "lsv2_render_decode", "lsv2_render_forward_tc", "lsv2_adam_step", "lsv2_pack_coeff",
     "lsv2_render_query_scratch_bytes", "lsv2_render_query",
+    "lsv2_render_backward_rgb", "lsv2_preprocess_backward",
 ]
 
 _lib = None
@@ -110,6 +119,8 @@ def lib() -> C.CDLL:
     L.lsv2_mark_visible.argtypes = [C.c_int32, _vp, _vp, _vp, _vp]
     L.lsv2_render_backward.argtypes = [P(View), P(Geom), P(Binning), P(Features), P(Image), _vp, _vp,
                                        C.c_int32, _vp, _vp, _vp]
+    L.lsv2_render_backward_rgb.argtypes = [P(View), P(Geom), P(Binning), P(Image), _vp, _vp, _vp]
+    L.lsv2_preprocess_backward.argtypes = [P(View), P(Scene), P(Geom), _vp, P(GeomGrads), _vp]
     L.lsv2_decode_scratch_bytes.restype = C.c_size_t
     L.lsv2_decode_scratch_bytes.argtypes = [C.c_int32, C.c_int32, C.c_int32]
     L.lsv2_decode.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int64, _vp, _vp, C.c_int32, C.c_int32,
@@ -135,8 +146,8 @@ def lib() -> C.CDLL:
     L.lsv2_adam_step.argtypes = [_vp, _vp, _vp, _vp, C.c_int64, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int64,
                                  C.c_int32, _vp, _vp]
     for name in ("lsv2_preprocess", "lsv2_bin", "lsv2_compact_coeff", "lsv2_render_forward", "lsv2_forward",
-                 "lsv2_mark_visible", "lsv2_render_backward", "lsv2_decode", "lsv2_decode_backward",
-                 "lsv2_topk_soft_code", "lsv2_topk_soft_code_backward", "lsv2_cos_loss_forward", "lsv2_cos_loss_backward",
+                 "lsv2_mark_visible", "lsv2_render_backward", "lsv2_render_backward_rgb", "lsv2_preprocess_backward",
+                 "lsv2_decode", "lsv2_decode_backward", "lsv2_topk_soft_code", "lsv2_topk_soft_code_backward", "lsv2_cos_loss_forward", "lsv2_cos_loss_backward",
                  "lsv2_gram_loss_forward", "lsv2_gram_loss_backward", "lsv2_colsumsq", "lsv2_segment_sum", "lsv2_render_decode",
                  "lsv2_render_forward_tc", "lsv2_gram_loss_forward_seg", "lsv2_gram_loss_backward_seg", "lsv2_adam_step", "lsv2_pack_coeff", "lsv2_render_query"):
         getattr(L, name).restype = C.c_int

@@ -210,6 +210,20 @@ int lsv2_render_backward(const lsv2_view* view, const lsv2_geom* geom, const lsv
                                   dL_dcoeff, dL_dcolors, (cudaStream_t)stream);
 }
 
+int lsv2_render_backward_rgb(const lsv2_view* view, const lsv2_geom* geom, const lsv2_binning* binning,
+                             const lsv2_image* image, const float* dL_dcolor, float* acc, void* stream)
+{
+    if (!view_ok(view) || !geom || !binning || !image) return LSV2_EINVAL;
+    return launch_render_backward_rgb(*view, *geom, *binning, *image, dL_dcolor, acc, (cudaStream_t)stream);
+}
+
+int lsv2_preprocess_backward(const lsv2_view* view, const lsv2_scene* scene, const lsv2_geom* geom, const float* acc,
+                             const lsv2_geom_grads* grads, void* stream)
+{
+    if (!view_ok(view) || !scene || !geom || !grads || scene->P < 0) return LSV2_EINVAL;
+    return launch_preprocess_backward(*view, *scene, *geom, acc, *grads, (cudaStream_t)stream);
+}
+
 size_t lsv2_decode_scratch_bytes(int32_t levels, int32_t Lc, int32_t D)
 {
     return decode_tc_scratch_bytes(levels, Lc, D);

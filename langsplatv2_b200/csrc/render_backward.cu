@@ -14,7 +14,8 @@
 namespace lsv2 {
 
 constexpr int RB_THREADS = TILE_PIX;
-constexpr int RB_BATCH = 128;
+constexpr int RB_WARPS = RB_THREADS / 32;
+constexpr int RB_BATCH = 64;
 constexpr int RB_KMAX = LSV2_SPARSE_CAP;
 constexpr uint32_t RB_ROW_DENSE = 0xFFFFFFFFu;
 
@@ -22,8 +23,7 @@ struct BackArgs {
     int W, H, gx, L;
     const uint2* ranges;
     const uint32_t* point_list;
-    const float2* xy;
-    const float4* conic_opacity;
+    const float4* rec;               // packed blend record of the forward (preprocess.cu): same alpha, same cut-off
     const uint32_t* n_contrib;
     const uint32_t* sp_count;
     const uint16_t* sp_index;
@@ -35,12 +35,11 @@ struct BackArgs {
 };
 
 struct BackInstance {
-    float2 xy;
-    float ax, b, az, op;
-    float thr;
+    float x, y, ax, b;
+    float az, thr, op, ext_y;
     uint32_t gid;
     uint32_t cnt;
-    uint32_t pad;
+    uint32_t pad0, pad1;
 };
 
 __device__ __forceinline__ float warp_sum(float v)
@@ -51,26 +50,29 @@ __device__ __forceinline__ float warp_sum(float v)
 }
 
 template <bool DENSE_GRAD, bool COLOR>
-__global__ void __launch_bounds__(RB_THREADS) k_render_backward(BackArgs a)
+__global__ void __launch_bounds__(RB_THREADS, 2) k_render_backward(BackArgs a)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     BackInstance* s_inst = reinterpret_cast<BackInstance*>(smem_raw);
     uint16_t* s_sidx = reinterpret_cast<uint16_t*>(s_inst + RB_BATCH);
-    float* s_grad = reinterpret_cast<float*>(s_sidx + RB_BATCH * RB_KMAX);   // [B][KMAX]
-    float* s_gradc = s_grad + RB_BATCH * RB_KMAX;                            // [B][4]
+    float* s_part = reinterpret_cast<float*>(s_sidx + RB_BATCH * RB_KMAX);   // [warp][B][KMAX], private per warp
+    float* s_gradc = s_part + RB_WARPS * RB_BATCH * RB_KMAX;                 // [B][4]
     float* s_dw = s_gradc + RB_BATCH * 4;                                    // [L][256]
+    __shared__ uint32_t s_mask[RB_WARPS][RB_BATCH / 32];
     __shared__ uint32_t s_max;
 
-    const int tid = threadIdx.x, lane = tid & 31;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile = blockIdx.x;
     const int tx = tile % a.gx, ty = tile / a.gx;
     const int px = tx * TILE + (tid & (TILE - 1));
     const int py = ty * TILE + (tid >> 4);
     const bool inside = px < a.W && py < a.H;
     const float pxf = (float)px, pyf = (float)py;
+    const float wy0 = (float)(ty * TILE + 2 * warp), wy1 = wy0 + 1.0f;       // the warp's two pixel rows
     const uint2 range = a.ranges[tile];
     const size_t HW = (size_t)a.H * a.W;
     const size_t pix = inside ? (size_t)py * a.W + px : 0;
+    float* my_part = s_part + warp * RB_BATCH * RB_KMAX;
 
     if (tid == 0) s_max = 0;
     __syncthreads();
@@ -90,24 +92,22 @@ __global__ void __launch_bounds__(RB_THREADS) k_render_backward(BackArgs a)
         __syncthreads();
         if (tid < batch_n) {
             const uint32_t g = a.point_list[range.x + off + tid];
-            const float4 co = a.conic_opacity[g];
+            const float4 r0 = a.rec[3 * (size_t)g + 0], r1 = a.rec[3 * (size_t)g + 1], r2 = a.rec[3 * (size_t)g + 2];
             BackInstance s;
-            s.xy = a.xy[g];
-            s.ax = -0.5f * co.x; s.b = -co.y; s.az = -0.5f * co.z; s.op = co.w;
-            s.thr = (co.w > 0.0f) ? -__logf(255.0f * co.w) - 0.01f : 1.0f;
+            s.x = r0.x; s.y = r0.y; s.ax = r0.z; s.b = r0.w;
+            s.az = r1.x; s.thr = r1.y; s.op = r1.z; s.ext_y = r2.z;
             s.gid = g;
             s.cnt = a.sp_count ? a.sp_count[g] : RB_ROW_DENSE;
-            s.pad = 0;
+            s.pad0 = s.pad1 = 0;
             s_inst[tid] = s;
         }
         if (!DENSE_GRAD) {
-            for (int e = tid; e < RB_BATCH * RB_KMAX; e += RB_THREADS) s_grad[e] = 0.0f;
-            const int inst = tid >> 1;
+            const int inst = tid >> 2;                          // 4 threads per instance
             if (inst < batch_n) {
                 const uint32_t g = a.point_list[range.x + off + inst];
                 const uint32_t cnt = a.sp_count[g];
                 if (cnt != RB_ROW_DENSE)
-                    for (uint32_t k = tid & 1; k < cnt; k += 2)
+                    for (uint32_t k = tid & 3; k < cnt; k += 4)
                         s_sidx[inst * RB_KMAX + k] = a.sp_index[(size_t)g * RB_KMAX + k];
             }
         }
@@ -116,69 +116,81 @@ __global__ void __launch_bounds__(RB_THREADS) k_render_backward(BackArgs a)
         }
         __syncthreads();
 
-        for (int j = 0; j < batch_n; ++j) {
-            const BackInstance& s = s_inst[j];
-            float w = 0.0f;
-            if (off + j < last) {
-                const float dx = s.xy.x - pxf, dy = s.xy.y - pyf;
-                const float power = fmaf(s.ax * dx, dx, fmaf(s.az * dy, dy, (s.b * dx) * dy));
-                if (!(power > 0.0f || power < s.thr)) {
-                    const float alpha = fminf(ALPHA_MAX, s.op * repro_expf(power));
-                    if (!(alpha < ALPHA_MIN)) {
-                        w = alpha * T;
-                        T = T * (1.0f - alpha);
+        for (int jb = 0; jb < batch_n; jb += 32) {
+            uint32_t wrote = 0u;
+            const int j_end = min(jb + 32, batch_n);
+#pragma unroll 1
+            for (int j = jb; j < j_end; ++j) {
+                const BackInstance& s = s_inst[j];
+                // rows this warp owns against the splat's alpha >= 1/255 extent (rounded outwards by the forward)
+                if (s.ext_y < 0.0f || s.y + s.ext_y < wy0 || s.y - s.ext_y > wy1) continue;
+                float w = 0.0f;
+                if (off + j < last) {
+                    const float dx = s.x - pxf, dy = s.y - pyf;
+                    const float power = fmaf(s.ax * dx, dx, fmaf(s.az * dy, dy, (s.b * dx) * dy));
+                    if (!(power > 0.0f || power < s.thr)) {
+                        const float alpha = fminf(ALPHA_MAX, s.op * repro_expf(power));
+                        if (!(alpha < ALPHA_MIN)) {
+                            w = alpha * T;
+                            T = T * (1.0f - alpha);
+                        }
+                    }
+                }
+                if (__ballot_sync(0xffffffffu, w != 0.0f) == 0u) continue;
+                const uint32_t cnt = s.cnt;
+                if (DENSE_GRAD || cnt == RB_ROW_DENSE) {
+                    // every channel (strict dense gradient, or a row too dense to compact)
+                    for (int c = 0; c < a.L; ++c) {
+                        // support-only gradient: channels whose coefficient is exactly 0 get none
+                        if (!DENSE_GRAD && __ldg(a.coeff_dense + (size_t)s.gid * a.L + c) == 0.0f) continue;
+                        const float v = warp_sum(w * s_dw[c * RB_THREADS + tid]);
+                        if (lane == 0 && v != 0.0f) atomicAdd(a.dL_dcoeff + (size_t)s.gid * a.L + c, v);
+                    }
+                } else {
+                    // four channels per pass: a transposing butterfly leaves channel k0 + q summed over the warp in
+                    // lane 8q (6 shuffles for 4 sums instead of 20); the sum goes to this warp's private row
+                    for (uint32_t k0 = 0; k0 < cnt; k0 += 4) {
+                        float a0, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
+                        a0 = w * s_dw[s_sidx[j * RB_KMAX + k0] * RB_THREADS + tid];
+                        if (k0 + 1 < cnt) a1 = w * s_dw[s_sidx[j * RB_KMAX + k0 + 1] * RB_THREADS + tid];
+                        if (k0 + 2 < cnt) a2 = w * s_dw[s_sidx[j * RB_KMAX + k0 + 2] * RB_THREADS + tid];
+                        if (k0 + 3 < cnt) a3 = w * s_dw[s_sidx[j * RB_KMAX + k0 + 3] * RB_THREADS + tid];
+                        const bool hi16 = lane & 16, hi8 = lane & 8;
+                        float b0 = hi16 ? a2 : a0, b1 = hi16 ? a3 : a1;
+                        b0 += __shfl_xor_sync(0xffffffffu, hi16 ? a0 : a2, 16);
+                        b1 += __shfl_xor_sync(0xffffffffu, hi16 ? a1 : a3, 16);
+                        float v = hi8 ? b1 : b0;
+                        v += __shfl_xor_sync(0xffffffffu, hi8 ? b0 : b1, 8);
+                        v += __shfl_xor_sync(0xffffffffu, v, 4);
+                        v += __shfl_xor_sync(0xffffffffu, v, 2);
+                        v += __shfl_xor_sync(0xffffffffu, v, 1);
+                        const uint32_t kq = k0 + (lane >> 3);
+                        if ((lane & 7) == 0 && kq < cnt) my_part[j * RB_KMAX + kq] = v;
+                    }
+                    wrote |= 1u << (j & 31);
+                }
+                if (COLOR) {
+                    const float v0 = warp_sum(w * dc0), v1 = warp_sum(w * dc1), v2 = warp_sum(w * dc2);
+                    if (lane == 0) {
+                        atomicAdd(&s_gradc[j * 4 + 0], v0);
+                        atomicAdd(&s_gradc[j * 4 + 1], v1);
+                        atomicAdd(&s_gradc[j * 4 + 2], v2);
                     }
                 }
             }
-            if (__ballot_sync(0xffffffffu, w != 0.0f) == 0u) continue;
-            const uint32_t cnt = s.cnt;
-            if (DENSE_GRAD || cnt == RB_ROW_DENSE) {
-                // every channel (strict dense gradient, or a row too dense to compact)
-                for (int c = 0; c < a.L; ++c) {
-                    // support-only gradient: channels whose coefficient is exactly 0 get none
-                    if (!DENSE_GRAD && __ldg(a.coeff_dense + (size_t)s.gid * a.L + c) == 0.0f) continue;
-                    const float v = warp_sum(w * s_dw[c * RB_THREADS + tid]);
-                    if (lane == 0 && v != 0.0f) atomicAdd(a.dL_dcoeff + (size_t)s.gid * a.L + c, v);
-                }
-            } else {
-                // four channels per pass: a transposing butterfly leaves channel k0 + q summed over the warp in lane 8q
-                // (6 shuffles for 4 sums instead of 20)
-                for (uint32_t k0 = 0; k0 < cnt; k0 += 4) {
-                    float a0, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
-                    a0 = w * s_dw[s_sidx[j * RB_KMAX + k0] * RB_THREADS + tid];
-                    if (k0 + 1 < cnt) a1 = w * s_dw[s_sidx[j * RB_KMAX + k0 + 1] * RB_THREADS + tid];
-                    if (k0 + 2 < cnt) a2 = w * s_dw[s_sidx[j * RB_KMAX + k0 + 2] * RB_THREADS + tid];
-                    if (k0 + 3 < cnt) a3 = w * s_dw[s_sidx[j * RB_KMAX + k0 + 3] * RB_THREADS + tid];
-                    const bool hi16 = lane & 16, hi8 = lane & 8;
-                    float b0 = hi16 ? a2 : a0, b1 = hi16 ? a3 : a1;
-                    b0 += __shfl_xor_sync(0xffffffffu, hi16 ? a0 : a2, 16);
-                    b1 += __shfl_xor_sync(0xffffffffu, hi16 ? a1 : a3, 16);
-                    float v = hi8 ? b1 : b0;
-                    v += __shfl_xor_sync(0xffffffffu, hi8 ? b0 : b1, 8);
-                    v += __shfl_xor_sync(0xffffffffu, v, 4);
-                    v += __shfl_xor_sync(0xffffffffu, v, 2);
-                    v += __shfl_xor_sync(0xffffffffu, v, 1);
-                    const uint32_t kq = k0 + (lane >> 3);
-                    if ((lane & 7) == 0 && kq < cnt) atomicAdd(&s_grad[j * RB_KMAX + kq], v);
-                }
-            }
-            if (COLOR) {
-                const float v0 = warp_sum(w * dc0), v1 = warp_sum(w * dc1), v2 = warp_sum(w * dc2);
-                if (lane == 0) {
-                    atomicAdd(&s_gradc[j * 4 + 0], v0);
-                    atomicAdd(&s_gradc[j * 4 + 1], v1);
-                    atomicAdd(&s_gradc[j * 4 + 2], v2);
-                }
-            }
+            if (lane == 0) s_mask[warp][jb >> 5] = wrote;                // warp-uniform
         }
         __syncthreads();
-        // flush the batch: one global atomic per (instance, channel) of this tile
+        // flush the batch: the warps' rows added in a fixed order, one global atomic per (instance, channel) of this tile
         if (!DENSE_GRAD) {
             for (int e = tid; e < batch_n * RB_KMAX; e += RB_THREADS) {
                 const int j = e / RB_KMAX, k = e % RB_KMAX;
                 const uint32_t cnt = s_inst[j].cnt;
                 if (cnt != RB_ROW_DENSE && (uint32_t)k < cnt) {
-                    const float v = s_grad[e];
+                    float v = 0.0f;
+#pragma unroll
+                    for (int w_ = 0; w_ < RB_WARPS; ++w_)
+                        if ((s_mask[w_][j >> 5] >> (j & 31)) & 1u) v += s_part[(w_ * RB_BATCH + j) * RB_KMAX + k];
                     if (v != 0.0f)
                         atomicAdd(a.dL_dcoeff + (size_t)s_inst[j].gid * a.L + s_sidx[e], v);
                 }
@@ -198,8 +210,9 @@ __global__ void __launch_bounds__(RB_THREADS) k_render_backward(BackArgs a)
 
 static size_t rb_smem_bytes(int L)
 {
-    return sizeof(BackInstance) * RB_BATCH + (size_t)RB_BATCH * RB_KMAX * (sizeof(uint16_t) + sizeof(float)) +
-           (size_t)RB_BATCH * 4 * sizeof(float) + (size_t)L * RB_THREADS * sizeof(float);
+    return sizeof(BackInstance) * RB_BATCH + (size_t)RB_BATCH * RB_KMAX * sizeof(uint16_t) +
+           (size_t)RB_WARPS * RB_BATCH * RB_KMAX * sizeof(float) + (size_t)RB_BATCH * 4 * sizeof(float) +
+           (size_t)L * RB_THREADS * sizeof(float);
 }
 
 int launch_render_backward(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b,
@@ -209,7 +222,9 @@ int launch_render_backward(const lsv2_view& v, const lsv2_geom& g, const lsv2_bi
 {
     const int gx = (v.width + TILE - 1) / TILE, gy = (v.height + TILE - 1) / TILE;
     if (gx * gy == 0) return LSV2_OK;
-    if (f.mode != LSV2_MODE_DENSE || f.L <= 0 || !f.coeff_dense || !dL_dwmap || !dL_dcoeff || !img.n_contrib) return LSV2_EINVAL;
+    if (f.mode != LSV2_MODE_DENSE || f.L <= 0 || !f.coeff_dense || !dL_dwmap || !dL_dcoeff || !img.n_contrib ||
+        !g.blend_rec)
+        return LSV2_EINVAL;
     const bool color = dL_dcolor != nullptr && dL_dcolors != nullptr;
     const bool have_sparse = f.sparse_count && f.sparse_index;
     const bool dense = dense_grad != 0 || !have_sparse;
@@ -219,8 +234,7 @@ int launch_render_backward(const lsv2_view& v, const lsv2_geom& g, const lsv2_bi
     a.W = v.width; a.H = v.height; a.gx = gx; a.L = f.L;
     a.ranges = reinterpret_cast<const uint2*>(b.ranges);
     a.point_list = b.point_list;
-    a.xy = reinterpret_cast<const float2*>(g.xy);
-    a.conic_opacity = reinterpret_cast<const float4*>(g.conic_opacity);
+    a.rec = reinterpret_cast<const float4*>(g.blend_rec);
     a.n_contrib = img.n_contrib;
     a.sp_count = have_sparse ? f.sparse_count : nullptr;
     a.sp_index = f.sparse_index;

@@ -66,6 +66,7 @@ class FrameState:
     status: torch.Tensor = None
     capacity: int = 0
     keep: list = field(default_factory=list)    # tensors the View struct points into
+    scene: dict = field(default_factory=dict)   # the op's geometry / colour inputs as passed to lsv2_preprocess
 
     @property
     def num_rendered(self) -> int:
@@ -75,13 +76,24 @@ class FrameState:
     def overflowed(self) -> bool:
         return bool(self.status[STATUS_OVERFLOW].item())
 
-    def for_backward(self) -> "FrameState":
-        """Shallow copy without the forward's output tensors (see _RasterizeGaussians.forward)."""
+    def for_backward(self, color_copy: bool = False) -> "FrameState":
+        """Shallow copy without the forward's output tensors (see _RasterizeGaussians.forward).  ``color_copy``:
+        the geometry backward needs the final colour of every pixel; it gets a private copy (3 H W floats), never
+        the output tensor itself."""
         b = FrameState(P=self.P, H=self.H, W=self.W, mode=self.mode, L=self.L, K=self.K, view=self.view,
                        geom=self.geom, binning=self.binning, feat=self.feat, status=self.status,
-                       capacity=self.capacity, keep=self.keep)
+                       capacity=self.capacity, keep=self.keep, scene=self.scene)
         b.image = {k: v for k, v in self.image.items() if k in ("final_T", "n_contrib")}
+        if color_copy:
+            b.image["color"] = self.image["color"].detach().clone()
         return b
+
+    def c_scene(self) -> Scene:
+        s = self.scene
+        shs = s.get("shs")
+        return Scene(self.P, 0 if shs is None else int(shs.shape[1]), _abi.ptr(s.get("means3D")),
+                     _abi.ptr(s.get("opacities")), _abi.ptr(s.get("scales")), _abi.ptr(s.get("rotations")),
+                     _abi.ptr(s.get("cov3D_precomp")), _abi.ptr(shs), _abi.ptr(s.get("colors_precomp")))
 
     def c_geom(self) -> Geom:
         g = self.geom
@@ -230,6 +242,8 @@ def rasterize_forward(rs: GaussianRasterizationSettings, means3D, opacities, shs
     st.feat = feat
     st.view = _make_view(rs, dev, st.keep)
     st.keep += [means3D, opacities, shs, colors_precomp, scales, rotations, cov3D_precomp]
+    st.scene = dict(means3D=means3D, opacities=opacities, shs=shs, colors_precomp=colors_precomp, scales=scales,
+                    rotations=rotations, cov3D_precomp=cov3D_precomp)
     gx, gy = (W + TILE - 1) // TILE, (H + TILE - 1) // TILE
 
     i32 = dict(dtype=torch.int32, device=dev)
@@ -452,6 +466,47 @@ def rasterize_backward(st: FrameState, grad_wmap: Optional[torch.Tensor], grad_c
     return d_coeff, d_colors
 
 
+def rasterize_backward_geometry(st: FrameState, grad_color: torch.Tensor, want: Optional[dict] = None) -> dict:
+    """The RGB stage's backward (train.py:169-172 without --include_feature): dL/d(means3D, means2D, opacities,
+    scales, rotations | cov3D_precomp, shs | colors_precomp) from dL/d rendered_image.  ``st.image['color']`` must
+    hold the forward's rendered image.  Two launches: ``lsv2_render_backward_rgb`` (per-tile replay, per-Gaussian
+    sums) and ``lsv2_preprocess_backward`` (per-Gaussian chain rule).  Returns a dict of the gradients, shaped like
+    the inputs."""
+    L_ = _abi.lib()
+    dev = st.status.device
+    if "color" not in st.image:
+        raise _abi.Lsv2Error("the geometry backward needs the forward's rendered image in state.image['color']")
+    gc = _f32c(grad_color, "grad_color")
+    if gc.shape != (3, st.H, st.W):
+        raise ValueError("grad_color must be [3, H, W]")
+    sc = st.scene
+    f32 = dict(dtype=torch.float32, device=dev)
+    acc = torch.zeros((st.P, _abi.GEOM_ACC), **f32)
+    out = {"means3D": torch.empty((st.P, 3), **f32), "means2D": torch.empty((st.P, 3), **f32),
+           "opacities": torch.empty((st.P,), **f32)}
+    if sc.get("cov3D_precomp") is not None:
+        out["cov3D_precomp"] = torch.empty((st.P, 6), **f32)
+    else:
+        out["scales"] = torch.empty((st.P, 3), **f32)
+        out["rotations"] = torch.empty((st.P, 4), **f32)
+    if sc.get("shs") is not None:
+        out["shs"] = torch.empty_like(sc["shs"])
+    else:
+        out["colors_precomp"] = torch.empty((st.P, 3), **f32)
+    geom_c, bin_c, img_c, scene_c = st.c_geom(), st.c_binning(), st.c_image(), st.c_scene()
+    stream = _abi.stream_ptr(dev)
+    with _abi.device_guard(dev):
+        _abi.check(L_.lsv2_render_backward_rgb(C.byref(st.view), C.byref(geom_c), C.byref(bin_c), C.byref(img_c),
+                                               _abi.ptr(gc), _abi.ptr(acc), stream), "lsv2_render_backward_rgb")
+        grads = _abi.GeomGrads(_abi.ptr(out["means3D"]), _abi.ptr(out["means2D"]), _abi.ptr(out["opacities"]),
+                               _abi.ptr(out.get("scales")), _abi.ptr(out.get("rotations")),
+                               _abi.ptr(out.get("cov3D_precomp")), _abi.ptr(out.get("shs")),
+                               _abi.ptr(out.get("colors_precomp")))
+        _abi.check(L_.lsv2_preprocess_backward(C.byref(st.view), C.byref(scene_c), C.byref(geom_c), _abi.ptr(acc),
+                                               C.byref(grads), stream), "lsv2_preprocess_backward")
+    return out
+
+
 class _RasterizeGaussians(torch.autograd.Function):
     last_state = None          # side channel forward -> GaussianRasterizer.forward (never referenced from ctx)
 
@@ -466,7 +521,14 @@ class _RasterizeGaussians(torch.autograd.Function):
         # what backward needs, WITHOUT the forward's outputs: a state holding `color` / `wmap` on ctx closes the cycle
         # output -> grad_fn -> ctx -> state -> output through C++ shared_ptrs, which Python's GC cannot collect --
         # every grad-enabled forward would leak its whole frame
-        ctx.state = st.for_backward()
+        # inputs: 0 means3D, 1 means2D, 2 sh, 3 colors_precomp, ..., 7 opacities, 8 scales, 9 rotations, 10 cov3D
+        need = ctx.needs_input_grad
+        # (means2D alone does not count outside the RGB stage: render() always passes it with requires_grad=True,
+        # gaussian_renderer/__init__.py:27-31, and only the RGB stage's densification reads its gradient)
+        ctx.geometry = bool(need[0] or need[2] or need[7] or need[8] or need[9] or need[10] or
+                            ((need[1] or need[3]) and st.mode == MODE_RGB))
+        ctx.state = st.for_backward(color_copy=ctx.geometry)
+        ctx.opacity_shape = opacities.shape
         ctx.color_is_precomp = colors_precomp is not None
         ctx.dense_grad = dense_coeff_grad
         ctx.debug = bool(raster_settings.debug)
@@ -489,10 +551,26 @@ class _RasterizeGaussians(torch.autograd.Function):
         need = ctx.needs_input_grad
         # inputs: 0 means3D, 1 means2D, 2 sh, 3 colors_precomp, 4 language_feature_precomp, 5 weights_quick,
         #         6 indices_quick, 7 opacities, 8 scales, 9 rotations, 10 cov3Ds_precomp, 11 settings
-        if need[0] or need[2] or need[7] or need[8] or need[9] or need[10]:
-            raise NotImplementedError(
-                "geometry / SH / opacity gradients (the RGB stage of train.py) are outside this build's hot path; "
-                "the feature stage freezes them (scene/gaussian_model.py:238-243)")
+        if ctx.geometry:
+            # the RGB stage (train.py without --include_feature): everything the rendered image depends on
+            if st.mode != MODE_RGB:
+                raise NotImplementedError(
+                    "geometry gradients through the language-feature weight map: the reference never asks for them "
+                    "(the feature stage freezes geometry, scene/gaussian_model.py:238-243; the RGB stage renders "
+                    "with include_feature=False)")
+            try:
+                g = rasterize_backward_geometry(st, grad_color)
+                if ctx.debug:
+                    torch.cuda.synchronize(grad_color.device)
+            except Exception:
+                if ctx.debug:
+                    _dump_snapshot("snapshot_bw.dump", dict(grad_color=grad_color, radii=st.geom.get("radii"),
+                                                            num_rendered=st.capacity))
+                raise
+            pick = lambda i, k: g.get(k) if need[i] else None
+            d_op = g["opacities"].reshape(ctx.opacity_shape) if need[7] else None
+            return (pick(0, "means3D"), pick(1, "means2D"), pick(2, "shs"), pick(3, "colors_precomp"), None, None,
+                    None, d_op, pick(8, "scales"), pick(9, "rotations"), pick(10, "cov3D_precomp"), None, None, None)
         d_coeff = d_colors = None
         if st.mode == MODE_DENSE and need[4]:
             gc = grad_color if (need[3] and ctx.color_is_precomp) else None

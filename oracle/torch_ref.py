@@ -152,7 +152,10 @@ def render(pre, binned, W, H, bg, coeff=None):
             dy = pre["xy"][g, 1:2] - ys[None].to(dt)
             con = pre["conic"][g]
             power = -0.5 * (con[:, 0:1] * dx * dx + con[:, 2:3] * dy * dy) - con[:, 1:2] * dx * dy
-            alpha = torch.clamp_max(pre["opacity"][g][:, None] * torch.exp(torch.clamp_max(power, 0.0)), 0.99)
+            alpha_raw = pre["opacity"][g][:, None] * torch.exp(torch.clamp_max(power, 0.0))
+            # the clamp at 0.99 is the identity in the derivative ([LINEAGE]: the 3DGS backward multiplies dL/dalpha
+            # by o and G without looking at the clamp); same forward value
+            alpha = alpha_raw + (torch.clamp_max(alpha_raw, 0.99) - alpha_raw).detach()
             valid = (power <= 0) & (alpha >= 1.0 / 255.0)
             a = torch.where(valid, alpha, torch.zeros_like(alpha))
             Tincl = torch.cumprod(1.0 - a, dim=0)

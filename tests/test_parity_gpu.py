@@ -190,6 +190,19 @@ def test_autograd_function_matches_backward_call():
     (wmap * target).sum().backward()
     pre, binned, fwd = oracle.forward(hp.oracle_scene(scene), hp.oracle_view(cam), mode=1, L=64,
                                       coeff_dense=dense, bg=BG)
+    # the op's own gradient is the strict one (every channel: what _C.rasterize_gaussians_backward returns);
+    # support-only (== what survives torch.where in utils/vq_utils.py:20) is the opt-in the trainer uses
+    ref = oracle.render_backward_coeff(pre, binned, fwd, W, H, 64, target.cpu().numpy(), dense=True,
+                                       coeff_dense=dense)
+    assert np.max(np.abs(coeff.grad.cpu().numpy() - ref)) <= 1e-4 * np.abs(ref).max() + 1e-6
+    coeff.grad = None
+    rast.dense_coeff_grad = False
+    _, wmap, _ = rast(means3D=scene["xyz"].cuda(), means2D=means2D, shs=scene["features"].cuda(),
+                      colors_precomp=None, language_feature_precomp=coeff,
+                      language_feature_weights_quick=ph, language_feature_indices=ph,
+                      opacities=scene["opacity"].cuda(), scales=scene["scaling"].cuda(),
+                      rotations=scene["rotation"].cuda(), cov3D_precomp=None)
+    (wmap * target).sum().backward()
     ref = oracle.render_backward_coeff(pre, binned, fwd, W, H, 64, target.cpu().numpy(), dense=False,
                                        coeff_dense=dense)
     assert np.max(np.abs(coeff.grad.cpu().numpy() - ref)) <= 1e-4 * np.abs(ref).max() + 1e-6
