@@ -407,6 +407,58 @@ def run_train(args, dev, rank, world, scene, barrier, wl=None):
                                     "[logits | codebook] buffer"}}
 
 
+def run_rgb_stage(args, dev, scene, steps=30):
+    """the RGB stage's rasterizer work (train.py without --include_feature, :169-172): forward in RGB
+    mode, L1 loss, backward to means / scales / rotations / opacity / SH through lsv2_render_backward_rgb +
+    lsv2_preprocess_backward.  ssim, the optimizer and densification are the reference's torch code and not timed."""
+    from langsplatv2_b200 import synth
+    from langsplatv2_b200.rasterizer import GaussianRasterizationSettings, GaussianRasterizer
+    W, H, N = TRAIN_WL["W"], TRAIN_WL["H"], scene["xyz"].shape[0]
+    cam = synth.ring_camera(0, VIEWS, W, H)
+    rs = GaussianRasterizationSettings(
+        image_height=H, image_width=W, tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"],
+        bg=torch.zeros(3, device=dev), scale_modifier=1.0, viewmatrix=cam["world_view_transform"].to(dev),
+        projmatrix=cam["full_proj_transform"].to(dev), sh_degree=scene["sh_degree"],
+        campos=cam["camera_center"].to(dev), prefiltered=False, debug=False, include_feature=False, quick_render=False)
+    leaf = lambda t: t.detach().float().to(dev).clone().requires_grad_(True)
+    p = dict(means3D=leaf(scene["xyz"]), opacities=leaf(scene["opacity"]), shs=leaf(scene["features"]),
+             scales=leaf(scene["scaling"]), rotations=leaf(scene["rotation"]))
+    gt = torch.rand(3, H, W, device=dev)
+    ph = torch.zeros((1,), device=dev)
+    state = {"cap": None}
+
+    def step():
+        for v in p.values():
+            v.grad = None
+        means2D = torch.zeros(N, 3, device=dev, requires_grad=True)
+        rast = GaussianRasterizer(raster_settings=rs, capacity=state["cap"])
+        color, _, _ = rast(means2D=means2D, colors_precomp=None, cov3D_precomp=None, language_feature_precomp=ph,
+                           language_feature_weights_quick=ph, language_feature_indices=ph, **p)
+        loss = (color - gt).abs().mean()
+        loss.backward()
+        if state["cap"] is None:
+            state["cap"] = int(rast.last_state.num_rendered * 1.2) + 4096
+        return loss
+
+    for _ in range(4):
+        step()
+    torch.cuda.synchronize(dev)
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+    evs[0].record()
+    for i in range(steps):
+        loss = step()
+        evs[i + 1].record()
+    torch.cuda.synchronize(dev)
+    per = [evs[i].elapsed_time(evs[i + 1]) for i in range(steps)]
+    ok = all(bool(torch.isfinite(v.grad).all()) for v in p.values())
+    return {"metric": "RGB-stage forward + backward iterations/s (rasterizer + L1 loss; 1M Gaussians, %dx%d)" % (W, H),
+            "value": 1e3 * steps / sum(per), "unit": "iter/s", "ms_per_iter_median": float(np.percentile(per, 50)),
+            "ms_per_iter_p95": float(np.percentile(per, 95)), "steps": steps, "final_loss": float(loss.detach()),
+            "grads_finite": ok, "launch": "eager",
+            "what": "gradients to means3D, means2D, scales, rotations, opacities, SH (degree 3): "
+                    "lsv2_render_backward_rgb + lsv2_preprocess_backward"}
+
+
 def run_reference_style(r, cams, steps, dev):
     """What a user of the reference runs per frame (eval_lerf.py:210-220): the drop-in op through its 3-tuple API
     (one host sync per frame for num_rendered, fp32 [192,H,W] weight map to HBM) followed by the reference's own
@@ -708,6 +760,12 @@ def run_gpu(args, wl):
         r.last_state = None
         torch.cuda.empty_cache()
         train = run_train(args, dev, rank, world, scene, barrier)
+        if world == 1:
+            torch.cuda.empty_cache()
+            from langsplatv2_b200 import synth as _synth
+            rgb_scene = _synth.make_scene(TRAIN_WL["N"], seed=0, levels=1, codebook_size=CODES, feat_dim=D, sh_degree=3)
+            train["rgb_stage"] = run_rgb_stage(args, dev, rgb_scene)
+            del rgb_scene
 
     t = torch.tensor([ms_total, e2e_ms, dom_ms], dtype=torch.float64, device=dev)
     if world > 1:

@@ -6,9 +6,12 @@
 //
 // One CTA per tile.  The tile of dL/dWmap is staged in shared memory once; the tile's
 // instance list is replayed with the forward's exact arithmetic up to each pixel's
-// n_contrib; the per-(instance, channel) sums are reduced with warp shuffles into a
-// shared-memory batch buffer and flushed with ONE global atomic per (instance, channel) per
-// tile -- not one per pixel.
+// n_contrib (read from the forward's packed blend record, so alpha, T and the cut-off are the
+// forward's bit for bit); a warp skips instances whose alpha >= 1/255 extent misses its two rows;
+// the per-(instance, channel) sums are reduced with warp shuffles into a shared-memory batch
+// buffer and flushed with ONE global atomic per (instance, channel) per tile -- not one per
+// pixel.  The replay is latency-bound: shared memory is budgeted for three CTAs per SM
+// (1.52 -> 1.21 ms at 1M Gaussians / 1008x756, profiles/r02h_train_launches.txt).
 #include "common.cuh"
 
 namespace lsv2 {
@@ -50,16 +53,17 @@ __device__ __forceinline__ float warp_sum(float v)
 }
 
 template <bool DENSE_GRAD, bool COLOR>
-__global__ void __launch_bounds__(RB_THREADS, 2) k_render_backward(BackArgs a)
+__global__ void __launch_bounds__(RB_THREADS, 3) k_render_backward(BackArgs a)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     BackInstance* s_inst = reinterpret_cast<BackInstance*>(smem_raw);
     uint16_t* s_sidx = reinterpret_cast<uint16_t*>(s_inst + RB_BATCH);
-    float* s_part = reinterpret_cast<float*>(s_sidx + RB_BATCH * RB_KMAX);   // [warp][B][KMAX], private per warp
-    float* s_gradc = s_part + RB_WARPS * RB_BATCH * RB_KMAX;                 // [B][4]
-    float* s_dw = s_gradc + RB_BATCH * 4;                                    // [L][256]
-    __shared__ uint32_t s_mask[RB_WARPS][RB_BATCH / 32];
+    float* s_grad = reinterpret_cast<float*>(s_sidx + RB_BATCH * RB_KMAX);   // [B][KMAX]
+    float* s_gradc = s_grad + RB_BATCH * RB_KMAX;                            // [B][4] (COLOR only)
+    float* s_dw = s_gradc + (COLOR ? RB_BATCH * 4 : 0);                      // [L][256]
     __shared__ uint32_t s_max;
+    // shared-memory budget: at L = 64 the dL/dWmap tile alone is 64 KB; everything else is kept under 10 KB so that
+    // THREE CTAs fit an SM -- the replay is latency-bound and time follows resident warps (profiles/r02h)
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile = blockIdx.x;
@@ -72,7 +76,6 @@ __global__ void __launch_bounds__(RB_THREADS, 2) k_render_backward(BackArgs a)
     const uint2 range = a.ranges[tile];
     const size_t HW = (size_t)a.H * a.W;
     const size_t pix = inside ? (size_t)py * a.W + px : 0;
-    float* my_part = s_part + warp * RB_BATCH * RB_KMAX;
 
     if (tid == 0) s_max = 0;
     __syncthreads();
@@ -102,6 +105,7 @@ __global__ void __launch_bounds__(RB_THREADS, 2) k_render_backward(BackArgs a)
             s_inst[tid] = s;
         }
         if (!DENSE_GRAD) {
+            for (int e = tid; e < RB_BATCH * RB_KMAX; e += RB_THREADS) s_grad[e] = 0.0f;
             const int inst = tid >> 2;                          // 4 threads per instance
             if (inst < batch_n) {
                 const uint32_t g = a.point_list[range.x + off + inst];
@@ -116,11 +120,9 @@ __global__ void __launch_bounds__(RB_THREADS, 2) k_render_backward(BackArgs a)
         }
         __syncthreads();
 
-        for (int jb = 0; jb < batch_n; jb += 32) {
-            uint32_t wrote = 0u;
-            const int j_end = min(jb + 32, batch_n);
+        {
 #pragma unroll 1
-            for (int j = jb; j < j_end; ++j) {
+            for (int j = 0; j < batch_n; ++j) {
                 const BackInstance& s = s_inst[j];
                 // rows this warp owns against the splat's alpha >= 1/255 extent (rounded outwards by the forward)
                 if (s.ext_y < 0.0f || s.y + s.ext_y < wy0 || s.y - s.ext_y > wy1) continue;
@@ -148,7 +150,7 @@ __global__ void __launch_bounds__(RB_THREADS, 2) k_render_backward(BackArgs a)
                     }
                 } else {
                     // four channels per pass: a transposing butterfly leaves channel k0 + q summed over the warp in
-                    // lane 8q (6 shuffles for 4 sums instead of 20); the sum goes to this warp's private row
+                    // lane 8q (6 shuffles for 4 sums instead of 20)
                     for (uint32_t k0 = 0; k0 < cnt; k0 += 4) {
                         float a0, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
                         a0 = w * s_dw[s_sidx[j * RB_KMAX + k0] * RB_THREADS + tid];
@@ -165,9 +167,8 @@ __global__ void __launch_bounds__(RB_THREADS, 2) k_render_backward(BackArgs a)
                         v += __shfl_xor_sync(0xffffffffu, v, 2);
                         v += __shfl_xor_sync(0xffffffffu, v, 1);
                         const uint32_t kq = k0 + (lane >> 3);
-                        if ((lane & 7) == 0 && kq < cnt) my_part[j * RB_KMAX + kq] = v;
+                        if ((lane & 7) == 0 && kq < cnt) atomicAdd(&s_grad[j * RB_KMAX + kq], v);
                     }
-                    wrote |= 1u << (j & 31);
                 }
                 if (COLOR) {
                     const float v0 = warp_sum(w * dc0), v1 = warp_sum(w * dc1), v2 = warp_sum(w * dc2);
@@ -178,19 +179,15 @@ __global__ void __launch_bounds__(RB_THREADS, 2) k_render_backward(BackArgs a)
                     }
                 }
             }
-            if (lane == 0) s_mask[warp][jb >> 5] = wrote;                // warp-uniform
         }
         __syncthreads();
-        // flush the batch: the warps' rows added in a fixed order, one global atomic per (instance, channel) of this tile
+        // flush the batch: one global atomic per (instance, channel) of this tile
         if (!DENSE_GRAD) {
             for (int e = tid; e < batch_n * RB_KMAX; e += RB_THREADS) {
                 const int j = e / RB_KMAX, k = e % RB_KMAX;
                 const uint32_t cnt = s_inst[j].cnt;
                 if (cnt != RB_ROW_DENSE && (uint32_t)k < cnt) {
-                    float v = 0.0f;
-#pragma unroll
-                    for (int w_ = 0; w_ < RB_WARPS; ++w_)
-                        if ((s_mask[w_][j >> 5] >> (j & 31)) & 1u) v += s_part[(w_ * RB_BATCH + j) * RB_KMAX + k];
+                    const float v = s_grad[e];
                     if (v != 0.0f)
                         atomicAdd(a.dL_dcoeff + (size_t)s_inst[j].gid * a.L + s_sidx[e], v);
                 }
@@ -208,11 +205,10 @@ __global__ void __launch_bounds__(RB_THREADS, 2) k_render_backward(BackArgs a)
     }
 }
 
-static size_t rb_smem_bytes(int L)
+static size_t rb_smem_bytes(int L, bool color)
 {
-    return sizeof(BackInstance) * RB_BATCH + (size_t)RB_BATCH * RB_KMAX * sizeof(uint16_t) +
-           (size_t)RB_WARPS * RB_BATCH * RB_KMAX * sizeof(float) + (size_t)RB_BATCH * 4 * sizeof(float) +
-           (size_t)L * RB_THREADS * sizeof(float);
+    return sizeof(BackInstance) * RB_BATCH + (size_t)RB_BATCH * RB_KMAX * (sizeof(uint16_t) + sizeof(float)) +
+           (color ? (size_t)RB_BATCH * 4 * sizeof(float) : 0) + (size_t)L * RB_THREADS * sizeof(float);
 }
 
 int launch_render_backward(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b,
@@ -228,7 +224,7 @@ int launch_render_backward(const lsv2_view& v, const lsv2_geom& g, const lsv2_bi
     const bool color = dL_dcolor != nullptr && dL_dcolors != nullptr;
     const bool have_sparse = f.sparse_count && f.sparse_index;
     const bool dense = dense_grad != 0 || !have_sparse;
-    const size_t smem = rb_smem_bytes(f.L);
+    const size_t smem = rb_smem_bytes(f.L, color);
     if (smem > 227 * 1024) return LSV2_EUNSUPPORTED;
     BackArgs a;
     a.W = v.width; a.H = v.height; a.gx = gx; a.L = f.L;
