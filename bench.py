@@ -742,6 +742,36 @@ def run_gpu(args, wl):
                               "achieved": q_bytes / (qk_ms * 1e-3) / 1e9, "unit": "GB/s"}}
         del rel
 
+    # ---- the same frame with a bf16 feature map (SURVEY 8f-3 "channels-last / bf16 output for consumers that want the
+    #      map"): half the write bytes; extra key only, the headline stays on the reference's fp32 map ----
+    bf16_out = None
+    if fused and not args.no_query and r.out_dtype == torch.float32:
+        out = None
+        torch.cuda.empty_cache()
+        r.out_dtype = torch.bfloat16
+        try:
+            for s in range(3):
+                ob = r.render(cams[my_views[s % len(my_views)]])
+            barrier()
+            b_b, b_e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            b_b.record()
+            for s in range(args.steps):
+                ob = r.render(cams[my_views[s % len(my_views)]])
+            b_e.record()
+            barrier()
+            tb = torch.tensor([b_b.elapsed_time(b_e)], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(tb, op=dist.ReduceOp.MAX)
+            b_ms = float(tb.item())
+            bf16_out = {"metric": "512-d feature-map FPS, bf16 output", "value": world * args.steps / (b_ms * 1e-3),
+                        "unit": UNIT, "ms_per_step": b_ms / args.steps,
+                        "out_bytes_per_frame": int(LEVELS * D * H * W * 2),
+                        "what": "same kernel, features rounded to bf16 in the epilogue (out_dtype=torch.bfloat16)"}
+            del ob
+        finally:
+            r.out_dtype = torch.float32
+        torch.cuda.empty_cache()
+
     ref_style = None
     if world == 1 and not args.no_reference_style:
         del out
@@ -821,6 +851,8 @@ def run_gpu(args, wl):
             line["reference_style"] = ref_style
         if query is not None:
             line["query"] = query
+        if bf16_out is not None:
+            line["bf16_out"] = bf16_out
         if world == 1 and not args.no_cpu_baseline:
             est, sample, threads = cpu_frame_time(scene, cpu_cams[0], wl, budget_s=20.0)
             line["cpu_baseline"] = {"value": 1.0 / est, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample}
