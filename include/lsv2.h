@@ -260,6 +260,21 @@ int lsv2_decode(int32_t levels, int32_t Lc, int32_t D, int64_t HW, const float* 
                 const float* codebooks, int32_t normalize, int32_t precision, int32_t out_dtype,
                 void* out, void* scratch, size_t scratch_bytes, void* stream);
 
+/* ---- lsv2_decode without caller scratch and without any allocation -------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ * Same computation as lsv2_decode(..., precision = LSV2_DECODE_BF16, ...): tensor-core decode, Lc == 64, D == 512,
+ * out_dtype 0 = f32 / 1 = bf16; the caller still passes wmap, codebooks and out.  The codebook image the kernel
+ * needs (64 KB per level) lives in a static device array inside the library, LSV2_DECODE_STATIC_MAX_LEVELS levels
+ * = 192 KB per GPU, held from library load to process exit.  levels > LSV2_DECODE_STATIC_MAX_LEVELS returns
+ * LSV2_ENOSPC; other shapes LSV2_EUNSUPPORTED.  Calls no cudaMalloc / cudaFree / allocating library routine.
+ * The array is shared by every call on a device and keeps the last call's contents (each call rewrites all it
+ * reads, nothing needs clearing): calls that overlap on the GPU -- different streams with no ordering between
+ * them -- race on it; serialise them (one stream, or events). */
+#define LSV2_DECODE_STATIC_MAX_LEVELS 3
+int lsv2_decode_static(int32_t levels, int32_t Lc, int32_t D, int64_t HW, const float* wmap,
+                       const float* codebooks, int32_t normalize, int32_t out_dtype, void* out, void* stream);
+
 /* ---- fused blend + decode (the serving path: eval_lerf.py:321-352 renders, then decodes) ----
  * renderCUDA forward and the codebook decode in ONE kernel: the blend's sparse-coefficient
  * accumulation runs on the tensor cores (alpha*T and coefficients as fp16 head + fp16 remainder,

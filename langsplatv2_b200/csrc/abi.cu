@@ -85,7 +85,7 @@ const char* lsv2_strerror(int code)
         case LSV2_OK: return "ok";
         case LSV2_EINVAL: return "invalid argument combination";
         case LSV2_ECUDA: return "CUDA error";
-        case LSV2_ENOSPC: return "scratch buffer too small";
+        case LSV2_ENOSPC: return "scratch buffer too small (or, for lsv2_decode_static, more levels than its built-in scratch holds)";
         case LSV2_EUNSUPPORTED: return "shape not supported by the sm_100a kernels";
         default: return "unknown error";
     }
@@ -242,6 +242,14 @@ int lsv2_decode(int32_t levels, int32_t Lc, int32_t D, int64_t HW, const float* 
         return launch_decode_tc(levels, Lc, D, HW, wmap, codebooks, normalize, out_dtype, out, scratch,
                                 scratch_bytes, (cudaStream_t)stream);
     return LSV2_EINVAL;
+}
+
+int lsv2_decode_static(int32_t levels, int32_t Lc, int32_t D, int64_t HW, const float* wmap, const float* codebooks,
+                       int32_t normalize, int32_t out_dtype, void* out, void* stream)
+{
+    if (levels < 0 || Lc <= 0 || D <= 0 || HW < 0 || !wmap || !codebooks || !out) return LSV2_EINVAL;
+    if (out_dtype != 0 && out_dtype != 1) return LSV2_EINVAL;
+    return launch_decode_tc_static(levels, Lc, D, HW, wmap, codebooks, normalize, out_dtype, out, (cudaStream_t)stream);
 }
 
 size_t lsv2_render_decode_scratch_bytes(int32_t levels) { return render_decode_scratch_bytes(levels); }

@@ -213,6 +213,8 @@ int launch_render_backward(const lsv2_view& v, const lsv2_geom& g, const lsv2_bi
                            const float* dL_dcolor, int dense_grad, float* dL_dcoeff, float* dL_dcolors,
                            cudaStream_t st);
 int launch_mark_visible(int P, const float* means3d, const float* viewmatrix, uint8_t* present, cudaStream_t st);
+int launch_decode_tc_static(int levels, int Lc, int D, int64_t HW, const float* wmap, const float* codebooks,
+                            int normalize, int out_dtype, void* out, cudaStream_t st);
 int launch_render_backward_rgb(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b, const lsv2_image& img,
                                const float* dL_dcolor, float* acc, cudaStream_t st);
 int launch_preprocess_backward(const lsv2_view& v, const lsv2_scene& s, const lsv2_geom& g, const float* acc,

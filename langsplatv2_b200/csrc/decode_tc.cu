@@ -205,4 +205,48 @@ int launch_decode_tc(int levels, int Lc, int D, int64_t HW, const float* wmap, c
     return LSV2_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// lsv2_decode_static: the tensor-core decode for callers that may not allocate (CUDA-graph capture, serving loops,
+// harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The only scratch the decode needs -- the bf16, 128B-swizzled image of the codebooks, 64 KB per level -- lives in a
+// file-scope device array of LSV2_DECODE_STATIC_MAX_LEVELS levels (192 KB, held by every GPU that loads the library
+// until the process exits).  k_decode_prep_b rewrites every byte the decode kernel reads on every call, so nothing
+// has to start at zero; the array keeps the last call's codebook image in between.  All calls on a device share the
+// array: two calls that overlap on the GPU (different streams, no ordering between them) race on it.
+// ---------------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) uint8_t g_decode_static_scratch[LSV2_DECODE_STATIC_MAX_LEVELS * DT_B_BYTES + 256];
+
+constexpr int DS_MAX_DEVICES = 64;
+static void* g_decode_static_ptr[DS_MAX_DEVICES];      // device address of the array, per device; 0 = not looked up yet
+
+// In host code `g_decode_static_scratch` is a host-side stand-in, not a device address: the address the kernels get
+// comes from cudaGetSymbolAddress, looked up once per device with that device current.
+static int decode_static_address(void** out)
+{
+    int dev = -1;
+    LSV2_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= DS_MAX_DEVICES) return LSV2_EUNSUPPORTED;
+    void* p = __atomic_load_n(&g_decode_static_ptr[dev], __ATOMIC_ACQUIRE);
+    if (!p) {
+        LSV2_CUDA_TRY(cudaGetSymbolAddress(&p, g_decode_static_scratch));
+        if (!p) return LSV2_ECUDA;
+        __atomic_store_n(&g_decode_static_ptr[dev], p, __ATOMIC_RELEASE);     // idempotent: every thread finds the same address
+    }
+    *out = p;
+    return LSV2_OK;
+}
+
+int launch_decode_tc_static(int levels, int Lc, int D, int64_t HW, const float* wmap, const float* codebooks,
+                            int normalize, int out_dtype, void* out, cudaStream_t st)
+{
+    if (levels <= 0 || HW <= 0) return LSV2_OK;
+    if (Lc != DT_LC || D != DT_D) return LSV2_EUNSUPPORTED;
+    if (levels > LSV2_DECODE_STATIC_MAX_LEVELS) return LSV2_ENOSPC;           // beyond the built-in scratch
+    void* scratch = nullptr;
+    const int rc = decode_static_address(&scratch);
+    if (rc != LSV2_OK) return rc;
+    return launch_decode_tc(levels, Lc, D, HW, wmap, codebooks, normalize, out_dtype, out, scratch,
+                            sizeof(g_decode_static_scratch), st);
+}
+
 }  // namespace lsv2
