@@ -68,6 +68,61 @@ def column_sumsq(x: torch.Tensor) -> torch.Tensor:
     return out
 
 
+class CodebookGradSink:
+    """Takes the codebook gradient of ``decode_cos_loss`` / ``decode_cos_loss_segments`` off autograd's critical path.
+
+    The loss's backward produces two independent things: dL/dWmap (which the blend backward and the top-k backward
+    are waiting for) and dL/dC (two pixel-axis GEMMs, ~0.65 ms at 1008x756, which nothing waits for until the
+    optimizer).  With a sink installed the backward only records what the GEMMs need; ``compute()`` -- called by the
+    trainer after ``loss.backward()`` has enqueued the rest of the backward pass -- runs them on a side stream and ADDS
+    the result into ``target`` (the codebook's slot of the flat gradient buffer); ``join()`` makes the current stream
+    wait for it.  At N > 1 the logits' reduce-scatter / sharded Adam / all-gather then run under the GEMMs instead of
+    after them.  Autograd sees ``None`` for the codebook (no double accumulation)."""
+
+    def __init__(self, target: torch.Tensor):
+        self.target = target
+        self.stream = torch.cuda.Stream(device=target.device)
+        self.fork = torch.cuda.Event()
+        self.done = torch.cuda.Event()
+        self.pending = None
+
+    def defer(self, fn, keep) -> None:
+        if self.pending is not None:
+            raise RuntimeError("CodebookGradSink: a second loss backward before compute()/join()")
+        self.fork.record(torch.cuda.current_stream(self.target.device))
+        self.pending = (fn, keep)           # `keep`: the operands stay referenced until the join
+
+    def compute(self) -> None:
+        if self.pending is None or self.pending[0] is None:
+            return
+        fn, keep = self.pending
+        with torch.cuda.stream(self.stream):
+            self.stream.wait_event(self.fork)
+            dC = fn()
+            self.target.add_(dC.reshape(self.target.shape))
+            keep.append(dC)
+            self.done.record(self.stream)
+        self.pending = (None, keep)
+
+    def join(self) -> None:
+        if self.pending is None:
+            return
+        if self.pending[0] is not None:
+            self.compute()
+        # the operands were allocated on the current stream and are released only now, after it has been ordered behind
+        # their last use on the side stream; the GEMMs' own temporaries never leave the side stream
+        torch.cuda.current_stream(self.target.device).wait_event(self.done)
+        self.pending = None
+
+
+_cb_sink = None
+
+
+def set_codebook_grad_sink(sink) -> None:
+    global _cb_sink
+    _cb_sink = sink
+
+
 class _GramCosLoss(torch.autograd.Function):
     """decode one codebook layer + normalise + cos loss without forming the [512, H, W] feature map
     (csrc/loss.cu, second half): two 64x512xHW GEMMs per iteration instead of three, no F / dF tensors."""
@@ -119,14 +174,23 @@ class _GramCosLoss(torch.autograd.Function):
                                               _abi.stream_ptr(dev)), "lsv2_gram_loss_backward")
         dC = None
         if ctx.needs_input_grad[1]:
-            dC = torch.zeros_like(Cb)
-            _decode_bwd(1, Lc, D, HW, aw, None, g, None, dC, dev)                  # (alpha w) gt^T
-            M = torch.zeros((Lc, Lc), dtype=torch.float32, device=dev)
-            _decode_bwd(1, Lc, Lc, HW, bw, None, w, None, M, dev)                  # (beta w) w^T
-            allow = torch.backends.cuda.matmul.allow_tf32
-            torch.backends.cuda.matmul.allow_tf32 = False
-            dC = (dC + M @ Cb).reshape(ctx.cb_shape)
-            torch.backends.cuda.matmul.allow_tf32 = allow
+            cb_shape = ctx.cb_shape
+
+            def codebook_grad():
+                dC_ = torch.zeros_like(Cb)
+                _decode_bwd(1, Lc, D, HW, aw, None, g, None, dC_, dev)             # (alpha w) gt^T
+                M = torch.zeros((Lc, Lc), dtype=torch.float32, device=dev)
+                _decode_bwd(1, Lc, Lc, HW, bw, None, w, None, M, dev)              # (beta w) w^T
+                allow = torch.backends.cuda.matmul.allow_tf32
+                torch.backends.cuda.matmul.allow_tf32 = False
+                out = (dC_ + M @ Cb).reshape(cb_shape)
+                torch.backends.cuda.matmul.allow_tf32 = allow
+                return out
+
+            if _cb_sink is not None:
+                _cb_sink.defer(codebook_grad, [aw, bw, w, g, Cb])
+            else:
+                dC = codebook_grad()
         return (dw if ctx.needs_input_grad[0] else None), dC, None, None, None, None
 
 
@@ -180,15 +244,24 @@ class _GramCosLossSeg(torch.autograd.Function):
                                                   bw.data_ptr(), _abi.stream_ptr(dev)), "lsv2_gram_loss_backward_seg")
         dC = None
         if ctx.needs_input_grad[1]:
-            Sm = torch.zeros((Lc, S), dtype=torch.float32, device=dev)
-            _abi.check(L_.lsv2_segment_sum(Lc, HW, S, aw.data_ptr(), sg.data_ptr(), Sm.data_ptr(),
-                                           _abi.stream_ptr(dev)), "lsv2_segment_sum")
-            M = torch.zeros((Lc, Lc), dtype=torch.float32, device=dev)
-            _decode_bwd(1, Lc, Lc, HW, bw, None, w, None, M, dev)                  # (beta w) w^T
-            allow = torch.backends.cuda.matmul.allow_tf32
-            torch.backends.cuda.matmul.allow_tf32 = False
-            dC = (Sm @ E + M @ Cb).reshape(ctx.cb_shape)
-            torch.backends.cuda.matmul.allow_tf32 = allow
+            cb_shape = ctx.cb_shape
+
+            def codebook_grad():
+                Sm = torch.zeros((Lc, S), dtype=torch.float32, device=dev)
+                _abi.check(L_.lsv2_segment_sum(Lc, HW, S, aw.data_ptr(), sg.data_ptr(), Sm.data_ptr(),
+                                               _abi.stream_ptr(dev)), "lsv2_segment_sum")
+                M = torch.zeros((Lc, Lc), dtype=torch.float32, device=dev)
+                _decode_bwd(1, Lc, Lc, HW, bw, None, w, None, M, dev)              # (beta w) w^T
+                allow = torch.backends.cuda.matmul.allow_tf32
+                torch.backends.cuda.matmul.allow_tf32 = False
+                out = (Sm @ E + M @ Cb).reshape(cb_shape)
+                torch.backends.cuda.matmul.allow_tf32 = allow
+                return out
+
+            if _cb_sink is not None:
+                _cb_sink.defer(codebook_grad, [aw, bw, w, sg, E, Cb])
+            else:
+                dC = codebook_grad()
         return (dw if ctx.needs_input_grad[0] else None), dC, None, None, None
 
 

@@ -153,3 +153,40 @@ def test_trainer_cuda_graph_replays_equal_eager_steps():
     # step scalars would be off by orders of magnitude more.
     np.testing.assert_allclose(la, lb, rtol=5e-3)
     assert lb[-1] < lb[0] - 0.2 and all(np.isfinite(lb))
+
+
+def test_deferred_codebook_gradient_equals_inline():
+    """loss.CodebookGradSink: the codebook gradient computed on a side stream after the rest of the backward must be
+    the gradient autograd would have produced inline -- dense and (seg, table) ground truth, eager and captured."""
+    from langsplatv2_b200 import synth
+    from langsplatv2_b200.trainer import synthetic_gt_segments
+    N, W, H = 20000, 256, 192
+    scene = synth.make_scene(N, seed=0, levels=1)
+    scene["scaling"] = scene["scaling"] * 2.0
+    cam = synth.ring_camera(0, 8, W, H)
+    cam = {k: (v.cuda() if torch.is_tensor(v) else v) for k, v in cam.items()}
+    gt, mask = synthetic_gt(H, W, device="cuda")
+    seg = synthetic_gt_segments(H, W, device="cuda")
+    for target in ((gt, mask), (seg, None)):
+        grads, losses = [], []
+        for defer in (False, True):
+            tr = FeatureTrainer(scene, topk=4, layers=1, lr=0.01, defer_codebook_grad=defer)
+            assert (tr._cb_sink is not None) == defer
+            tr.keep_last_grad = True
+            losses.append(float(tr.step(cam, *target)))
+            grads.append(tr.last_grad.clone())
+            n_log = tr.n_log
+        a, b = grads
+        assert losses[0] == pytest.approx(losses[1], rel=1e-6)
+        cb_a, cb_b = a[n_log:], b[n_log:]
+        assert float(cb_a.abs().max()) > 0
+        assert float((cb_a - cb_b).abs().max()) <= 1e-5 * float(cb_a.abs().max())
+        assert float((a[:n_log] - b[:n_log]).abs().max()) <= 1e-4 * float(a[:n_log].abs().max())
+    # captured iterations with the side stream inside the graph: same losses as eager deferred steps
+    runs = []
+    for graph in (False, True):
+        tr = FeatureTrainer(scene, topk=4, layers=1, lr=0.01, defer_codebook_grad=True, use_graph=graph)
+        tr.calibrate([cam])
+        runs.append([float(tr.step(cam, gt, mask, view_id=0)) for _ in range(6)])
+    np.testing.assert_allclose(runs[0], runs[1], rtol=5e-3)
+    assert runs[1][-1] < runs[1][0]
