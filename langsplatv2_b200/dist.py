@@ -197,6 +197,13 @@ class ShardedExchange:
             self._side.wait_event(ev)
             self._ag[i] = dist.all_gather_into_tensor(self.p[a:b], self.p[lo:hi], async_op=True)
 
+    def all_gather_all(self) -> None:
+        """Deferred form: every block's shard is final on the current stream (the previous iteration's Adam); start all
+        the gathers on the side stream.  The caller runs work that does not read the parameters (the next iteration's
+        preprocess + binning) and then calls ``finish()``."""
+        for i in range(len(self.blocks)):
+            self.all_gather_params(i)
+
     def finish(self) -> None:
         """The current stream waits for every outstanding gather (call before the next forward)."""
         for i, w in enumerate(self._ag):

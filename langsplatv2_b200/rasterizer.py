@@ -167,7 +167,8 @@ def rasterize_forward(rs: GaussianRasterizationSettings, means3D, opacities, shs
                       scales=None, rotations=None, cov3D_precomp=None, language_feature_precomp=None,
                       language_feature_weights_quick=None, language_feature_indices=None,
                       capacity: Optional[int] = None, debug_buffers: bool = False,
-                      render: bool = True, blend: str = "auto", packed: Optional[torch.Tensor] = None) -> FrameState:
+                      render: bool = True, blend: str = "auto", packed: Optional[torch.Tensor] = None,
+                      prepared: Optional[FrameState] = None) -> FrameState:
     """Preprocess -> bin -> blend.  ``capacity=None`` reads the instance count back between the two
     halves (one host sync, as the reference does); an integer capacity runs the whole frame with no
     host involvement and flags overflow in ``state.status``.
@@ -187,7 +188,8 @@ def rasterize_forward(rs: GaussianRasterizationSettings, means3D, opacities, shs
                                      language_feature_precomp=language_feature_precomp,
                                      language_feature_weights_quick=language_feature_weights_quick,
                                      language_feature_indices=language_feature_indices, capacity=capacity,
-                                     debug_buffers=debug_buffers, render=render, blend=blend, packed=packed)
+                                     debug_buffers=debug_buffers, render=render, blend=blend, packed=packed,
+                                     prepared=prepared)
     P = int(means3D.shape[0])
     H, W = int(rs.image_height), int(rs.image_width)
     mode = feature_mode(rs)
@@ -240,6 +242,38 @@ def rasterize_forward(rs: GaussianRasterizationSettings, means3D, opacities, shs
         feat["packed"] = packed
     st = FrameState(P=P, H=H, W=W, mode=mode, L=L, K=K)
     st.feat = feat
+    if prepared is not None:
+        if (prepared.P, prepared.H, prepared.W) != (P, H, W) or prepared.capacity is None or not prepared.binning:
+            raise ValueError("prepared must be the state of rasterize_forward(..., render=False) for this view and scene")
+        if not render:
+            raise ValueError("prepared and render=False together do nothing")
+        st.view, st.keep, st.scene = prepared.view, prepared.keep, prepared.scene
+        st.geom, st.binning, st.status, st.capacity = prepared.geom, prepared.binning, prepared.status, prepared.capacity
+        f32_ = dict(dtype=torch.float32, device=dev)
+        st.image["color"] = torch.empty((3, H, W), **f32_)
+        st.image["final_T"] = torch.empty((H, W), **f32_)
+        st.image["n_contrib"] = torch.empty((H, W), dtype=torch.int32, device=dev)
+        if mode != MODE_RGB:
+            st.image["wmap"] = torch.empty((L, H, W), **f32_)
+        if blend not in ("auto", "tc", "simt"):
+            raise ValueError("blend must be 'auto', 'tc' or 'simt'")
+        tc_ok_ = mode != MODE_RGB and L > 0 and L % 64 == 0 and L <= 192 and (mode == MODE_DENSE or 0 < K <= SPARSE_CAP)
+        if blend == "tc" and not tc_ok_:
+            raise _abi.Lsv2Error("blend='tc' needs L a multiple of 64 up to 192 and at most 16 entries per Gaussian")
+        geom_c, bin_c = st.c_geom(), st.c_binning()
+        feat_c, img_c = st.c_features(), st.c_image()
+        stream_ = _abi.stream_ptr(dev)
+        if mode == MODE_DENSE:
+            _abi.check(L_.lsv2_compact_coeff(P, C.byref(geom_c), C.byref(feat_c), stream_), "lsv2_compact_coeff")
+        if tc_ok_ and blend != "simt":
+            st.ensure_packed(geom_c)
+            feat_c = st.c_features()
+            _abi.check(L_.lsv2_render_forward_tc(C.byref(st.view), C.byref(geom_c), C.byref(bin_c), C.byref(feat_c),
+                                                 C.byref(img_c), stream_), "lsv2_render_forward_tc")
+        else:
+            _abi.check(L_.lsv2_render_forward(C.byref(st.view), C.byref(geom_c), C.byref(bin_c), C.byref(feat_c),
+                                              C.byref(img_c), stream_), "lsv2_render_forward")
+        return st
     st.view = _make_view(rs, dev, st.keep)
     st.keep += [means3D, opacities, shs, colors_precomp, scales, rotations, cov3D_precomp]
     st.scene = dict(means3D=means3D, opacities=opacities, shs=shs, colors_precomp=colors_precomp, scales=scales,
@@ -512,12 +546,13 @@ class _RasterizeGaussians(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, language_feature_precomp, weights_quick, indices_quick,
-                opacities, scales, rotations, cov3Ds_precomp, raster_settings, capacity=None, dense_coeff_grad=None):
+                opacities, scales, rotations, cov3Ds_precomp, raster_settings, capacity=None, dense_coeff_grad=None,
+                prepared=None):
         st = rasterize_forward(raster_settings, means3D, opacities, shs=sh, colors_precomp=colors_precomp,
                                scales=scales, rotations=rotations, cov3D_precomp=cov3Ds_precomp,
                                language_feature_precomp=language_feature_precomp,
                                language_feature_weights_quick=weights_quick, language_feature_indices=indices_quick,
-                               capacity=capacity)
+                               capacity=capacity, prepared=prepared)
         # what backward needs, WITHOUT the forward's outputs: a state holding `color` / `wmap` on ctx closes the cycle
         # output -> grad_fn -> ctx -> state -> output through C++ shared_ptrs, which Python's GC cannot collect --
         # every grad-enabled forward would leak its whole frame
@@ -570,7 +605,8 @@ class _RasterizeGaussians(torch.autograd.Function):
             pick = lambda i, k: g.get(k) if need[i] else None
             d_op = g["opacities"].reshape(ctx.opacity_shape) if need[7] else None
             return (pick(0, "means3D"), pick(1, "means2D"), pick(2, "shs"), pick(3, "colors_precomp"), None, None,
-                    None, d_op, pick(8, "scales"), pick(9, "rotations"), pick(10, "cov3D_precomp"), None, None, None)
+                    None, d_op, pick(8, "scales"), pick(9, "rotations"), pick(10, "cov3D_precomp"), None, None, None,
+                    None)
         d_coeff = d_colors = None
         if st.mode == MODE_DENSE and need[4]:
             gc = grad_color if (need[3] and ctx.color_is_precomp) else None
@@ -585,7 +621,7 @@ class _RasterizeGaussians(torch.autograd.Function):
                 raise
         elif need[3]:
             raise NotImplementedError("colour gradients are produced together with the feature backward only")
-        return (None, None, None, d_colors, d_coeff, None, None, None, None, None, None, None, None, None)
+        return (None, None, None, d_colors, d_coeff, None, None, None, None, None, None, None, None, None, None)
 
 
 class GaussianRasterizer(nn.Module):
@@ -599,6 +635,7 @@ class GaussianRasterizer(nn.Module):
         self.raster_settings = raster_settings
         self.capacity = capacity
         self.dense_coeff_grad: Optional[bool] = None     # None: module default DENSE_COEFF_GRAD (strict)
+        self.prepared: Optional[FrameState] = None       # extension: geometry stage done earlier (rasterize_forward)
         self.last_state: Optional[FrameState] = None
 
     def markVisible(self, positions: torch.Tensor) -> torch.Tensor:
@@ -622,7 +659,8 @@ class GaussianRasterizer(nn.Module):
             raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
         out = _RasterizeGaussians.apply(means3D, means2D, shs, colors_precomp, language_feature_precomp,
                                         language_feature_weights_quick, language_feature_indices, opacities,
-                                        scales, rotations, cov3D_precomp, rs, self.capacity, self.dense_coeff_grad)
+                                        scales, rotations, cov3D_precomp, rs, self.capacity, self.dense_coeff_grad,
+                                        self.prepared)
         # the full frame state (outputs included) lives on the module, outside the autograd graph
         self.last_state = _RasterizeGaussians.last_state
         _RasterizeGaussians.last_state = None

@@ -129,6 +129,12 @@ class FeatureTrainer:
         if defer_codebook_grad and dev.type == "cuda" and self.gram_loss and self.layers == 1:
             from .loss import CodebookGradSink
             self._cb_sink = CodebookGradSink(self.codebooks.grad[0:1])
+        # N > 1, zero1: the all-gather of the updated parameters is deferred to the START of the next iteration, where it
+        # runs under that iteration's preprocess + binning (which read no trainable parameter: the geometry is frozen).
+        # Between iterations a rank's copy of the shards it does not own is one step old: call sync_params() before
+        # reading logits / codebooks from outside (checkpoints, evaluation).
+        self.defer_gather = (self.collective == "zero1" and os.environ.get("LSV2_DEFER_AG", "1") != "0")
+        self.split_prepare = dev.type == "cuda" and os.environ.get("LSV2_SPLIT_PREPARE", "1") != "0"
         self.keep_last_grad = False
         self.last_grad = None
         self.iteration = 0
@@ -153,6 +159,12 @@ class FeatureTrainer:
         cs = self.codebook_size
         w = [softmax_to_topk_soft_code(self.logits[:, i * cs:(i + 1) * cs], self.topk) for i in range(self.layers)]
         return w[0] if len(w) == 1 else torch.cat(w, dim=-1)
+
+    def sync_params(self) -> None:
+        """Make every rank's logits / codebooks current (N > 1 with the deferred all-gather; no-op otherwise)."""
+        if self.defer_gather and self.exchange is not None:
+            self.exchange.all_gather_all()
+            self.exchange.finish()
 
     def settings(self, cam: Dict) -> GaussianRasterizationSettings:
         d = self.dev
@@ -194,7 +206,22 @@ class FeatureTrainer:
 
     def loss(self, cam: Dict, gt, mask: Optional[torch.Tensor], gt_sumsq: Optional[torch.Tensor] = None,
              view_id=None) -> torch.Tensor:
-        rasterizer = GaussianRasterizer(raster_settings=self.settings(cam), capacity=self.capacity)
+        rs = self.settings(cam)
+        gather = self.defer_gather and self.exchange is not None
+        if gather:
+            self.exchange.all_gather_all()          # last iteration's parameter shards -> every rank (side stream)
+        prepared = None
+        if self.split_prepare and self.capacity is not None:
+            # geometry stage first: it reads no trainable parameter, so it runs while the gather is in flight
+            from .rasterizer import rasterize_forward
+            with torch.no_grad():
+                prepared = rasterize_forward(rs._replace(include_feature=False), self.xyz, self.opacity, shs=self.shs,
+                                             scales=self.scales, rotations=self.rotations, capacity=self.capacity,
+                                             render=False)
+        if gather:
+            self.exchange.finish()
+        rasterizer = GaussianRasterizer(raster_settings=rs, capacity=self.capacity)
+        rasterizer.prepared = prepared
         rasterizer.dense_coeff_grad = False         # the top-k mask follows (utils/vq_utils.py:20): support-only is exact
         zero = torch.zeros((1,), dtype=torch.float32, device=self.dev)
         _, wmap, _ = rasterizer(means3D=self.xyz, means2D=self.means2D, shs=self.shs, colors_precomp=None,
@@ -290,20 +317,24 @@ class FeatureTrainer:
             if not use_sink:
                 for i in range(nb - 1):
                     ex.reduce_scatter(i)
+            defer = self.defer_gather
             for i in range(nb - 1):                                      # the logits' row blocks
                 ex.wait_grad(i)
                 lo, hi = ex.shard_range(i)
                 opt.step_range(lo, hi, grad=ex.shard_grad[i])
-                ex.all_gather_params(i)
+                if not defer:
+                    ex.all_gather_params(i)
             join_codebook_grad()
             ex.reduce_scatter(nb - 1)                                    # codebooks (+ pad)
             ex.wait_grad(nb - 1)
             lo, hi = ex.shard_range(nb - 1)
             opt.step_range(lo, hi, grad=ex.shard_grad[nb - 1])
-            ex.all_gather_params(nb - 1)
+            if not defer:
+                ex.all_gather_params(nb - 1)
             if self.keep_last_grad:
                 self.last_grad = ex.full_reduced_grad()
-            ex.finish()
+            if not defer:
+                ex.finish()
         elif self.collective == "allreduce":
             bk = self.bucket
             if not use_sink:
