@@ -44,7 +44,7 @@ constexpr int FD_CB_BYTES = 128 * 128;                   // codebook chunk [128 
 constexpr int FD_CB_SLOTS = 2;
 constexpr int FD_CHUNKS = FD_D / 128;                    // 4 chunks of 128 features per level
 #ifndef FD_NFEAT_OPT
-#define FD_NFEAT_OPT 32
+#define FD_NFEAT_OPT 64
 #endif
 constexpr int FD_NFEAT = FD_NFEAT_OPT;                   // features per decode MMA / F slot
 constexpr int FD_FGROUPS = 128 / FD_NFEAT;               // feature groups per chunk
@@ -177,6 +177,25 @@ __device__ __forceinline__ uint32_t fd_strip_mask_ext(float y_rel, float x_rel, 
     if (hi < lo) return 0u;
     const int wlo = lo >> 1, whi = hi >> 1;
     return ((1u << (whi + 1)) - 1u) & ~((1u << wlo) - 1u);
+}
+
+// The fused kernel's blend warps each own an 8 x 4 pixel block of a 16 x 8 half band (bit = 2 * (row block) + (column
+// block)): a splat is skipped by every warp whose block its alpha >= 1/255 bounding box misses.  Blocks instead of
+// 16 x 2 strips: for a splat of radius r the boxes touched shrink from (2r + 16)(2r + 2) to (2r + 8)(2r + 4) pixels --
+// 15-20 % fewer (pixel, instance) pairs at the radii of the metric's scene.  Conservative like fd_strip_mask_ext (the
+// extents are rounded outwards, an integer row must lie inside the y range, the x test is on the continuous range),
+// so no blend decision changes.
+__device__ __forceinline__ uint32_t fd_block_mask_ext(float y_rel, float x_rel, float dy, float dx)
+{
+    if (!(dy >= 0.0f)) return 0u;
+    const float lo_f = ceilf(y_rel - dy), hi_f = floorf(y_rel + dy);
+    if (lo_f != lo_f || hi_f != hi_f) return 0xFu;
+    if (hi_f < lo_f) return 0u;
+    const float xlo = x_rel - dx, xhi = x_rel + dx;
+    const uint32_t rows = ((lo_f <= 3.0f && hi_f >= 0.0f) ? 1u : 0u) | ((lo_f <= 7.0f && hi_f >= 4.0f) ? 2u : 0u);
+    const uint32_t cols = (!(xhi < 0.0f || xlo > 7.0f) ? 1u : 0u) | (!(xhi < 8.0f || xlo > 15.0f) ? 2u : 0u);
+    // bit 2 * by + bx
+    return ((rows & 1u) ? cols : 0u) | ((rows & 2u) ? (cols << 2) : 0u);
 }
 
 // barrier with an OR reduction over the participating threads (uniform result)
