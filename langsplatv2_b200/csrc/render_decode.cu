@@ -337,8 +337,8 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
     if (warp == FD_WARP_PROD || warp == FD_WARP_PROD + 1) {
         // ======================================= producers =======================================
         // Warp t serves tile list t (the left / right tile of the band): lanes i and i + 16 share instance slot i.
-        // Depth of the software pipeline, per list: instance ids 7 batches ahead, an L2 prefetch of their records and
-        // coefficient rows 5 batches ahead, the register gather 1 batch ahead, so the memory latency stays off the
+        // Depth of the software pipeline, per list: instance ids 8 batches ahead, an L2 prefetch of their records and
+        // coefficient rows 6 batches ahead, the register gather 2 batches ahead, so the memory latency stays off the
         // per-batch path: wait stage -> zero the S tile -> scatter -> arrive.
         const int t = warp - FD_WARP_PROD;
         const int inst = lane & 15, part = lane >> 4;
@@ -346,6 +346,9 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
         uint32_t use_g = 0;                             // stage uses so far (global)
         FD_PROF_DECL
         FD_TIC();
+        // Units are claimed from a global counter.  (Dealing most of them round-robin without the atomic, and walking the
+        // next unit's set-up chain -- range, ids, records -- during the current unit, with registers or with cp.async
+        // into shared memory, were both measured on one box against this form: within +-1 %, profiles/r02m.)
         for (uint32_t u_iter = 0;; ++u_iter) {
             if (ptid == 0) s_misc[0] = atomicAdd(a.tile_counter, 1u);
             named_bar_sync(1, FD_PROD_THREADS);
@@ -364,14 +367,15 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
                 const uint32_t i = b * FD_BATCH + (uint32_t)inst;
                 return i < n_inst ? __ldg(a.point_list + range.x + i) : 0xFFFFFFFFu;
             };
-            FdGather cur, nxt;
-            uint32_t idq[5];                            // ids of batches b+2 .. b+6
+            FdGather cur, nxt, nx2;                     // batches b, b + 1 (gathers in flight / landed), b + 2 (id only)
+            uint32_t idq[5];                            // ids of batches b+3 .. b+7
             {
-                const uint32_t i0 = load_id(0), i1 = load_id(1);
+                const uint32_t i0 = load_id(0), i1 = load_id(1), i2 = load_id(2);
 #pragma unroll
-                for (int k = 0; k < 5; ++k) idq[k] = load_id(2 + k);
+                for (int k = 0; k < 5; ++k) idq[k] = load_id(3 + k);
                 fd_gather(a, i0, part, cur);
-                nxt.g = i1;
+                fd_gather(a, i1, part, nxt);
+                nx2.g = i2;
 #pragma unroll
                 for (int k = 0; k < 3; ++k) fd_prefetch(a, idq[k], part);
             }
@@ -402,12 +406,15 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
                     ++use_g;
                     break;
                 }
+                FD_TOC(3);
                 unsigned char* S = S_base + (size_t)s * FD_STAGE_BYTES;
                 for (int q = lane; q < FD_S_BYTES / 16; q += 32) reinterpret_cast<uint4*>(S)[q] = make_uint4(0, 0, 0, 0);
-                fd_gather(a, nxt.g, part, nxt);              // batch b + 1
-                fd_prefetch(a, idq[3], part);                // batch b + 5
-                const uint32_t id_new = load_id(b + 7);
+                fd_gather(a, nx2.g, part, nx2);              // batch b + 2: under the write stream an L2 hit takes about one
+                                                             // batch time, so the gather gets two batches to land
+                fd_prefetch(a, idq[3], part);                // batch b + 6
+                const uint32_t id_new = load_id(b + 8);
                 __syncwarp();
+                FD_TOC(4);
                 uint32_t m4 = 0;
                 if (cur.g != 0xFFFFFFFFu) {
                     if (part == 0) {
@@ -441,6 +448,7 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
                         }
                     }
                 }
+                if (b == 0) FD_TOC(5); else FD_TOC(1);
 #pragma unroll
                 for (int w = 0; w < 4; ++w) {
                     const uint32_t bal = __ballot_sync(0xffffffffu, (m4 >> w) & 1u);     // part-0 lanes: bit i = instance i
@@ -450,14 +458,15 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
                 fence_async_smem();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(full + s);
-                // batch b + 1 becomes current (its loads have had the whole assembly to land); queue the id of b + 2
+                // batch b + 1 becomes current; queue the id of b + 3
                 cur = nxt;
-                nxt.g = idq[0];
+                nxt = nx2;
+                nx2.g = idq[0];
 #pragma unroll
                 for (int k = 0; k < 4; ++k) idq[k] = idq[k + 1];
                 idq[4] = id_new;
                 ++use_g;
-                FD_TOC(1);
+                FD_TOC(6);
             }
             if (exit_now) break;
         }
@@ -795,77 +804,86 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
                 unsigned char* A = ring + (size_t)s * FD_STAGE_BYTES + (size_t)half * FD_AHALF_BYTES;
                 const uint32_t m = warp_done ? 0u : Hd.mask[warp];
                 FD_TOCB(0);
-                // One group of 4 instances per iteration, NOT unrolled: the hot loop stays ~200 instructions (3 KB), so
-                // the five warp roles' loops share the instruction caches (L0 6 KB, L1.5 32 KB) instead of thrashing
-                // them -- with the 16 instances unrolled (15 KB) every role ran ~5x slower.
+                // The hot loop is NOT unrolled: it stays a few hundred instructions, so the five warp roles' loops share
+                // the instruction caches (L0 6 KB, L1.5 32 KB) instead of thrashing them -- with the 16 instances
+                // unrolled (15 KB) every role ran ~5x slower.
+                // The mask is warp-uniform: the warp walks only the instances whose alpha >= 1/255 box reaches its 8 x 4
+                // block, four set bits per iteration (the four quadratic forms / exps interleave; a short tail repeats
+                // its last instance with the weight forced to 0).  Skipped instances would have added w = 0 exactly, so
+                // colour, T, n_contrib and the weight tile are bit-identical to walking all sixteen.  The A row is
+                // zeroed first; each (pixel, instance) hit then stores its fp16 head / remainder at the instance's column.
+                {
+                    const uint32_t off0 = sw64_offset((uint32_t)row, 0u), off1 = sw64_offset((uint32_t)row, 1u);
+                    const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
+                    *reinterpret_cast<uint4*>(A + off0) = z4;
+                    *reinterpret_cast<uint4*>(A + (off0 ^ 32u)) = z4;
+                    *reinterpret_cast<uint4*>(A + off1) = z4;
+                    *reinterpret_cast<uint4*>(A + (off1 ^ 32u)) = z4;
+                }
+                uint32_t mm = __shfl_sync(0xffffffffu, m, 0);     // uniform by construction; make it so for the compiler
 #pragma unroll 1
-                for (int g8 = 0; g8 < FD_BATCH / 8; ++g8) {
-                    // eight instances per iteration = one 16-byte chunk of heads + one of remainders per row: with the
-                    // 64-byte row pitch a warp's STS.128 touches every bank exactly 4 times (512 B in 4 wavefronts),
-                    // where two STS.64 took 4 wavefronts each
-                    uint32_t hw[4] = {0u, 0u, 0u, 0u}, lw[4] = {0u, 0u, 0u, 0u};
+                while (mm != 0u) {
+                    int jj[4];
+                    bool vk[4];
 #pragma unroll
-                    for (int h2 = 0; h2 < 2; ++h2) {
-                    const int g4 = 2 * g8 + h2;
-                    const uint32_t m4 = (m >> (4 * g4)) & 0xFu;
-                    if (m4 != 0u) {
-                        // stage 1: the four quadratic forms and alphas are independent (ILP); alpha does not
-                        // depend on T.  stage 2: the short sequential transmittance chain.
-                        float pw_[4], op_[4], cr_[4];
-                        bool hit[4];
-                        bool any = false;
-                        const int j0 = half * FD_BATCH + 4 * g4;
+                    for (int u = 0; u < 4; ++u) {
+                        vk[u] = mm != 0u;
+                        jj[u] = vk[u] ? (__ffs((int)mm) - 1) : (u > 0 ? jj[u - 1] : 0);
+                        mm &= mm - 1u;
+                    }
+                    float pw_[4], op_[4], cr_[4];
+                    bool hit[4];
+                    bool any = false;
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const int j = half * FD_BATCH + jj[u];
+                        const float4 g0 = Hd.g0[j];
+                        const float4 g1 = Hd.g1[j];
+                        const float dx = g0.x - pxf, dy = g0.y - pyf;
+                        pw_[u] = fmaf(g0.z * dx, dx, fmaf(g1.x * dy, dy, (g0.w * dx) * dy));
+                        hit[u] = vk[u] && !(pw_[u] > 0.0f || pw_[u] < g1.y);
+                        op_[u] = g1.z;
+                        cr_[u] = g1.w;
+                        any |= hit[u];
+                    }
+                    FD_TOCB(1);
+                    if (any && !done) {
+                        // a hit has cut-off <= power <= 0 (cut-off > -6), so the unchecked exp is exact there;
+                        // evaluated for all four so the chains interleave, discarded where !hit
+                        float al[4], xe[4], e4[4];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) xe[u] = fmaxf(fminf(pw_[u], 0.0f), -80.0f);
+                        repro_expf_inrange4(xe, e4);
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) al[u] = hit[u] ? fminf(ALPHA_MAX, op_[u] * e4[u]) : 0.0f;
+                        FD_TOCB(2);
 #pragma unroll
                         for (int u = 0; u < 4; ++u) {
-                            const float4 g0 = Hd.g0[j0 + u];
-                            const float4 g1 = Hd.g1[j0 + u];
-                            const float dx = g0.x - pxf, dy = g0.y - pyf;
-                            pw_[u] = fmaf(g0.z * dx, dx, fmaf(g1.x * dy, dy, (g0.w * dx) * dy));
-                            hit[u] = ((m4 >> u) & 1u) && !(pw_[u] > 0.0f || pw_[u] < g1.y);
-                            op_[u] = g1.z;
-                            cr_[u] = g1.w;
-                            any |= hit[u];
-                        }
-                        FD_TOCB(1);
-                        if (any && !done) {
-                            // a hit has cut-off <= power <= 0 (cut-off > -6), so the unchecked exp is exact there;
-                            // evaluated for all four so the chains interleave, discarded where !hit
-                            float al[4], xe[4], e4[4], wgt[4];
-#pragma unroll
-                            for (int u = 0; u < 4; ++u) xe[u] = fmaxf(fminf(pw_[u], 0.0f), -80.0f);
-                            repro_expf_inrange4(xe, e4);
-#pragma unroll
-                            for (int u = 0; u < 4; ++u) al[u] = hit[u] ? fminf(ALPHA_MAX, op_[u] * e4[u]) : 0.0f;
-                            FD_TOCB(2);
-#pragma unroll
-                            for (int u = 0; u < 4; ++u) {
-                                // select-only form of: skip if alpha < 1/255 or done; stop if T' < 1e-4; else blend.
-                                // A skipped instance adds w = 0 (exact), so the sums match the branching form bit for bit.
-                                const bool valid = !(al[u] < ALPHA_MIN) && !done;
-                                const float test_T = T * (1.0f - al[u]);
-                                const bool stop = valid && (test_T < T_MIN);
-                                const bool use = valid && !stop;
-                                done = done || stop;
-                                const float w = use ? al[u] * T : 0.0f;
-                                const float2 g2 = Hd.g2[j0 + u];
-                                C0 = fmaf(cr_[u], w, C0);
-                                C1 = fmaf(g2.x, w, C1);
-                                C2 = fmaf(g2.y, w, C2);
-                                wgt[u] = w;
-                                T = use ? test_T : T;
-                                last = use ? (uint32_t)nb * FD_BATCH + (uint32_t)(4 * g4 + u) + 1u : last;
+                            // select-only form of: skip if alpha < 1/255 or done; stop if T' < 1e-4; else blend.
+                            // A skipped instance adds w = 0 (exact), so the sums match the branching form bit for bit.
+                            const bool valid = !(al[u] < ALPHA_MIN) && !done;
+                            const float test_T = T * (1.0f - al[u]);
+                            const bool stop = valid && (test_T < T_MIN);
+                            const bool use = valid && !stop;
+                            done = done || stop;
+                            const float w = use ? al[u] * T : 0.0f;
+                            const float2 g2 = Hd.g2[half * FD_BATCH + jj[u]];
+                            C0 = fmaf(cr_[u], w, C0);
+                            C1 = fmaf(g2.x, w, C1);
+                            C2 = fmaf(g2.y, w, C2);
+                            T = use ? test_T : T;
+                            last = use ? (uint32_t)nb * FD_BATCH + (uint32_t)jj[u] + 1u : last;
+                            if (use) {
+                                // fp16 head + fp16 remainder at column jj[u] of this pixel's row (k-slice 0 | k-slice 1)
+                                const __half hh = __float2half_rn(w);
+                                const __half ll = __float2half_rn(__fsub_rn(w, __half2float(hh)));
+                                const uint32_t o = sw64_offset((uint32_t)row, (uint32_t)(jj[u] >> 3)) + (uint32_t)(jj[u] & 7) * 2u;
+                                *reinterpret_cast<__half*>(A + o) = hh;
+                                *reinterpret_cast<__half*>(A + (o ^ 32u)) = ll;
                             }
-                            FD_TOCB(3);
-                            split_f16x2(wgt[0], wgt[1], hw[2 * h2], lw[2 * h2]);
-                            split_f16x2(wgt[2], wgt[3], hw[2 * h2 + 1], lw[2 * h2 + 1]);
-                            FD_TOCB(4);
                         }
+                        FD_TOCB(3);
                     }
-                    }
-                    // 16 bytes of heads at k-slice 0, 16 bytes of remainders at k-slice 1 (chunk index + 2)
-                    const uint32_t off = sw64_offset((uint32_t)row, (uint32_t)g8);
-                    *reinterpret_cast<uint4*>(A + off) = make_uint4(hw[0], hw[1], hw[2], hw[3]);
-                    *reinterpret_cast<uint4*>(A + (off ^ 32u)) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
                     FD_TOCB(5);
                 }
                 ++nb;

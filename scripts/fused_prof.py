@@ -24,7 +24,8 @@ off = 256 + levels * 512 * 128 + levels * 128 * 128
 prof = scratch[off:off + 148 * 6 * 8 * 8].cpu().numpy().view(np.int64).reshape(148, 6, 8).astype(np.float64)
 names = {0: ["wait full (producer)", "blend batch compute", "wait w_full (last MMA)", "wait dec_done (prev decode)",
              "pass A (TMEM -> fp16 rows)", "colour out + Gram norm (u_full waits)", "unit setup"],
-         1: ["wait stage_free", "assemble batch", "unit setup / loop"],
+         1: ["wait stage_free", "scatter (batches 1..)", "unit setup / loop", "stop check + look-ahead links",
+             "zero S + issue gathers", "scatter (batch 0 of a unit: first use of its gather)", "masks + fence + arrive + rotate"],
          2: ["wait wraw (blend side)", "wait codebook chunk", "wait F slot free (epilogue)", "issue"],
          3: ["wait inv_full (unit hand-off)", "wait F slot full (MMA)", "tcgen05.ld + stores"],
          4: ["header / mask read", "stage 1: loads + quadratic forms", "exp x4 + alpha", "transmittance chain",
