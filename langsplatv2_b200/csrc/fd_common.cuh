@@ -16,7 +16,7 @@ using namespace tc;
 // 32 pixels, so every store instruction of the epilogue writes one full 128-byte line.
 constexpr int FD_BATCH = 16;                             // depth-sorted instances per batch (one MMA k-slice)
 constexpr int FD_STAGES = 2;
-constexpr int FD_BLEND_WARPS = 8;                        // warps 0-7: one thread per pixel; warp = 16x2 strip of a half
+constexpr int FD_BLEND_WARPS = 8;                        // warps 0-7: one thread per pixel; warp = 8x4 block of a half band
 constexpr int FD_EPI_WARPS = 4;                          // warps 8-11: F slots (TMEM) -> scaled 128-byte-line stores
 constexpr int FD_WARP_PROD = 12;                         // warps 12, 13: one per tile list -- gather instances, build S
 constexpr int FD_PROD_THREADS = 64;
@@ -55,7 +55,7 @@ struct __align__(16) FdHeader {
     float4 g0[2 * FD_BATCH];             // x, y, -a/2, -b             (list 0: [0,16), list 1: [16,32))
     float4 g1[2 * FD_BATCH];             // -c/2, power cut-off, opacity, r
     float2 g2[2 * FD_BATCH];             // g, b
-    uint32_t mask[FD_BLEND_WARPS];       // per strip (half*4 + strip): which of its list's 16 instances can reach it
+    uint32_t mask[FD_BLEND_WARPS];       // per blend warp (half*4 + block): which of its list's 16 instances can reach its block
     int32_t count;                       // >= 0 batch ; -1 end of unit ; -2 no more units
     int32_t unit;
     int32_t batches;                     // terminator: batches this unit had

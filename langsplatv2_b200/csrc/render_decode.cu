@@ -1,33 +1,37 @@
-// render_decode.cu -- K6+K7 fused: per-tile alpha blending whose sparse-coefficient accumulation runs on the
-// 5th-gen tensor cores, overlapped in the same CTA with the global codebook decode + L2 normalisation of the
-// previous tile, whose 512-d features leave through shared-memory staging and TMA tensor stores.
+// render_decode.cu -- K6+K7 fused: alpha blending whose sparse-coefficient accumulation runs on the 5th-gen tensor
+// cores, overlapped in the same CTA with the global codebook decode + L2 normalisation of the previous work unit,
+// whose 512-d features go from TMEM through registers straight to HBM as full 128-byte lines.
 // The L-channel weight map never exists in HBM (nor in shared memory as read-modify-write accumulators).
 // Replaces renderCUDA (forward) + the einsum/norm/divide every caller runs after it
 // (/root/reference/gaussian_renderer/__init__.py:108-119 ; eval_lerf.py:214-218 ; SURVEY.md rows R8+R9).
+// Three paths share the kernel (template PATH): weight map only (the 3-tuple op), decode, relevancy query.
 //
-// Persistent CTAs (one per SM), tiles handed out by an atomic counter.  Warp roles (fd_common.cuh):
-//   warps 0-7   blend: one thread per pixel of the 32x8 band (warp = 8x4 block of a half band).  Pixels 0..127 are rows of MMA
-//               half 0, pixels 128..255 of half 1; thread = TMEM lane.  At the end of a tile the same threads move
-//               the weight tile W (TMEM, fp32) into the decode's fp16 operand and L2-normalise it (Gram matrix).
-//   warp 12     producer: gathers the packed blend records of 16 depth-sorted instances per batch, builds the
-//               per-strip cut-off masks, and scatters each instance's (channel, weight) pairs -- split into an fp16
-//               head and an fp16 remainder -- into a zeroed B tile  S[L channels][hi 16 | lo 16]  (K-major, SW64).
-//   warp 13     one thread issues the blend MMAs.
-//   warp 14     one thread issues the Gram and decode MMAs and the bulk copies of the codebook chunks.
-//   warps 8-11  epilogue: F slots (TMEM) -> registers -> swizzled staging -> cp.async.bulk.tensor stores.
+// Persistent CTAs (one per SM); work unit = a 32 x 8 pixel band (the 8-row halves of two horizontally adjacent 16x16
+// tiles, each half with its own tile's depth-sorted list), handed out by an atomic counter.  Warp roles (fd_common.cuh):
+//   warps 0-7   blend: one thread per pixel; warp = one 8 x 4 block of a half band; thread = A-tile row = TMEM lane of
+//               the blend MMA.  At the end of a unit the same threads move the weight tile W (TMEM, fp32) into the
+//               decode's fp16 operand (pass A) and compute the per-pixel 1/norm from the Gram product (pass B).
+//   warps 12-13 producers, one per tile list: gather the packed blend records and packed coefficient rows of 16
+//               depth-sorted instances per batch (ids 8 batches ahead, L2 prefetch 6 ahead, registers 2 ahead), write
+//               the header + per-block cut-off masks, scatter each instance's (channel, fp16 head | fp16 remainder)
+//               pairs into a zeroed B tile  S[L channels][hi 16 | lo 16]  (K-major, 64-byte swizzle).
+//   warp 14     MB: issues the blend MMAs (converged warp, elect.sync); owns the TMEM allocation.
+//   warp 15     MD: issues the Gram and decode MMAs and the bulk copies of the codebook chunks.
+//   warps 8-11  epilogue: F slots (TMEM) -> registers -> x 1/norm -> st.global.cs, lane = x: every store instruction
+//               writes one full 128-byte line of one feature plane (or 128 contiguous bytes of a pixel, channels-last).
 //
-// Blend, per batch:  the pixel threads evaluate alpha and T exactly as k_render_forward does (same fp32
-// operations, same thresholds => identical n_contrib / final_T / RGB) and store the blending weight alpha*T of
-// each (pixel, instance) as fp16 head + fp16 remainder into the A tile [128 px][hi 16 | lo 16] of their half;
+// Blend, per batch:  the pixel threads evaluate alpha and T exactly as k_render_forward does (same fp32 operations,
+// same thresholds => identical n_contrib / final_T / RGB), walking only the instances whose alpha >= 1/255 box reaches
+// their warp's block, and store the blending weight alpha*T of each hit as fp16 head + fp16 remainder into the A tile
+// [128 px][hi 16 | lo 16] of their half;
 //   W[128 x L] += A_hi.S_hi + A_lo.S_hi + A_hi.S_lo        (M = 128, N = L, three K = 16 MMAs, fp32 in TMEM)
-// which carries ~22 significant bits per factor: the weight map meets the fp32-blend tolerance (1e-4).
-// End of tile:  W -> fp16 rows of Wdec[level][256 px][64 codes];  U_l = Wdec_l.(G_hi + G_lo) with G_l = s C_l C_l^T
-// gives |F_l|^2 = w^T G w per pixel (thread-local dot product), the rows are rescaled by 1/(|F_l| + 1e-10) and the
-// blend warps move on to the next tile while
-// Decode (transposed):  F^T[128 features x 32 px] = C_l^T[chunk] . Wdec_l[32 px]^T  runs chunk by chunk into four
-// TMEM slots; an epilogue warp owns 32 feature lanes, reads its 32 pixels (two tile rows) per feature, writes them
-// as 16-byte pieces into a [2 rows][32 features][16 px] box image (64-byte swizzle, conflict-free) and one lane
-// issues the tensor store.  No per-thread global stores, no second pass over F.
+// which carries ~22 significant bits per factor: the weight map meets the fp32-blend tolerance (1e-4 of its norm).
+// End of unit:  W -> fp16 rows of Wdec[level][256 px][64 codes];  U_l = Wdec_l.(G_hi + G_lo) with G_l = s C_l C_l^T
+// gives |F_l|^2 = w^T G w per pixel; the blend warps move on to the next unit while
+// Decode:  F[128 px x 64 features] = Wdec_l[128 px x 64] . C_l[64 x 64 features]  runs chunk by chunk into two TMEM
+// slots (the 128 columns the two W halves leave free), codebook chunks streamed from an L2-resident fp16 image.
+// The history of this kernel (what was measured and dropped: TMA tensor stores, transposed decode, unrolled role
+// loops, divergent MMA issue, look-ahead across units) is in DESIGN.md 5.1 / 5.2 and profiles/r02*.
 #include <string.h>
 
 #include "fd_common.cuh"
@@ -299,7 +303,7 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
     uint64_t* f_full = bars + 19;                 // [4]  F slot ready                     (commit)
     uint64_t* f_free = bars + 23;                 // [4]  F slot drained                   (4 arrivals)
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(bars + 27);
-    uint32_t* s_ndone = s_tmem + 1;               // [2]  saturated strips, by unit parity
+    uint32_t* s_ndone = s_tmem + 1;               // [2]  saturated blend warps, by unit parity
     FdTileInfo* tinfo = reinterpret_cast<FdTileInfo*>(s_tmem + 4);     // [2] by unit parity
     uint32_t* s_misc = s_tmem + 8;                // [3]  producers: unit id, batches of list 0 / 1
     float* s_inv = reinterpret_cast<float*>(smem + FD_SMEM_INV);       // [2][3][256] by unit parity
@@ -394,8 +398,8 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
                 if (use > 0) mbar_wait_sleep(stage_free + s, (use - 1) & 1);
                 FD_TOC(0);
                 FdHeader& Hd = hdrs[s];
-                // s_ndone[parity] only ever grows: every blend warp adds exactly one per unit (when its strip saturates,
-                // or at the end of the unit), so "all 8 strips of this unit are done" is count - 8 * (u_iter / 2) >= 8
+                // s_ndone[parity] only ever grows: every blend warp adds exactly one per unit (when its block saturates,
+                // or at the end of the unit), so "all 8 blocks of this unit are done" is count - 8 * (u_iter / 2) >= 8
                 const bool stop_l = exit_now || b >= n_batches ||
                                     (int32_t)(*(volatile uint32_t*)(s_ndone + (u_iter & 1)) - FD_BLEND_WARPS * (u_iter >> 1)) >= FD_BLEND_WARPS;
                 // s_ndone may change between the 64 reads: OR-reduce so the decision is uniform over both warps
