@@ -153,6 +153,7 @@ class FeatureTrainer:
         self.use_graph = bool(use_graph) and dev.type == "cuda"
         self._graphs = {}
         self._graph_pool = None
+        self._eager_iters = 0
 
     # ---- reference: GaussianModel.get_render_weights (scene/gaussian_model.py:510-518) ----
     def render_weights(self) -> torch.Tensor:
@@ -231,11 +232,14 @@ class FeatureTrainer:
         self._last_state = rasterizer.last_state
         layer_idx = self.layer_index()
         cs = self.codebook_size
+        # one layer: the weight map IS the first layer's -- slicing it would make autograd pad the gradient back with a
+        # zero fill + a 195 MB copy (0.46 ms at 1008x756, seen in the N = 2 timeline)
+        w0 = wmap if wmap.shape[0] == cs else wmap[:cs]
         if isinstance(gt, (tuple, list)):
             # ground truth as (seg [H, W] int, table [S, 512]) -- scene/cameras.py:59-96 before the expansion
             seg, table = gt
             if self.gram_loss and layer_idx == 0 and cs == 64 and self.use_cos and not self.use_l1:
-                return decode_cos_loss_segments(wmap[:cs], self.codebooks[0:1], seg, table, normalize=self.normalize)
+                return decode_cos_loss_segments(w0, self.codebooks[0:1], seg, table, normalize=self.normalize)
             valid = (seg >= 0)
             gt = table[seg.clamp(min=0).long()].permute(2, 0, 1).contiguous() * valid.unsqueeze(0)
             mask = valid.unsqueeze(0).to(torch.float32)
@@ -252,7 +256,7 @@ class FeatureTrainer:
                     g2 = self._g2_by_view[view_id] = column_sumsq(gt)
             if g2 is None:
                 g2 = column_sumsq(gt)
-            return decode_cos_loss(wmap[:cs], self.codebooks[0:1], gt, mask, normalize=self.normalize, gt_sumsq=g2)
+            return decode_cos_loss(w0, self.codebooks[0:1], gt, mask, normalize=self.normalize, gt_sumsq=g2)
         feat = self.layer_feature_map(wmap, layer_idx)
         if self.fused_loss and self.use_cos and not self.use_l1 and mask.numel() == feat[0].numel():
             return normalized_cos_loss(feat, gt, mask, normalize=self.normalize)
@@ -387,7 +391,9 @@ class FeatureTrainer:
         for a given ``view_id`` must then be the same (resident) tensors on every call."""
         self.iteration += 1
         calibrated = self.capacity is not None
-        if self.use_graph and calibrated and view_id is not None and gt_sumsq is None:
+        # the first iteration always runs eagerly: libraries create handles / workspaces on first use (cuBLAS, NCCL
+        # communicators), which is not allowed under stream capture
+        if self.use_graph and calibrated and view_id is not None and gt_sumsq is None and self._eager_iters > 0:
             key = (view_id, self.layer_index())
             entry = self._graphs.get(key)
             if entry is None:
@@ -408,6 +414,7 @@ class FeatureTrainer:
         else:
             self.optimizer.begin_step()
             loss = self._iteration(cam, gt, mask, gt_sumsq, view_id)
+            self._eager_iters += 1
         st = self._last_state
         if not calibrated and st is not None:
             self._max_seen = max(self._max_seen, st.num_rendered)

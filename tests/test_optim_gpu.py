@@ -233,3 +233,26 @@ def test_trainer_split_iteration_equals_unsplit(monkeypatch):
         runs.append([float(tr.step(cam, gt, mask)) for _ in range(5)])
     np.testing.assert_allclose(runs[0], runs[1], rtol=5e-3)
     assert runs[0][0] == pytest.approx(runs[1][0], rel=1e-6)          # the first forward is the same arithmetic
+
+
+def test_trainer_graph_from_the_first_step():
+    """use_graph=True with step(view_id=...) as the very first call after calibrate(): the first iteration must run
+    eagerly (cuBLAS creates its handle on first use, which is illegal under stream capture), the later ones captured."""
+    import subprocess, sys, textwrap
+    code = textwrap.dedent("""
+        import torch
+        from langsplatv2_b200 import synth
+        from langsplatv2_b200.trainer import FeatureTrainer, synthetic_gt
+        scene = synth.make_scene(20000, seed=0, levels=1)
+        cam = synth.ring_camera(0, 8, 256, 192)
+        cam = {k: (v.cuda() if torch.is_tensor(v) else v) for k, v in cam.items()}
+        gt, mask = synthetic_gt(192, 256, device="cuda")
+        tr = FeatureTrainer(scene, topk=4, layers=1, lr=0.01, use_graph=True)
+        tr.calibrate([cam])
+        losses = [float(tr.step(cam, gt, mask, view_id=0)) for _ in range(4)]
+        assert len(tr._graphs) == 1 and losses[-1] < losses[0], (len(tr._graphs), losses)
+        print("ok")
+    """)
+    # a fresh process: in this one cuBLAS has long been initialised by the other tests
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]
