@@ -503,6 +503,25 @@ ok = ok and torch.allclose(ex.full_reduced_grad(), grads.sum(0), rtol=1e-6, atol
 # every rank holds the same parameters bit for bit (each element was computed by exactly one rank)
 ref = pb.clone(); dist.broadcast(ref, 0)
 ok = ok and torch.equal(ref, pb)
+# scheme C (the trainer's default): two iterations with the all-gather DEFERRED to the start of the next one
+# (all_gather_all + finish before the parameters are read), against two all-reduce iterations
+pc = flat_p0.clone(); gc = grads[rank].clone()
+pd = flat_p0.clone()
+exc = lsdist.ShardedExchange(gc, pc, blocks)
+for it in range(2):
+    exc.all_gather_all(); exc.finish()                       # previous iteration's shards (a no-op on the first)
+    gc.copy_(grads[rank] * (1.0 + it) + 0.01 * pc)           # this iteration's gradient depends on the parameters
+    gd = grads[rank] * (1.0 + it) + 0.01 * pd
+    dist.all_reduce(gd, op=dist.ReduceOp.SUM)
+    pd -= lr * gd
+    for i in range(len(blocks)):
+        exc.reduce_scatter(i)
+    for i in range(len(blocks)):
+        exc.wait_grad(i)
+        lo, hi = exc.shard_range(i)
+        pc[lo:hi] -= lr * exc.shard_grad[i]
+exc.all_gather_all(); exc.finish()                           # == FeatureTrainer.sync_params()
+ok = ok and torch.allclose(pc, pd, rtol=1e-5, atol=1e-6)
 try:
     lsdist.ShardedExchange(gb, pb, [(0, 6)])
     ok = False
