@@ -56,7 +56,8 @@ class FeatureTrainer:
     def __init__(self, scene: Dict, topk: int = 4, lr: float = 0.0025, device="cuda", normalize: bool = True,
                  use_cos: bool = True, use_l1: bool = False, layers: Optional[int] = None,
                  fused_loss: bool = True, gram_loss: bool = True, collective: str = "zero1",
-                 use_graph: bool = False, check_every: int = 64, defer_codebook_grad: Optional[bool] = None):
+                 use_graph: bool = False, check_every: int = 64, defer_codebook_grad: Optional[bool] = None,
+                 geometry_cache_gb: float = 0.0):
         dev = torch.device(device)
         f32 = lambda t: t.to(dev, torch.float32).contiguous()
         self.dev = dev
@@ -135,6 +136,16 @@ class FeatureTrainer:
         # reading logits / codebooks from outside (checkpoints, evaluation).
         self.defer_gather = (self.collective == "zero1" and os.environ.get("LSV2_DEFER_AG", "1") != "0")
         self.split_prepare = dev.type == "cuda" and os.environ.get("LSV2_SPLIT_PREPARE", "1") != "0"
+        # Geometry-stage cache (opt-in).  The feature stage freezes the geometry (scene/gaussian_model.py:238-243), so a
+        # view's preprocess + binning result is the same in every iteration that renders it: what the blend and its
+        # backward read of it (radii, the packed blend record, the sorted id list, the tile ranges: ~90 MB per view at 1M
+        # Gaussians / 1008x756) can stay resident -- a 300-view scene is 27 GB of a B200's 180 GB -- and the iteration
+        # then starts at the top-k kernel.  cache_geometry(cam, view_id) fills it; step(view_id=...) uses it.
+        self.geometry_cache_bytes = int(geometry_cache_gb * 1e9)
+        self._geom_cache = {}
+        self._geom_cache_used = 0
+        self.geometry_cache_hits = 0
+        self._tiny_scratch = torch.zeros(4096, dtype=torch.uint8, device=dev) if dev.type == "cuda" else None
         self.keep_last_grad = False
         self.last_grad = None
         self.iteration = 0
@@ -160,6 +171,35 @@ class FeatureTrainer:
         cs = self.codebook_size
         w = [softmax_to_topk_soft_code(self.logits[:, i * cs:(i + 1) * cs], self.topk) for i in range(self.layers)]
         return w[0] if len(w) == 1 else torch.cat(w, dim=-1)
+
+    def _geometry_stage(self, rs):
+        from .rasterizer import rasterize_forward
+        with torch.no_grad():
+            return rasterize_forward(rs._replace(include_feature=False), self.xyz, self.opacity, shs=self.shs,
+                                     scales=self.scales, rotations=self.rotations, capacity=self.capacity, render=False)
+
+    def cache_geometry(self, cam: Dict, view_id) -> bool:
+        """Run the geometry stage of ``cam`` once and keep what the blend needs of it under ``view_id`` (see
+        ``geometry_cache_gb``).  Returns False when the budget is exhausted or the capacity is not calibrated yet.
+        Not to be called under stream capture."""
+        from .rasterizer import FrameState
+        if self.geometry_cache_bytes <= 0 or self.capacity is None or view_id is None:
+            return False
+        if view_id in self._geom_cache:
+            return True
+        full = self._geometry_stage(self.settings(cam))
+        keep = FrameState(P=full.P, H=full.H, W=full.W, mode=full.mode, L=full.L, K=full.K, view=full.view,
+                          status=full.status, capacity=full.capacity, keep=full.keep, scene=full.scene)
+        keep.geom = {k: full.geom[k] for k in ("radii", "blend_rec")}
+        keep.binning = {"point_list": full.binning["point_list"], "ranges": full.binning["ranges"],
+                        "scratch": self._tiny_scratch}         # the blend kernels use its first 256 bytes (unit counter)
+        nbytes = sum(t.numel() * t.element_size() for t in list(keep.geom.values()) + [keep.binning["point_list"],
+                                                                                       keep.binning["ranges"]])
+        if self._geom_cache_used + nbytes > self.geometry_cache_bytes:
+            return False
+        self._geom_cache[view_id] = keep
+        self._geom_cache_used += nbytes
+        return True
 
     def sync_params(self) -> None:
         """Make every rank's logits / codebooks current (N > 1 with the deferred all-gather; no-op otherwise)."""
@@ -211,14 +251,12 @@ class FeatureTrainer:
         gather = self.defer_gather and self.exchange is not None
         if gather:
             self.exchange.all_gather_all()          # last iteration's parameter shards -> every rank (side stream)
-        prepared = None
-        if self.split_prepare and self.capacity is not None:
+        prepared = self._geom_cache.get(view_id) if (view_id is not None and self._geom_cache) else None
+        if prepared is not None:
+            self.geometry_cache_hits += 1
+        elif self.split_prepare and self.capacity is not None:
             # geometry stage first: it reads no trainable parameter, so it runs while the gather is in flight
-            from .rasterizer import rasterize_forward
-            with torch.no_grad():
-                prepared = rasterize_forward(rs._replace(include_feature=False), self.xyz, self.opacity, shs=self.shs,
-                                             scales=self.scales, rotations=self.rotations, capacity=self.capacity,
-                                             render=False)
+            prepared = self._geometry_stage(rs)
         if gather:
             self.exchange.finish()
         rasterizer = GaussianRasterizer(raster_settings=rs, capacity=self.capacity)
@@ -427,6 +465,8 @@ class FeatureTrainer:
                 self._sticky.zero_()
                 self.capacity = int(self.capacity * 1.5) + 4096
                 self._graphs.clear()
+                self._geom_cache.clear()                                 # cached lists were built under the old capacity
+                self._geom_cache_used = 0
                 import warnings
                 warnings.warn(f"instance capacity overflowed; grown to {self.capacity} (the affected iterations used "
                               "truncated instance lists)")

@@ -256,3 +256,43 @@ def test_trainer_graph_from_the_first_step():
     # a fresh process: in this one cuBLAS has long been initialised by the other tests
     out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]
+
+
+def test_trainer_geometry_cache_is_exact():
+    """geometry_cache_gb: with the geometry frozen, a view's preprocess + binning result can stay resident; the iteration
+    on the cached state must produce the same loss and gradient as the recomputed one, eager and captured."""
+    from langsplatv2_b200 import synth
+    scene = synth.make_scene(20000, seed=0, levels=1)
+    scene["scaling"] = scene["scaling"] * 2.0
+    cams = [synth.ring_camera(v, 8, 256, 192) for v in range(2)]
+    cams = [{k: (v.cuda() if torch.is_tensor(v) else v) for k, v in c.items()} for c in cams]
+    gt, mask = synthetic_gt(192, 256, device="cuda")
+    out = []
+    for gb in (0.0, 1.0):
+        tr = FeatureTrainer(scene, topk=4, layers=1, lr=0.01, geometry_cache_gb=gb)
+        tr.calibrate(cams)
+        if gb:
+            assert tr.cache_geometry(cams[0], 0) and tr.cache_geometry(cams[1], 1) and tr.cache_geometry(cams[1], 1)
+            assert 0 < tr._geom_cache_used < 50e6
+        tr.keep_last_grad = True
+        l0 = float(tr.step(cams[0], gt, mask, view_id=0))
+        g0 = tr.last_grad.clone()
+        tr.keep_last_grad = False
+        rest = [float(tr.step(cams[i % 2], gt, mask, view_id=i % 2)) for i in range(1, 6)]
+        out.append((l0, g0, rest, tr.geometry_cache_hits))
+    (la, ga, ra, ha), (lb, gb_, rb, hb) = out
+    assert ha == 0 and hb == 6
+    assert la == lb                                                  # same kernels on the same data
+    assert float((ga - gb_).abs().max()) <= 1e-5 * float(ga.abs().max())
+    np.testing.assert_allclose(ra, rb, rtol=5e-3)
+    # captured iterations on cached geometry
+    tr = FeatureTrainer(scene, topk=4, layers=1, lr=0.01, geometry_cache_gb=1.0, use_graph=True)
+    tr.calibrate(cams)
+    tr.cache_geometry(cams[0], 0)
+    tr.step(cams[0], gt, mask)                                       # the eager first iteration
+    lg = [float(tr.step(cams[0], gt, mask, view_id=0)) for _ in range(5)]
+    assert len(tr._graphs) == 1 and lg[-1] < lg[0]
+    # a tiny budget refuses instead of growing
+    tr = FeatureTrainer(scene, topk=4, layers=1, geometry_cache_gb=1e-6)
+    tr.calibrate(cams)
+    assert not tr.cache_geometry(cams[0], 0)
