@@ -224,6 +224,8 @@ struct PreBackArgs {
 };
 
 constexpr int PB_THREADS = 128;
+constexpr int PB_SH_FLOATS = 48;                 // degree-3 row: 16 coefficients x RGB
+constexpr int PB_SH_STRIDE = PB_SH_FLOATS + 1;    // odd stride: conflict-free per-thread rows
 
 __global__ void __launch_bounds__(PB_THREADS) k_preprocess_backward(PreBackArgs a)
 {
@@ -235,15 +237,15 @@ __global__ void __launch_bounds__(PB_THREADS) k_preprocess_backward(PreBackArgs 
     else if (tid < 35) s_cam[tid - 32] = a.campos[tid - 32];
     __syncthreads();
     const int i = blockIdx.x * PB_THREADS + tid;
-    if (i >= a.P) return;
+    const bool live = i < a.P;                              // no early exit: the SH rows go through block-wide staging
     const float* vm = s_m;
     const float* pm = s_m + 16;
-    const size_t si = (size_t)i;
+    const size_t si = (size_t)(live ? i : 0);
 
     float dmean[3] = {0.f, 0.f, 0.f}, dm2[2] = {0.f, 0.f}, dop = 0.f;
     float dscale[3] = {0.f, 0.f, 0.f}, drot[4] = {0.f, 0.f, 0.f, 0.f}, dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     float drgb[3] = {0.f, 0.f, 0.f};
-    const bool vis = a.radii[i] > 0;
+    const bool vis = live && a.radii[i] > 0;
     const int ncoef = (a.deg + 1) * (a.deg + 1);
 
     if (vis) {
@@ -404,10 +406,37 @@ __global__ void __launch_bounds__(PB_THREADS) k_preprocess_backward(PreBackArgs 
     }
 
     // ---- colour: SH coefficients and the view direction's dependence on the mean
+    // The SH block is the bulk of this kernel's bytes (192 B read + 192 B written per Gaussian).  A CTA's rows are one
+    // contiguous block: they are staged through shared memory with 16-byte coalesced accesses (per-thread row accesses
+    // touch 32 different lines per instruction), only rows of visible Gaussians are read, and the gradient row
+    // overwrites the staged coefficients in place (element (k, c) is read before it is written).
+    __shared__ float s_sh[PB_THREADS * PB_SH_STRIDE];
+    __shared__ int s_visf[PB_THREADS];
+    const int row_f = a.M * 3;
+    const bool staged = a.shs && a.d_shs && row_f == PB_SH_FLOATS &&
+                        ((reinterpret_cast<uintptr_t>(a.shs) | reinterpret_cast<uintptr_t>(a.d_shs)) & 15) == 0;
+    const size_t blk_base = (size_t)blockIdx.x * PB_THREADS;
+    const int blk_rows = min(PB_THREADS, a.P - (int)blk_base);
+    if (staged) {
+        s_visf[tid] = vis ? 1 : 0;
+        __syncthreads();
+        const float4* src4 = reinterpret_cast<const float4*>(a.shs + blk_base * PB_SH_FLOATS);
+        for (int e = tid; e < blk_rows * (PB_SH_FLOATS / 4); e += PB_THREADS) {
+            const int r = e / (PB_SH_FLOATS / 4), q = e - r * (PB_SH_FLOATS / 4);
+            float* d = s_sh + r * PB_SH_STRIDE + 4 * q;
+            if (s_visf[r]) {
+                const float4 v = __ldg(src4 + e);
+                d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+            } else {
+                d[0] = 0.f; d[1] = 0.f; d[2] = 0.f; d[3] = 0.f;         // culled: the gradient row is zero
+            }
+        }
+        __syncthreads();
+    }
     if (a.shs) {
-        float* dsh = a.d_shs ? a.d_shs + si * a.M * 3 : nullptr;
+        float* dsh = staged ? s_sh + tid * PB_SH_STRIDE : (a.d_shs && live ? a.d_shs + si * a.M * 3 : nullptr);
         if (vis) {
-            const float* sh = a.shs + si * a.M * 3;
+            const float* sh = staged ? s_sh + tid * PB_SH_STRIDE : a.shs + si * a.M * 3;
             const float p0 = a.means[3 * si + 0], p1 = a.means[3 * si + 1], p2 = a.means[3 * si + 2];
             const float d0 = p0 - s_cam[0], d1 = p1 - s_cam[1], d2 = p2 - s_cam[2];
             const float len = sqrtf((d0 * d0 + d1 * d1) + d2 * d2);
@@ -465,13 +494,23 @@ __global__ void __launch_bounds__(PB_THREADS) k_preprocess_backward(PreBackArgs 
             dmean[0] += (gx - x * dot) / len;
             dmean[1] += (gy - y * dot) / len;
             dmean[2] += (gz - z * dot) / len;
-        } else if (dsh) {
+        } else if (dsh && !staged) {
             for (int k = 0; k < a.M * 3; ++k) dsh[k] = 0.0f;
         }
-    } else if (a.d_colors) {
+    } else if (a.d_colors && live) {
 #pragma unroll
         for (int c = 0; c < 3; ++c) a.d_colors[3 * si + c] = drgb[c];
     }
+    if (staged) {
+        __syncthreads();
+        float4* dst4 = reinterpret_cast<float4*>(a.d_shs + blk_base * PB_SH_FLOATS);
+        for (int e = tid; e < blk_rows * (PB_SH_FLOATS / 4); e += PB_THREADS) {
+            const int r = e / (PB_SH_FLOATS / 4), q = e - r * (PB_SH_FLOATS / 4);
+            const float* d = s_sh + r * PB_SH_STRIDE + 4 * q;
+            dst4[e] = make_float4(d[0], d[1], d[2], d[3]);
+        }
+    }
+    if (!live) return;
 
     if (a.d_means) { a.d_means[3 * si + 0] = dmean[0]; a.d_means[3 * si + 1] = dmean[1]; a.d_means[3 * si + 2] = dmean[2]; }
     if (a.d_means2d) { a.d_means2d[3 * si + 0] = dm2[0]; a.d_means2d[3 * si + 1] = dm2[1]; a.d_means2d[3 * si + 2] = 0.0f; }
