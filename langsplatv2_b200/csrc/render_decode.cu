@@ -36,6 +36,46 @@
 
 #include "fd_common.cuh"
 
+// -DFD_WATCHDOG (debug library liblsv2_wd.so only, `make wd`): every mbarrier wait that spins for more than ~0.2 s
+// writes (line, block, warp, parity) once into a host-mapped buffer (lsv2_debug_set_watchdog) and keeps waiting, so a
+// deadlocked launch can be read out from the host while it hangs: scripts/fused_watchdog.py.
+#ifdef FD_WATCHDOG
+namespace lsv2 {
+__device__ unsigned int* g_fd_wd = nullptr;          // [0] = records written, then 4 words per record
+__device__ __noinline__ void fd_wd_report(int line, uint32_t parity)
+{
+    unsigned int* w = g_fd_wd;
+    if (!w) return;
+    const unsigned int k = atomicAdd(w, 1u);
+    if (k < 1000u) {
+        w[4 + 4 * k + 0] = (unsigned int)line;
+        w[4 + 4 * k + 1] = blockIdx.x;
+        w[4 + 4 * k + 2] = threadIdx.x >> 5;
+        w[4 + 4 * k + 3] = parity;
+        __threadfence_system();
+    }
+}
+__device__ __forceinline__ void fd_wait_wd(uint64_t* bar, uint32_t parity, int line)
+{
+    long long t0 = clock64();
+    bool told = false;
+    while (!mbar_try_wait(bar, parity)) {
+        if (!told && clock64() - t0 > 400000000LL) { told = true; if ((threadIdx.x & 31) == 0) fd_wd_report(line, parity); }
+        __nanosleep(64);
+    }
+}
+}  // namespace lsv2
+extern "C" int lsv2_debug_set_watchdog(void* mapped_words)
+{
+    return cudaMemcpyToSymbol(lsv2::g_fd_wd, &mapped_words, sizeof(void*)) == cudaSuccess ? 0 : 2;
+}
+#define FD_WAIT(bar, par) fd_wait_wd(bar, par, __LINE__)
+#define FD_WAIT_SLEEP(bar, par) fd_wait_wd(bar, par, __LINE__)
+#else
+#define FD_WAIT(bar, par) mbar_wait(bar, par)
+#define FD_WAIT_SLEEP(bar, par) mbar_wait_sleep(bar, par)
+#endif
+
 // -DFD_PROF: per-CTA cycle counters of where each warp role waits (debug library liblsv2_prof.so only; the
 // counters land behind the Gram images in the scratch buffer, see scripts/fused_prof.py)
 #ifdef FD_PROF
@@ -47,6 +87,18 @@
 #define FD_TICB() profb_t0 = clock64()
 #define FD_TOCB(i) do { const long long _t = clock64(); profb_acc[i] += _t - profb_t0; profb_t0 = _t; } while (0)
 #define FD_PROFB_FLUSH(role) do { if (a.prof) for (int _i = 0; _i < 8; ++_i) a.prof[((size_t)blockIdx.x * 6 + (role)) * 8 + _i] = profb_acc[_i]; } while (0)
+#elif defined(FD_WATCHDOG)
+// heartbeat: the last phase marker every warp passed, [CTA][warp], readable from the host while the kernel hangs
+#define FD_WD_MARK(code) do { unsigned int* _w = g_fd_wd; if (_w && (threadIdx.x & 31) == 0) \
+        *(volatile unsigned int*)(_w + 4100 + blockIdx.x * 16 + (threadIdx.x >> 5)) = (unsigned int)(code); } while (0)
+#define FD_PROFB_DECL
+#define FD_TICB() FD_WD_MARK(100)
+#define FD_TOCB(i) FD_WD_MARK(101 + (i))
+#define FD_PROFB_FLUSH(role)
+#define FD_PROF_DECL
+#define FD_TIC() FD_WD_MARK(1)
+#define FD_TOC(i) FD_WD_MARK(2 + (i))
+#define FD_PROF_FLUSH(role) FD_WD_MARK(99)
 #else
 #define FD_PROFB_DECL
 #define FD_TICB()
@@ -277,7 +329,8 @@ __device__ __forceinline__ void fd_put(unsigned char* S, uint32_t c, uint32_t in
     *reinterpret_cast<__half*>(S + (off ^ 32u)) = __float2half_rn(__fsub_rn(w, __half2float(h)));
 }
 
-template <bool OUT_BF16, int PATH>
+// HWC: channels-last output (compile-time, so that neither variant carries the other's epilogue in its hot loop).
+template <bool OUT_BF16, int PATH, bool HWC = false>
 __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS_NODECODE, 1) k_render_decode(FdArgs a)
 {
     constexpr bool DECODE = PATH == FD_PATH_DECODE;     // codebook decode + epilogue warps
@@ -395,7 +448,7 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
                 const int s = use_g & 1;
                 const uint32_t use = use_g >> 1;
                 FD_TOC(2);
-                if (use > 0) mbar_wait_sleep(stage_free + s, (use - 1) & 1);
+                if (use > 0) FD_WAIT_SLEEP(stage_free + s, (use - 1) & 1);
                 FD_TOC(0);
                 FdHeader& Hd = hdrs[s];
                 // s_ndone[parity] only ever grows: every blend warp adds exactly one per unit (when its block saturates,
@@ -486,9 +539,9 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
         for (uint32_t use_g = 0;; ++use_g) {
             const int s = use_g & 1;
             const uint32_t par = (use_g >> 1) & 1;
-            mbar_wait_sleep(full + s, par);
+            FD_WAIT_SLEEP(full + s, par);
             const int count = (int)bcast0((uint32_t)hdrs[s].count);
-            mbar_wait(a_full + s, par);                  // batches: A tiles written; terminators: header read by all
+            FD_WAIT(a_full + s, par);                  // batches: A tiles written; terminators: header read by all
             if (count == -2) break;
             if (count >= 0) {
                 tc_fence_after();
@@ -522,6 +575,7 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
         // Converged warp, one elected lane issues.
         constexpr uint32_t idesc_u = umma_idesc_f16_f32(128, FD_LC);
         constexpr uint32_t idesc_dec = umma_idesc_f16_f32(128, FD_NFEAT);
+        static_assert(FD_NFEAT == 64, "the channels-last decode swaps the operands of an M = 128, N = 64 MMA");
         const uint32_t tmem_u = bcast0(tmem);
         // operand descriptors are built once; a k-step (32 bytes) or a row block only adds to the address field
         const uint64_t desc_w0 = umma_desc_k_sw128(bcast0(smem_u32(wdec))), desc_cb0 = umma_desc_k_sw128(bcast0(smem_u32(s_cb)));
@@ -532,7 +586,7 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
         FD_TIC();
         auto fetch_next = [&]() {                        // codebook-ring job `cb_issued` -> slot cb_issued & 1
             const int slot = (int)(cb_issued & 1u);
-            if (cb_issued >= FD_CB_SLOTS) mbar_wait(cb_free + slot, ((cb_issued >> 1) - 1) & 1);
+            if (cb_issued >= FD_CB_SLOTS) FD_WAIT(cb_free + slot, ((cb_issued >> 1) - 1) & 1);
             const int j = (int)(cb_issued % (uint32_t)jobs_per_unit);
             const uint8_t* src = QUERY ? ((j & 1) ? a.qimg : a.gimg) + (size_t)(j >> 1) * FD_CB_BYTES
                                        : (j < n_g ? a.gimg + (size_t)j * FD_CB_BYTES : a.bimg + (size_t)(j - n_g) * FD_CB_BYTES);
@@ -553,14 +607,14 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
                 // rows of level l are in shared memory (all levels are needed before the decode starts anyway;
                 // the per-level barrier lets the Gram products start while later levels are still converted)
                 FD_TOC(3);
-                mbar_wait_sleep(wraw_full + l, it & 1);
+                FD_WAIT_SLEEP(wraw_full + l, it & 1);
                 FD_TOC(0);
                 if (l == 0 && (int)bcast0((uint32_t)tinfo[it & 1].unit) < 0) { stop = true; break; }
                 if (!normalize) continue;
                 tc_fence_after();
                 const uint32_t n = cb_used;
                 const int slot = (int)(n & 1u);
-                mbar_wait(cb_full + slot, (n >> 1) & 1);
+                FD_WAIT(cb_full + slot, (n >> 1) & 1);
                 if (elect_one()) {
                     const uint64_t g_hi = desc_cb0 + (uint64_t)(slot * (FD_CB_BYTES >> 4)), g_lo = g_hi + (uint64_t)((64 * 128) >> 4);
 #pragma unroll
@@ -586,8 +640,8 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
                     const uint32_t nq = it * (uint32_t)levels + (uint32_t)l;
                     const uint32_t n2 = cb_used;
                     const int slot2 = (int)(n2 & 1u);
-                    mbar_wait(cb_full + slot2, (n2 >> 1) & 1);
-                    if (nq >= 1) mbar_wait(f_free, (nq - 1) & 1);
+                    FD_WAIT(cb_full + slot2, (n2 >> 1) & 1);
+                    if (nq >= 1) FD_WAIT(f_free, (nq - 1) & 1);
                     tc_fence_after();
                     if (elect_one()) {
                         const uint64_t q_hi = desc_cb0 + (uint64_t)(slot2 * (FD_CB_BYTES >> 4)), q_lo = q_hi + (uint64_t)((64 * 128) >> 4);
@@ -620,19 +674,26 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
                     const uint32_t n = cb_used;
                     const int slot = (int)(n & 1u);
                     FD_TOC(3);
-                    mbar_wait(cb_full + slot, (n >> 1) & 1);
+                    FD_WAIT(cb_full + slot, (n >> 1) & 1);
                     FD_TOC(1);
 #pragma unroll 1
                     for (int gm = 0; gm < 2 * FD_FGROUPS; ++gm) {
                         const int g = gm >> 1, m = gm & 1;
                         const int fs = (int)(f_n % FD_FSLOTS);
                         FD_TOC(3);
-                        if (f_n >= FD_FSLOTS) mbar_wait(f_free + fs, ((f_n / FD_FSLOTS) - 1) & 1);
+                        if (f_n >= FD_FSLOTS) FD_WAIT(f_free + fs, ((f_n / FD_FSLOTS) - 1) & 1);
                         FD_TOC(2);
                         tc_fence_after();
                         if (elect_one()) {
-                            const uint64_t db = desc_cb0 + (uint64_t)(slot * (FD_CB_BYTES >> 4) + g * ((FD_NFEAT * 128) >> 4));
-                            const uint64_t da = desc_w0 + (uint64_t)(l * (FD_WDEC_LEVEL >> 4) + m * ((128 * 128) >> 4));
+                            // CHW: D[128 px (half m)][64 features (group g)] -- lane = pixel, so a store instruction
+                            // writes 32 pixels of one feature plane.  Channels-last: the operands swap roles,
+                            // D[128 features (the chunk)][64 px (decode rows 64 gm ..)] -- lane = feature, so a store
+                            // instruction writes 32 consecutive features of one pixel.  Same bytes in shared memory, same
+                            // descriptor layout (both K-major, 128-byte swizzle), same instruction shape M = 128, N = 64.
+                            const uint64_t db = HWC ? desc_w0 + (uint64_t)(l * (FD_WDEC_LEVEL >> 4) + gm * ((64 * 128) >> 4))
+                                                      : desc_cb0 + (uint64_t)(slot * (FD_CB_BYTES >> 4) + g * ((FD_NFEAT * 128) >> 4));
+                            const uint64_t da = HWC ? desc_cb0 + (uint64_t)(slot * (FD_CB_BYTES >> 4))
+                                                      : desc_w0 + (uint64_t)(l * (FD_WDEC_LEVEL >> 4) + m * ((128 * 128) >> 4));
                             const uint32_t d = tmem_u + (uint32_t)(FD_TMEM_F + fs * FD_NFEAT);
 #pragma unroll
                             for (int ks = 0; ks < 4; ++ks)
@@ -653,7 +714,7 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
         }
         if (lane == 0) FD_PROF_FLUSH(2);
         // drain the codebook prefetch that no unit consumed
-        while (cb_used < cb_issued) { mbar_wait(cb_full + (cb_used & 1u), (cb_used >> 1) & 1); ++cb_used; }
+        while (cb_used < cb_issued) { FD_WAIT(cb_full + (cb_used & 1u), (cb_used >> 1) & 1); ++cb_used; }
     } else if (DECODE && warp >= FD_BLEND_WARPS && warp < FD_BLEND_WARPS + FD_EPI_WARPS) {
         // ==================================== epilogue: F slots -> global ====================================
         // Decode MMA block m covers band rows 4m .. 4m+3; TMEM lane quadrant q = this warp = band row 4m + q,
@@ -665,7 +726,7 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
         FD_TIC();
         for (uint32_t it = 0;; ++it) {
             FD_TOC(2);
-            mbar_wait_sleep(inv_full, it & 1);
+            FD_WAIT_SLEEP(inv_full, it & 1);
             FD_TOC(0);
             const int unit = tinfo[it & 1].unit;
             if (unit < 0) break;
@@ -682,7 +743,7 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
                     for (int m = 0; m < 2; ++m) {
                         const int fs = (int)(f_n % FD_FSLOTS);
                         FD_TOC(2);
-                        mbar_wait(f_full + fs, (f_n / FD_FSLOTS) & 1);
+                        FD_WAIT(f_full + fs, (f_n / FD_FSLOTS) & 1);
                         FD_TOC(1);
                         ++f_n;
                         tc_fence_after();
@@ -700,23 +761,39 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
                                 __syncwarp();
                                 if (lane == 0) mbar_arrive(f_free + fs);     // slot drained: the next MMA may overwrite it
                             }
-                            if (in && a.hwc) {
-                                // channels-last: this thread's 32 features are contiguous
-                                const size_t e0 = (((size_t)l * a.H + py) * a.W + px) * FD_D + (size_t)cg * FD_NFEAT + (size_t)hh * 32;
-                                if (OUT_BF16) {
-                                    uint4* o = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(a.out) + e0);
+                            // channels-last (transposed decode): this lane = feature (cg >> 1) * 128 + 32 q + lane,
+                            // r[j] = decode row 64 pg + 32 hh + j = the pixel (x = j, band row 2 pg + hh); one store
+                            // instruction = 32 consecutive features of one pixel = one 128-byte line
+                            if (HWC) {
+                                const int pg = (cg & 1) * 2 + m;
+                                const int yy = band * FD_UNIT_H + 2 * pg + hh;
+                                const int rr0 = 64 * pg + 32 * hh;
+                                const size_t feat = (size_t)(cg >> 1) * 128 + (size_t)(q * 32 + lane);
+                                if (yy < a.H) {
+                                    uint64_t pp = (uint64_t)(uintptr_t)a.out +
+                                                  ((((size_t)l * a.H + yy) * a.W + (size_t)pair * FD_UNIT_W) * FD_D + feat) * esz;
+                                    const int nx = min(32, a.W - pair * FD_UNIT_W);
+                                    // 1/norm of pixel j: lane j fetches it once and the warp passes it round -- a
+                                    // shared-memory load between the `asm volatile` stores would be ordered behind the
+                                    // previous store by its "memory" clobber (32 serialised load latencies per chunk:
+                                    // the first version of this path ran at 7.5 ms per frame)
+                                    const float inv_l = normalize ? inv_u[l * 256 + rr0 + lane] : 1.0f;
+                                    float invr[32];
 #pragma unroll
-                                    for (int i = 0; i < 4; ++i)
-                                        o[i] = make_uint4(pack_bf16x2(__uint_as_float(r[8 * i]) * sc, __uint_as_float(r[8 * i + 1]) * sc),
-                                                          pack_bf16x2(__uint_as_float(r[8 * i + 2]) * sc, __uint_as_float(r[8 * i + 3]) * sc),
-                                                          pack_bf16x2(__uint_as_float(r[8 * i + 4]) * sc, __uint_as_float(r[8 * i + 5]) * sc),
-                                                          pack_bf16x2(__uint_as_float(r[8 * i + 6]) * sc, __uint_as_float(r[8 * i + 7]) * sc));
-                                } else {
-                                    float* o = reinterpret_cast<float*>(a.out) + e0;
+                                    for (int j = 0; j < 32; ++j) invr[j] = __shfl_sync(0xffffffffu, inv_l, j);
 #pragma unroll
-                                    for (int i = 0; i < 8; ++i)
-                                        st_stream_f32x4(o + 4 * i, __uint_as_float(r[4 * i]) * sc, __uint_as_float(r[4 * i + 1]) * sc,
-                                                        __uint_as_float(r[4 * i + 2]) * sc, __uint_as_float(r[4 * i + 3]) * sc);
+                                    for (int j = 0; j < 32; ++j) {
+                                        if (j < nx) {
+                                            const float v = __uint_as_float(r[j]) * invr[j];
+                                            if (OUT_BF16) {
+                                                const unsigned short hv = __bfloat16_as_ushort(__float2bfloat16_rn(v));
+                                                asm volatile("st.global.cs.u16 [%0], %1;" ::"l"(pp), "h"(hv) : "memory");
+                                            } else {
+                                                asm volatile("st.global.cs.f32 [%0], %1;" ::"l"(pp), "f"(v) : "memory");
+                                            }
+                                        }
+                                        pp += (uint64_t)FD_D * esz;
+                                    }
                                 }
                             } else if (in) {
                                 const size_t d0 = (size_t)l * FD_D + (size_t)cg * FD_NFEAT + (size_t)hh * 32;
@@ -781,7 +858,7 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
             for (;; ++use_g) {
                 const int s = use_g & 1;
                 FD_TOC(1);
-                mbar_wait(full + s, (use_g >> 1) & 1);
+                FD_WAIT(full + s, (use_g >> 1) & 1);
                 FD_TOC(0);
                 const FdHeader& Hd = hdrs[s];
                 count = Hd.count;
@@ -907,9 +984,17 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
                     // last unit must not arrive while slower warps still owe their arrival of that unit's phase (8
                     // arrivals complete a phase no matter who made them -- the epilogue would be released before the
                     // slow warps' 1/norm values exist).
+                    // ... and it must not arrive before the epilogue has CONSUMED the last unit's inv_full phase: a waiter
+                    // that falls two phases behind sees the parity it waits for as "not yet completed" and waits
+                    // forever.  Every other phase is protected by the data flow (a unit's pass A waits for the previous
+                    // unit's dec_done, which implies the epilogue passed that unit's inv_full); the terminator is not --
+                    // it follows the last pass B within a microsecond.  dec_done of the last unit (decode MMAs complete
+                    // => all but the last F slots drained => the epilogue is inside that unit) closes it.  Found with the
+                    // watchdog build (scripts/fused_watchdog.py) when a slower epilogue variant lost the race every time.
                     if (units_done > 0) {
-                        mbar_wait(wraw_full, (units_done - 1) & 1);
-                        if (DECODE) mbar_wait(inv_full, (units_done - 1) & 1);
+                        FD_WAIT(wraw_full, (units_done - 1) & 1);
+                        if (DECODE) FD_WAIT(inv_full, (units_done - 1) & 1);
+                        if (DECODE) FD_WAIT(dec_done, (units_done - 1) & 1);
                     }
                     if (tid == 0) { tinfo[units_done & 1].unit = -1; tinfo[units_done & 1].nb = 0; }
                     __syncwarp();
@@ -922,12 +1007,12 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
 
             // ---------------- W: TMEM -> fp16 rows of the decode operand ----------------
             FD_TOC(6);
-            mbar_wait(w_full, units_done & 1);
+            FD_WAIT(w_full, units_done & 1);
             FD_TOC(2);
             tc_fence_after();
             if (WROWS) {
                 // the previous unit's MMAs are done with Wdec (query: its last product was waited for by every thread)
-                if (DECODE && units_done > 0) mbar_wait(dec_done, (units_done - 1) & 1);
+                if (DECODE && units_done > 0) FD_WAIT(dec_done, (units_done - 1) & 1);
                 FD_TOC(3);
                 if (tid == 0) { tinfo[units_done & 1].unit = unit; tinfo[units_done & 1].nb = nb; }
             }
@@ -989,7 +1074,7 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
                     const int qx = (unit % a.ux) * FD_UNIT_W + (int)(nrow & 31u), qy = (unit / a.ux) * FD_UNIT_H + (int)(nrow >> 5);
                     for (int l = 0; l < levels; ++l) {
                         const unsigned char* Wl = wdec + (size_t)l * FD_WDEC_LEVEL;
-                        mbar_wait(u_full + l, units_done & 1);
+                        FD_WAIT(u_full + l, units_done & 1);
                         tc_fence_after();
                         float ss = 0.0f;
 #pragma unroll
@@ -1016,7 +1101,7 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
                             // min over the negatives of softmax(10 [pos, neg])[0] = 1 / (1 + exp(10 (max neg - pos)))
                             // (eval/openclip_encoder.py:126-137: the pairwise softmax is monotone in the negative)
                             const uint32_t nq = units_done * (uint32_t)levels + (uint32_t)l;
-                            mbar_wait(f_full, nq & 1);
+                            FD_WAIT(f_full, nq & 1);
                             tc_fence_after();
                             uint32_t s0[32], s1[32];
                             tmem_ld32(lane_base + (uint32_t)(FD_TMEM_F + half * 64), s0);
@@ -1137,13 +1222,14 @@ int launch_render_decode(const lsv2_view& v, const lsv2_geom& g, const lsv2_binn
     a.prof = reinterpret_cast<long long*>(gimg + (size_t)levels * FD_CB_BYTES);
 #endif
     const int grid = min(NUM_SMS, a.n_units);
-#define FD_LAUNCH(O)                                                                                            \
+#define FD_LAUNCH(O, C)                                                                                         \
     do {                                                                                                        \
-        LSV2_CUDA_TRY(cudaFuncSetAttribute(k_render_decode<O, FD_PATH_DECODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+        LSV2_CUDA_TRY(cudaFuncSetAttribute(k_render_decode<O, FD_PATH_DECODE, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                            (int)FD_SMEM_TOTAL));                                                \
-        k_render_decode<O, FD_PATH_DECODE><<<grid, FD_THREADS, FD_SMEM_TOTAL, st>>>(a);                         \
+        k_render_decode<O, FD_PATH_DECODE, C><<<grid, FD_THREADS, FD_SMEM_TOTAL, st>>>(a);                      \
     } while (0)
-    if (out_dtype == 0) FD_LAUNCH(false); else FD_LAUNCH(true);
+    if (out_hwc) { if (out_dtype == 0) FD_LAUNCH(false, true); else FD_LAUNCH(true, true); }
+    else         { if (out_dtype == 0) FD_LAUNCH(false, false); else FD_LAUNCH(true, false); }
 #undef FD_LAUNCH
     LSV2_LAUNCH_CHECK("k_render_decode");
     return LSV2_OK;
