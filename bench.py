@@ -790,8 +790,30 @@ def run_gpu(args, wl):
                         "out_bytes_per_frame": int(LEVELS * D * H * W * 2),
                         "what": "same kernel, features rounded to bf16 in the epilogue (out_dtype=torch.bfloat16)"}
             del ob
+            torch.cuda.empty_cache()
+            # ... and with a channels-last fp32 map ([levels, H, W, 512], what eval_lerf.py:352 permutes the map to)
+            r.out_dtype = torch.float32
+            r.out_layout = "HWC"
+            for s in range(3):
+                ob = r.render(cams[my_views[s % len(my_views)]])
+            barrier()
+            h_b, h_e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            h_b.record()
+            for s in range(args.steps):
+                ob = r.render(cams[my_views[s % len(my_views)]])
+            h_e.record()
+            barrier()
+            th = torch.tensor([h_b.elapsed_time(h_e)], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(th, op=dist.ReduceOp.MAX)
+            h_ms = float(th.item())
+            bf16_out["channels_last_f32"] = {"value": world * args.steps / (h_ms * 1e-3), "unit": UNIT, "ms_per_step": h_ms / args.steps,
+                                             "shape": [int(x) for x in ob.shape],
+                                             "what": "out_layout='HWC': the decode MMA's operands swapped (lane = feature), one 128-byte line per store"}
+            del ob
         finally:
             r.out_dtype = torch.float32
+            r.out_layout = "CHW"
         torch.cuda.empty_cache()
 
     ref_style = None
