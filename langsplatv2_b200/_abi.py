@@ -177,6 +177,24 @@ def stream_ptr(device=None) -> int:
     return torch.cuda.current_stream(device).cuda_stream
 
 
+def guarded(get_device):
+    """Decorator: run the call with the tensors' CUDA device current (liblsv2 launches on the CURRENT device; a caller
+    holding several GPUs in one process need not have switched)."""
+    import functools
+
+    def deco(fn):
+        @functools.wraps(fn)
+        def wrapper(*a, **k):
+            dev = get_device(*a, **k)
+            if dev is not None and dev.type == "cuda" and torch.cuda.is_available() and \
+                    torch.cuda.current_device() != (dev.index if dev.index is not None else torch.cuda.current_device()):
+                with torch.cuda.device(dev):
+                    return fn(*a, **k)
+            return fn(*a, **k)
+        return wrapper
+    return deco
+
+
 def device_guard(device):
     """Context manager making ``device`` the current CUDA device for the launches inside it: the kernels,
     cudaFuncSetAttribute and the tensor-map encode of liblsv2 act on the CURRENT device, which need not be the

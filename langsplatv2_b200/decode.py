@@ -63,6 +63,7 @@ class _Decode(torch.autograd.Function):
         return dW, dC, None
 
 
+@_abi.guarded(lambda weight_map, *a, **k: weight_map.device)
 def decode_feature_map(weight_map: torch.Tensor, codebooks: torch.Tensor, normalize: bool = True,
                        precision: str = "bf16", out_dtype: torch.dtype = torch.float32) -> torch.Tensor:
     """weight_map [levels*Lc, H, W] (the op's 2nd return value), codebooks [levels, Lc, D]

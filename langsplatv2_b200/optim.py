@@ -46,6 +46,7 @@ class FlatAdam:
             self._scal_dev[0:1].fill_(a)
             self._scal_dev[1:2].fill_(b)
 
+    @_abi.guarded(lambda self, *a, **k: self.p.device)
     def step_range(self, a: int = 0, b: Optional[int] = None, zero_grad: bool = False,
                    grad: Optional[torch.Tensor] = None) -> None:
         """One Adam step on flat elements [a, b) (a multiple of 4).  ``grad``: take the gradient of that range from

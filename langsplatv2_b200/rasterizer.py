@@ -395,6 +395,7 @@ def _dump_snapshot(path: str, items: dict) -> None:
         pass
 
 
+@_abi.guarded(lambda st, *a, **k: st.status.device)
 def render_decode(st: FrameState, codebooks: torch.Tensor, normalize: bool = True,
                   out_dtype: torch.dtype = torch.float32, want_wmap: bool = False,
                   out_layout: str = "CHW") -> torch.Tensor:
@@ -439,6 +440,7 @@ def render_decode(st: FrameState, codebooks: torch.Tensor, normalize: bool = Tru
     return out
 
 
+@_abi.guarded(lambda st, *a, **k: st.status.device)
 def render_query(st: FrameState, codebooks: torch.Tensor, phrase_embeds: torch.Tensor, n_pos: int) -> torch.Tensor:
     """Fused blend + relevancy query on a preprocessed and binned frame: ``phrase_embeds [P + N, 512]`` (positives
     first, as ``torch.cat([pos_embeds, neg_embeds])`` at eval/openclip_encoder.py:127) -> relevancy ``[levels, P, H, W]``
@@ -480,6 +482,7 @@ def render_query(st: FrameState, codebooks: torch.Tensor, phrase_embeds: torch.T
 QUICK_CHANNELS = 192
 
 
+@_abi.guarded(lambda st, *a, **k: st.status.device)
 def rasterize_backward(st: FrameState, grad_wmap: Optional[torch.Tensor], grad_color: Optional[torch.Tensor] = None,
                        dense_grad: Optional[bool] = None):
     """dL/d language_feature_precomp [P, L] (and dL/d colours [P, 3] when grad_color is given)."""

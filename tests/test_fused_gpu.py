@@ -159,3 +159,22 @@ def test_fused_bf16_output_and_renderer_paths_agree():
     assert h.dtype == torch.bfloat16
     assert float((h.float() - a).abs().max()) <= 1e-3          # bf16 rounding of |x| < 0.25
     assert torch.equal(r_f.last_state.image["color"], r_u.last_state.image["color"])
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
+def test_entry_points_follow_the_tensors_device():
+    """liblsv2 launches on the CURRENT device; every Python entry point switches to the device its tensors live on.
+    Render on cuda:1 while cuda:0 is current and compare with the same frame rendered on cuda:0."""
+    from langsplatv2_b200 import decode_feature_map
+    scene, cam = hp.make_case(8000, 160, 96, seed=5, levels=3, scale_boost=2.0)
+    _, wq, iq = hp.coeffs(scene, k=4)
+    outs = []
+    for dev in ("cuda:0", "cuda:1"):
+        torch.cuda.set_device(0)
+        st = hp.run_cuda(scene, cam, BG, hp.MODE_QUICK, wq=wq, iq=iq, device=dev)
+        two = decode_feature_map(st.image["wmap"], scene["codebooks"].to(dev), precision="fp32")
+        fused = render_decode(st, scene["codebooks"].to(dev))
+        torch.cuda.synchronize(dev)
+        assert fused.device == torch.device(dev) and torch.cuda.current_device() == 0
+        outs.append((fused.cpu(), two.cpu(), st.image["n_contrib"].cpu()))
+    assert torch.equal(outs[0][2], outs[1][2]) and torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
