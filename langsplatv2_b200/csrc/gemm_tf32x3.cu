@@ -141,7 +141,7 @@ k_gemm_nt_tf32x3(const float* __restrict__ X, const float* __restrict__ Y, float
                 h.y = __uint_as_float(__float_as_uint(v.y) & 0xffffe000u); l.y = v.y - h.y;
                 h.z = __uint_as_float(__float_as_uint(v.z) & 0xffffe000u); l.z = v.z - h.z;
                 h.w = __uint_as_float(__float_as_uint(v.w) & 0xffffe000u); l.w = v.w - h.w;
-                *reinterpret_cast<float4*>(hi) = h;
+                // the head is not written back: kind::tf32 truncates its fp32 operands itself (see k_gemm_h_tf32x3)
                 *reinterpret_cast<float4*>(lo) = l;
             }
             fence_async_smem();
@@ -230,7 +230,11 @@ k_gemm_nt_tf32x3(const float* __restrict__ X, const float* __restrict__ Y, float
 constexpr int GH_A_BYTES = 32 * 512;               // 32 d rows x 128 pixels fp32 = 4 panels of 4 KB
 constexpr int GH_B_BYTES = 64 * 128;               // 64 codes x 32 d
 constexpr int GH_STAGE = GH_A_BYTES + GH_B_BYTES;  // 24 KB
-constexpr int GH_LO_OFF = GX_STAGES * GH_STAGE;
+// deeper ring than the pixel-axis kernels: this one streams 1.56 GB with one CTA per SM, and what it keeps in flight
+// (GH_PF stages x 16 KB) bounds its bandwidth: 2 stages in flight measured 2.6 TB/s (profiles/r02r)
+constexpr int GH_STAGES = 5;
+constexpr int GH_PF = 4;                           // stages requested ahead of the one being split
+constexpr int GH_LO_OFF = GH_STAGES * GH_STAGE;
 constexpr int GH_BAR_OFF = GH_LO_OFF + 2 * GH_STAGE;
 constexpr int GH_TOTAL = GH_BAR_OFF + 1024 + 128;
 constexpr int GH_THREADS = GX_LOADERS + 32 + 128;
@@ -264,8 +268,8 @@ k_gemm_h_tf32x3(const float* __restrict__ C, const float* __restrict__ gt, float
     unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + GH_BAR_OFF);
     uint64_t* full = bars;
-    uint64_t* empty = bars + GX_STAGES;
-    uint64_t* acc_full = bars + 2 * GX_STAGES;
+    uint64_t* empty = bars + GH_STAGES;
+    uint64_t* acc_full = bars + 2 * GH_STAGES;
     uint64_t* acc_free = acc_full + 2;
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(acc_free + 2);
 
@@ -276,7 +280,7 @@ k_gemm_h_tf32x3(const float* __restrict__ C, const float* __restrict__ gt, float
     const int nsteps = my_tiles * dsteps;
 
     if (tid == 0) {
-        for (int s = 0; s < GX_STAGES; ++s) { mbar_init(full + s, GX_LOADERS); mbar_init(empty + s, 1); }
+        for (int s = 0; s < GH_STAGES; ++s) { mbar_init(full + s, GX_LOADERS); mbar_init(empty + s, 1); }
         for (int b = 0; b < 2; ++b) { mbar_init(acc_full + b, 1); mbar_init(acc_free + b, 128); }
         mbar_fence_init();
     }
@@ -288,7 +292,7 @@ k_gemm_h_tf32x3(const float* __restrict__ C, const float* __restrict__ gt, float
 
     if (warp < GX_LW) {
         auto issue = [&](int s) {
-            unsigned char* st = smem + (s % GX_STAGES) * GH_STAGE;
+            unsigned char* st = smem + (s % GH_STAGES) * GH_STAGE;
             const int64_t p0 = ((int64_t)blockIdx.x + (int64_t)(s / dsteps) * gridDim.x) * 128;
             const int d0 = (s % dsteps) * GX_KSTEP;
 #pragma unroll
@@ -309,13 +313,18 @@ k_gemm_h_tf32x3(const float* __restrict__ C, const float* __restrict__ gt, float
             }
             cp_async_commit();
         };
-        if (nsteps > 0) issue(0);
-        if (nsteps > 1) issue(1);
+#pragma unroll
+        for (int p = 0; p < GH_PF; ++p)
+            if (nsteps > p) issue(p);
         for (int s = 0; s < nsteps; ++s) {
-            if (s + 1 < nsteps) cp_async_wait<1>();
+            // copies of step s have landed when at most min(GH_PF - 1, steps still to come) groups are outstanding
+            const int later = nsteps - 1 - s;
+            if (later >= 3) cp_async_wait<3>();
+            else if (later == 2) cp_async_wait<2>();
+            else if (later == 1) cp_async_wait<1>();
             else cp_async_wait<0>();
-            if (s >= 2) mbar_wait(empty + (s - 2) % GX_STAGES, ((s - 2) / GX_STAGES) & 1);
-            unsigned char* st = smem + (s % GX_STAGES) * GH_STAGE;
+            if (s >= 2) mbar_wait(empty + (s - 2) % GH_STAGES, ((s - 2) / GH_STAGES) & 1);
+            unsigned char* st = smem + (s % GH_STAGES) * GH_STAGE;
             unsigned char* lo_st = smem + GH_LO_OFF + (s & 1) * GH_STAGE;
 #pragma unroll
             for (int i = 0; i < GH_ACH + GH_BCH; ++i) {
@@ -328,14 +337,18 @@ k_gemm_h_tf32x3(const float* __restrict__ C, const float* __restrict__ gt, float
                 hh.y = __uint_as_float(__float_as_uint(v.y) & 0xffffe000u); ll.y = v.y - hh.y;
                 hh.z = __uint_as_float(__float_as_uint(v.z) & 0xffffe000u); ll.z = v.z - hh.z;
                 hh.w = __uint_as_float(__float_as_uint(v.w) & 0xffffe000u); ll.w = v.w - hh.w;
-                *reinterpret_cast<float4*>(st + off) = hh;
+                // `hh` is not written back: kind::tf32 ignores the 13 low mantissa bits of its fp32 operands (truncation),
+                // so the raw tile IS the head; only the remainder needs a tile of its own (one STS.128 less per chunk;
+                // tests/test_train_gpu.py::test_codebook_gradient_tensor_core_3xtf32_matches_fp64 would see a rounding
+                // tensor core as a 100x larger error)
                 *reinterpret_cast<float4*>(lo_st + off) = ll;
             }
             fence_async_smem();
-            mbar_arrive(full + s % GX_STAGES);
-            if (s + 2 < nsteps) {
-                if (s >= 1) mbar_wait(empty + (s - 1) % GX_STAGES, ((s - 1) / GX_STAGES) & 1);
-                issue(s + 2);
+            mbar_arrive(full + s % GH_STAGES);
+            if (s + GH_PF < nsteps) {
+                // the stage of step s + GH_PF was last read by the MMAs of step s + GH_PF - GH_STAGES = s - 1
+                if (s >= 1) mbar_wait(empty + (s - 1) % GH_STAGES, ((s - 1) / GH_STAGES) & 1);
+                issue(s + GH_PF);
             }
         }
     } else if (warp > GX_LW) {
@@ -379,9 +392,9 @@ k_gemm_h_tf32x3(const float* __restrict__ C, const float* __restrict__ gt, float
                 mbar_wait(acc_free + bsel, ((c >> 1) - 1) & 1);
                 tc_fence_after();
             }
-            mbar_wait(full + s % GX_STAGES, (s / GX_STAGES) & 1);
+            mbar_wait(full + s % GH_STAGES, (s / GH_STAGES) & 1);
             tc_fence_after();
-            const uint32_t st = smem_u32(smem + (s % GX_STAGES) * GH_STAGE);
+            const uint32_t st = smem_u32(smem + (s % GH_STAGES) * GH_STAGE);
             const uint32_t lo = smem_u32(smem + GH_LO_OFF + (s & 1) * GH_STAGE);
 #pragma unroll
             for (int k8 = 0; k8 < GX_KSTEP / 8; ++k8) {
@@ -395,7 +408,7 @@ k_gemm_h_tf32x3(const float* __restrict__ C, const float* __restrict__ gt, float
                 umma_tf32(d_t, a_hi, b_lo, idesc, 1u);
                 umma_tf32(d_t, a_hi, b_hi, idesc, 1u);
             }
-            umma_commit(empty + s % GX_STAGES);
+            umma_commit(empty + s % GH_STAGES);
             if (s % GX_CHUNK == GX_CHUNK - 1) umma_commit(acc_full + bsel);
         }
     }
