@@ -465,7 +465,8 @@ __global__ void __launch_bounds__(PATH != FD_PATH_WMAP ? FD_THREADS : FD_THREADS
                 }
                 FD_TOC(3);
                 unsigned char* S = S_base + (size_t)s * FD_STAGE_BYTES;
-                for (int q = lane; q < FD_S_BYTES / 16; q += 32) reinterpret_cast<uint4*>(S)[q] = make_uint4(0, 0, 0, 0);
+                // only the L channel rows the blend MMA reads (N = L): 4 KB at L = 64 (training), 12 KB at L = 192
+                for (int q = lane; q < L * 4; q += 32) reinterpret_cast<uint4*>(S)[q] = make_uint4(0, 0, 0, 0);
                 fd_gather(a, nx2.g, part, nx2);              // batch b + 2: under the write stream an L2 hit takes about one
                                                              // batch time, so the gather gets two batches to land
                 fd_prefetch(a, idq[3], part);                // batch b + 6
