@@ -61,6 +61,10 @@ class FeatureRenderer:
         self.last_state: Optional[FrameState] = None
         self.packed: Optional[torch.Tensor] = None     # lsv2_pack_coeff table: depends on the weights only, built once
         self.hook = None                        # optional callable(tag) for event timing in bench.py
+        # overflow of the bounded instance buffers is sticky on the device: every frame ORs its flag into this word, so
+        # one read (check_overflow) covers every frame since the previous check
+        self._sticky = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.overflow_events = 0
 
     def settings(self, cam: Dict) -> GaussianRasterizationSettings:
         return GaussianRasterizationSettings(
@@ -95,6 +99,8 @@ class FeatureRenderer:
         if self.fused:
             st = self._raster(cam, cap, render=False)
             self.last_state = st
+            if self.bounded:
+                self._sticky.bitwise_or_(st.status[1:2])
             if self.hook:
                 self.hook("decode_begin")
             out = render_decode(st, self.codebooks, normalize=True, out_dtype=self.out_dtype,
@@ -105,6 +111,8 @@ class FeatureRenderer:
             return out
         st = self._raster(cam, cap)
         self.last_state = st
+        if self.bounded:
+            self._sticky.bitwise_or_(st.status[1:2])
         self.packed = st.feat.get("packed", self.packed)
         if self.hook:
             self.hook("decode_begin")
@@ -127,6 +135,8 @@ class FeatureRenderer:
             cap = self.calibrate([cam])
         st = self._raster(cam, cap, render=False)
         self.last_state = st
+        if self.bounded:
+            self._sticky.bitwise_or_(st.status[1:2])
         if self.hook:
             self.hook("decode_begin")
         e = torch.cat([pos_embeds.to(self.device, torch.float32), neg_embeds.to(self.device, torch.float32)], dim=0)
@@ -143,11 +153,19 @@ class FeatureRenderer:
         one launch; outputs are static buffers owned by the graph."""
         return GraphedFrame(self, cam)
 
-    def check_overflow(self) -> None:
-        st = self.last_state
-        if st is not None and st.overflowed:
-            raise _abi.Lsv2Error(f"instance capacity {st.capacity} overflowed ({st.num_rendered} needed); "
-                                 "call calibrate() with representative views")
+    def check_overflow(self, grow: bool = True) -> None:
+        """One small device->host read: raises if ANY frame since the previous check was rendered from a truncated
+        instance list (the flag is sticky on the device), after growing the capacity by 1.5x (``grow``) so that the
+        caller can simply render the affected frames again."""
+        if int(self._sticky.item()):
+            self._sticky.zero_()
+            self.overflow_events += 1
+            old = self.capacity
+            if grow and self.capacity is not None:
+                self.capacity = int(self.capacity * 1.5) + 4096
+            raise _abi.Lsv2Error(f"instance capacity {old} overflowed in at least one frame since the last check"
+                                 + (f"; grown to {self.capacity}: render those frames again" if grow else
+                                    "; call calibrate() with representative views"))
 
 
 class GraphedFrame:

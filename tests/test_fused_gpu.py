@@ -178,3 +178,26 @@ def test_entry_points_follow_the_tensors_device():
         assert fused.device == torch.device(dev) and torch.cuda.current_device() == 0
         outs.append((fused.cpu(), two.cpu(), st.image["n_contrib"].cpu()))
     assert torch.equal(outs[0][2], outs[1][2]) and torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+
+
+def test_renderer_overflow_is_sticky_and_capacity_grows():
+    """FeatureRenderer with bounded instance buffers: a frame that overflows is flagged on the device and the flag
+    survives later frames that fit, until check_overflow() reads it once, grows the capacity and raises."""
+    from langsplatv2_b200 import synth, _abi
+    from langsplatv2_b200.renderer import FeatureRenderer
+    scene = synth.make_scene(30000, seed=0, levels=3)
+    scene["scaling"] = scene["scaling"] * 2.0
+    small = {k: (v.cuda() if torch.is_tensor(v) else v) for k, v in synth.ring_camera(0, 8, 160, 96).items()}
+    big = {k: (v.cuda() if torch.is_tensor(v) else v) for k, v in synth.ring_camera(0, 8, 640, 384).items()}
+    r = FeatureRenderer(scene, topk=4, fused=True)
+    r.calibrate([small])
+    cap0 = r.capacity
+    r.render(small)
+    r.check_overflow()                                   # fits: silent
+    r.render(big)                                        # needs far more instances than the small view's capacity
+    r.render(small)                                      # a later frame that fits must not hide it
+    with pytest.raises(_abi.Lsv2Error):
+        r.check_overflow()
+    assert r.capacity > cap0 and r.overflow_events == 1
+    r.render(small)
+    r.check_overflow()                                   # the flag was cleared by the read
