@@ -323,6 +323,13 @@ int lsv2_decode_backward(int32_t levels, int32_t Lc, int32_t D, int64_t HW, cons
 int lsv2_topk_soft_code(int64_t N, int32_t C, int32_t k, const float* logits, float* dense,
                         float* weights, float* indices, void* stream);
 
+/* The same producer for 64 codes per row, emitting in the same pass what the blend reads (replaces
+ * utils/vq_utils.py:9-40 + the compaction / packing of a training iteration): the dense row (may be NULL), the
+ * compacted row of lsv2_compact_coeff (sparse_count u32[N], sparse_index u16[N][16], sparse_weight f32[N][16]) and the
+ * packed row of lsv2_pack_coeff (packed u32[N][LSV2_PACKED_WORDS]).  k <= 16. */
+int lsv2_topk_soft_code_sparse(int64_t N, int32_t k, const float* logits, float* dense, uint32_t* sparse_count,
+                               uint16_t* sparse_index, float* sparse_weight, uint32_t* packed, void* stream);
+
 /* Backward of the dense form (autograd of utils/vq_utils.py:9-24, reached from
  * scene/gaussian_model.py:510-518 during train.py:173): `dense` is the forward's output
  * (its non-zeros are the top-k mask), d_dense = dL/d dense, d_logits = dL/d logits, all f32[N][C]. */

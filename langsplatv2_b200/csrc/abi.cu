@@ -295,6 +295,14 @@ int lsv2_topk_soft_code(int64_t N, int32_t C, int32_t k, const float* logits, fl
     return launch_topk_soft_code(N, C, k, logits, dense, weights, indices, (cudaStream_t)stream);
 }
 
+int lsv2_topk_soft_code_sparse(int64_t N, int32_t k, const float* logits, float* dense, uint32_t* sparse_count,
+                               uint16_t* sparse_index, float* sparse_weight, uint32_t* packed, void* stream)
+{
+    if (N < 0) return LSV2_EINVAL;
+    return launch_topk_soft_code_sparse(N, k, logits, dense, sparse_count, sparse_index, sparse_weight, packed,
+                                        (cudaStream_t)stream);
+}
+
 int lsv2_topk_soft_code_backward(int64_t N, int32_t C, const float* logits, const float* dense,
                                  const float* d_dense, float* d_logits, void* stream)
 {

@@ -213,6 +213,8 @@ int launch_render_backward(const lsv2_view& v, const lsv2_geom& g, const lsv2_bi
                            const float* dL_dcolor, int dense_grad, float* dL_dcoeff, float* dL_dcolors,
                            cudaStream_t st);
 int launch_mark_visible(int P, const float* means3d, const float* viewmatrix, uint8_t* present, cudaStream_t st);
+int launch_topk_soft_code_sparse(int64_t N, int k, const float* logits, float* dense, uint32_t* sp_count,
+                                 uint16_t* sp_index, float* sp_weight, uint32_t* packed, cudaStream_t st);
 int launch_decode_tc_static(int levels, int Lc, int D, int64_t HW, const float* wmap, const float* codebooks,
                             int normalize, int out_dtype, void* out, cudaStream_t st);
 int launch_render_backward_rgb(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b, const lsv2_image& img,

@@ -6,6 +6,7 @@
 // The tensor-core variant lives in decode_tc.cu; this one is the fp32-exact option and the
 // backward GEMMs of the decode.
 #include "common.cuh"
+#include <cuda_fp16.h>
 
 namespace lsv2 {
 
@@ -382,9 +383,20 @@ __device__ __forceinline__ float group8_sum_in_order(float loc, int lane)
     return t;
 }
 
+// Optional extra outputs (the producer emits what the blend reads, directly): the compacted row of
+// lsv2_compact_coeff (count, u16 index[16], f32 weight[16]: entries != 0 in ascending channel order) and the packed
+// row of lsv2_pack_coeff (16 x (fp16 head | fp16 remainder << 16), 16 channel bytes, count, padding), so that a
+// training iteration needs neither of those two kernels after its top-k.
+struct TopkSparseOut {
+    uint32_t* sp_count;      // [N]
+    uint16_t* sp_index;      // [N][16]
+    float* sp_weight;        // [N][16]
+    uint32_t* packed;        // [N][24]
+};
+
 __global__ void __launch_bounds__(256)
 k_topk_soft_code_c64(int64_t N, int k, const float* __restrict__ logits, float* __restrict__ dense,
-                     float* __restrict__ weights, float* __restrict__ indices)
+                     float* __restrict__ weights, float* __restrict__ indices, TopkSparseOut so)
 {
     const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
     const int lane = threadIdx.x & 31, sub = threadIdx.x & 7;
@@ -431,10 +443,23 @@ k_topk_soft_code_c64(int64_t N, int k, const float* __restrict__ logits, float* 
         const int c = __shfl_sync(0xffffffffu, cnt, (lane & ~7) + l);
         if (l < sub) before += c;
     }
-    if (!live) return;
     float y[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) y[i] = ((sel >> i) & 1u) ? v[i] / den : 0.0f;
+    // for the sparse rows: which kept entries are not exactly 0, and where this lane's go in the row
+    uint32_t nz = 0, incl = 0, total = 0;
+    if (so.sp_count) {                                         // uniform over the grid
+#pragma unroll
+        for (int i = 0; i < 8; ++i) nz |= (((sel >> i) & 1u) && y[i] != 0.0f ? 1u : 0u) << i;
+        incl = __popc(nz);
+#pragma unroll
+        for (int o = 1; o < 8; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o, 8);
+            if (sub >= o) incl += t;
+        }
+        total = __shfl_sync(0xffffffffu, incl, 7, 8);
+    }
+    if (!live) return;
     if (dense) {
         float4* d4 = reinterpret_cast<float4*>(dense + (size_t)row * 64 + sub * 8);
         d4[0] = make_float4(y[0], y[1], y[2], y[3]);
@@ -452,9 +477,49 @@ k_topk_soft_code_c64(int64_t N, int k, const float* __restrict__ logits, float* 
             }
         }
     }
+    if (so.sp_count) {
+        // the rows lsv2_compact_coeff / lsv2_pack_coeff would build from `dense`: entries that are exactly 0 (a kept
+        // probability that underflowed) are not part of the row, as there.  All 8 lanes of a live row are here.
+        uint32_t* prow = so.packed + (size_t)row * LSV2_PACKED_WORDS;
+        // zero the 24 words first (3 per lane), then every lane drops its entries in
+        prow[3 * sub + 0] = (3 * sub + 0 == 20) ? min(total, 16u) : 0u;
+        prow[3 * sub + 1] = (3 * sub + 1 == 20) ? min(total, 16u) : 0u;
+        prow[3 * sub + 2] = (3 * sub + 2 == 20) ? min(total, 16u) : 0u;
+        __syncwarp(__activemask());                            // whole rows (8 lanes) leave together above
+        uint32_t pos = incl - __popc(nz);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            if ((nz >> i) & 1u) {
+                if (pos < 16u) {
+                    const int ch = sub * 8 + i;
+                    so.sp_index[(size_t)row * 16 + pos] = (uint16_t)ch;
+                    so.sp_weight[(size_t)row * 16 + pos] = y[i];
+                    const __half h = __float2half_rn(y[i]);
+                    const __half lo = __float2half_rn(__fsub_rn(y[i], __half2float(h)));
+                    prow[pos] = (uint32_t)__half_as_ushort(h) | ((uint32_t)__half_as_ushort(lo) << 16);
+                    reinterpret_cast<uint8_t*>(prow + 16)[pos] = (uint8_t)ch;
+                }
+                ++pos;
+            }
+        }
+        if (sub == 0) so.sp_count[row] = total;          // k <= 16 here, so never a "dense" row
+    }
 }
 
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+int launch_topk_soft_code_sparse(int64_t N, int k, const float* logits, float* dense, uint32_t* sp_count,
+                                 uint16_t* sp_index, float* sp_weight, uint32_t* packed, cudaStream_t st)
+{
+    if (N <= 0) return LSV2_OK;
+    if (k <= 0 || k > 16) return LSV2_EUNSUPPORTED;
+    if (!logits || !sp_count || !sp_index || !sp_weight || !packed || !aligned16(logits) || (dense && !aligned16(dense)))
+        return LSV2_EINVAL;
+    TopkSparseOut so{sp_count, sp_index, sp_weight, packed};
+    k_topk_soft_code_c64<<<(unsigned)ceil_div(N * 8, 256), 256, 0, st>>>(N, k, logits, dense, nullptr, nullptr, so);
+    LSV2_LAUNCH_CHECK("k_topk_soft_code_c64<sparse>");
+    return LSV2_OK;
+}
 
 int launch_topk_soft_code(int64_t N, int C, int k, const float* logits, float* dense, float* weights,
                           float* indices, cudaStream_t st)
@@ -462,7 +527,8 @@ int launch_topk_soft_code(int64_t N, int C, int k, const float* logits, float* d
     if (N <= 0) return LSV2_OK;
     if (C <= 0 || C > 256 || k <= 0 || k > C) return LSV2_EUNSUPPORTED;
     if (C == 64 && aligned16(logits) && aligned16(dense)) {
-        k_topk_soft_code_c64<<<(unsigned)ceil_div(N * 8, 256), 256, 0, st>>>(N, k, logits, dense, weights, indices);
+        k_topk_soft_code_c64<<<(unsigned)ceil_div(N * 8, 256), 256, 0, st>>>(N, k, logits, dense, weights, indices,
+                                                                             TopkSparseOut{nullptr, nullptr, nullptr, nullptr});
         LSV2_LAUNCH_CHECK("k_topk_soft_code_c64");
         return LSV2_OK;
     }

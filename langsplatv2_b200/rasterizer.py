@@ -168,7 +168,7 @@ def rasterize_forward(rs: GaussianRasterizationSettings, means3D, opacities, shs
                       language_feature_weights_quick=None, language_feature_indices=None,
                       capacity: Optional[int] = None, debug_buffers: bool = False,
                       render: bool = True, blend: str = "auto", packed: Optional[torch.Tensor] = None,
-                      prepared: Optional[FrameState] = None) -> FrameState:
+                      prepared: Optional[FrameState] = None, sparse_rows: Optional[dict] = None) -> FrameState:
     """Preprocess -> bin -> blend.  ``capacity=None`` reads the instance count back between the two
     halves (one host sync, as the reference does); an integer capacity runs the whole frame with no
     host involvement and flags overflow in ``state.status``.
@@ -176,7 +176,11 @@ def rasterize_forward(rs: GaussianRasterizationSettings, means3D, opacities, shs
     ``blend``: ``"tc"`` accumulates the sparse coefficients on the tensor cores (``lsv2_render_forward_tc``: weight
     map within 1e-4 of its per-pixel norm, everything else bit-identical), ``"simt"`` is the CUDA-core kernel whose
     weight map reproduces the checker's fp32 operation order bit for bit, ``"auto"`` picks ``"tc"`` where the shape
-    allows it (L a multiple of 64 up to 192, K <= 16)."""
+    allows it (L a multiple of 64 up to 192, K <= 16).
+
+    ``sparse_rows`` (extension, include_feature only): the compacted and packed rows of ``language_feature_precomp``
+    as ``sparse.softmax_to_topk_soft_code_rows`` emits them with the dense rows; the frame then launches neither
+    ``lsv2_compact_coeff`` nor ``lsv2_pack_coeff``."""
     L_ = _abi.lib()
     dev = means3D.device
     _abi.require_cuda(means3D, "means3D")
@@ -189,7 +193,7 @@ def rasterize_forward(rs: GaussianRasterizationSettings, means3D, opacities, shs
                                      language_feature_weights_quick=language_feature_weights_quick,
                                      language_feature_indices=language_feature_indices, capacity=capacity,
                                      debug_buffers=debug_buffers, render=render, blend=blend, packed=packed,
-                                     prepared=prepared)
+                                     prepared=prepared, sparse_rows=sparse_rows)
     P = int(means3D.shape[0])
     H, W = int(rs.image_height), int(rs.image_width)
     mode = feature_mode(rs)
@@ -222,9 +226,18 @@ def rasterize_forward(rs: GaussianRasterizationSettings, means3D, opacities, shs
         cd = _f32c(language_feature_precomp, "language_feature_precomp")
         L = int(cd.shape[1])
         feat["coeff_dense"] = cd
-        feat["sparse_count"] = torch.empty(P, dtype=torch.int32, device=dev)
-        feat["sparse_index"] = torch.empty((P, SPARSE_CAP), dtype=torch.int16, device=dev)
-        feat["sparse_weight"] = torch.empty((P, SPARSE_CAP), dtype=torch.float32, device=dev)
+        if sparse_rows is not None:
+            want = dict(sparse_count=((P,), torch.int32), sparse_index=((P, SPARSE_CAP), torch.int16),
+                        sparse_weight=((P, SPARSE_CAP), torch.float32), packed=((P, PACKED_WORDS), torch.int32))
+            for key, (shape, dt) in want.items():
+                t = sparse_rows.get(key)
+                if t is None or tuple(t.shape) != shape or t.dtype != dt or not t.is_contiguous() or t.device != dev:
+                    raise ValueError(f"sparse_rows[{key!r}] must be a contiguous {dt} tensor of shape {shape} on {dev}")
+                feat[key] = t
+        else:
+            feat["sparse_count"] = torch.empty(P, dtype=torch.int32, device=dev)
+            feat["sparse_index"] = torch.empty((P, SPARSE_CAP), dtype=torch.int16, device=dev)
+            feat["sparse_weight"] = torch.empty((P, SPARSE_CAP), dtype=torch.float32, device=dev)
     elif mode == MODE_QUICK:
         wq, iq = language_feature_weights_quick, language_feature_indices
         if wq is None or iq is None or wq.dim() != 2 or wq.shape != iq.shape or wq.shape[0] != P:
@@ -236,6 +249,8 @@ def rasterize_forward(rs: GaussianRasterizationSettings, means3D, opacities, shs
         # callers hard-wire 3 levels x 64 codes (eval_lerf.py:215); tolerate other level counts
         L = int(getattr(rs, "quick_channels", 0) or QUICK_CHANNELS)
 
+    if sparse_rows is not None and mode != MODE_DENSE:
+        raise ValueError("sparse_rows goes with include_feature (language_feature_precomp)")
     if packed is not None and mode == MODE_QUICK:
         if packed.shape != (P, PACKED_WORDS) or packed.dtype != torch.int32 or not packed.is_contiguous():
             raise ValueError("packed must be the [P, 24] int32 table of a previous frame's state.feat['packed']")
@@ -263,7 +278,7 @@ def rasterize_forward(rs: GaussianRasterizationSettings, means3D, opacities, shs
         geom_c, bin_c = st.c_geom(), st.c_binning()
         feat_c, img_c = st.c_features(), st.c_image()
         stream_ = _abi.stream_ptr(dev)
-        if mode == MODE_DENSE:
+        if mode == MODE_DENSE and sparse_rows is None:
             _abi.check(L_.lsv2_compact_coeff(P, C.byref(geom_c), C.byref(feat_c), stream_), "lsv2_compact_coeff")
         if tc_ok_ and blend != "simt":
             st.ensure_packed(geom_c)
@@ -327,7 +342,7 @@ def rasterize_forward(rs: GaussianRasterizationSettings, means3D, opacities, shs
 
     def run_blend(geom_c, bin_c):
         feat_c, img_c = st.c_features(), st.c_image()
-        if mode == MODE_DENSE:
+        if mode == MODE_DENSE and sparse_rows is None:
             _abi.check(L_.lsv2_compact_coeff(P, C.byref(geom_c), C.byref(feat_c), stream), "lsv2_compact_coeff")
         if use_tc:
             st.ensure_packed(geom_c)
@@ -550,12 +565,12 @@ class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, language_feature_precomp, weights_quick, indices_quick,
                 opacities, scales, rotations, cov3Ds_precomp, raster_settings, capacity=None, dense_coeff_grad=None,
-                prepared=None):
+                prepared=None, sparse_rows=None):
         st = rasterize_forward(raster_settings, means3D, opacities, shs=sh, colors_precomp=colors_precomp,
                                scales=scales, rotations=rotations, cov3D_precomp=cov3Ds_precomp,
                                language_feature_precomp=language_feature_precomp,
                                language_feature_weights_quick=weights_quick, language_feature_indices=indices_quick,
-                               capacity=capacity, prepared=prepared)
+                               capacity=capacity, prepared=prepared, sparse_rows=sparse_rows)
         # what backward needs, WITHOUT the forward's outputs: a state holding `color` / `wmap` on ctx closes the cycle
         # output -> grad_fn -> ctx -> state -> output through C++ shared_ptrs, which Python's GC cannot collect --
         # every grad-enabled forward would leak its whole frame
@@ -609,7 +624,7 @@ class _RasterizeGaussians(torch.autograd.Function):
             d_op = g["opacities"].reshape(ctx.opacity_shape) if need[7] else None
             return (pick(0, "means3D"), pick(1, "means2D"), pick(2, "shs"), pick(3, "colors_precomp"), None, None,
                     None, d_op, pick(8, "scales"), pick(9, "rotations"), pick(10, "cov3D_precomp"), None, None, None,
-                    None)
+                    None, None)
         d_coeff = d_colors = None
         if st.mode == MODE_DENSE and need[4]:
             gc = grad_color if (need[3] and ctx.color_is_precomp) else None
@@ -624,7 +639,8 @@ class _RasterizeGaussians(torch.autograd.Function):
                 raise
         elif need[3]:
             raise NotImplementedError("colour gradients are produced together with the feature backward only")
-        return (None, None, None, d_colors, d_coeff, None, None, None, None, None, None, None, None, None, None)
+        return (None, None, None, d_colors, d_coeff, None, None, None, None, None, None, None, None, None, None,
+                None)
 
 
 class GaussianRasterizer(nn.Module):
@@ -639,6 +655,7 @@ class GaussianRasterizer(nn.Module):
         self.capacity = capacity
         self.dense_coeff_grad: Optional[bool] = None     # None: module default DENSE_COEFF_GRAD (strict)
         self.prepared: Optional[FrameState] = None       # extension: geometry stage done earlier (rasterize_forward)
+        self.sparse_rows: Optional[dict] = None          # extension: rows emitted by the top-k producer (rasterize_forward)
         self.last_state: Optional[FrameState] = None
 
     def markVisible(self, positions: torch.Tensor) -> torch.Tensor:
@@ -663,7 +680,7 @@ class GaussianRasterizer(nn.Module):
         out = _RasterizeGaussians.apply(means3D, means2D, shs, colors_precomp, language_feature_precomp,
                                         language_feature_weights_quick, language_feature_indices, opacities,
                                         scales, rotations, cov3D_precomp, rs, self.capacity, self.dense_coeff_grad,
-                                        self.prepared)
+                                        self.prepared, self.sparse_rows)
         # the full frame state (outputs included) lives on the module, outside the autograd graph
         self.last_state = _RasterizeGaussians.last_state
         _RasterizeGaussians.last_state = None

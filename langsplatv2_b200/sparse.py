@@ -16,6 +16,28 @@ def _topk_dense(x: torch.Tensor, k: int) -> torch.Tensor:
     return dense
 
 
+SPARSE_CAP, PACKED_WORDS = 16, 24       # include/lsv2.h: entries per compacted row, words per packed row
+
+
+def _topk_dense_rows(x: torch.Tensor, k: int):
+    """Dense rows + the compacted / packed rows of the same coefficients, one kernel (``lsv2_topk_soft_code_sparse``)."""
+    L_ = _abi.lib()
+    N, Cc = x.shape
+    if Cc != 64 or not 0 < k <= SPARSE_CAP:
+        raise _abi.Lsv2Error("the fused row producer handles 64 codes per row and k <= 16")
+    dev = x.device
+    dense = torch.empty_like(x)
+    rows = dict(sparse_count=torch.empty(N, dtype=torch.int32, device=dev),
+                sparse_index=torch.empty((N, SPARSE_CAP), dtype=torch.int16, device=dev),
+                sparse_weight=torch.empty((N, SPARSE_CAP), dtype=torch.float32, device=dev),
+                packed=torch.empty((N, PACKED_WORDS), dtype=torch.int32, device=dev))
+    _abi.check(L_.lsv2_topk_soft_code_sparse(N, k, x.data_ptr(), dense.data_ptr(), rows["sparse_count"].data_ptr(),
+                                             rows["sparse_index"].data_ptr(), rows["sparse_weight"].data_ptr(),
+                                             rows["packed"].data_ptr(), _abi.stream_ptr(dev)),
+               "lsv2_topk_soft_code_sparse")
+    return dense, rows
+
+
 class GradSink:
     """Where ``_TopkSoftCode.backward`` writes d logits when a trainer wants the gradient chunk by chunk (N > 1 ranks:
     the all-reduce of chunk i runs under the kernel of chunk i + 1, ``dist.GradBucket.reduce_slice``).  ``target`` is
@@ -38,10 +60,15 @@ def set_grad_sink(sink) -> None:
 class _TopkSoftCode(torch.autograd.Function):
     """One kernel forward, one kernel backward (the reference's autograd graph holds ~6 [N, C] temporaries)."""
 
+    rows = None                # side channel forward -> softmax_to_topk_soft_code_rows (never referenced from ctx)
+
     @staticmethod
-    def forward(ctx, logits, k):
+    def forward(ctx, logits, k, want_rows=False):
         x = logits.contiguous().float()
-        dense = _topk_dense(x, k)
+        if want_rows:
+            dense, _TopkSoftCode.rows = _topk_dense_rows(x, k)
+        else:
+            dense = _topk_dense(x, k)
         ctx.save_for_backward(x, dense)
         return dense
 
@@ -59,12 +86,12 @@ class _TopkSoftCode(torch.autograd.Function):
                                                            _abi.stream_ptr(x.device)), "lsv2_topk_soft_code_backward")
                 sink.on_chunk(a * C, b * C)
             sink.used_upto = N * C
-            return None, None            # the gradient already sits in logits.grad (the bucket view)
+            return None, None, None      # the gradient already sits in logits.grad (the bucket view)
         dx = torch.empty_like(x)
         _abi.check(L_.lsv2_topk_soft_code_backward(x.shape[0], x.shape[1], x.data_ptr(), dense.data_ptr(),
                                                    g.data_ptr(), dx.data_ptr(), _abi.stream_ptr(x.device)),
                    "lsv2_topk_soft_code_backward")
-        return dx, None
+        return dx, None, None
 
 
 def softmax_to_topk_soft_code(logits: torch.Tensor, k: int) -> torch.Tensor:
@@ -75,6 +102,18 @@ def softmax_to_topk_soft_code(logits: torch.Tensor, k: int) -> torch.Tensor:
     if torch.is_grad_enabled() and logits.requires_grad:
         return _TopkSoftCode.apply(logits, k)
     return _topk_dense(logits.detach().contiguous().float(), k)
+
+
+def softmax_to_topk_soft_code_rows(logits: torch.Tensor, k: int):
+    """``softmax_to_topk_soft_code`` + what the rasterizer would derive from its result: returns ``(dense, rows)``,
+    ``rows`` being the ``sparse_rows=`` argument of ``rasterize_forward`` / ``GaussianRasterizer.sparse_rows`` for a
+    frame whose ``language_feature_precomp`` is ``dense``.  64 codes per row (one level), k <= 16."""
+    _abi.require_cuda(logits, "logits")
+    if torch.is_grad_enabled() and logits.requires_grad:
+        dense = _TopkSoftCode.apply(logits, k, True)
+        rows, _TopkSoftCode.rows = _TopkSoftCode.rows, None
+        return dense, rows
+    return _topk_dense_rows(logits.detach().contiguous().float(), k)
 
 
 def get_weights_and_indices(logits: torch.Tensor, k: int):

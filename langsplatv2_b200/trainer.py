@@ -57,11 +57,13 @@ class FeatureTrainer:
                  use_cos: bool = True, use_l1: bool = False, layers: Optional[int] = None,
                  fused_loss: bool = True, gram_loss: bool = True, collective: str = "zero1",
                  use_graph: bool = False, check_every: int = 64, defer_codebook_grad: Optional[bool] = None,
-                 geometry_cache_gb: float = 0.0):
+                 geometry_cache_gb: float = 0.0, fused_rows: Optional[bool] = None):
         dev = torch.device(device)
         f32 = lambda t: t.to(dev, torch.float32).contiguous()
         self.dev = dev
         self.topk = topk
+        # one level of 64 codes: the top-k kernel writes the compacted + packed rows too (LSV2_FUSED_ROWS=0: A/B switch)
+        self.fused_rows = (os.environ.get("LSV2_FUSED_ROWS", "1") != "0") if fused_rows is None else bool(fused_rows)
         self.normalize, self.use_cos, self.use_l1 = normalize, use_cos, use_l1
         self.fused_loss = fused_loss        # cos loss (+ the normalisation) as two kernels instead of torch's ~28 passes
         self.gram_loss = gram_loss          # ... and, for a single layer, without forming the [512, H, W] feature map
@@ -263,8 +265,13 @@ class FeatureTrainer:
         rasterizer.prepared = prepared
         rasterizer.dense_coeff_grad = False         # the top-k mask follows (utils/vq_utils.py:20): support-only is exact
         zero = torch.zeros((1,), dtype=torch.float32, device=self.dev)
+        if self.fused_rows and self.layers == 1 and self.codebook_size == 64 and self.topk <= 16:
+            # one level: the top-k kernel also writes the rows the blend reads (no compaction / packing launches)
+            coeff, rasterizer.sparse_rows = lssparse.softmax_to_topk_soft_code_rows(self.logits, self.topk)
+        else:
+            coeff = self.render_weights()
         _, wmap, _ = rasterizer(means3D=self.xyz, means2D=self.means2D, shs=self.shs, colors_precomp=None,
-                                language_feature_precomp=self.render_weights(), language_feature_weights_quick=zero,
+                                language_feature_precomp=coeff, language_feature_weights_quick=zero,
                                 language_feature_indices=zero, opacities=self.opacity, scales=self.scales,
                                 rotations=self.rotations, cov3D_precomp=None)
         self._last_state = rasterizer.last_state

@@ -178,9 +178,9 @@ def test_deferred_codebook_gradient_equals_inline():
             n_log = tr.n_log
         a, b = grads
         assert losses[0] == pytest.approx(losses[1], rel=1e-6)
-        cb_a, cb_b = a[n_log:], b[n_log:]
+        cb_a, cb_b = a[n_log:].detach(), b[n_log:].detach()
         assert float(cb_a.abs().max()) > 0
-        assert float((cb_a - cb_b).abs().max()) <= 1e-5 * float(cb_a.detach().abs().max())
+        assert float((cb_a - cb_b).abs().max()) <= 1e-5 * float(cb_a.abs().max())
         assert float((a[:n_log] - b[:n_log]).abs().max()) <= 1e-4 * float(a[:n_log].abs().max())
     # captured iterations with the side stream inside the graph: same losses as eager deferred steps
     runs = []
@@ -296,3 +296,68 @@ def test_trainer_geometry_cache_is_exact():
     tr = FeatureTrainer(scene, topk=4, layers=1, geometry_cache_gb=1e-6)
     tr.calibrate(cams)
     assert not tr.cache_geometry(cams[0], 0)
+
+
+def test_topk_row_producer_equals_compaction_and_packing():
+    """lsv2_topk_soft_code_sparse: the dense rows are those of lsv2_topk_soft_code, and the compacted / packed rows are
+    bit for bit what lsv2_compact_coeff + lsv2_pack_coeff derive from them (entries that underflowed to 0 left out);
+    a frame rendered from the emitted rows equals the frame that compacts and packs for itself."""
+    from langsplatv2_b200 import sparse
+    from langsplatv2_b200.rasterizer import rasterize_forward
+    scene, cam = hp.make_case(20003, 256, 192, seed=4, levels=1, scale_boost=2.0)
+    g = lambda k: scene[k].cuda()
+    P = scene["xyz"].shape[0]
+    gen = torch.Generator(device="cuda").manual_seed(3)
+    logits = torch.randn((P, 64), device="cuda", generator=gen) * 3.0
+    logits[::11, 2:] -= 500.0                     # two live codes: the other kept probabilities are exactly 0
+    logits[::13, 1:] -= 500.0                     # one live code
+    logits[5] = 0.0                               # ties: lowest channels win
+    rs = hp.settings(cam, scene, (0.1, 0.2, 0.3), include_feature=True, quick_render=False)
+    geo = dict(shs=g("features"), scales=g("scaling"), rotations=g("rotation"))
+    for k in (1, 4, 16):
+        dense0 = sparse.softmax_to_topk_soft_code(logits, k)
+        dense, rows = sparse.softmax_to_topk_soft_code_rows(logits, k)
+        assert torch.equal(dense, dense0)
+        a = rasterize_forward(rs, g("xyz"), g("opacity"), capacity=400000, language_feature_precomp=dense0, **geo)
+        b = rasterize_forward(rs, g("xyz"), g("opacity"), capacity=400000, language_feature_precomp=dense,
+                              sparse_rows=rows, **geo)
+        vis = a.geom["radii"] > 0
+        assert int(vis.sum()) > 1000
+        cnt = a.feat["sparse_count"][vis]
+        assert torch.equal(cnt, b.feat["sparse_count"][vis])
+        assert int(cnt.min()) >= 1 and int(cnt.max()) == k and (k == 1 or int(cnt.min()) < k)
+        live = (torch.arange(16, device="cuda")[None, :] < cnt[:, None])
+        for key in ("sparse_index", "sparse_weight"):
+            assert torch.equal(a.feat[key][vis][live], b.feat[key][vis][live]), (k, key)
+        assert torch.equal(a.feat["packed"][vis], b.feat["packed"][vis]), k
+        # rows of Gaussians outside the frustum: still a valid row (the count the dense row has), never read by the blend
+        assert torch.equal(b.feat["sparse_count"], (dense != 0).sum(1).to(torch.int32))
+        for key in ("color", "wmap", "final_T", "n_contrib"):
+            assert torch.equal(a.image[key], b.image[key]), (k, key)
+    with pytest.raises(ValueError):
+        rasterize_forward(rs, g("xyz"), g("opacity"), capacity=400000, language_feature_precomp=dense,
+                          sparse_rows=dict(rows, packed=rows["packed"][:-1]), **geo)
+    with pytest.raises(_abi.Lsv2Error):
+        sparse.softmax_to_topk_soft_code_rows(logits[:, :32].contiguous(), 4)
+    # autograd: the gradient through the row-emitting producer is the plain producer's
+    x1 = logits[:4096].clone().requires_grad_(True)
+    x2 = logits[:4096].clone().requires_grad_(True)
+    up = torch.randn((4096, 64), device="cuda", generator=gen)
+    sparse.softmax_to_topk_soft_code(x1, 4).backward(up)
+    d2, r2 = sparse.softmax_to_topk_soft_code_rows(x2, 4)
+    assert r2 is not None and not r2["packed"].requires_grad
+    d2.backward(up)
+    assert torch.equal(x1.grad, x2.grad)
+
+
+def test_trainer_fused_rows_equal_separate_kernels(monkeypatch):
+    """FeatureTrainer with the row-emitting top-k (default) against the compaction + packing kernels (LSV2_FUSED_ROWS=0)."""
+    runs = []
+    for flag in ("0", "1"):
+        monkeypatch.setenv("LSV2_FUSED_ROWS", flag)
+        tr, cam, gt, mask = _small_trainer()
+        assert tr.fused_rows == (flag == "1")
+        tr.calibrate([cam])
+        runs.append([float(tr.step(cam, gt, mask)) for _ in range(5)])
+    np.testing.assert_allclose(runs[0], runs[1], rtol=5e-3)
+    assert runs[0][0] == pytest.approx(runs[1][0], rel=1e-6)
