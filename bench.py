@@ -481,6 +481,41 @@ def run_rgb_stage(args, dev, scene, steps=30):
                     "lsv2_render_backward_rgb + lsv2_preprocess_backward"}
 
 
+def run_scene_init(dev, scene):
+    """distCUDA2 over the scene's positions (scale initialisation): this repo's kernel, CUDA events; and, when
+    oracle/_ref/libsimple_knn_ref.so travelled, the reference's own compiled SimpleKNN::knn on the same points (it
+    synchronises inside: host wall clock), with a bit comparison of the two results."""
+    from langsplatv2_b200.knn import distCUDA2
+    pts = scene["xyz"].to(dev).float().contiguous()
+    for _ in range(3):
+        ours = distCUDA2(pts)
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        ours = distCUDA2(pts)
+    e1.record()
+    torch.cuda.synchronize(dev)
+    out = {"op": "distCUDA2 (mean squared distance to the 3 nearest neighbours)", "points": int(pts.shape[0]),
+           "ms": e0.elapsed_time(e1) / 10, "gpu_launches_per_call": 9}
+    try:
+        from oracle import knn_ref                      # reference leg only: the compiled reference, never the product
+        if knn_ref.reference_lib() is not None:
+            for _ in range(2):
+                ref = knn_ref.reference_dist_cuda2(pts)
+            t0 = time.perf_counter()
+            for _ in range(5):
+                ref = knn_ref.reference_dist_cuda2(pts)
+            out["reference_ms"] = (time.perf_counter() - t0) / 5 * 1e3
+            out["reference"] = "SimpleKNN::knn compiled from the reference's simple_knn.cu (oracle/_ref), same GPU"
+            out["bit_identical_to_reference"] = bool(torch.equal(ref.view(torch.int32), ours.view(torch.int32)))
+        else:
+            out["reference"] = "oracle/_ref/libsimple_knn_ref.so not built"
+    except Exception as ex:                              # the baseline leg must not take the bench line down
+        out["reference"] = "failed: " + str(ex).split("\n")[0]
+    return out
+
+
 def run_reference_style(r, cams, steps, dev):
     """What a user of the reference runs per frame (eval_lerf.py:210-220): the drop-in op through its 3-tuple API
     (one host sync per frame for num_rendered, fp32 [192,H,W] weight map to HBM) followed by the reference's own
@@ -839,6 +874,7 @@ def run_gpu(args, wl):
             from langsplatv2_b200 import synth as _synth
             rgb_scene = _synth.make_scene(TRAIN_WL["N"], seed=0, levels=1, codebook_size=CODES, feat_dim=D, sh_degree=3)
             train["rgb_stage"] = run_rgb_stage(args, dev, rgb_scene)
+            train["scene_init"] = run_scene_init(dev, rgb_scene)
             del rgb_scene
 
     t = torch.tensor([ms_total, e2e_ms, dom_ms], dtype=torch.float64, device=dev)

@@ -323,6 +323,14 @@ int lsv2_decode_backward(int32_t levels, int32_t Lc, int32_t D, int64_t HW, cons
 int lsv2_topk_soft_code(int64_t N, int32_t C, int32_t k, const float* logits, float* dense,
                         float* weights, float* indices, void* stream);
 
+/* simple_knn._C.distCUDA2 (submodules/simple-knn/spatial.cu:15-25 -> simple_knn.cu:148-220; the one call site is
+ * scene/gaussian_model.py:194): mean_dist2[i] = mean of the squared distances from points[i] (f32[P][3]) to its three
+ * nearest other points (fewer than three: FLT_MAX stays in the sum, as there).  Same values as the reference bit for bit (the search
+ * only prunes).  No host synchronisation; scratch >= lsv2_knn_scratch_bytes(P). */
+size_t lsv2_knn_scratch_bytes(int32_t P);
+int lsv2_dist2_knn3(int32_t P, const float* points, float* mean_dist2, void* scratch, size_t scratch_bytes,
+                    void* stream);
+
 /* The same producer for 64 codes per row, emitting in the same pass what the blend reads (replaces
  * utils/vq_utils.py:9-40 + the compaction / packing of a training iteration): the dense row (may be NULL), the
  * compacted row of lsv2_compact_coeff (sparse_count u32[N], sparse_index u16[N][16], sparse_weight f32[N][16]) and the

@@ -77,7 +77,7 @@ EXPORTS = [
     "lsv2_gram_loss_forward_seg", "lsv2_gram_loss_backward_seg",
     "lsv2_render_decode_scratch_bytes", "lsv2_render_decode", "lsv2_render_forward_tc", "lsv2_adam_step", "lsv2_pack_coeff",
     "lsv2_render_query_scratch_bytes", "lsv2_render_query",
-    "lsv2_render_backward_rgb", "lsv2_preprocess_backward", "lsv2_decode_static", "lsv2_topk_soft_code_sparse",
+    "lsv2_render_backward_rgb", "lsv2_preprocess_backward", "lsv2_decode_static", "lsv2_topk_soft_code_sparse", "lsv2_knn_scratch_bytes", "lsv2_dist2_knn3",
 ]
 
 _lib = None
@@ -129,6 +129,10 @@ def lib() -> C.CDLL:
     L.lsv2_decode_static.restype = C.c_int
     L.lsv2_decode_backward.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int64, _vp, _vp, _vp, _vp, _vp, _vp]
     L.lsv2_topk_soft_code.argtypes = [C.c_int64, C.c_int32, C.c_int32, _vp, _vp, _vp, _vp, _vp]
+    L.lsv2_knn_scratch_bytes.argtypes = [C.c_int32]
+    L.lsv2_knn_scratch_bytes.restype = C.c_size_t
+    L.lsv2_dist2_knn3.argtypes = [C.c_int32, _vp, _vp, _vp, C.c_size_t, _vp]
+    L.lsv2_dist2_knn3.restype = C.c_int
     L.lsv2_topk_soft_code_sparse.argtypes = [C.c_int64, C.c_int32, _vp, _vp, _vp, _vp, _vp, _vp, _vp]
     L.lsv2_topk_soft_code_sparse.restype = C.c_int
     L.lsv2_topk_soft_code_backward.argtypes = [C.c_int64, C.c_int32, _vp, _vp, _vp, _vp, _vp]

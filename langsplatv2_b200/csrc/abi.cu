@@ -295,6 +295,15 @@ int lsv2_topk_soft_code(int64_t N, int32_t C, int32_t k, const float* logits, fl
     return launch_topk_soft_code(N, C, k, logits, dense, weights, indices, (cudaStream_t)stream);
 }
 
+size_t lsv2_knn_scratch_bytes(int32_t P) { return knn_scratch_bytes(P); }
+
+int lsv2_dist2_knn3(int32_t P, const float* points, float* mean_dist2, void* scratch, size_t scratch_bytes,
+                    void* stream)
+{
+    if (P < 0) return LSV2_EINVAL;
+    return launch_dist2_knn3(P, points, mean_dist2, scratch, scratch_bytes, (cudaStream_t)stream);
+}
+
 int lsv2_topk_soft_code_sparse(int64_t N, int32_t k, const float* logits, float* dense, uint32_t* sparse_count,
                                uint16_t* sparse_index, float* sparse_weight, uint32_t* packed, void* stream)
 {

@@ -213,6 +213,12 @@ int launch_render_backward(const lsv2_view& v, const lsv2_geom& g, const lsv2_bi
                            const float* dL_dcolor, int dense_grad, float* dL_dcoeff, float* dL_dcolors,
                            cudaStream_t st);
 int launch_mark_visible(int P, const float* means3d, const float* viewmatrix, uint8_t* present, cudaStream_t st);
+int sort_num_passes(int nbits);
+int sort_words(uint64_t* k_a, uint64_t* k_b, const uint32_t* count, uint64_t n, int nbits, void* scratch,
+               size_t scratch_bytes, cudaStream_t st);
+size_t knn_scratch_bytes(int P);
+int launch_dist2_knn3(int P, const float* points, float* mean_dist2, void* scratch, size_t scratch_bytes,
+                      cudaStream_t st);
 int launch_topk_soft_code_sparse(int64_t N, int k, const float* logits, float* dense, uint32_t* sp_count,
                                  uint16_t* sp_index, float* sp_weight, uint32_t* packed, cudaStream_t st);
 int launch_decode_tc_static(int levels, int Lc, int D, int64_t HW, const float* wmap, const float* codebooks,

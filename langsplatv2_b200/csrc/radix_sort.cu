@@ -386,6 +386,14 @@ int launch_sort(const lsv2_binning& b, int tile_bits, int n_tiles, bool* ranges_
                        scratch, scratch_bytes, st);
 }
 
+// Stable sort of n packed words on the `nbits` low bits of their high word (the Morton order of knn.cu); input in k_b
+// when sort_num_passes(nbits) is odd, result in k_a.
+int sort_words(uint64_t* k_a, uint64_t* k_b, const uint32_t* count, uint64_t n, int nbits, void* scratch,
+               size_t scratch_bytes, cudaStream_t st)
+{
+    return sort_packed(k_a, k_b, nullptr, count, n, make_plan(nbits), nullptr, 0, scratch, scratch_bytes, st);
+}
+
 // number of passes over a `nbits` field -- lsv2_bin uses it to pick the buffer the instances are emitted into.
 int sort_num_passes(int nbits) { return make_plan(nbits).npass; }
 

@@ -565,3 +565,32 @@ def test_golden_relevancy_query(tag):
     assert got.shape == Q[f"{tag}_relev"].shape
     np.testing.assert_allclose(got, Q[f"{tag}_relev"], rtol=0, atol=2e-6)
     assert np.allclose(got[0, :, 0, 0], 0.5)                 # the empty pixel: every similarity is 0
+
+
+# ---------------------------------------------------------------------------------------------
+# distCUDA2: the CPU restatement against outputs of the reference's own compiled SimpleKNN::knn
+# (tests/golden/knn_golden.npz, tests/golden/make_knn_golden.py -- generated on a GPU box)
+def test_golden_knn_restatement_matches_the_reference():
+    from oracle import knn_ref
+    z = np.load(os.path.join(ROOT, "tests", "golden", "knn_golden.npz"))
+    names = sorted({k.split("/")[0] for k in z.files})
+    assert {"uniform_3000", "clusters_5000", "duplicates_1500", "plane_2049", "far_offset_1025", "tiny_1",
+            "tiny_4"} <= set(names)
+    for n in names:
+        pts, want = z[n + "/points"], z[n + "/dist2"]
+        for fn in (knn_ref.dist_cuda2_bruteforce, knn_ref.dist_cuda2):
+            got = fn(pts)
+            assert got.dtype == np.float32 and got.shape == want.shape
+            fin = np.isfinite(want)
+            assert np.array_equal(np.isinf(got), ~fin), n
+            # the fp32 fma is emulated through float64: at most the last bit (the fixture run saw none differ)
+            assert np.all(np.abs(got[fin] - want[fin]) <= np.spacing(want[fin])), n
+    # duplicates count as neighbours at distance 0; fewer than three other points leave FLT_MAX in the sum:
+    # two others -> FLT_MAX / 3, fewer -> +inf
+    assert z["duplicates_1500/dist2"][305] == 0.0
+    assert np.all(z["tiny_3/dist2"] == np.float32(np.finfo(np.float32).max) / np.float32(3))
+    assert np.all(np.isinf(z["tiny_2/dist2"])) and np.all(np.isinf(z["tiny_1/dist2"]))
+    # the k-d tree path of the checker against its brute force beyond the brute-force cut-over
+    pts = np.random.default_rng(5).normal(0, 1, (6000, 3)).astype(np.float32)
+    pts[10:30] = pts[10]                          # more coincident points than the tree returns candidates
+    assert np.array_equal(knn_ref.dist_cuda2(pts), knn_ref.dist_cuda2_bruteforce(pts))
