@@ -218,6 +218,17 @@ int lsv2_render_backward(const lsv2_view* view, const lsv2_geom* geom, const lsv
                          const float* dL_dwmap, const float* dL_dcolor, int32_t dense_grad,
                          float* dL_dcoeff, float* dL_dcolors, void* stream);
 
+/* The same with the gradient in the order of the COMPACTED rows (support-only by construction): dL_drows
+ * f32[P][row_stride], zero-initialised by the caller, entry e of row g receives the sum for channel
+ * sparse_index[g][e], e < sparse_count[g] (entries e >= row_stride are dropped; rows with more than 16 non-zeros have
+ * no row form and get nothing -- lsv2_topk_soft_code_sparse never emits one).  For top-4 that is 16 B per Gaussian
+ * instead of 256 B: less to clear, less for lsv2_topk_soft_code_backward_rows to read, and all a data-parallel
+ * trainer has to exchange (the top-k backward is linear in this gradient, so ranks sum the rows and run it once). */
+int lsv2_render_backward_rows(const lsv2_view* view, const lsv2_geom* geom, const lsv2_binning* binning,
+                              const lsv2_features* feat, const lsv2_image* image, const float* dL_dwmap,
+                              const float* dL_dcolor, int32_t row_stride, float* dL_drows, float* dL_dcolors,
+                              void* stream);
+
 /* ---- RGB-stage backward (replaces _C.rasterize_gaussians_backward for train.py WITHOUT --include_feature:
  *      train.py:169-172 l1 + ssim on the RGB render, :247-258 optimizer / densification;
  *      gradients reach means3D, means2D, shs / colors_precomp, opacities, scales, rotations / cov3D_precomp
@@ -343,6 +354,12 @@ int lsv2_topk_soft_code_sparse(int64_t N, int32_t k, const float* logits, float*
  * (its non-zeros are the top-k mask), d_dense = dL/d dense, d_logits = dL/d logits, all f32[N][C]. */
 int lsv2_topk_soft_code_backward(int64_t N, int32_t C, const float* logits, const float* dense,
                                  const float* d_dense, float* d_logits, void* stream);
+
+/* ... with the upstream gradient in row form (lsv2_render_backward_rows): 64 codes per row; logits / dense /
+ * d_logits f32[N][64], sparse_count u32[N], sparse_index u16[N][16], d_rows f32[N][row_stride]. */
+int lsv2_topk_soft_code_backward_rows(int64_t N, const float* logits, const float* dense,
+                                      const uint32_t* sparse_count, const uint16_t* sparse_index,
+                                      const float* d_rows, int32_t row_stride, float* d_logits, void* stream);
 
 /* ---- feature-stage loss (train.py:157-164, utils/loss_utils.py:24-25) -----------------
  * loss = 1 - mean_p cos(a_p, b_p),  a = mask * F / (|F| + 1e-10) (normalize != 0) or mask * F,  b = mask * gt,

@@ -78,6 +78,7 @@ EXPORTS = [
     "lsv2_render_decode_scratch_bytes", "lsv2_render_decode", "lsv2_render_forward_tc", "lsv2_adam_step", "lsv2_pack_coeff",
     "lsv2_render_query_scratch_bytes", "lsv2_render_query",
     "lsv2_render_backward_rgb", "lsv2_preprocess_backward", "lsv2_decode_static", "lsv2_topk_soft_code_sparse", "lsv2_knn_scratch_bytes", "lsv2_dist2_knn3",
+    "lsv2_render_backward_rows", "lsv2_topk_soft_code_backward_rows",
 ]
 
 _lib = None
@@ -119,6 +120,11 @@ def lib() -> C.CDLL:
     L.lsv2_mark_visible.argtypes = [C.c_int32, _vp, _vp, _vp, _vp]
     L.lsv2_render_backward.argtypes = [P(View), P(Geom), P(Binning), P(Features), P(Image), _vp, _vp,
                                        C.c_int32, _vp, _vp, _vp]
+    L.lsv2_render_backward_rows.argtypes = [P(View), P(Geom), P(Binning), P(Features), P(Image), _vp, _vp,
+                                            C.c_int32, _vp, _vp, _vp]
+    L.lsv2_render_backward_rows.restype = C.c_int
+    L.lsv2_topk_soft_code_backward_rows.argtypes = [C.c_int64, _vp, _vp, _vp, _vp, _vp, C.c_int32, _vp, _vp]
+    L.lsv2_topk_soft_code_backward_rows.restype = C.c_int
     L.lsv2_render_backward_rgb.argtypes = [P(View), P(Geom), P(Binning), P(Image), _vp, _vp, _vp]
     L.lsv2_preprocess_backward.argtypes = [P(View), P(Scene), P(Geom), _vp, P(GeomGrads), _vp]
     L.lsv2_decode_scratch_bytes.restype = C.c_size_t

@@ -210,6 +210,26 @@ int lsv2_render_backward(const lsv2_view* view, const lsv2_geom* geom, const lsv
                                   dL_dcoeff, dL_dcolors, (cudaStream_t)stream);
 }
 
+int lsv2_render_backward_rows(const lsv2_view* view, const lsv2_geom* geom, const lsv2_binning* binning,
+                              const lsv2_features* feat, const lsv2_image* image, const float* dL_dwmap,
+                              const float* dL_dcolor, int32_t row_stride, float* dL_drows, float* dL_dcolors,
+                              void* stream)
+{
+    if (!view_ok(view) || !geom || !binning || !feat || !image || row_stride <= 0) return LSV2_EINVAL;
+    if (!feat->sparse_count || !feat->sparse_index) return LSV2_EINVAL;
+    return launch_render_backward(*view, *geom, *binning, *feat, *image, dL_dwmap, dL_dcolor, 0, dL_drows,
+                                  dL_dcolors, (cudaStream_t)stream, row_stride);
+}
+
+int lsv2_topk_soft_code_backward_rows(int64_t N, const float* logits, const float* dense,
+                                      const uint32_t* sparse_count, const uint16_t* sparse_index,
+                                      const float* d_rows, int32_t row_stride, float* d_logits, void* stream)
+{
+    if (N < 0) return LSV2_EINVAL;
+    return launch_topk_soft_code_bwd_rows(N, logits, dense, sparse_count, sparse_index, d_rows, row_stride, d_logits,
+                                          (cudaStream_t)stream);
+}
+
 int lsv2_render_backward_rgb(const lsv2_view* view, const lsv2_geom* geom, const lsv2_binning* binning,
                              const lsv2_image* image, const float* dL_dcolor, float* acc, void* stream)
 {

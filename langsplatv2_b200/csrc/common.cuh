@@ -211,7 +211,10 @@ int launch_render_forward(const lsv2_view& v, const lsv2_geom& g, const lsv2_bin
 int launch_render_backward(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b,
                            const lsv2_features& f, const lsv2_image& img, const float* dL_dwmap,
                            const float* dL_dcolor, int dense_grad, float* dL_dcoeff, float* dL_dcolors,
-                           cudaStream_t st);
+                           cudaStream_t st, int row_stride = 0);
+int launch_topk_soft_code_bwd_rows(int64_t N, const float* logits, const float* dense, const uint32_t* sp_count,
+                                   const uint16_t* sp_index, const float* d_rows, int row_stride, float* d_logits,
+                                   cudaStream_t st);
 int launch_mark_visible(int P, const float* means3d, const float* viewmatrix, uint8_t* present, cudaStream_t st);
 int sort_num_passes(int nbits);
 int sort_words(uint64_t* k_a, uint64_t* k_b, const uint32_t* count, uint64_t n, int nbits, void* scratch,

@@ -609,10 +609,21 @@ k_topk_soft_code_bwd(int64_t N, int C, const float* __restrict__ logits, const f
     }
 }
 
-// C == 64 version of the backward: same 8-lanes-per-row layout as k_topk_soft_code_c64
+// C == 64 version of the backward: same 8-lanes-per-row layout as k_topk_soft_code_c64.
+// ROWS: the upstream gradient arrives in the compacted row form of lsv2_render_backward_rows -- d_rows[row][e] belongs
+// to channel sp_index[row][e], e < sp_count[row] (<= row_stride) -- instead of a dense [N, 64] array: 16 B per row
+// instead of 256 B for top-4, which is also all a data-parallel exchange has to move.
+struct TopkRowsGrad {
+    const uint32_t* sp_count;
+    const uint16_t* sp_index;      // [N][16]
+    const float* d_rows;           // [N][row_stride]
+    int row_stride;
+};
+
+template <bool ROWS>
 __global__ void __launch_bounds__(256)
 k_topk_soft_code_bwd_c64(int64_t N, const float* __restrict__ logits, const float* __restrict__ dense,
-                         const float* __restrict__ d_dense, float* __restrict__ d_logits)
+                         const float* __restrict__ d_dense, float* __restrict__ d_logits, TopkRowsGrad rg)
 {
     const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
     const int sub = threadIdx.x & 7;
@@ -621,10 +632,30 @@ k_topk_soft_code_bwd_c64(int64_t N, const float* __restrict__ logits, const floa
     const size_t base = (size_t)r * 64 + sub * 8;
     const float4 xa = *reinterpret_cast<const float4*>(logits + base), xb = *reinterpret_cast<const float4*>(logits + base + 4);
     const float4 ya = *reinterpret_cast<const float4*>(dense + base), yb = *reinterpret_cast<const float4*>(dense + base + 4);
-    const float4 ga = *reinterpret_cast<const float4*>(d_dense + base), gb = *reinterpret_cast<const float4*>(d_dense + base + 4);
     float v[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
     const float y[8] = {ya.x, ya.y, ya.z, ya.w, yb.x, yb.y, yb.z, yb.w};
-    const float g[8] = {ga.x, ga.y, ga.z, ga.w, gb.x, gb.y, gb.z, gb.w};
+    float g[8];
+    if (ROWS) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) g[i] = 0.0f;
+        const int kmax = min(rg.row_stride, 16);
+        const int cnt = min((int)min(rg.sp_count[r], 16u), kmax);
+        // lane `sub` fetches entries sub and sub + 8 of its row, the 8 lanes pass them round
+        int ch0 = -1, ch1 = -1;
+        float w0 = 0.0f, w1 = 0.0f;
+        if (sub < cnt) { ch0 = rg.sp_index[(size_t)r * 16 + sub]; w0 = rg.d_rows[(size_t)r * rg.row_stride + sub]; }
+        if (sub + 8 < cnt) { ch1 = rg.sp_index[(size_t)r * 16 + sub + 8]; w1 = rg.d_rows[(size_t)r * rg.row_stride + sub + 8]; }
+        for (int e = 0; e < kmax; ++e) {                       // kmax is uniform over the grid
+            const int ch = __shfl_sync(0xffffffffu, e < 8 ? ch0 : ch1, e & 7, 8);
+            const float w = __shfl_sync(0xffffffffu, e < 8 ? w0 : w1, e & 7, 8);
+            const bool mine = ch >= 0 && (ch >> 3) == sub;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) g[i] = (mine && (ch & 7) == i) ? w : g[i];
+        }
+    } else {
+        const float4 ga = *reinterpret_cast<const float4*>(d_dense + base), gb = *reinterpret_cast<const float4*>(d_dense + base + 4);
+        g[0] = ga.x; g[1] = ga.y; g[2] = ga.z; g[3] = ga.w; g[4] = gb.x; g[5] = gb.y; g[6] = gb.z; g[7] = gb.w;
+    }
     float mx = v[0];
 #pragma unroll
     for (int i = 1; i < 8; ++i) mx = fmaxf(mx, v[i]);
@@ -664,13 +695,27 @@ k_topk_soft_code_bwd_c64(int64_t N, const float* __restrict__ logits, const floa
     o4[1] = make_float4(v[4] * (dp[4] - Dd), v[5] * (dp[5] - Dd), v[6] * (dp[6] - Dd), v[7] * (dp[7] - Dd));
 }
 
+int launch_topk_soft_code_bwd_rows(int64_t N, const float* logits, const float* dense, const uint32_t* sp_count,
+                                   const uint16_t* sp_index, const float* d_rows, int row_stride, float* d_logits,
+                                   cudaStream_t st)
+{
+    if (N == 0) return LSV2_OK;
+    if (row_stride <= 0 || !logits || !dense || !sp_count || !sp_index || !d_rows || !d_logits) return LSV2_EINVAL;
+    if (!aligned16(logits) || !aligned16(dense) || !aligned16(d_logits)) return LSV2_EINVAL;
+    k_topk_soft_code_bwd_c64<true><<<(unsigned)ceil_div(N * 8, 256), 256, 0, st>>>(
+        N, logits, dense, nullptr, d_logits, TopkRowsGrad{sp_count, sp_index, d_rows, row_stride});
+    LSV2_LAUNCH_CHECK("k_topk_soft_code_bwd_c64<rows>");
+    return LSV2_OK;
+}
+
 int launch_topk_soft_code_bwd(int64_t N, int C, const float* logits, const float* dense, const float* d_dense,
                               float* d_logits, cudaStream_t st)
 {
     if (N == 0) return LSV2_OK;
     if (C <= 0 || C > 256) return LSV2_EUNSUPPORTED;
     if (C == 64 && aligned16(logits) && aligned16(dense) && aligned16(d_dense) && aligned16(d_logits)) {
-        k_topk_soft_code_bwd_c64<<<(unsigned)ceil_div(N * 8, 256), 256, 0, st>>>(N, logits, dense, d_dense, d_logits);
+        k_topk_soft_code_bwd_c64<false><<<(unsigned)ceil_div(N * 8, 256), 256, 0, st>>>(N, logits, dense, d_dense, d_logits,
+                                                                                        TopkRowsGrad{nullptr, nullptr, nullptr, 0});
         LSV2_LAUNCH_CHECK("k_topk_soft_code_bwd_c64");
         return LSV2_OK;
     }

@@ -35,6 +35,7 @@ struct BackArgs {
     const float* dL_dcolor;
     float* dL_dcoeff;
     float* dL_dcolors;
+    int row_stride;                  // > 0: dL_dcoeff is [P][row_stride] in the order of the compacted row (entry e), not [P][L]
 };
 
 struct BackInstance {
@@ -101,6 +102,7 @@ __global__ void __launch_bounds__(RB_THREADS, 3) k_render_backward(BackArgs a)
             s.az = r1.x; s.thr = r1.y; s.op = r1.z; s.ext_y = r2.z;
             s.gid = g;
             s.cnt = a.sp_count ? a.sp_count[g] : RB_ROW_DENSE;
+            if (a.row_stride > 0 && s.cnt == RB_ROW_DENSE) s.cnt = 0;   // no row form for > 16 non-zeros (never emitted by the producer)
             s.pad0 = s.pad1 = 0;
             s_inst[tid] = s;
         }
@@ -188,8 +190,13 @@ __global__ void __launch_bounds__(RB_THREADS, 3) k_render_backward(BackArgs a)
                 const uint32_t cnt = s_inst[j].cnt;
                 if (cnt != RB_ROW_DENSE && (uint32_t)k < cnt) {
                     const float v = s_grad[e];
-                    if (v != 0.0f)
-                        atomicAdd(a.dL_dcoeff + (size_t)s_inst[j].gid * a.L + s_sidx[e], v);
+                    if (v != 0.0f) {
+                        if (a.row_stride > 0) {
+                            if (k < a.row_stride) atomicAdd(a.dL_dcoeff + (size_t)s_inst[j].gid * a.row_stride + k, v);
+                        } else {
+                            atomicAdd(a.dL_dcoeff + (size_t)s_inst[j].gid * a.L + s_sidx[e], v);
+                        }
+                    }
                 }
             }
         }
@@ -214,7 +221,7 @@ static size_t rb_smem_bytes(int L, bool color)
 int launch_render_backward(const lsv2_view& v, const lsv2_geom& g, const lsv2_binning& b,
                            const lsv2_features& f, const lsv2_image& img, const float* dL_dwmap,
                            const float* dL_dcolor, int dense_grad, float* dL_dcoeff, float* dL_dcolors,
-                           cudaStream_t st)
+                           cudaStream_t st, int row_stride)
 {
     const int gx = (v.width + TILE - 1) / TILE, gy = (v.height + TILE - 1) / TILE;
     if (gx * gy == 0) return LSV2_OK;
@@ -224,6 +231,7 @@ int launch_render_backward(const lsv2_view& v, const lsv2_geom& g, const lsv2_bi
     const bool color = dL_dcolor != nullptr && dL_dcolors != nullptr;
     const bool have_sparse = f.sparse_count && f.sparse_index;
     const bool dense = dense_grad != 0 || !have_sparse;
+    if (row_stride < 0 || (row_stride > 0 && dense)) return LSV2_EINVAL;      // the row form IS the support-only gradient
     const size_t smem = rb_smem_bytes(f.L, color);
     if (smem > 227 * 1024) return LSV2_EUNSUPPORTED;
     BackArgs a;
@@ -236,6 +244,7 @@ int launch_render_backward(const lsv2_view& v, const lsv2_geom& g, const lsv2_bi
     a.sp_index = f.sparse_index;
     a.coeff_dense = f.coeff_dense;
     a.dL_dwmap = dL_dwmap; a.dL_dcolor = dL_dcolor; a.dL_dcoeff = dL_dcoeff; a.dL_dcolors = dL_dcolors;
+    a.row_stride = row_stride;
 #define RB_LAUNCH(D, C)                                                                                      \
     do {                                                                                                     \
         LSV2_CUDA_TRY(cudaFuncSetAttribute(k_render_backward<D, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, \

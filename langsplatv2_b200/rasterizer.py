@@ -499,8 +499,12 @@ QUICK_CHANNELS = 192
 
 @_abi.guarded(lambda st, *a, **k: st.status.device)
 def rasterize_backward(st: FrameState, grad_wmap: Optional[torch.Tensor], grad_color: Optional[torch.Tensor] = None,
-                       dense_grad: Optional[bool] = None):
-    """dL/d language_feature_precomp [P, L] (and dL/d colours [P, 3] when grad_color is given)."""
+                       dense_grad: Optional[bool] = None, rows_out: Optional[torch.Tensor] = None):
+    """dL/d language_feature_precomp [P, L] (and dL/d colours [P, 3] when grad_color is given).
+
+    ``rows_out`` (extension): a zero-initialised float32 [P, stride] tensor; the gradient is ADDED to it in the order
+    of the compacted rows (entry e of row g = channel ``sparse_index[g, e]``; ``lsv2_render_backward_rows``) and the
+    first return value is None -- 16 B per Gaussian for top-4 instead of a 256-B dense row."""
     L_ = _abi.lib()
     if st.mode != MODE_DENSE:
         raise _abi.Lsv2Error("backward is defined for include_feature (dense coefficient) mode only")
@@ -508,9 +512,18 @@ def rasterize_backward(st: FrameState, grad_wmap: Optional[torch.Tensor], grad_c
     dense = DENSE_COEFF_GRAD if dense_grad is None else dense_grad
     gw = _f32c(grad_wmap, "grad_wmap")
     gc = _f32c(grad_color, "grad_color") if grad_color is not None else None
-    d_coeff = torch.zeros((st.P, st.L), dtype=torch.float32, device=dev)
     d_colors = torch.zeros((st.P, 3), dtype=torch.float32, device=dev) if gc is not None else None
     geom_c, bin_c, feat_c, img_c = st.c_geom(), st.c_binning(), st.c_features(), st.c_image()
+    if rows_out is not None:
+        if rows_out.dim() != 2 or rows_out.shape[0] != st.P or rows_out.dtype != torch.float32 or \
+                not rows_out.is_contiguous() or rows_out.device != dev:
+            raise ValueError("rows_out must be a contiguous float32 [P, stride] tensor on the frame's device")
+        _abi.check(L_.lsv2_render_backward_rows(C.byref(st.view), C.byref(geom_c), C.byref(bin_c), C.byref(feat_c),
+                                                C.byref(img_c), _abi.ptr(gw), _abi.ptr(gc), int(rows_out.shape[1]),
+                                                _abi.ptr(rows_out), _abi.ptr(d_colors), _abi.stream_ptr(dev)),
+                   "lsv2_render_backward_rows")
+        return None, d_colors
+    d_coeff = torch.zeros((st.P, st.L), dtype=torch.float32, device=dev)
     _abi.check(L_.lsv2_render_backward(C.byref(st.view), C.byref(geom_c), C.byref(bin_c), C.byref(feat_c),
                                        C.byref(img_c), _abi.ptr(gw), _abi.ptr(gc), 1 if dense else 0,
                                        _abi.ptr(d_coeff), _abi.ptr(d_colors), _abi.stream_ptr(dev)),
@@ -561,6 +574,7 @@ def rasterize_backward_geometry(st: FrameState, grad_color: torch.Tensor, want: 
 
 class _RasterizeGaussians(torch.autograd.Function):
     last_state = None          # side channel forward -> GaussianRasterizer.forward (never referenced from ctx)
+    last_rows = None           # side channel backward -> caller: the sparse_rows dict whose "grad_rows" was just written
 
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, language_feature_precomp, weights_quick, indices_quick,
@@ -584,6 +598,9 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.opacity_shape = opacities.shape
         ctx.color_is_precomp = colors_precomp is not None
         ctx.dense_grad = dense_coeff_grad
+        # extension: the coefficient gradient in row form, written into the caller's buffer (None flows back instead)
+        ctx.grad_rows = sparse_rows.get("grad_rows") if sparse_rows is not None else None
+        ctx.sparse_rows = sparse_rows if ctx.grad_rows is not None else None    # dies with the graph if never used
         ctx.debug = bool(raster_settings.debug)
         _RasterizeGaussians.last_state = st
         H, W = st.H, st.W
@@ -629,7 +646,10 @@ class _RasterizeGaussians(torch.autograd.Function):
         if st.mode == MODE_DENSE and need[4]:
             gc = grad_color if (need[3] and ctx.color_is_precomp) else None
             try:
-                d_coeff, d_colors = rasterize_backward(st, grad_wmap, gc, dense_grad=ctx.dense_grad)
+                d_coeff, d_colors = rasterize_backward(st, grad_wmap, gc, dense_grad=ctx.dense_grad,
+                                                       rows_out=ctx.grad_rows)
+                if ctx.grad_rows is not None:
+                    _RasterizeGaussians.last_rows, ctx.sparse_rows = ctx.sparse_rows, None
                 if ctx.debug:
                     torch.cuda.synchronize(grad_wmap.device)
             except Exception:

@@ -116,6 +116,30 @@ def softmax_to_topk_soft_code_rows(logits: torch.Tensor, k: int):
     return _topk_dense_rows(logits.detach().contiguous().float(), k)
 
 
+def topk_backward_rows(logits: torch.Tensor, dense: torch.Tensor, rows: dict, d_rows: torch.Tensor,
+                       out: torch.Tensor, row_range=None) -> torch.Tensor:
+    """d logits from the coefficient gradient in row form (``rasterize_backward(rows_out=)``): ``out[r]`` for the rows
+    ``row_range = (a, b)`` (default all) of ``logits`` / ``dense`` / ``rows``; ``d_rows`` and ``out`` hold exactly those
+    rows ([b - a, stride] and [b - a, 64]).  One kernel (``lsv2_topk_soft_code_backward_rows``)."""
+    L_ = _abi.lib()
+    N, Cc = logits.shape
+    a, b = (0, N) if row_range is None else (int(row_range[0]), int(row_range[1]))
+    n = b - a
+    if Cc != 64 or not (0 <= a <= b <= N):
+        raise ValueError("64 codes per row, 0 <= a <= b <= N")
+    if d_rows.shape[0] != n or d_rows.dim() != 2 or out.shape != (n, Cc) or not d_rows.is_contiguous() or \
+            not out.is_contiguous() or not logits.is_contiguous() or not dense.is_contiguous():
+        raise ValueError("d_rows must be [b - a, stride], out [b - a, 64], all contiguous")
+    if n == 0:
+        return out
+    x, y = logits.detach(), dense.detach()
+    _abi.check(L_.lsv2_topk_soft_code_backward_rows(
+        n, x[a:].data_ptr(), y[a:].data_ptr(), rows["sparse_count"][a:].data_ptr(),
+        rows["sparse_index"][a:].data_ptr(), d_rows.data_ptr(), int(d_rows.shape[1]), out.data_ptr(),
+        _abi.stream_ptr(x.device)), "lsv2_topk_soft_code_backward_rows")
+    return out
+
+
 def get_weights_and_indices(logits: torch.Tensor, k: int):
     """utils/vq_utils.py:26-40: (weights [N,k], indices [N,k] as float, ascending channel order)."""
     L_ = _abi.lib()

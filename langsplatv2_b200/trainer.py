@@ -121,6 +121,25 @@ class FeatureTrainer:
                 self.bucket = lsdist.GradBucket([self.logits, self.codebooks])   # only its slice machinery is used
                 self.bucket.flat = self.flat_g
                 self.bucket.attached = True
+        # ---- coefficient gradient in row form (one level of 64 codes; LSV2_ROW_GRAD=0: A/B switch).  The blend backward
+        # writes [N, k] instead of a dense [N, 64] array; the top-k backward is linear in it, so at N > 1 the ranks
+        # reduce-scatter the ROWS (16 B per Gaussian instead of 256 B) and each runs the top-k backward + Adam on its
+        # own shard of rows only ----
+        self.row_grad = (self.fused_rows and self._sink_ok and lg.shape[1] == 64 and self.topk <= 16 and
+                         os.environ.get("LSV2_ROW_GRAD", "1") != "0" and self.collective in ("none", "zero1"))
+        self._row_stride = -(-self.topk // 4) * 4
+        self._rows_g = None
+        self.rows_exchange = None
+        self._row_ctx = None
+        if self.row_grad:
+            self._rows_g = torch.zeros((n, self._row_stride), dtype=torch.float32, device=dev)
+            if self.collective == "zero1":
+                try:
+                    self.rows_exchange = lsdist.ShardedExchange(
+                        self._rows_g.view(-1), None, [(a * self._row_stride, b * self._row_stride)
+                                                      for a, b in self._chunk_rows])
+                except ValueError:
+                    self.row_grad = False
         # the codebook gradient (two pixel-axis GEMMs nobody waits for until the optimizer) can be computed on a side
         # stream after the rest of the backward has been enqueued (loss.CodebookGradSink): at N > 1 the logits' gradient
         # exchange runs under it; at N = 1 it overlaps the tail of the blend backward and the top-k backward
@@ -248,7 +267,10 @@ class FeatureTrainer:
         return min(int(self.iteration / 10000 * self.layers), self.layers - 1)            # train.py:155
 
     def loss(self, cam: Dict, gt, mask: Optional[torch.Tensor], gt_sumsq: Optional[torch.Tensor] = None,
-             view_id=None) -> torch.Tensor:
+             view_id=None, _row_grad: bool = False) -> torch.Tensor:
+        """The iteration's loss; ``loss.backward()`` fills ``logits.grad`` / ``codebooks.grad`` through autograd.
+        (``_row_grad``: step()'s own form, whose backward stops at the blend and leaves the coefficient gradient in
+        row form for _run_backward -- not for callers that run ``backward()`` themselves.)"""
         rs = self.settings(cam)
         gather = self.defer_gather and self.exchange is not None
         if gather:
@@ -265,7 +287,17 @@ class FeatureTrainer:
         rasterizer.prepared = prepared
         rasterizer.dense_coeff_grad = False         # the top-k mask follows (utils/vq_utils.py:20): support-only is exact
         zero = torch.zeros((1,), dtype=torch.float32, device=self.dev)
-        if self.fused_rows and self.layers == 1 and self.codebook_size == 64 and self.topk <= 16:
+        if _row_grad and self.row_grad and torch.is_grad_enabled():
+            # ... and the blend backward hands its gradient back in row form: the top-k backward is run by
+            # _run_backward / _finish_update (after the exchange at N > 1), not by autograd
+            with torch.no_grad():
+                coeff, rows = lssparse.softmax_to_topk_soft_code_rows(self.logits, self.topk)
+            self._rows_g.zero_()
+            rows["grad_rows"] = self._rows_g
+            rows["dense"] = coeff.detach()           # what the top-k backward needs besides the rows
+            coeff.requires_grad_(True)
+            rasterizer.sparse_rows = rows            # lives on the autograd graph: a forward nobody backpropagates pins nothing
+        elif self.fused_rows and self.layers == 1 and self.codebook_size == 64 and self.topk <= 16:
             # one level: the top-k kernel also writes the rows the blend reads (no compaction / packing launches)
             coeff, rasterizer.sparse_rows = lssparse.softmax_to_topk_soft_code_rows(self.logits, self.topk)
         else:
@@ -335,6 +367,20 @@ class FeatureTrainer:
 
     def _run_backward(self, loss: torch.Tensor, use_sink: bool) -> None:
         n_log = self.n_log
+        if self.row_grad:
+            from .rasterizer import _RasterizeGaussians
+            _RasterizeGaussians.last_rows = None
+            loss.backward()                          # ends with the blend backward: self._rows_g holds this rank's rows
+            rows, _RasterizeGaussians.last_rows = _RasterizeGaussians.last_rows, None
+            if rows is None or rows.get("grad_rows") is not self._rows_g:
+                raise RuntimeError("the blend backward did not hand back the row-form gradient of this trainer's loss()")
+            if self.rows_exchange is not None:
+                for i in range(len(self._chunk_rows)):
+                    self.rows_exchange.reduce_scatter(i)
+                self._row_ctx = (rows["dense"], rows)                    # until _finish_update
+            else:
+                lssparse.topk_backward_rows(self.logits, rows["dense"], rows, self._rows_g, self.logits.grad)
+            return
         if use_sink:
             if self.collective == "zero1":
                 on_chunk = lambda a, b, _s=self: _s.exchange.reduce_scatter(_s._block_of[a])
@@ -363,13 +409,23 @@ class FeatureTrainer:
         nb = len(self._blocks)
         if self.collective == "zero1":
             ex = self.exchange
-            if not use_sink:
+            if not use_sink and self._row_ctx is None:
                 for i in range(nb - 1):
                     ex.reduce_scatter(i)
             defer = self.defer_gather
+            row_ctx, self._row_ctx = self._row_ctx, None
+            C = self.logits.shape[1]
             for i in range(nb - 1):                                      # the logits' row blocks
-                ex.wait_grad(i)
                 lo, hi = ex.shard_range(i)
+                if row_ctx is not None:
+                    # this rank's rows of block i, summed over the ranks -> d logits of those rows only
+                    rex = self.rows_exchange
+                    rex.wait_grad(i)
+                    lssparse.topk_backward_rows(self.logits, row_ctx[0], row_ctx[1],
+                                                rex.shard_grad[i].view(-1, self._row_stride),
+                                                ex.shard_grad[i].view(-1, C), row_range=(lo // C, hi // C))
+                else:
+                    ex.wait_grad(i)
                 opt.step_range(lo, hi, grad=ex.shard_grad[i])
                 if not defer:
                     ex.all_gather_params(i)
@@ -421,7 +477,7 @@ class FeatureTrainer:
 
     def _iteration(self, cam, gt, mask, gt_sumsq, view_id) -> torch.Tensor:
         """forward + backward + update; the caller has advanced the optimizer's step count (begin_step)."""
-        loss = self.loss(cam, gt, mask, gt_sumsq=gt_sumsq, view_id=view_id)
+        loss = self.loss(cam, gt, mask, gt_sumsq=gt_sumsq, view_id=view_id, _row_grad=True)
         self._backward_and_update(loss)
         st = self._last_state
         if st is not None and self.capacity is not None:

@@ -36,7 +36,8 @@ for name, kw in (("allreduce", dict(collective="allreduce", defer_codebook_grad=
     out[name] = (p, losses)
     if rank == 0:
         print(f"{name:24s} losses {losses[0]:.5f} -> {losses[-1]:.5f}   max |p - p_rank0| = {same_across:.1e}  "
-              f"defer_gather={tr.defer_gather} cb_sink={tr._cb_sink is not None}", flush=True)
+              f"defer_gather={tr.defer_gather} cb_sink={tr._cb_sink is not None} row_exchange={tr.rows_exchange is not None}",
+              flush=True)
     assert same_across == 0.0 or name.startswith("allreduce"), "replicas diverged"
     del tr
 ref = out["allreduce"][0]

@@ -361,3 +361,66 @@ def test_trainer_fused_rows_equal_separate_kernels(monkeypatch):
         runs.append([float(tr.step(cam, gt, mask)) for _ in range(5)])
     np.testing.assert_allclose(runs[0], runs[1], rtol=5e-3)
     assert runs[0][0] == pytest.approx(runs[1][0], rel=1e-6)
+
+
+def test_row_form_gradient_equals_dense_support_gradient():
+    """lsv2_render_backward_rows + lsv2_topk_soft_code_backward_rows against the dense pair (support-only
+    lsv2_render_backward + lsv2_topk_soft_code_backward): same sums entry by entry, same d logits."""
+    from langsplatv2_b200 import sparse
+    from langsplatv2_b200.rasterizer import rasterize_forward, rasterize_backward
+    scene, cam = hp.make_case(20003, 256, 192, seed=6, levels=1, scale_boost=2.0)
+    g = lambda k: scene[k].cuda()
+    P = scene["xyz"].shape[0]
+    gen = torch.Generator(device="cuda").manual_seed(8)
+    logits = torch.randn((P, 64), device="cuda", generator=gen) * 2.0
+    logits[::17, 3:] -= 500.0                      # rows with fewer live entries than k
+    rs = hp.settings(cam, scene, (0.0, 0.0, 0.0), include_feature=True, quick_render=False)
+    geo = dict(shs=g("features"), scales=g("scaling"), rotations=g("rotation"))
+    gw = torch.randn((64, 192, 256), device="cuda", generator=gen)
+    for k, stride in ((4, 4), (3, 4), (12, 12), (16, 16)):
+        dense, rows = sparse.softmax_to_topk_soft_code_rows(logits, k)
+        st = rasterize_forward(rs, g("xyz"), g("opacity"), capacity=400000, language_feature_precomp=dense,
+                               sparse_rows=rows, **geo)
+        d_dense, _ = rasterize_backward(st, gw, dense_grad=False)
+        d_rows = torch.zeros((P, stride), device="cuda")
+        none, _ = rasterize_backward(st, gw, rows_out=d_rows)
+        assert none is None
+        idx = rows["sparse_index"][:, :stride].long()
+        live = torch.arange(stride, device="cuda")[None, :] < rows["sparse_count"][:, None]
+        want = torch.gather(d_dense, 1, idx.clamp(0, 63)) * live
+        assert float(want.abs().max()) > 0
+        torch.testing.assert_close(d_rows * live, want, rtol=1e-4, atol=1e-5 * float(want.abs().max()))
+        assert not (d_rows * ~live).any()                      # nothing lands beyond a row's count
+        # everything the dense gradient holds is in the rows (support-only): scatter back and compare the totals
+        back = torch.zeros_like(d_dense).scatter_add_(1, idx.clamp(0, 63), d_rows * live)
+        torch.testing.assert_close(back, d_dense, rtol=1e-4, atol=1e-5 * float(want.abs().max()))
+        # top-k backward: row form == dense form on the same numbers, whole array and a row range
+        dx_dense = torch.empty_like(logits)
+        _abi.check(_abi.lib().lsv2_topk_soft_code_backward(P, 64, logits.data_ptr(), dense.data_ptr(), back.data_ptr(),
+                                                           dx_dense.data_ptr(), _abi.stream_ptr()), "bwd")
+        dx_rows = sparse.topk_backward_rows(logits, dense, rows, (d_rows * live).contiguous(), torch.empty_like(logits))
+        assert torch.equal(dx_rows, dx_dense), k
+        a, b = 5000, 12345
+        part = sparse.topk_backward_rows(logits, dense, rows, (d_rows * live)[a:b].contiguous(),
+                                         torch.empty((b - a, 64), device="cuda"), row_range=(a, b))
+        assert torch.equal(part, dx_dense[a:b])
+    with pytest.raises(ValueError):
+        rasterize_backward(st, gw, rows_out=torch.zeros((P - 1, 4), device="cuda"))
+
+
+def test_trainer_row_gradient_equals_dense_gradient(monkeypatch):
+    """FeatureTrainer with the gradient in row form (default) against the dense [N, 64] gradient (LSV2_ROW_GRAD=0)."""
+    runs, grads = [], []
+    for flag in ("0", "1"):
+        monkeypatch.setenv("LSV2_ROW_GRAD", flag)
+        tr, cam, gt, mask = _small_trainer()
+        assert tr.row_grad == (flag == "1")
+        tr.keep_last_grad = True
+        tr.calibrate([cam])
+        first = float(tr.step(cam, gt, mask))
+        grads.append(tr.last_grad.detach().clone())              # same parameters in both runs: same gradient
+        runs.append([first] + [float(tr.step(cam, gt, mask)) for _ in range(4)])
+    np.testing.assert_allclose(runs[0], runs[1], rtol=5e-3)
+    assert runs[0][0] == pytest.approx(runs[1][0], rel=1e-6)
+    scale = float(grads[0].abs().max())
+    assert scale > 0 and float((grads[0] - grads[1]).abs().max()) <= 1e-4 * scale
