@@ -416,6 +416,14 @@ def run_train(args, dev, rank, world, scene, barrier, wl=None):
             "zero1": "reduce-scatter of the flat gradient in %d row blocks (pipelined with the top-k backward) -> Adam on "
                      "this rank's 1/N shard -> all-gather of the parameters" % len(tr._blocks),
             "allreduce": "all-reduce of the flat gradient in %d row blocks, every rank steps everything" % len(tr._blocks)}
+    exch_bytes = int(tr.flat_g.numel() * 4) if world > 1 else 0
+    if world > 1 and tr.rows_exchange is not None:
+        coll["zero1"] = ("reduce-scatter of the coefficient gradient in ROW form ([N, %d] fp32 = %d B per Gaussian instead of "
+                         "the 256-B dense logits row; the top-k backward is linear in it) in %d row blocks -> top-k backward + "
+                         "Adam on this rank's 1/N shard of rows -> all-gather of the parameters (deferred under the next "
+                         "iteration's geometry stage); codebook gradient: reduce-scatter of its own block"
+                         % (tr._row_stride, 4 * tr._row_stride, len(tr._chunk_rows)))
+        exch_bytes = int(tr._rows_g.numel() * 4 + (tr.flat_g.numel() - tr.n_log) * 4)
     return {"metric": "train iter/s", "segments_gt": seg_line, "geometry_cached": cached_line,
             "value": steps / (ms * 1e-3), "unit": "iter/s",
             "views_per_s": world * steps / (ms * 1e-3), "ms_per_iter": ms / steps, "ms_per_iter_median": pct(per, 50),
@@ -423,7 +431,7 @@ def run_train(args, dev, rank, world, scene, barrier, wl=None):
             "n_gpus": world, "scaling": "weak", "final_loss": loss, "dtype": "f32", "launch": graph_note,
             "overflow_events": tr.overflow_events,
             "config": {"workload": wl["name"], "views_per_iter": world,
-                       "grad_exchange_bytes": int(tr.flat_g.numel() * 4) if world > 1 else 0,
+                       "grad_exchange_bytes": exch_bytes, "row_form_gradient": bool(tr.row_grad),
                        "grad_exchange": coll[tr.collective],
                        "optimizer": "lsv2_adam_step (hand-written, torch.optim.Adam(eps=1e-15) semantics) on the flat "
                                     "[logits | codebook] buffer"}}
