@@ -522,6 +522,46 @@ for it in range(2):
         pc[lo:hi] -= lr * exc.shard_grad[i]
 exc.all_gather_all(); exc.finish()                           # == FeatureTrainer.sync_params()
 ok = ok and torch.allclose(pc, pd, rtol=1e-5, atol=1e-6)
+# scheme D (the trainer's exchange since the row form): the logits' gradient is J(x)^T d_coeff with the Jacobian of
+# softmax -> top-k -> renormalise (utils/vq_utils.py:9-24), the same on every rank, and d_coeff lives on the top-k
+# support only.  The ranks reduce-scatter d_coeff in ROW form ([N, k] instead of [N, 64]) over a second ShardedExchange
+# whose blocks are the same row blocks, then apply J^T to their own shard of rows only.  Must equal the all-reduce of the
+# dense d logits; the row shards of the two exchanges must coincide.
+C, K, N = 64, 4, n_log // 64
+def soft_code(x):
+    p = torch.softmax(x, dim=1)
+    idx = torch.topk(p, K, dim=1).indices.sort(dim=1).values
+    m = torch.zeros_like(p).scatter_(1, idx, 1.0)
+    y = p * m
+    return y / (y.sum(1, keepdim=True) + 1e-10), idx
+x0 = flat_p0[:n_log].view(N, C).clone()
+gen = torch.Generator().manual_seed(5)
+d_rows_all = torch.randn(world, N, K, generator=gen)             # rank r's blend-backward output, row form
+xr = x0.clone().requires_grad_(True)
+y, idx = soft_code(xr)
+dense_g = torch.zeros(N, C).scatter_(1, idx, d_rows_all[rank])   # the same gradient as a dense support-only array
+dx = torch.autograd.grad(y, xr, dense_g)[0]
+dist.all_reduce(dx, op=dist.ReduceOp.SUM)
+p_ref = x0 - lr * dx                                             # all-reduce of d logits, every rank steps everything
+pe = flat_p0.clone()
+row_blocks = [(a // C, b // C) for a, b in blocks[:-1]]
+pex = lsdist.ShardedExchange(torch.zeros_like(pe), pe, blocks)   # parameters (all-gather) -- gradient side unused here
+rows_flat = d_rows_all[rank].reshape(-1).clone()
+rex = lsdist.ShardedExchange(rows_flat, None, [(a * K, b * K) for a, b in row_blocks])
+for i in range(len(row_blocks)):
+    rex.reduce_scatter(i)
+for i in range(len(row_blocks)):
+    rex.wait_grad(i)
+    lo, hi = pex.shard_range(i)
+    r0, r1 = lo // C, hi // C
+    ok = ok and (r0 * K, r1 * K) == rex.shard_range(i)           # the two exchanges shard the same rows
+    xs = x0[r0:r1].clone().requires_grad_(True)
+    ys, idxs = soft_code(xs)
+    gs = torch.zeros(r1 - r0, C).scatter_(1, idxs, rex.shard_grad[i].view(-1, K))
+    pe[lo:hi] -= lr * torch.autograd.grad(ys, xs, gs)[0].reshape(-1)
+    pex.all_gather_params(i)
+pex.finish()
+ok = ok and torch.allclose(pe[:n_log].view(N, C), p_ref, rtol=1e-5, atol=1e-6)
 try:
     lsdist.ShardedExchange(gb, pb, [(0, 6)])
     ok = False
@@ -535,7 +575,8 @@ sys.exit(0 if ok else 3)
 
 def test_sharded_exchange_equals_allreduce_gloo(tmp_path):
     """dist.ShardedExchange (reduce-scatter -> sharded step -> all-gather of the parameters) gives every rank the
-    parameters the all-reduce scheme gives, on 2 gloo ranks."""
+    parameters the all-reduce scheme gives, on 2 gloo ranks -- with the dense gradient, with the deferred gather, and
+    with the coefficient gradient exchanged in row form ahead of the (linear) top-k backward."""
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
     port = s.getsockname()[1]
