@@ -128,3 +128,13 @@ def test_scene_from_point_cloud_and_level_merge(tmp_path):
         assert torch.equal(merged["indices_quick"][:, 4 * lvl:4 * lvl + 4], i + 64.0 * lvl)
         assert torch.equal(merged["codebooks"][lvl], levels[lvl]["codebooks"][0])
     assert merged["indices_quick"].dtype == torch.float32 and float(merged["indices_quick"].max()) <= 191
+    # ... which is a scene the resident renderer takes as it is: checkpoints on disk -> normalised 512-d map
+    from langsplatv2_b200.renderer import FeatureRenderer
+    r = FeatureRenderer(merged)
+    assert torch.equal(r.weights, merged["weights_quick"]) and torch.equal(r.indices, merged["indices_quick"])
+    cam_gpu = {k: (v.cuda() if torch.is_tensor(v) else v) for k, v in cam.items()}
+    feat = r.render(cam_gpu)
+    assert feat.shape == (3, 512, 96, 128) and torch.isfinite(feat).all()
+    norms = feat.norm(dim=1)
+    covered = norms > 0.5
+    assert int(covered.sum()) > 100 and torch.allclose(norms[covered], torch.ones_like(norms[covered]), atol=5e-3)
