@@ -132,3 +132,39 @@ def test_checkpoint_tuple_round_trip(tmp_path, with_features):
     assert torch.equal(s2["features"], s["features"])
     with pytest.raises(ValueError, match="length 3"):
         scene_io.read_checkpoint(((1, 2, 3), 0))
+
+
+def test_ply_big_endian_and_leading_element(tmp_path):
+    """PLY variants plyfile would also read: big-endian payload, and a fixed-size element in front of the vertices."""
+    rng = np.random.default_rng(4)
+    xyz = rng.normal(0, 1, (9, 3)).astype(np.float32)
+    rgb = rng.integers(0, 256, (9, 3))
+    head = "ply\nformat binary_big_endian 1.0\nobj_info made by a test\nelement camera 2\nproperty float fx\n" \
+           "property int id\nelement vertex 9\n" + \
+           "".join(f"property float {n}\n" for n in ("x", "y", "z")) + \
+           "".join(f"property uchar {n}\n" for n in ("red", "green", "blue")) + "end_header\n"
+    body = struct.pack(">fi", 1.5, 7) + struct.pack(">fi", 2.5, 8) + \
+        b"".join(struct.pack(">3f3B", *xyz[i], *rgb[i]) for i in range(9))
+    p = tmp_path / "be.ply"
+    p.write_bytes(head.encode() + body)
+    pos, col, nrm = scene_io.read_point_cloud(str(p))
+    np.testing.assert_array_equal(pos.astype(np.float32), xyz)
+    np.testing.assert_allclose(col * 255.0, rgb)
+    assert nrm.shape == (9, 3) and not nrm.any()                 # no nx/ny/nz in the file
+    # a list property in the vertex element is not something the reference writes: refused, not misread
+    bad = "ply\nformat ascii 1.0\nelement vertex 1\nproperty float x\nproperty list uchar int idx\nend_header\n0 1 5\n"
+    p.write_bytes(bad.encode())
+    with pytest.raises(ValueError, match="list property"):
+        scene_io.read_point_cloud(str(p))
+
+
+def test_checkpoint_scene_has_what_renderer_and_trainer_read():
+    """The dictionary of read_checkpoint carries every key FeatureRenderer / FeatureTrainer take from a scene
+    (renderer.py:35-44, trainer.py: xyz, opacity, scaling, rotation, features, logits, codebooks + the sizes)."""
+    src = synth.make_scene(64, seed=1, levels=1)
+    s = scene_io.read_checkpoint(scene_io.checkpoint_tuple(src, 7))
+    for k in ("xyz", "opacity", "scaling", "rotation", "features", "logits", "codebooks", "levels", "codebook_size",
+              "sh_degree", "feat_dim"):
+        assert k in s, k
+    assert s["opacity"].shape == (64, 1) and s["features"].shape == (64, 16, 3) and s["codebooks"].shape == (1, 64, 512)
+    assert set(src) - set(s) == set(), set(src) - set(s)         # everything synth.make_scene provides is there
